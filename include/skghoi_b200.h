@@ -1,0 +1,104 @@
+/* skghoi_b200 -- C ABI of the B200-native SKGHOI interaction-head library (libskghoi_b200.so).
+ *
+ * This is the drop-in boundary: plain pointers and sizes, no torch types.  Every entry point
+ * replaces one piece of the reference's Python operator surface and cites it (paths relative to
+ * the reference checkout; "head.py" = heads/adamixer_transH_spatial_r50_head.py).
+ *
+ * Conventions
+ *   - all pointers are DEVICE pointers on the caller's current device unless marked "host";
+ *   - caller allocates every buffer; the library allocates nothing in steady state;
+ *   - work is enqueued on `stream` (cudaStream_t passed as void*-compatible handle) and the call
+ *     returns without synchronising;
+ *   - return value: 0 = ok, SKG_ERR_INVALID (-1) bad argument, SKG_ERR_CUDA (-2) CUDA failure,
+ *     SKG_ERR_UNSUPPORTED (-3); skg_last_error() gives the text (thread-local);
+ *   - fp32 tensors are row-major contiguous; indices follow the reference (int64 for the
+ *     torch-visible index tensors, int32 for internal row maps).
+ */
+#ifndef SKGHOI_B200_H_
+#define SKGHOI_B200_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SKG_ABI_VERSION 1
+
+#ifndef __CUDA_RUNTIME_H__
+typedef struct CUstream_st* cudaStream_t;
+#endif
+
+const char* skg_last_error(void);
+int skg_abi_version(void);
+int skg_num_sms(void);
+
+/* ---- pair enumeration + spatial encoding --------------------------------------------------
+ * Replaces, for a whole batch in one launch: the meshgrid / nonzero(x != y) pair construction of
+ * GraphHead.forward (head.py:847-860), ops.compute_spatial_ratio_encodings (ops.py:85-157,
+ * num_features = 23 -> 46 columns) or ops.compute_spatial_encodings (ops.py:20-83, 18 -> 36), and
+ * the NaN guard (head.py:866-868, nan_guard != 0).
+ * Segment table (device): box_off[B+1] prefix of n, n_h[B], cell_off[B+1] prefix of n_h*n,
+ * pair_off[B+1] prefix of n_h*(n-1), hum_off[B+1] prefix of n_h, hw[B,3] = (h, w, h*w) as fp32.
+ * Outputs: enc[cells, 2F] (required); all index outputs optional (NULL to skip):
+ *   x, y [cells] int64 (flattened meshgrid, head.py:860); x_keep, y_keep [pairs] int64 (head.py:852);
+ *   cell2pair [cells] (pair rank or -1), cell_hrow / cell_orow / cell_img [cells], pair2cell [pairs];
+ *   nan_flag [B] (1 when the image's encoding held a NaN before the guard). */
+int skg_pairs_spatial_encode(const float* boxes, const int32_t* box_off, const int32_t* n_h,
+                             const int64_t* cell_off, const int64_t* pair_off, const int32_t* hum_off,
+                             const float* hw, int num_images, int64_t total_cells, int num_features,
+                             float eps, int nan_guard, float* enc, int64_t* x, int64_t* y,
+                             int64_t* x_keep, int64_t* y_keep, int32_t* cell2pair, int32_t* cell_hrow,
+                             int32_t* cell_orow, int32_t* cell_img, int32_t* pair2cell, int32_t* nan_flag,
+                             cudaStream_t stream);
+
+/* ops.compute_spatial_encodings / compute_spatial_ratio_encodings on explicit box rows
+ * (ops.py:20-23, 85-88): boxes_1/boxes_2 [rows,4] are the concatenated lists, row_off[num_lists+1]
+ * their prefix offsets, hw[num_lists,3] = (h, w, h*w). */
+int skg_spatial_encode_rows(const float* boxes_1, const float* boxes_2, const int64_t* row_off,
+                            const float* hw, int num_lists, int64_t rows, int num_features, float eps,
+                            float* enc, int32_t* nan_flag, cudaStream_t stream);
+
+/* ---- TransH ------------------------------------------------------------------------------
+ * TransH.forward (heads/TransH/TransH.py:87-106, 'normal' mode): score[t] =
+ * || norm(h - (h.w^)w^) + norm(r) - norm(t - (t.w^)w^) ||_p  with w^ = w/max(||w||,1e-12);
+ * norm() applied when norm_flag.  h_out/r_out/w_out/t_out [T,dim] receive the RAW gathered rows
+ * the fork returns (all four or none). */
+int skg_transh_forward(const float* ent, const float* rel, const float* nrm, int ent_tot, int rel_tot,
+                       int dim, const int64_t* head, const int64_t* relation, const int64_t* tail,
+                       int64_t num_triples, int p_norm, int norm_flag, float* h_out, float* r_out,
+                       float* w_out, float* t_out, float* score, cudaStream_t stream);
+
+/* transH_head.forward (head.py:558-582) without materialising the index vectors: triple
+ * t = cell*rel_tot + r has head = head_const, relation = r, tail = cell_tail[cell]
+ * (cell_tail NULL -> tail = cell). */
+int skg_transh_forward_grid(const float* ent, const float* rel, const float* nrm, int ent_tot, int rel_tot,
+                            int dim, int64_t head_const, const int64_t* cell_tail, int64_t num_cells,
+                            int p_norm, int norm_flag, float* h_out, float* r_out, float* w_out,
+                            float* t_out, float* score, cudaStream_t stream);
+
+/* Backward of skg_transh_forward wrt the three tables: d_* += dscore[t] * d score[t] / d table
+ * (fp32 atomics; caller zeroes d_ent/d_rel/d_nrm). */
+int skg_transh_backward(const float* ent, const float* rel, const float* nrm, int ent_tot, int rel_tot,
+                        int dim, const int64_t* head, const int64_t* relation, const int64_t* tail,
+                        int64_t num_triples, int p_norm, int norm_flag, const float* dscore, float* d_ent,
+                        float* d_rel, float* d_nrm, cudaStream_t stream);
+
+/* MarginLoss.forward (heads/MarginLoss.py:28-36) for p_score[rows] broadcast against
+ * n_score[rows, cols]; use_adv selects the self-adversarial weighting (MarginLoss.py:25-30).
+ * loss[0] receives the scalar.  d_p[rows] / d_n[rows, cols] (both or neither) receive
+ * grad_scale * d loss / d score. */
+int skg_margin_loss(const float* p_score, const float* n_score, int64_t rows, int64_t cols, float margin,
+                    float adv_temperature, int use_adv, float* loss, float* d_p, float* d_n,
+                    float grad_scale, cudaStream_t stream);
+
+/* ---- losses --------------------------------------------------------------------------------
+ * ops.binary_focal_loss (ops.py:159-211), element-wise: loss[i] (optional) and, when dx is set,
+ * dx[i] = grad_out[i] * d loss[i] / d x[i].  Reductions (sum / mean) are done by the caller. */
+int skg_focal_loss(const float* x, const float* y, int64_t n, float alpha, float gamma, float eps,
+                   float* loss, const float* grad_out, float* dx, cudaStream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SKGHOI_B200_H_ */

@@ -1,0 +1,53 @@
+// Shared helpers for the skghoi_b200 CUDA library (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <cuda_bf16.h>
+#include <stdint.h>
+#include <stdio.h>
+
+#define SKG_OK 0
+#define SKG_ERR_INVALID (-1)
+#define SKG_ERR_CUDA (-2)
+#define SKG_ERR_UNSUPPORTED (-3)
+
+namespace skg {
+
+// last error text, retrievable through skg_last_error() (no exceptions cross the C boundary)
+void set_error(const char* fmt, ...);
+int check_launch(const char* what);
+
+#define SKG_REQUIRE(cond, ...)                                  \
+  do {                                                          \
+    if (!(cond)) {                                              \
+      skg::set_error(__VA_ARGS__);                              \
+      return SKG_ERR_INVALID;                                   \
+    }                                                           \
+  } while (0)
+
+#define SKG_CUDA(call)                                                              \
+  do {                                                                              \
+    cudaError_t e__ = (call);                                                       \
+    if (e__ != cudaSuccess) {                                                       \
+      skg::set_error("%s failed: %s", #call, cudaGetErrorString(e__));              \
+      return SKG_ERR_CUDA;                                                          \
+    }                                                                               \
+  } while (0)
+
+__host__ __device__ inline int64_t ceil_div64(int64_t a, int64_t b) { return (a + b - 1) / b; }
+__host__ __device__ inline int ceil_div(int a, int b) { return (a + b - 1) / b; }
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+
+// number of SMs of the current device (cached)
+int num_sms();
+
+}  // namespace skg

@@ -1,0 +1,271 @@
+// Pair enumeration + pairwise spatial encoding (reference head.py:847-868, ops.py:20-157).
+//
+// One launch covers every image of the batch: the human x box grid cells of all images are
+// numbered consecutively (cell r of image b = cell_off[b] + i*n + j, row-major like
+// torch.meshgrid(indexing='ij')), one thread per cell.  The kernel is HBM-write bound
+// (46 fp32 = 184 B per cell): each CTA stages a 128-cell tile in shared memory laid out exactly
+// like the output rows and drains it with ONE bulk asynchronous copy (cp.async.bulk, the 1-D TMA
+// path, SASS UBLKCP) so the global writes are perfectly coalesced 128-byte lines regardless of
+// the 184-byte row pitch; the next tile is computed into the other buffer meanwhile.
+//
+// Valid-pair compaction (torch.nonzero(x != y), head.py:852): in row i exactly the cell j == i is
+// dropped (i < n_h <= n), so the row-major rank of a kept cell is p = i*(n-1) + j - (j > i):
+// bit-exact with nonzero() ordering, no scan and no host sync.
+//
+// Compiled with -fmad=false: the reference materialises every intermediate in fp32, so products
+// must not be contracted into FMAs.
+#include "common.cuh"
+#include "skghoi_b200.h"
+
+namespace skg {
+
+constexpr int kTileCells = 128;
+
+struct SegTable {
+  const int32_t* box_off;    // [B+1] prefix sum of n
+  const int32_t* n_h;        // [B]
+  const int64_t* cell_off;   // [B+1] prefix sum of n_h*n
+  const int64_t* pair_off;   // [B+1] prefix sum of n_h*(n-1)
+  const int32_t* hum_off;    // [B+1] prefix sum of n_h
+  const float* hw;           // [B,3] = h, w, h*w (as fp32)
+  int B;
+};
+
+__device__ __forceinline__ int find_segment(const int64_t* __restrict__ off, int B, int64_t r) {
+  int lo = 0, hi = B;  // invariant: off[lo] <= r < off[hi]
+  while (hi - lo > 1) {
+    int mid = (lo + hi) >> 1;
+    if (__ldg(off + mid) <= r) lo = mid; else hi = mid;
+  }
+  return lo;
+}
+
+// Writes 2*F floats for one (b1, b2) pair.  F == 23: compute_spatial_ratio_encodings (ops.py:107-155),
+// F == 18: compute_spatial_encodings (ops.py:46-79).  Returns true when any value is NaN.
+template <int F>
+__device__ __forceinline__ bool encode_pair(float4 b1, float4 b2, float h, float w, float hw, float eps,
+                                            float* __restrict__ out) {
+  const float c1_x = (b1.x + b1.z) / 2.f, c1_y = (b1.y + b1.w) / 2.f;
+  const float c2_x = (b2.x + b2.z) / 2.f, c2_y = (b2.y + b2.w) / 2.f;
+  const float b1_w = b1.z - b1.x, b1_h = b1.w - b1.y;
+  const float b2_w = b2.z - b2.x, b2_h = b2.w - b2.y;
+  const float d_x = fabsf(c2_x - c1_x) / (b1_w + eps);
+  const float d_y = fabsf(c2_y - c1_y) / (b1_h + eps);
+  // torchvision box_iou diagonal: no eps, 0/0 -> NaN
+  const float area1 = b1_w * b1_h, area2 = b2_w * b2_h;
+  const float iw = fmaxf(fminf(b1.z, b2.z) - fmaxf(b1.x, b2.x), 0.f);
+  const float ih = fmaxf(fminf(b1.w, b2.w) - fmaxf(b1.y, b2.y), 0.f);
+  const float inter = iw * ih;
+  const float iou = inter / ((area1 + area2) - inter);
+  const float gx = (c2_x > c1_x) ? 1.f : 0.f, lx = (c2_x < c1_x) ? 1.f : 0.f;
+  const float gy = (c2_y > c1_y) ? 1.f : 0.f, ly = (c2_y < c1_y) ? 1.f : 0.f;
+  float f[F];
+  if (F == 23) {
+    const float c1_xw = c1_x / w, c1_yh = c1_y / h, c2_xw = c2_x / w, c2_yh = c2_y / h;
+    const float b1_ww = b1_w / w, b1_hh = b1_h / h, b2_ww = b2_w / w, b2_hh = b2_h / h;
+    const float a1 = area1 / hw, a2 = area2 / hw;
+    f[0] = c1_xw; f[1] = c1_yh; f[2] = c2_xw; f[3] = c2_yh;
+    f[4] = c1_xw / (c2_xw + eps); f[5] = c1_yh / (c2_yh + eps);
+    f[6] = b1_ww; f[7] = b1_hh; f[8] = b2_ww; f[9] = b2_hh;
+    f[10] = b1_ww / (b2_ww + eps); f[11] = b1_hh / (b2_hh + eps);
+    f[12] = a1; f[13] = a2; f[14] = a1 / (a2 + eps);
+    f[15] = area2 / (area1 + eps);
+    f[16] = b1_w / (b1_h + eps); f[17] = b2_w / (b2_h + eps);
+    f[18] = iou;
+    f[19] = gx * d_x; f[20] = lx * d_x; f[21] = gy * d_y; f[22] = ly * d_y;
+  } else {
+    f[0] = c1_x / w; f[1] = c1_y / h; f[2] = c2_x / w; f[3] = c2_y / h;
+    f[4] = b1_w / w; f[5] = b1_h / h; f[6] = b2_w / w; f[7] = b2_h / h;
+    f[8] = area1 / hw; f[9] = area2 / hw;
+    f[10] = area2 / (area1 + eps);
+    f[11] = b1_w / (b1_h + eps); f[12] = b2_w / (b2_h + eps);
+    f[13] = iou;
+    f[14] = gx * d_x; f[15] = lx * d_x; f[16] = gy * d_y; f[17] = ly * d_y;
+  }
+  bool has_nan = false;
+#pragma unroll
+  for (int k = 0; k < F; ++k) {
+    const float l = logf(f[k] + eps);
+    out[k] = f[k];
+    out[F + k] = l;
+    has_nan |= (f[k] != f[k]) | (l != l);
+  }
+  return has_nan;
+}
+
+__device__ __forceinline__ void bulk_store_tile(float* gdst, const float* ssrc, uint32_t bytes) {
+  uint32_t saddr = (uint32_t)__cvta_generic_to_shared(ssrc);
+  asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;\n" ::"l"(gdst), "r"(saddr), "r"(bytes)
+               : "memory");
+  asm volatile("cp.async.bulk.commit_group;\n" ::: "memory");
+}
+
+struct PairOutputs {
+  float* enc;          // [cells, 2F]
+  int64_t* x;          // [cells] human index within image (may be null)
+  int64_t* y;          // [cells] box index within image (may be null)
+  int64_t* x_keep;     // [pairs] (may be null)
+  int64_t* y_keep;     // [pairs] (may be null)
+  int32_t* cell2pair;  // [cells] global pair index or -1 (may be null)
+  int32_t* cell_hrow;  // [cells] global human-node row (may be null)
+  int32_t* cell_orow;  // [cells] global box row (may be null)
+  int32_t* cell_img;   // [cells] image index (may be null)
+  int32_t* pair2cell;  // [pairs] global cell index (may be null)
+  int32_t* nan_flag;   // [B] set to 1 when the image's encoding holds a NaN (may be null)
+};
+
+template <int F>
+__global__ void __launch_bounds__(kTileCells) pairs_spatial_kernel(const float4* __restrict__ boxes, SegTable seg,
+                                                                   int64_t total_cells, float eps, PairOutputs o) {
+  constexpr int W = 2 * F;
+  __shared__ __align__(128) float tile[2][kTileCells * W];
+  const int tid = threadIdx.x;
+  const int64_t num_tiles = (total_cells + kTileCells - 1) / kTileCells;
+  int buf = 0;
+  for (int64_t t = blockIdx.x; t < num_tiles; t += gridDim.x, buf ^= 1) {
+    const int64_t r0 = t * kTileCells;
+    const int64_t r = r0 + tid;
+    // the bulk store that last read tile[buf] (two iterations ago) must have finished reading smem
+    if (tid == 0) asm volatile("cp.async.bulk.wait_group.read 1;\n" ::: "memory");
+    __syncthreads();
+    if (r < total_cells) {
+      const int b = find_segment(seg.cell_off, seg.B, r);
+      const int boff = __ldg(seg.box_off + b);
+      const int n = __ldg(seg.box_off + b + 1) - boff;
+      const int64_t c = r - __ldg(seg.cell_off + b);
+      const int i = (int)(c / n), j = (int)(c - (int64_t)i * n);
+      const float4 b1 = __ldg(boxes + boff + i);
+      const float4 b2 = __ldg(boxes + boff + j);
+      const float h = __ldg(seg.hw + 3 * b), w = __ldg(seg.hw + 3 * b + 1), hw = __ldg(seg.hw + 3 * b + 2);
+      const bool has_nan = encode_pair<F>(b1, b2, h, w, hw, eps, &tile[buf][tid * W]);
+      if (has_nan && o.nan_flag) atomicOr(o.nan_flag + b, 1);
+      if (o.x) o.x[r] = i;
+      if (o.y) o.y[r] = j;
+      if (o.cell_hrow) o.cell_hrow[r] = __ldg(seg.hum_off + b) + i;
+      if (o.cell_orow) o.cell_orow[r] = boff + j;
+      if (o.cell_img) o.cell_img[r] = b;
+      const bool valid = (i != j);
+      const int64_t p = __ldg(seg.pair_off + b) + (int64_t)i * (n - 1) + j - (j > i ? 1 : 0);
+      if (o.cell2pair) o.cell2pair[r] = valid ? (int32_t)p : -1;
+      if (valid) {
+        if (o.x_keep) o.x_keep[p] = i;
+        if (o.y_keep) o.y_keep[p] = j;
+        if (o.pair2cell) o.pair2cell[p] = (int32_t)r;
+      }
+    }
+    // make the generic-proxy smem writes visible to the async (TMA) proxy, then drain the tile
+    asm volatile("fence.proxy.async.shared::cta;\n" ::: "memory");
+    __syncthreads();
+    const int64_t cells_here = (total_cells - r0 < kTileCells) ? (total_cells - r0) : kTileCells;
+    float* gdst = o.enc + r0 * W;
+    const uint32_t bytes = (uint32_t)(cells_here * W * sizeof(float));
+    if ((bytes & 15u) == 0 && ((reinterpret_cast<uintptr_t>(gdst) & 15u) == 0)) {
+      if (tid == 0) bulk_store_tile(gdst, tile[buf], bytes);
+    } else {  // ragged tail: plain coalesced stores
+      for (int e = tid; e < cells_here * W; e += kTileCells) gdst[e] = tile[buf][e];
+    }
+  }
+  if (tid == 0) asm volatile("cp.async.bulk.wait_group 0;\n" ::: "memory");
+}
+
+// ops.compute_spatial_encodings / compute_spatial_ratio_encodings on explicit (boxes_1, boxes_2) rows.
+template <int F>
+__global__ void __launch_bounds__(kTileCells) spatial_rows_kernel(const float4* __restrict__ b1s,
+                                                                  const float4* __restrict__ b2s,
+                                                                  const int64_t* __restrict__ row_off,
+                                                                  const float* __restrict__ hw, int num_lists,
+                                                                  int64_t rows, float eps, float* __restrict__ enc,
+                                                                  int32_t* __restrict__ nan_flag) {
+  constexpr int W = 2 * F;
+  __shared__ __align__(128) float tile[kTileCells * W];
+  const int tid = threadIdx.x;
+  const int64_t num_tiles = (rows + kTileCells - 1) / kTileCells;
+  for (int64_t t = blockIdx.x; t < num_tiles; t += gridDim.x) {
+    const int64_t r0 = t * kTileCells, r = r0 + tid;
+    __syncthreads();
+    if (r < rows) {
+      const int b = find_segment(row_off, num_lists, r);
+      const bool has_nan = encode_pair<F>(__ldg(b1s + r), __ldg(b2s + r), __ldg(hw + 3 * b), __ldg(hw + 3 * b + 1),
+                                          __ldg(hw + 3 * b + 2), eps, &tile[tid * W]);
+      if (has_nan && nan_flag) atomicOr(nan_flag + b, 1);
+    }
+    __syncthreads();
+    const int64_t here = (rows - r0 < kTileCells) ? (rows - r0) : kTileCells;
+    for (int e = tid; e < here * W; e += kTileCells) enc[r0 * W + e] = tile[e];
+  }
+}
+
+// head.py:866-868: only when the image's encoding holds a NaN, torch.nan_to_num the whole tensor
+// (NaN -> 0, +inf -> FLT_MAX, -inf -> -FLT_MAX); images without NaN keep their infs.
+__global__ void nan_guard_kernel(float* __restrict__ enc, const int64_t* __restrict__ cell_off,
+                                 const int32_t* __restrict__ nan_flag, int B, int W) {
+  const int b = blockIdx.y;
+  if (b >= B || nan_flag[b] == 0) return;
+  const int64_t lo = cell_off[b] * W, hi = cell_off[b + 1] * W;
+  for (int64_t e = lo + blockIdx.x * (int64_t)blockDim.x + threadIdx.x; e < hi; e += (int64_t)gridDim.x * blockDim.x) {
+    float v = enc[e];
+    if (v != v) v = 0.f;
+    else if (isinf(v)) v = v > 0 ? 3.4028234663852886e38f : -3.4028234663852886e38f;
+    enc[e] = v;
+  }
+}
+
+}  // namespace skg
+
+using namespace skg;
+
+extern "C" int skg_pairs_spatial_encode(const float* boxes, const int32_t* box_off, const int32_t* n_h,
+                                        const int64_t* cell_off, const int64_t* pair_off, const int32_t* hum_off,
+                                        const float* hw, int num_images, int64_t total_cells, int num_features,
+                                        float eps, int nan_guard, float* enc, int64_t* x, int64_t* y,
+                                        int64_t* x_keep, int64_t* y_keep, int32_t* cell2pair, int32_t* cell_hrow,
+                                        int32_t* cell_orow, int32_t* cell_img, int32_t* pair2cell, int32_t* nan_flag,
+                                        cudaStream_t stream) {
+  SKG_REQUIRE(num_features == 18 || num_features == 23, "num_features must be 18 or 23, got %d", num_features);
+  SKG_REQUIRE(num_images >= 0 && total_cells >= 0, "negative sizes");
+  SKG_REQUIRE(!nan_guard || nan_flag, "nan_guard needs a nan_flag buffer");
+  if (total_cells == 0 || num_images == 0) return SKG_OK;
+  SKG_REQUIRE(boxes && box_off && n_h && cell_off && pair_off && hum_off && hw && enc, "null pointer argument");
+  SKG_REQUIRE((reinterpret_cast<uintptr_t>(boxes) & 15u) == 0, "boxes must be 16-byte aligned");
+  SegTable seg{box_off, n_h, cell_off, pair_off, hum_off, hw, num_images};
+  PairOutputs o{enc, x, y, x_keep, y_keep, cell2pair, cell_hrow, cell_orow, cell_img, pair2cell, nan_flag};
+  if (nan_flag) SKG_CUDA(cudaMemsetAsync(nan_flag, 0, sizeof(int32_t) * num_images, stream));
+  const int64_t tiles = ceil_div64(total_cells, kTileCells);
+  // 4 resident 128-thread CTAs per SM (2 x 23.5 KB smem each); grid is a multiple of the SM count
+  const int grid = (int)(tiles < (int64_t)num_sms() * 8 ? tiles : (int64_t)num_sms() * 8);
+  if (num_features == 23)
+    pairs_spatial_kernel<23><<<grid, kTileCells, 0, stream>>>((const float4*)boxes, seg, total_cells, eps, o);
+  else
+    pairs_spatial_kernel<18><<<grid, kTileCells, 0, stream>>>((const float4*)boxes, seg, total_cells, eps, o);
+  int rc = check_launch("pairs_spatial_kernel");
+  if (rc) return rc;
+  if (nan_guard) {
+    const int gx = 4;  // clean images exit at once; a flagged image is at most a few thousand rows
+    for (int b0 = 0; b0 < num_images; b0 += 65535) {
+      int nb = num_images - b0 < 65535 ? num_images - b0 : 65535;
+      nan_guard_kernel<<<dim3(gx, nb), 256, 0, stream>>>(enc, cell_off + b0, nan_flag + b0, nb, 2 * num_features);
+    }
+    rc = check_launch("nan_guard_kernel");
+  }
+  return rc;
+}
+
+extern "C" int skg_spatial_encode_rows(const float* boxes_1, const float* boxes_2, const int64_t* row_off,
+                                       const float* hw, int num_lists, int64_t rows, int num_features, float eps,
+                                       float* enc, int32_t* nan_flag, cudaStream_t stream) {
+  SKG_REQUIRE(num_features == 18 || num_features == 23, "num_features must be 18 or 23, got %d", num_features);
+  if (rows == 0) return SKG_OK;
+  SKG_REQUIRE(boxes_1 && boxes_2 && row_off && hw && enc && num_lists > 0, "null pointer argument");
+  SKG_REQUIRE(((reinterpret_cast<uintptr_t>(boxes_1) | reinterpret_cast<uintptr_t>(boxes_2)) & 15u) == 0,
+              "box arrays must be 16-byte aligned");
+  if (nan_flag) SKG_CUDA(cudaMemsetAsync(nan_flag, 0, sizeof(int32_t) * num_lists, stream));
+  const int64_t tiles = ceil_div64(rows, kTileCells);
+  const int grid = (int)(tiles < (int64_t)num_sms() * 8 ? tiles : (int64_t)num_sms() * 8);
+  if (num_features == 23)
+    spatial_rows_kernel<23><<<grid, kTileCells, 0, stream>>>((const float4*)boxes_1, (const float4*)boxes_2, row_off,
+                                                            hw, num_lists, rows, eps, enc, nan_flag);
+  else
+    spatial_rows_kernel<18><<<grid, kTileCells, 0, stream>>>((const float4*)boxes_1, (const float4*)boxes_2, row_off,
+                                                            hw, num_lists, rows, eps, enc, nan_flag);
+  return check_launch("spatial_rows_kernel");
+}

@@ -1,0 +1,396 @@
+// TransH knowledge-graph scoring, its backward, and the margin loss
+// (reference heads/TransH/TransH.py:56-106, heads/MarginLoss.py:28-36, heads/NegativeSampling.py:30-63).
+//
+// Bandwidth-bound gather kernel: the three embedding tables (80x50 + 2x117x50 fp32 = 62.8 KB for
+// the HOI label graph) are staged once per CTA in shared memory; one warp handles one triple at a
+// time with the embedding dimension spread over the lanes, so every global access (index reads,
+// the optional materialised h_, r, w, t_ rows, the score) is a coalesced warp-wide transaction and
+// the per-triple reductions are register shuffles.  Tables that do not fit in shared memory
+// (large public KGs) are read through L2 instead.
+#include "common.cuh"
+#include "skghoi_b200.h"
+
+namespace skg {
+
+constexpr int kTranshThreads = 256;
+constexpr int kTranshWarps = kTranshThreads / 32;
+
+struct TripleIndex {
+  // explicit mode: head/relation/tail arrays.  implicit (grid) mode (head.py:570-572):
+  //   head = head_const, relation = t % rel_tot, tail = cell_tail ? cell_tail[t / rel_tot] : t / rel_tot
+  const int64_t* head;
+  const int64_t* relation;
+  const int64_t* tail;
+  const int64_t* cell_tail;
+  int64_t head_const;
+  int rel_tot;
+  int implicit;
+  __device__ __forceinline__ void get(int64_t t, int64_t& h, int64_t& r, int64_t& tl) const {
+    if (implicit) {
+      const int64_t c = t / rel_tot;
+      h = head_const;
+      r = t - c * rel_tot;
+      tl = cell_tail ? __ldg(cell_tail + c) : c;
+    } else {
+      h = __ldg(head + t); r = __ldg(relation + t); tl = __ldg(tail + t);
+    }
+  }
+};
+
+struct TranshTriple {   // per-lane slice of one triple's intermediate state
+  float inv_w, a_h, a_t, inv_h, inv_t, inv_r, nrm_s;
+};
+
+// Forward math for one triple held EPL-elements-per-lane.  Returns the score (all lanes).
+template <int EPL>
+__device__ __forceinline__ float transh_triple_fwd(const float (&h)[EPL], const float (&t)[EPL], const float (&r)[EPL],
+                                                   const float (&w)[EPL], int p_norm, int norm_flag, float (&s)[EPL],
+                                                   TranshTriple& st) {
+  float ww = 0.f, hw = 0.f, tw = 0.f, rr = 0.f;
+#pragma unroll
+  for (int e = 0; e < EPL; ++e) { ww += w[e] * w[e]; hw += h[e] * w[e]; tw += t[e] * w[e]; rr += r[e] * r[e]; }
+  ww = warp_sum(ww); hw = warp_sum(hw); tw = warp_sum(tw); rr = warp_sum(rr);
+  const float inv_w = 1.f / fmaxf(sqrtf(ww), 1e-12f);      // F.normalize(norm, 2, -1)  TransH.py:76
+  const float a_h = hw * inv_w, a_t = tw * inv_w;            // sum(e * w_hat)           TransH.py:85
+  float hp[EPL], tp[EPL];
+  float hh = 0.f, tt = 0.f;
+#pragma unroll
+  for (int e = 0; e < EPL; ++e) {
+    const float wn = w[e] * inv_w;
+    hp[e] = h[e] - a_h * wn; tp[e] = t[e] - a_t * wn;
+    hh += hp[e] * hp[e]; tt += tp[e] * tp[e];
+  }
+  float inv_h = 1.f, inv_t = 1.f, inv_r = 1.f;
+  if (norm_flag) {                                           // TransH.py:57-60
+    hh = warp_sum(hh); tt = warp_sum(tt);
+    inv_h = 1.f / fmaxf(sqrtf(hh), 1e-12f); inv_t = 1.f / fmaxf(sqrtf(tt), 1e-12f);
+    inv_r = 1.f / fmaxf(sqrtf(rr), 1e-12f);
+  }
+  float acc = 0.f;
+#pragma unroll
+  for (int e = 0; e < EPL; ++e) {
+    s[e] = (hp[e] * inv_h + r[e] * inv_r) - tp[e] * inv_t;   // (h + r) - t   TransH.py:68
+    acc += (p_norm == 1) ? fabsf(s[e]) : s[e] * s[e];
+  }
+  acc = warp_sum(acc);
+  const float score = (p_norm == 1) ? acc : sqrtf(acc);      // torch.norm(score, p, -1)  TransH.py:70
+  st.inv_w = inv_w; st.a_h = a_h; st.a_t = a_t; st.inv_h = inv_h; st.inv_t = inv_t; st.inv_r = inv_r; st.nrm_s = score;
+  return score;
+}
+
+template <int EPL, bool SMEM_TABLES>
+__global__ void __launch_bounds__(kTranshThreads) transh_forward_kernel(
+    const float* __restrict__ ent, const float* __restrict__ rel, const float* __restrict__ nrm, int ent_tot, int rel_tot,
+    int dim, TripleIndex idx, int64_t T, int p_norm, int norm_flag, float* __restrict__ h_out, float* __restrict__ r_out,
+    float* __restrict__ w_out, float* __restrict__ t_out, float* __restrict__ score_out) {
+  extern __shared__ __align__(16) float smem[];
+  const float* E = ent; const float* R = rel; const float* W = nrm;
+  if (SMEM_TABLES) {
+    float* sE = smem; float* sR = sE + (size_t)ent_tot * dim; float* sW = sR + (size_t)rel_tot * dim;
+    for (int e = threadIdx.x; e < ent_tot * dim; e += blockDim.x) sE[e] = __ldg(ent + e);
+    for (int e = threadIdx.x; e < rel_tot * dim; e += blockDim.x) { sR[e] = __ldg(rel + e); sW[e] = __ldg(nrm + e); }
+    __syncthreads();
+    E = sE; R = sR; W = sW;
+  }
+  const int lane = threadIdx.x & 31;
+  const int64_t warp = (int64_t)blockIdx.x * kTranshWarps + (threadIdx.x >> 5);
+  const int64_t nwarps = (int64_t)gridDim.x * kTranshWarps;
+  for (int64_t t = warp; t < T; t += nwarps) {
+    int64_t hi, ri, ti;
+    idx.get(t, hi, ri, ti);
+    float h[EPL], tl[EPL], r[EPL], w[EPL], s[EPL];
+#pragma unroll
+    for (int e = 0; e < EPL; ++e) {
+      const int d = lane + 32 * e;
+      const bool in = d < dim;
+      h[e] = in ? E[hi * dim + d] : 0.f; tl[e] = in ? E[ti * dim + d] : 0.f;
+      r[e] = in ? R[ri * dim + d] : 0.f; w[e] = in ? W[ri * dim + d] : 0.f;
+    }
+    TranshTriple st;
+    const float score = transh_triple_fwd<EPL>(h, tl, r, w, p_norm, norm_flag, s, st);
+    if (h_out) {   // API-faithful mode: the fork returns the RAW gathered rows (TransH.py:106)
+#pragma unroll
+      for (int e = 0; e < EPL; ++e) {
+        const int d = lane + 32 * e;
+        if (d < dim) {
+          const int64_t o = t * dim + d;
+          __stcs(h_out + o, h[e]); __stcs(r_out + o, r[e]); __stcs(w_out + o, w[e]); __stcs(t_out + o, tl[e]);
+        }
+      }
+    }
+    if (lane == 0) score_out[t] = score;
+  }
+}
+
+// d(tables) += d(score) * d score / d tables.  Gradients accumulate into fp32 tables with atomics;
+// when the tables fit they are privatised per CTA in shared memory and flushed once.
+template <int EPL, bool SMEM_TABLES>
+__global__ void __launch_bounds__(kTranshThreads) transh_backward_kernel(
+    const float* __restrict__ ent, const float* __restrict__ rel, const float* __restrict__ nrm, int ent_tot, int rel_tot,
+    int dim, TripleIndex idx, int64_t T, int p_norm, int norm_flag, const float* __restrict__ dscore,
+    float* __restrict__ d_ent, float* __restrict__ d_rel, float* __restrict__ d_nrm) {
+  extern __shared__ __align__(16) float smem[];
+  float* gE = d_ent; float* gR = d_rel; float* gW = d_nrm;
+  const int nE = ent_tot * dim, nR = rel_tot * dim;
+  if (SMEM_TABLES) {
+    gE = smem; gR = gE + nE; gW = gR + nR;
+    for (int e = threadIdx.x; e < nE + 2 * nR; e += blockDim.x) smem[e] = 0.f;
+    __syncthreads();
+  }
+  const int lane = threadIdx.x & 31;
+  const int64_t warp = (int64_t)blockIdx.x * kTranshWarps + (threadIdx.x >> 5);
+  const int64_t nwarps = (int64_t)gridDim.x * kTranshWarps;
+  for (int64_t t = warp; t < T; t += nwarps) {
+    const float g = __ldg(dscore + t);
+    if (g == 0.f) continue;    // warp-uniform
+    int64_t hi, ri, ti;
+    idx.get(t, hi, ri, ti);
+    float h[EPL], tl[EPL], r[EPL], w[EPL], s[EPL];
+#pragma unroll
+    for (int e = 0; e < EPL; ++e) {
+      const int d = lane + 32 * e;
+      const bool in = d < dim;
+      h[e] = in ? __ldg(ent + hi * dim + d) : 0.f; tl[e] = in ? __ldg(ent + ti * dim + d) : 0.f;
+      r[e] = in ? __ldg(rel + ri * dim + d) : 0.f; w[e] = in ? __ldg(nrm + ri * dim + d) : 0.f;
+    }
+    TranshTriple st;
+    transh_triple_fwd<EPL>(h, tl, r, w, p_norm, norm_flag, s, st);
+    // g_s = g * d||s||_p / ds   (zero sub-gradient at s == 0, as torch.norm)
+    float gs[EPL];
+#pragma unroll
+    for (int e = 0; e < EPL; ++e) {
+      if (p_norm == 1) gs[e] = g * ((s[e] > 0.f) - (s[e] < 0.f));
+      else gs[e] = st.nrm_s > 0.f ? g * s[e] / st.nrm_s : 0.f;
+    }
+    // unit vectors u = hp*inv_h, q = r*inv_r, v = tp*inv_t ;  s = u + q - v
+    float wn[EPL], hp[EPL], tp[EPL];
+    float ugs = 0.f, vgs = 0.f, qgs = 0.f;
+#pragma unroll
+    for (int e = 0; e < EPL; ++e) {
+      wn[e] = w[e] * st.inv_w;
+      hp[e] = h[e] - st.a_h * wn[e]; tp[e] = tl[e] - st.a_t * wn[e];
+      ugs += hp[e] * st.inv_h * gs[e]; vgs += tp[e] * st.inv_t * gs[e]; qgs += r[e] * st.inv_r * gs[e];
+    }
+    float g_hp[EPL], g_tp[EPL], g_r[EPL];
+    if (norm_flag) {
+      ugs = warp_sum(ugs); vgs = warp_sum(vgs); qgs = warp_sum(qgs);
+#pragma unroll
+      for (int e = 0; e < EPL; ++e) {
+        g_hp[e] = (gs[e] - hp[e] * st.inv_h * ugs) * st.inv_h;
+        g_tp[e] = -(gs[e] - tp[e] * st.inv_t * vgs) * st.inv_t;
+        g_r[e] = (gs[e] - r[e] * st.inv_r * qgs) * st.inv_r;
+      }
+    } else {
+#pragma unroll
+      for (int e = 0; e < EPL; ++e) { g_hp[e] = gs[e]; g_tp[e] = -gs[e]; g_r[e] = gs[e]; }
+    }
+    // hp = h - (h.wn) wn  ->  g_h = g_hp - (g_hp.wn) wn ;  g_wn += -(a_h g_hp + (g_hp.wn) h)   (same for t)
+    float bh = 0.f, bt = 0.f;
+#pragma unroll
+    for (int e = 0; e < EPL; ++e) { bh += g_hp[e] * wn[e]; bt += g_tp[e] * wn[e]; }
+    bh = warp_sum(bh); bt = warp_sum(bt);
+    float g_wn[EPL];
+    float wg = 0.f;
+#pragma unroll
+    for (int e = 0; e < EPL; ++e) {
+      g_wn[e] = -(st.a_h * g_hp[e] + bh * h[e]) - (st.a_t * g_tp[e] + bt * tl[e]);
+      wg += wn[e] * g_wn[e];
+    }
+    wg = warp_sum(wg);
+#pragma unroll
+    for (int e = 0; e < EPL; ++e) {
+      const int d = lane + 32 * e;
+      if (d < dim) {
+        atomicAdd(gE + hi * dim + d, g_hp[e] - bh * wn[e]);
+        atomicAdd(gE + ti * dim + d, g_tp[e] - bt * wn[e]);
+        atomicAdd(gR + ri * dim + d, g_r[e]);
+        atomicAdd(gW + ri * dim + d, (g_wn[e] - wn[e] * wg) * st.inv_w);   // w_hat = w / ||w||
+      }
+    }
+  }
+  if (SMEM_TABLES) {
+    __syncthreads();
+    for (int e = threadIdx.x; e < nE; e += blockDim.x) { const float v = smem[e]; if (v != 0.f) atomicAdd(d_ent + e, v); }
+    for (int e = threadIdx.x; e < nR; e += blockDim.x) {
+      const float v = smem[nE + e]; if (v != 0.f) atomicAdd(d_rel + e, v);
+      const float u = smem[nE + nR + e]; if (u != 0.f) atomicAdd(d_nrm + e, u);
+    }
+  }
+}
+
+// MarginLoss.forward (MarginLoss.py:28-36): p [rows] broadcast against n [rows, cols].
+//   plain: mean_{rows,cols}(max(p - n, -margin)) + margin
+//   adv  : mean_rows( sum_cols softmax_cols(-n*T) * max(p - n, -margin) ) + margin  (weights detached)
+// One CTA per row chunk; partial sums are reduced with one atomicAdd per CTA into loss[0], which the
+// host wrapper zeroes first and then finalises (+margin) with a tiny second kernel.
+__global__ void margin_loss_kernel(const float* __restrict__ p, const float* __restrict__ n, int64_t rows, int64_t cols,
+                                   float margin, float adv_t, int use_adv, float* __restrict__ loss_acc,
+                                   float* __restrict__ d_p, float* __restrict__ d_n, float gscale) {
+  __shared__ float red[32];
+  float local = 0.f;
+  for (int64_t row = blockIdx.x; row < rows; row += gridDim.x) {
+    const float pv = __ldg(p + row);
+    const float* nr = n + row * cols;
+    float mx = -INFINITY, den = 1.f;
+    if (use_adv) {   // softmax over the row
+      for (int64_t c = threadIdx.x; c < cols; c += blockDim.x) mx = fmaxf(mx, -nr[c] * adv_t);
+      mx = warp_max(mx);
+      if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = mx;
+      __syncthreads();
+      mx = -INFINITY;
+      for (int i = 0; i < (blockDim.x >> 5); ++i) mx = fmaxf(mx, red[i]);
+      __syncthreads();
+      float s = 0.f;
+      for (int64_t c = threadIdx.x; c < cols; c += blockDim.x) s += expf(-nr[c] * adv_t - mx);
+      s = warp_sum(s);
+      if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = s;
+      __syncthreads();
+      den = 0.f;
+      for (int i = 0; i < (blockDim.x >> 5); ++i) den += red[i];
+      __syncthreads();
+    }
+    float dp = 0.f;
+    for (int64_t c = threadIdx.x; c < cols; c += blockDim.x) {
+      const float nv = nr[c];
+      const float diff = pv - nv;
+      const bool active = diff > -margin;          // torch.max(a, b): gradient to a where a > b
+      const float wgt = use_adv ? expf(-nv * adv_t - mx) / den : 1.f;
+      local += wgt * fmaxf(diff, -margin);
+      if (d_n) {
+        const float gsc = active ? gscale * wgt : 0.f;
+        d_n[row * cols + c] = -gsc;
+        dp += gsc;
+      }
+    }
+    if (d_p) {
+      dp = warp_sum(dp);
+      if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = dp;
+      __syncthreads();
+      if (threadIdx.x == 0) { float a = 0.f; for (int i = 0; i < (blockDim.x >> 5); ++i) a += red[i]; d_p[row] = a; }
+      __syncthreads();
+    }
+  }
+  local = warp_sum(local);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = local;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float a = 0.f;
+    for (int i = 0; i < (blockDim.x >> 5); ++i) a += red[i];
+    atomicAdd(loss_acc, a);
+  }
+}
+
+__global__ void margin_loss_finalize(float* loss, float inv_count, float margin) { loss[0] = loss[0] * inv_count + margin; }
+
+template <int EPL>
+static int launch_transh(bool backward, const float* ent, const float* rel, const float* nrm, int ent_tot, int rel_tot,
+                         int dim, const TripleIndex& idx, int64_t T, int p_norm, int norm_flag, float* h_out,
+                         float* r_out, float* w_out, float* t_out, float* score, const float* dscore, float* d_ent,
+                         float* d_rel, float* d_nrm, cudaStream_t stream) {
+  const size_t table_bytes = ((size_t)ent_tot + 2 * (size_t)rel_tot) * dim * sizeof(float);
+  const bool fits = table_bytes <= 96 * 1024;
+  const int64_t want = ceil_div64(T, kTranshWarps * 4);
+  const int per_sm = fits ? (table_bytes > 48 * 1024 ? 2 : 4) : 8;
+  int grid = (int)(want < (int64_t)num_sms() * per_sm ? want : (int64_t)num_sms() * per_sm);
+  if (grid < 1) grid = 1;
+  if (!backward) {
+    if (fits) {
+      auto k = transh_forward_kernel<EPL, true>;
+      SKG_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)table_bytes));
+      k<<<grid, kTranshThreads, table_bytes, stream>>>(ent, rel, nrm, ent_tot, rel_tot, dim, idx, T, p_norm, norm_flag,
+                                                       h_out, r_out, w_out, t_out, score);
+    } else {
+      transh_forward_kernel<EPL, false><<<grid, kTranshThreads, 0, stream>>>(ent, rel, nrm, ent_tot, rel_tot, dim, idx, T,
+                                                                             p_norm, norm_flag, h_out, r_out, w_out,
+                                                                             t_out, score);
+    }
+    return check_launch("transh_forward_kernel");
+  }
+  if (fits) {
+    auto k = transh_backward_kernel<EPL, true>;
+    SKG_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)table_bytes));
+    k<<<grid, kTranshThreads, table_bytes, stream>>>(ent, rel, nrm, ent_tot, rel_tot, dim, idx, T, p_norm, norm_flag,
+                                                     dscore, d_ent, d_rel, d_nrm);
+  } else {
+    transh_backward_kernel<EPL, false><<<grid, kTranshThreads, 0, stream>>>(ent, rel, nrm, ent_tot, rel_tot, dim, idx, T,
+                                                                            p_norm, norm_flag, dscore, d_ent, d_rel, d_nrm);
+  }
+  return check_launch("transh_backward_kernel");
+}
+
+static int dispatch_transh(bool backward, const float* ent, const float* rel, const float* nrm, int ent_tot, int rel_tot,
+                           int dim, const TripleIndex& idx, int64_t T, int p_norm, int norm_flag, float* h_out,
+                           float* r_out, float* w_out, float* t_out, float* score, const float* dscore, float* d_ent,
+                           float* d_rel, float* d_nrm, cudaStream_t stream) {
+  SKG_REQUIRE(dim >= 1 && dim <= 256, "TransH dim must be in [1, 256], got %d", dim);
+  SKG_REQUIRE(p_norm == 1 || p_norm == 2, "p_norm must be 1 or 2, got %d", p_norm);
+  SKG_REQUIRE(ent_tot > 0 && rel_tot > 0 && T >= 0, "bad table sizes");
+  if (T == 0) return SKG_OK;
+  SKG_REQUIRE(ent && rel && nrm, "null table pointer");
+#define SKG_TRANSH_CASE(E)                                                                                          \
+  return launch_transh<E>(backward, ent, rel, nrm, ent_tot, rel_tot, dim, idx, T, p_norm, norm_flag, h_out, r_out, \
+                          w_out, t_out, score, dscore, d_ent, d_rel, d_nrm, stream)
+  if (dim <= 32) SKG_TRANSH_CASE(1);
+  if (dim <= 64) SKG_TRANSH_CASE(2);
+  if (dim <= 128) SKG_TRANSH_CASE(4);
+  SKG_TRANSH_CASE(8);
+#undef SKG_TRANSH_CASE
+}
+
+}  // namespace skg
+
+using namespace skg;
+
+extern "C" int skg_transh_forward(const float* ent, const float* rel, const float* nrm, int ent_tot, int rel_tot,
+                                  int dim, const int64_t* head, const int64_t* relation, const int64_t* tail,
+                                  int64_t num_triples, int p_norm, int norm_flag, float* h_out, float* r_out,
+                                  float* w_out, float* t_out, float* score, cudaStream_t stream) {
+  SKG_REQUIRE(num_triples == 0 || (head && relation && tail && score), "null index/score pointer");
+  SKG_REQUIRE((h_out != nullptr) == (r_out != nullptr) && (h_out != nullptr) == (w_out != nullptr) &&
+                  (h_out != nullptr) == (t_out != nullptr),
+              "h_out, r_out, w_out, t_out must be all set or all null");
+  TripleIndex idx{head, relation, tail, nullptr, 0, rel_tot, 0};
+  return dispatch_transh(false, ent, rel, nrm, ent_tot, rel_tot, dim, idx, num_triples, p_norm, norm_flag, h_out, r_out,
+                         w_out, t_out, score, nullptr, nullptr, nullptr, nullptr, stream);
+}
+
+extern "C" int skg_transh_forward_grid(const float* ent, const float* rel, const float* nrm, int ent_tot, int rel_tot,
+                                       int dim, int64_t head_const, const int64_t* cell_tail, int64_t num_cells,
+                                       int p_norm, int norm_flag, float* h_out, float* r_out, float* w_out,
+                                       float* t_out, float* score, cudaStream_t stream) {
+  SKG_REQUIRE(num_cells == 0 || score, "null score pointer");
+  SKG_REQUIRE(head_const >= 0 && head_const < ent_tot, "head_const out of range");
+  SKG_REQUIRE((h_out != nullptr) == (r_out != nullptr) && (h_out != nullptr) == (w_out != nullptr) &&
+                  (h_out != nullptr) == (t_out != nullptr),
+              "h_out, r_out, w_out, t_out must be all set or all null");
+  TripleIndex idx{nullptr, nullptr, nullptr, cell_tail, head_const, rel_tot, 1};
+  return dispatch_transh(false, ent, rel, nrm, ent_tot, rel_tot, dim, idx, num_cells * rel_tot, p_norm, norm_flag, h_out,
+                         r_out, w_out, t_out, score, nullptr, nullptr, nullptr, nullptr, stream);
+}
+
+extern "C" int skg_transh_backward(const float* ent, const float* rel, const float* nrm, int ent_tot, int rel_tot,
+                                   int dim, const int64_t* head, const int64_t* relation, const int64_t* tail,
+                                   int64_t num_triples, int p_norm, int norm_flag, const float* dscore, float* d_ent,
+                                   float* d_rel, float* d_nrm, cudaStream_t stream) {
+  SKG_REQUIRE(num_triples == 0 || (head && relation && tail && dscore && d_ent && d_rel && d_nrm), "null pointer");
+  TripleIndex idx{head, relation, tail, nullptr, 0, rel_tot, 0};
+  return dispatch_transh(true, ent, rel, nrm, ent_tot, rel_tot, dim, idx, num_triples, p_norm, norm_flag, nullptr,
+                         nullptr, nullptr, nullptr, nullptr, dscore, d_ent, d_rel, d_nrm, stream);
+}
+
+extern "C" int skg_margin_loss(const float* p_score, const float* n_score, int64_t rows, int64_t cols, float margin,
+                               float adv_temperature, int use_adv, float* loss, float* d_p, float* d_n,
+                               float grad_scale, cudaStream_t stream) {
+  SKG_REQUIRE(rows > 0 && cols > 0 && p_score && n_score && loss, "margin loss needs non-empty scores");
+  SKG_REQUIRE((d_p != nullptr) == (d_n != nullptr), "d_p and d_n must both be set or both null");
+  SKG_CUDA(cudaMemsetAsync(loss, 0, sizeof(float), stream));
+  const float inv_count = use_adv ? 1.f / (float)rows : 1.f / ((float)rows * (float)cols);
+  const int threads = cols >= 256 ? 256 : (cols >= 64 ? 64 : 32);
+  const int grid = (int)(rows < 4096 ? rows : 4096);
+  margin_loss_kernel<<<grid, threads, 0, stream>>>(p_score, n_score, rows, cols, margin, adv_temperature, use_adv, loss,
+                                                   d_p, d_n, grad_scale * inv_count);
+  int rc = check_launch("margin_loss_kernel");
+  if (rc) return rc;
+  margin_loss_finalize<<<1, 1, 0, stream>>>(loss, inv_count, margin);
+  return check_launch("margin_loss_finalize");
+}
