@@ -98,6 +98,44 @@ int skg_margin_loss(const float* p_score, const float* n_score, int64_t rows, in
 int skg_focal_loss(const float* x, const float* y, int64_t n, float alpha, float gamma, float eps,
                    float* loss, const float* grad_out, float* dx, cudaStream_t stream);
 
+/* ---- bf16 tensor-core GEMM with fused epilogues ---------------------------------------------
+ * C[M,N] = epilogue(A[M,K] x B[N,K]^T), A and B bf16 with K contiguous (B in nn.Linear weight
+ * layout), fp32 accumulation in TMEM (tcgen05.mma).  Carries every dense layer of the head:
+ * MultiBranchFusion / MessageMBF (head.py:431-530, concatenated-branch form), box_head,
+ * spatial_head, fc_head / fc_tail (head.py:635-701), predictor / suppressor (models.py:176-177).
+ *
+ * The output columns are split into up to 4 groups (sorted, n_begin multiples of block_n); for a
+ * row r and a column c of group g (lc = c - n_begin):
+ *     v = acc + bias[c]                                   (bias NULL -> 0; indexed by GLOBAL column)
+ *     raw_bf16[out_row[r]][lc] = v                        (optional copy before the product)
+ *     v *= mul_p[row_p[r]][lc] (+ mul_q[row_q[r]][lc])    (optional Hadamard with gathered fp32 tables)
+ *     v = max(v, 0)                                       (flags & SKG_EPI_RELU)
+ *     v += residual[row_r[r]][lc]                         (optional)
+ *     dot_out[out_row[r]][tile] = sum_lc v * dot_w[lc]    (optional fused row-dot, one partial per N tile)
+ *     out_bf16 / out_f32 [out_row[r]][lc] = v             (optional; out_row NULL = r, < 0 = skip row)
+ * row_* NULL means the identity map.  bias, dot_w and the gathered tables are read in 32-column
+ * chunks, so they (and out_bf16 / raw_bf16 rows) must be padded to a multiple of 32 columns;
+ * out_f32 is masked at N exactly. */
+#define SKG_EPI_RELU 1
+typedef struct skg_epilogue_group {
+  int32_t n_begin;
+  int32_t flags;
+  const float* bias;
+  const float* mul_p; const int32_t* row_p; int32_t ld_p;
+  const float* mul_q; const int32_t* row_q; int32_t ld_q;
+  const float* residual; const int32_t* row_r; int32_t ld_r;
+  const float* dot_w; float* dot_out; int32_t ld_dot;
+  void* out_bf16; int32_t ld_ob;
+  float* out_f32; int32_t ld_of;
+  void* raw_bf16; int32_t ld_raw;
+  const int32_t* out_row;
+} skg_epilogue_group;
+
+/* groups is a HOST array of num_groups descriptors (copied into the launch).  block_n = 128, 256
+ * or 0 (auto: 256 when N % 256 == 0).  lda / ldb are row pitches in elements (multiples of 8). */
+int skg_gemm_bf16(const void* A, int64_t lda, const void* B, int64_t ldb, int M, int N, int K,
+                  const skg_epilogue_group* groups, int num_groups, int block_n, cudaStream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -85,3 +85,59 @@ def require_cuda(*tensors):
         if t is not None and not t.is_cuda:
             raise SkgError("skghoi_b200 runs on CUDA tensors only (got a %s tensor); there is no CPU fallback"
                            % t.device.type)
+
+
+class EpilogueGroup(ctypes.Structure):
+    """Mirror of ``skg_epilogue_group`` (include/skghoi_b200.h)."""
+    _fields_ = [
+        ("n_begin", ctypes.c_int32), ("flags", ctypes.c_int32),
+        ("bias", c_void_p),
+        ("mul_p", c_void_p), ("row_p", c_void_p), ("ld_p", ctypes.c_int32),
+        ("mul_q", c_void_p), ("row_q", c_void_p), ("ld_q", ctypes.c_int32),
+        ("residual", c_void_p), ("row_r", c_void_p), ("ld_r", ctypes.c_int32),
+        ("dot_w", c_void_p), ("dot_out", c_void_p), ("ld_dot", ctypes.c_int32),
+        ("out_bf16", c_void_p), ("ld_ob", ctypes.c_int32),
+        ("out_f32", c_void_p), ("ld_of", ctypes.c_int32),
+        ("raw_bf16", c_void_p), ("ld_raw", ctypes.c_int32),
+        ("out_row", c_void_p),
+    ]
+
+
+EPI_RELU = 1
+_SIGNATURES["skg_gemm_bf16"] = (I, [P, L, P, L, I, I, I, ctypes.POINTER(EpilogueGroup), I, I, P])
+
+
+def epilogue_group(n_begin=0, relu=False, bias=None, mul_p=None, row_p=None, mul_q=None, row_q=None,
+                   residual=None, row_r=None, dot_w=None, dot_out=None, out_bf16=None, out_f32=None,
+                   raw_bf16=None, out_row=None):
+    """Builds one epilogue group from tensors (leading dimensions are taken from ``stride(0)``)."""
+    def a(t):
+        return t.data_ptr() if t is not None else None
+
+    def ld(t):
+        return int(t.stride(0)) if t is not None and t.dim() >= 2 else 0
+    g = EpilogueGroup()
+    g.n_begin = int(n_begin); g.flags = EPI_RELU if relu else 0
+    g.bias = a(bias)
+    g.mul_p, g.row_p, g.ld_p = a(mul_p), a(row_p), ld(mul_p)
+    g.mul_q, g.row_q, g.ld_q = a(mul_q), a(row_q), ld(mul_q)
+    g.residual, g.row_r, g.ld_r = a(residual), a(row_r), ld(residual)
+    g.dot_w, g.dot_out, g.ld_dot = a(dot_w), a(dot_out), ld(dot_out)
+    g.out_bf16, g.ld_ob = a(out_bf16), ld(out_bf16)
+    g.out_f32, g.ld_of = a(out_f32), ld(out_f32)
+    g.raw_bf16, g.ld_raw = a(raw_bf16), ld(raw_bf16)
+    g.out_row = a(out_row)
+    return g
+
+
+def gemm_bf16(A, B, groups, M=None, N=None, K=None, block_n=0):
+    """C = epilogue(A[M,K] @ B[N,K]^T); A, B bf16 CUDA tensors with unit inner stride."""
+    require_cuda(A, B)
+    assert A.dtype == torch.bfloat16 and B.dtype == torch.bfloat16 and A.stride(1) == 1 and B.stride(1) == 1
+    M = A.shape[0] if M is None else M
+    N = B.shape[0] if N is None else N
+    K = A.shape[1] if K is None else K
+    arr = (EpilogueGroup * len(groups))(*groups)
+    with torch.cuda.device(A.device):
+        call("skg_gemm_bf16", ptr(A), A.stride(0), ptr(B), B.stride(0), M, N, K, arr, len(groups), block_n,
+             stream_ptr(A.device))
