@@ -129,12 +129,51 @@ typedef struct skg_epilogue_group {
   float* out_f32; int32_t ld_of;
   void* raw_bf16; int32_t ld_raw;
   const int32_t* out_row;
+  void* lo_bf16; int32_t ld_lo;   /* optional: bf16(v - float(bf16(v))), the rounding residual of out_bf16 */
 } skg_epilogue_group;
 
 /* groups is a HOST array of num_groups descriptors (copied into the launch).  block_n = 128, 256
  * or 0 (auto: 256 when N % 256 == 0).  lda / ldb are row pitches in elements (multiples of 8). */
 int skg_gemm_bf16(const void* A, int64_t lda, const void* B, int64_t ldb, int M, int N, int K,
                   const skg_epilogue_group* groups, int num_groups, int block_n, cudaStream_t stream);
+
+/* ---- glue kernels between the GEMMs (csrc/headops.cu) ---------------------------------------- */
+
+/* dst[r, 0:cols_pad] = bf16(relu?(src[r, 0:cols] + bias)), zero padded (operand packing for the GEMMs). */
+int skg_cast_pad_bf16(const float* src, int64_t ld_src, const float* bias, int relu, int64_t rows, int cols,
+                      void* dst, int64_t ld_dst, int cols_pad, cudaStream_t stream);
+
+/* spatial_head layer 0 (head.py:663-664), fp32 math: out_bf16[cells,128] = relu(enc[cells,46] W^T + b). */
+int skg_spatial_fc1(const float* enc, const float* weight, const float* bias, int64_t cells, int in_features,
+                    int out_features, void* out_bf16, cudaStream_t stream);
+
+/* Inputs of fc_head / fc_tail (head.py:875-885): h_in[humans, ld] = cat(node_enc[human box], E[human_idx]),
+ * o_in[boxes, ld] = cat(node_enc[box], E[box index within image]) as bf16, zero padded to ld. */
+int skg_node_inputs(const void* node_enc_bf16, int enc_dim, const float* ent, int ent_dim, int ent_tot,
+                    int human_idx, const int32_t* box_off, const int32_t* hum_off, int num_images,
+                    int total_boxes, int total_humans, void* h_in, void* o_in, int ld, cudaStream_t stream);
+
+/* avg_pool(features['3']).flatten(1) (head.py:811): planes = B*C, hw = H*W. */
+int skg_global_pool(const float* features, int64_t planes, int hw, void* out_bf16, float* out_f32,
+                    cudaStream_t stream);
+
+/* Message aggregation (head.py:897, 909-910, 916-921): adjacency = sum(dot_part) + adj_bias,
+ * Z_h[i] = sum_j softmax_j(adj[i,:]) H_os[i,j], Z_o[j] = sum_i softmax_i(adj[:,j]) H_so[i,j] (bf16). */
+int skg_message_aggregate(const float* dot_part, int num_part, float adj_bias, const void* H_os, const void* H_so,
+                          int64_t ld_h, const int32_t* box_off, const int32_t* hum_off, const int64_t* cell_off,
+                          int num_images, int total_boxes, int total_humans, int max_per_image, int width,
+                          void* Z_h, void* Z_o, float* adjacency, cudaStream_t stream);
+
+/* LayerNorm (head.py:912-914, 923-925): rows [0, rows_a) use (w_a, b_a), the rest (w_b, b_b). */
+int skg_layernorm(const float* x, int64_t rows, int64_t rows_a, int width, const float* w_a, const float* b_a,
+                  const float* w_b, const float* b_b, float eps, float* out_f32, void* out_bf16,
+                  cudaStream_t stream);
+
+/* Branch product of the final attention head (head.py:966-970):
+ * H[cell] = bf16(relu(S_raw[cell] * (U_h[hrow[cell]] + U_o[orow[cell]]))). */
+int skg_hadamard_cells(const void* S_raw, int64_t ld_s, const float* U_h, int64_t ld_uh, const float* U_o,
+                       int64_t ld_uo, const int32_t* hrow, const int32_t* orow, int64_t cells, int width,
+                       void* H, int64_t ld_hh, cudaStream_t stream);
 
 #ifdef __cplusplus
 }

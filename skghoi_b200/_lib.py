@@ -26,6 +26,13 @@ _SIGNATURES = {
     "skg_transh_backward": (I, [P, P, P, I, I, I, P, P, P, L, I, I, P, P, P, P, P]),
     "skg_margin_loss": (I, [P, P, L, L, F, F, I, P, P, P, F, P]),
     "skg_focal_loss": (I, [P, P, L, F, F, F, P, P, P, P]),
+    "skg_cast_pad_bf16": (I, [P, L, P, I, L, I, P, L, I, P]),
+    "skg_spatial_fc1": (I, [P, P, P, L, I, I, P, P]),
+    "skg_node_inputs": (I, [P, I, P, I, I, I, P, P, I, I, I, P, P, I, P]),
+    "skg_global_pool": (I, [P, L, I, P, P, P]),
+    "skg_message_aggregate": (I, [P, I, F, P, P, L, P, P, P, I, I, I, I, I, P, P, P, P]),
+    "skg_layernorm": (I, [P, L, L, I, P, P, P, P, F, P, P, P]),
+    "skg_hadamard_cells": (I, [P, L, P, L, P, L, P, P, L, I, P, L, P]),
 }
 
 _lib = None
@@ -100,6 +107,7 @@ class EpilogueGroup(ctypes.Structure):
         ("out_f32", c_void_p), ("ld_of", ctypes.c_int32),
         ("raw_bf16", c_void_p), ("ld_raw", ctypes.c_int32),
         ("out_row", c_void_p),
+        ("lo_bf16", c_void_p), ("ld_lo", ctypes.c_int32),
     ]
 
 
@@ -109,7 +117,7 @@ _SIGNATURES["skg_gemm_bf16"] = (I, [P, L, P, L, I, I, I, ctypes.POINTER(Epilogue
 
 def epilogue_group(n_begin=0, relu=False, bias=None, mul_p=None, row_p=None, mul_q=None, row_q=None,
                    residual=None, row_r=None, dot_w=None, dot_out=None, out_bf16=None, out_f32=None,
-                   raw_bf16=None, out_row=None):
+                   raw_bf16=None, out_row=None, lo_bf16=None):
     """Builds one epilogue group from tensors (leading dimensions are taken from ``stride(0)``)."""
     def a(t):
         return t.data_ptr() if t is not None else None
@@ -127,6 +135,7 @@ def epilogue_group(n_begin=0, relu=False, bias=None, mul_p=None, row_p=None, mul
     g.out_f32, g.ld_of = a(out_f32), ld(out_f32)
     g.raw_bf16, g.ld_raw = a(raw_bf16), ld(raw_bf16)
     g.out_row = a(out_row)
+    g.lo_bf16, g.ld_lo = a(lo_bf16), ld(lo_bf16)
     return g
 
 

@@ -303,6 +303,16 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             dst[j >> 3] = make_uint4(pack_bf16(v[j], v[j + 1]), pack_bf16(v[j + 2], v[j + 3]), pack_bf16(v[j + 4], v[j + 5]),
                                      pack_bf16(v[j + 6], v[j + 7]));
         }
+        if (store_ok && G.lo_bf16) {   // residual of the bf16 rounding: v ~= hi + lo to ~16 mantissa bits
+          uint4* dst = reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(G.lo_bf16) + (int64_t)ro * G.ld_lo + lc);
+#pragma unroll
+          for (int j = 0; j < 32; j += 8) {
+            float l[8];
+#pragma unroll
+            for (int t = 0; t < 8; ++t) l[t] = v[j + t] - __bfloat162float(__float2bfloat16(v[j + t]));
+            dst[j >> 3] = make_uint4(pack_bf16(l[0], l[1]), pack_bf16(l[2], l[3]), pack_bf16(l[4], l[5]), pack_bf16(l[6], l[7]));
+          }
+        }
         if (store_ok && G.out_f32) {
           float* dst = G.out_f32 + (int64_t)ro * G.ld_of + lc;
           if (col + 32 <= N && (G.ld_of & 3) == 0) {
@@ -406,6 +416,7 @@ extern "C" int skg_gemm_bf16(const void* A, int64_t lda, const void* B, int64_t 
     SKG_REQUIRE(!g.mul_q || g.mul_p, "group %d: mul_q requires mul_p", i);
     SKG_REQUIRE(!g.out_bf16 || g.ld_ob % 8 == 0, "group %d: ld_ob must be a multiple of 8", i);
     SKG_REQUIRE(!g.raw_bf16 || g.ld_raw % 8 == 0, "group %d: ld_raw must be a multiple of 8", i);
+    SKG_REQUIRE(!g.lo_bf16 || g.ld_lo % 8 == 0, "group %d: ld_lo must be a multiple of 8", i);
     SKG_REQUIRE(!g.mul_p || g.ld_p % 4 == 0, "group %d: ld_p must be a multiple of 4", i);
     SKG_REQUIRE(!g.mul_q || g.ld_q % 4 == 0, "group %d: ld_q must be a multiple of 4", i);
     SKG_REQUIRE(!g.residual || g.ld_r % 4 == 0, "group %d: ld_r must be a multiple of 4", i);

@@ -1,0 +1,62 @@
+"""GPU parity of the full interaction-head pipeline against the reference goldens and the CPU oracle."""
+import pytest
+import torch
+
+from helpers import load_golden, build_head, synthetic, logits_close
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda:0"
+_heads = {}
+
+
+def gpu_head(seed=42):
+    if seed not in _heads:
+        ih = build_head(seed)
+        ih.box_pair_head.transh_head.set_tables(*synthetic.make_transh_tables(42))
+        _heads[seed] = ih.to(DEV).eval()
+        ih.box_pair_head.transh_head.transh.to(DEV)
+    return _heads[seed]
+
+
+def _run_core(gold, **kw):
+    from skghoi_b200 import engine
+    ih = gpu_head()
+    batch = synthetic.make_batch(gold["shapes_hn"], seed=gold["seed"], image_shapes=gold["image_shapes"],
+                                 with_targets=gold["train"])
+    meta = engine._host_meta(batch["box_labels"], batch["box_scores"], 49)
+    boxes_cat = torch.cat(batch["box_coords"]).to(DEV)
+    with torch.no_grad():
+        out = engine.head_forward(ih, batch["features"]["3"].to(DEV), batch["image_shapes"],
+                                  batch["box_features"].to(DEV), boxes_cat, meta, want_taps=True, **kw)
+    torch.cuda.synchronize()
+    return out, batch
+
+
+@pytest.mark.parametrize("case", ["head_small2_eval", "head_c1_eval"])
+@pytest.mark.parametrize("precise", [True, False])
+def test_head_core_logits_vs_reference(case, precise):
+    gold = load_golden(case)
+    out, batch = _run_core(gold, precise_logits=precise)
+    nc = 117
+    lp, ls = out["logits"][:, :nc].cpu(), out["logits"][:, nc:].cpu()
+    assert torch.equal(out["x_keep"].cpu(), torch.cat(gold["x_keep"]))
+    assert torch.equal(out["y_keep"].cpu(), torch.cat(gold["y_keep"]))
+    torch.testing.assert_close(out["enc"].cpu(), torch.cat(gold["spatial46"]), rtol=1e-5, atol=1e-5)
+    NH = out["NH"]
+    # intermediates (bf16 pipeline vs fp32 reference): loose, they only localise failures
+    for got, ref, name in ((out["hN32"].cpu(), torch.cat(gold["graph_human_node"]), "graph_human_node"),
+                           (out["oN32"].cpu(), torch.cat(gold["graph_object_node"]), "graph_object_node"),
+                           (out["adjacency"].cpu(), torch.cat([a.flatten() for a in gold["adjacency"]]), "adjacency"),
+                           (out["enc32"][:NH].cpu(), torch.cat(gold["h_node_enc"]), "h_node_enc"),
+                           (out["enc32"][NH:].cpu(), torch.cat(gold["node_enc"]), "node_enc")):
+        err = float((got - ref).abs().max()); scale = float(ref.abs().max())
+        assert err <= 3e-2 * scale, (name, err, scale)
+    ok_p, st_p = logits_close(lp, gold["logits_p"])
+    ok_s, st_s = logits_close(ls, gold["logits_s"])
+    rel_p = float((lp - gold["logits_p"]).norm() / gold["logits_p"].norm())
+    print(case, "precise" if precise else "plain", "logits_p", st_p, "rel_l2", rel_p, "logits_s", st_s)
+    # north_star: interaction logits within 1e-2 relative
+    assert st_p["max_abs"] <= 1e-2 * st_p["ref_max"] and rel_p <= 1e-2
+    assert st_s["max_abs"] <= 1e-2 * st_s["ref_max"]
+    if precise:
+        assert ok_p and ok_s, (st_p, st_s)      # SURVEY 8(d) per-element form
