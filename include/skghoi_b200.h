@@ -175,6 +175,44 @@ int skg_hadamard_cells(const void* S_raw, int64_t ld_s, const float* U_h, int64_
                        int64_t ld_uo, const int32_t* hrow, const int32_t* orow, int64_t cells, int width,
                        void* H, int64_t ld_hh, cudaStream_t stream);
 
+/* ---- priors, ground-truth association, post-processing (csrc/postproc.cu) ---------------------- */
+typedef struct skg_post_tables {
+  const int32_t* verb_off;    /* [num_obj_cls+1] CSR of valid verbs per object class, ascending (object_class_to_target_class) */
+  const int32_t* verb_idx;    /* [nnz] */
+  const int32_t* pair2cell;   /* [P]     from skg_pairs_spatial_encode */
+  const int32_t* cell_hrow;   /* [cells] */
+  const int32_t* cell_orow;   /* [cells] */
+  const int32_t* cell_img;    /* [cells] */
+  const int32_t* hum_off;     /* [B+1] */
+  const int32_t* box_off;     /* [B+1] */
+  const int64_t* pair_off;    /* [B+1] */
+  const int64_t* labels;      /* [boxes] object class per box */
+  const float* scores;        /* [boxes] detection scores */
+  const int32_t* box_prefix;  /* [boxes]  exclusive within-image prefix of box_cnt (postprocess only) */
+  const int32_t* box_cnt;     /* [boxes]  number of valid verbs of the box's class (postprocess only) */
+  const int64_t* hum_base;    /* [humans] batch-global output offset of each human row (postprocess only) */
+} skg_post_tables;
+
+/* InteractionHead.postprocess (head.py:291-337) for the whole batch: logits [P, ld] holds num_cls verb
+ * logits followed by the suppressor logit.  For every (pair, valid verb) entry e (row-major nonzero order
+ * of prior[0], head.py:315): index, prediction, scores = sigmoid(logit) * prior_h * prior_o * weights,
+ * prior [2, total_entries]; per pair: weights = sigmoid(suppressor logit), object class; with gt_labels
+ * [P, num_cls]: labels per entry and unary_labels per pair (head.py:325-330).  tables is a HOST struct
+ * of DEVICE pointers. */
+int skg_postprocess(const float* logits, int ld_logits, int num_cls, const skg_post_tables* tables, int64_t pairs,
+                    float prior_power, const float* gt_labels, int64_t total_entries, int64_t* out_index,
+                    int64_t* out_pred, float* out_scores, float* out_prior, float* out_weights,
+                    float* out_labels, float* out_unary, int64_t* out_object, cudaStream_t stream);
+
+/* compute_prior_scores (head.py:721-767): dense prior [2, P, num_cls]. */
+int skg_prior_dense(const skg_post_tables* tables, int64_t pairs, int num_cls, float prior_power, float* prior,
+                    cudaStream_t stream);
+
+/* associate_with_ground_truth (head.py:703-719): labels [P, num_cls] (zeroed here), GT pairs in CSR by image. */
+int skg_associate_gt(const float* boxes, const skg_post_tables* tables, int64_t pairs, int num_cls,
+                     const int32_t* gt_off, const float* gt_boxes_h, const float* gt_boxes_o,
+                     const int64_t* gt_verb, float fg_iou_thresh, float* labels, cudaStream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

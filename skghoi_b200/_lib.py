@@ -111,6 +111,17 @@ class EpilogueGroup(ctypes.Structure):
     ]
 
 
+class PostTables(ctypes.Structure):
+    """Mirror of ``skg_post_tables``."""
+    _fields_ = [(k, c_void_p) for k in ("verb_off", "verb_idx", "pair2cell", "cell_hrow", "cell_orow", "cell_img",
+                                        "hum_off", "box_off", "pair_off", "labels", "scores", "box_prefix", "box_cnt",
+                                        "hum_base")]
+
+
+_SIGNATURES["skg_postprocess"] = (I, [P, I, I, ctypes.POINTER(PostTables), L, F, P, L, P, P, P, P, P, P, P, P, P])
+_SIGNATURES["skg_prior_dense"] = (I, [ctypes.POINTER(PostTables), L, I, F, P, P])
+_SIGNATURES["skg_associate_gt"] = (I, [P, ctypes.POINTER(PostTables), L, I, P, P, P, P, F, P, P])
+
 EPI_RELU = 1
 _SIGNATURES["skg_gemm_bf16"] = (I, [P, L, P, L, I, I, I, ctypes.POINTER(EpilogueGroup), I, I, P])
 

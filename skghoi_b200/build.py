@@ -11,7 +11,7 @@ LIB = os.path.join(HERE, "libskghoi_b200.so")
 ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
 COMMON = ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC", "-I", os.path.join(ROOT, "include"), "-I", CSRC]
 # per-file extra flags: the elementwise parity kernels must not contract a*b+c into FMAs
-EXTRA = {"spatial.cu": ["-fmad=false"]}
+EXTRA = {"spatial.cu": ["-fmad=false"], "postproc.cu": ["-fmad=false"]}
 
 
 def _sources():

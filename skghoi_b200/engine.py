@@ -410,3 +410,286 @@ def head_forward(ih, features3: Tensor, image_shapes, box_features: Tensor, boxe
     out.update(logits=logits, feat=feat, adjacency=adjacency, node16=node, hN32=hN32, oN32=oN32, enc32=enc32,
                enc16=enc16, sp=sp, NH=NH, NB=NB)
     return out
+
+
+# =============================================================================================
+# priors / post-processing / API-level forwards
+# =============================================================================================
+class VerbTable:
+    """object_class_to_target_class as a CSR table on the device (ascending verb ids, de-duplicated:
+    the scatter at head.py:759-760 is idempotent and ``nonzero`` returns ascending columns)."""
+
+    def __init__(self, object_to_verb: List[list], device):
+        lens, flat = [], []
+        for verbs in object_to_verb:
+            v = sorted(set(int(t) for t in verbs))
+            lens.append(len(v)); flat.extend(v)
+        self.lens = np.asarray(lens, dtype=np.int64)
+        off = np.concatenate([[0], np.cumsum(self.lens)]).astype(np.int32)
+        self.d_off = torch.from_numpy(off).to(device)
+        self.d_idx = torch.tensor(flat if flat else [0], dtype=torch.int32).to(device)
+        self.device = device
+
+
+def _verb_table(G, device) -> VerbTable:
+    vt = G.__dict__.get("_skg_verbs")
+    if vt is None or vt.device != device:
+        vt = VerbTable(G.object_class_to_target_class, device)
+        G.__dict__["_skg_verbs"] = vt
+    return vt
+
+
+def _post_tables(G, run: dict, meta: dict, labels_dev: Tensor, scores_dev: Tensor, with_counts: bool):
+    """Builds the skg_post_tables struct; with_counts adds the closed-form output offsets."""
+    seg: Segments = run["seg"]
+    dev = seg.device
+    vt = _verb_table(G, dev)
+    t = _lib.PostTables()
+    keep = [labels_dev, scores_dev]
+    t.verb_off, t.verb_idx = vt.d_off.data_ptr(), vt.d_idx.data_ptr()
+    t.pair2cell, t.cell_hrow = run["pair2cell"].data_ptr(), run["cell_hrow"].data_ptr()
+    t.cell_orow, t.cell_img = run["cell_orow"].data_ptr(), run["cell_img"].data_ptr()
+    t.hum_off, t.box_off, t.pair_off = seg.d_hum_off.data_ptr(), seg.d_box_off.data_ptr(), seg.d_pair_off.data_ptr()
+    t.labels, t.scores = labels_dev.data_ptr(), scores_dev.data_ptr()
+    entries_per_image = None
+    if with_counts:
+        labels = meta["labels"]; scores = meta["scores"]
+        cnt = vt.lens[labels] if len(labels) else np.zeros(0, np.int64)
+        prefix = np.zeros_like(cnt); hum_base = np.zeros(seg.total_humans, dtype=np.int64)
+        entries_per_image = np.zeros(seg.B, dtype=np.int64)
+        total = 0
+        for b in range(seg.B):
+            lo, hi = int(seg.box_off[b]), int(seg.box_off[b + 1])
+            c = cnt[lo:hi]
+            prefix[lo:hi] = np.cumsum(c) - c
+            nh = int(seg.n_h[b])
+            if nh:
+                S = int(c.sum())
+                live = scores[lo:lo + nh] > 0
+                row_tot = np.where(live, S - c[:nh], 0)
+                h0 = int(seg.hum_off[b])
+                hum_base[h0:h0 + nh] = total + np.cumsum(row_tot) - row_tot
+                entries_per_image[b] = int(row_tot.sum())
+                total += int(row_tot.sum())
+        d_cnt = torch.from_numpy(cnt.astype(np.int32)).to(dev)
+        d_prefix = torch.from_numpy(prefix.astype(np.int32)).to(dev)
+        d_hbase = torch.from_numpy(hum_base).to(dev)
+        keep += [d_cnt, d_prefix, d_hbase]
+        t.box_cnt, t.box_prefix, t.hum_base = d_cnt.data_ptr(), d_prefix.data_ptr(), d_hbase.data_ptr()
+    return t, keep, entries_per_image
+
+
+def _gt_labels(G, run: dict, tables, boxes_cat: Tensor, targets: List[dict]) -> Tensor:
+    """associate_with_ground_truth for the batch (head.py:703-719, 934) -> labels [P, num_cls]."""
+    seg: Segments = run["seg"]
+    dev = seg.device
+    Pn = seg.total_pairs
+    counts = [int(t["boxes_h"].shape[0]) for t in targets]
+    gt_off = torch.tensor(np.concatenate([[0], np.cumsum(counts)]).astype(np.int32)).to(dev)
+    if sum(counts):
+        gh = torch.cat([t["boxes_h"] for t in targets]).to(dev, torch.float32).contiguous()
+        go = torch.cat([t["boxes_o"] for t in targets]).to(dev, torch.float32).contiguous()
+        gv = torch.cat([t["labels"] for t in targets]).to(dev, torch.int64).contiguous()
+    else:
+        gh = go = torch.zeros(1, 4, device=dev); gv = torch.zeros(1, dtype=torch.int64, device=dev)
+    labels = torch.empty(Pn, G.num_cls, dtype=torch.float32, device=dev)
+    with torch.cuda.device(dev):
+        _lib.call("skg_associate_gt", _lib.ptr(boxes_cat), ctypes_byref(tables), Pn, G.num_cls, _lib.ptr(gt_off),
+                  _lib.ptr(gh), _lib.ptr(go), _lib.ptr(gv), float(G.fg_iou_thresh), _lib.ptr(labels), _lib.stream_ptr(dev))
+    return labels
+
+
+def ctypes_byref(x):
+    import ctypes
+    return ctypes.byref(x)
+
+
+def _prep_inputs(G, features, box_features, box_coords, box_labels, box_scores, meta):
+    dev = box_features.device
+    _lib.require_cuda(box_features, features["3"], *box_coords)
+    meta = _host_meta(box_labels, box_scores, G.human_idx, meta)
+    boxes_cat = (torch.cat(list(box_coords)) if len(box_coords) else torch.zeros(0, 4, device=dev)).to(torch.float32).contiguous()
+    labels_dev = (torch.cat(list(box_labels)) if len(box_labels) else torch.zeros(0, device=dev)).to(torch.int64).contiguous()
+    scores_dev = (torch.cat(list(box_scores)) if len(box_scores) else torch.zeros(0, device=dev)).to(torch.float32).contiguous()
+    return meta, boxes_cat, labels_dev, scores_dev
+
+
+def _split(t: Tensor, sizes, dim=0):
+    return list(torch.split(t, [int(s) for s in sizes], dim=dim))
+
+
+def _transh_pos_neg(G, run, labels: Tensor, targets):
+    """TransH positive / negative selection (head.py:926-963).  The score of pair (i, j) and verb v is
+    score(h=human_idx, r=v, t=j): it does not depend on i, so no [n_h, n, 117] grid is materialised --
+    the selected triples are scored directly (differentiably, through csrc/transh.cu).  Negatives are
+    drawn with the CPU generator like the reference (torch.randperm, head.py:939)."""
+    seg: Segments = run["seg"]
+    th = G.transh_head
+    tr = th.transh
+    dev = seg.device
+    lab_img = _split(labels, seg.pair_off[1:] - seg.pair_off[:-1])
+    yk_img = _split(run["y_keep"], seg.pair_off[1:] - seg.pair_off[:-1])
+    pos_s, neg_s, ents_h, ents_t, rels, rnorms = [], [], [], [], [], []
+    for b in range(seg.B):
+        if seg.n_h[b] == 0:
+            continue
+        tl, yk = lab_img[b], yk_img[b]
+        px, py = torch.nonzero(tl).unbind(1)
+        neg_xy = (tl == 0).nonzero()
+        perm = torch.randperm(neg_xy.size(0))[:len(px)].to(dev)
+        nx, ny = neg_xy[perm].unbind(1)
+        pair_idx = torch.cat([px, nx]); verb = torch.cat([py, ny])
+        tails = yk[pair_idx]
+        heads = torch.full_like(tails, th.human_idx)
+        h_, r, w, t_, score = tr(heads, verb, tails)
+        k = len(px)
+        pos_s.append(score[:k]); neg_s.append(score[k:])
+        ents_h.append(h_); ents_t.append(t_); rels.append(r); rnorms.append(w)
+    return pos_s, neg_s, ents_h, ents_t, rels, rnorms
+
+
+def graph_head_forward(G, features, image_shapes, box_features, box_coords, box_labels, box_scores, targets=None,
+                       meta=None, ih=None):
+    """GraphHead.forward (head.py:769-993): the 8-tuple (eval) / 12-tuple (train) of per-image lists.
+    ``GraphHead`` alone has no predictor, so a shell InteractionHead is needed for the packed weights;
+    when called stand-alone one is created around it (predictor / suppressor unused)."""
+    if G.training:
+        assert targets is not None, "Targets should be passed during training"          # head.py:808-809
+    shell = ih if ih is not None else _shell_for(G)
+    meta, boxes_cat, labels_dev, scores_dev = _prep_inputs(G, features, box_features, box_coords, box_labels, box_scores, meta)
+    run = head_forward(shell, features["3"], image_shapes, box_features, boxes_cat, meta, precise_logits=False)
+    seg: Segments = run["seg"]
+    dev = seg.device
+    Pn = seg.total_pairs
+    psz = seg.pair_off[1:] - seg.pair_off[:-1]
+    R2 = 2 * G.representation_size
+    feats = _split(run["feat"][:, :R2].float(), psz)
+    tables, keep, _ = _post_tables(G, run, meta, labels_dev, scores_dev, with_counts=False)
+    prior = torch.empty(2, Pn, G.num_cls, dtype=torch.float32, device=dev)
+    with torch.cuda.device(dev):
+        _lib.call("skg_prior_dense", ctypes_byref(tables), Pn, G.num_cls, 1.0 if G.training else 2.8, _lib.ptr(prior),
+                  _lib.stream_ptr(dev))
+    priors = _split(prior, psz, dim=1)
+    p2c = run["pair2cell"].long()
+    hrow_box = (run["cell_orow"].long() - run["y"] + run["x"])[p2c] if Pn else torch.zeros(0, dtype=torch.int64, device=dev)
+    orow = run["cell_orow"].long()[p2c] if Pn else hrow_box
+    boxes_h = _split(boxes_cat[hrow_box], psz); boxes_o = _split(boxes_cat[orow], psz)
+    obj = _split(labels_dev[orow], psz)
+    all_labels, pos, neg, eh, et, rl, rn = [], [], [], [], [], [], []
+    if targets is not None:
+        labels = _gt_labels(G, run, tables, boxes_cat, targets)
+        all_labels = _split(labels, psz)
+        pos, neg, eh, et, rl, rn = _transh_pos_neg(G, run, labels, targets)
+    G.__dict__["_skg_last_run"] = run
+    if G.training:
+        return feats, boxes_h, boxes_o, obj, all_labels, priors, pos, neg, eh, et, rl, rn
+    return feats, boxes_h, boxes_o, obj, all_labels, priors, pos, neg
+
+
+def _shell_for(G):
+    sh = G.__dict__.get("_skg_shell")
+    if sh is None:
+        from .head import InteractionHead
+        dev = next(G.parameters()).device
+        pred = torch.nn.Linear(2 * G.representation_size, G.num_cls).to(dev)
+        sup = torch.nn.Linear(2 * G.representation_size, 1).to(dev)
+        sh = InteractionHead(None, G, sup, pred, G.human_idx, G.num_cls)
+        G.__dict__["_skg_shell"] = sh
+    return sh
+
+
+def interaction_head_from_pooled(ih, features, image_shapes, box_features, box_coords, box_labels, box_scores,
+                                 targets=None, meta=None) -> List[dict]:
+    """InteractionHead.forward from the pooled box features on (head.py:389-427)."""
+    from . import ops
+    from .kge import MarginLoss, NegativeSampling
+    G = ih.box_pair_head
+    if ih.training:
+        assert targets is not None, "Targets should be passed during training"          # head.py:380-381
+    meta, boxes_cat, labels_dev, scores_dev = _prep_inputs(G, features, box_features, box_coords, box_labels, box_scores, meta)
+    run = head_forward(ih, features["3"], image_shapes, box_features, boxes_cat, meta)
+    seg: Segments = run["seg"]
+    dev = seg.device
+    Pn = seg.total_pairs
+    nc = G.num_cls
+    tables, keep, per_img = _post_tables(G, run, meta, labels_dev, scores_dev, with_counts=True)
+    L = int(per_img.sum())
+    gt = _gt_labels(G, run, tables, boxes_cat, targets) if targets is not None else None
+    i64 = dict(dtype=torch.int64, device=dev); f32 = dict(dtype=torch.float32, device=dev)
+    index = torch.empty(L, **i64); pred = torch.empty(L, **i64); scores = torch.empty(L, **f32)
+    prior = torch.empty(2, L, **f32); weights = torch.empty(Pn, **f32); obj = torch.empty(Pn, **i64)
+    lab_e = torch.empty(L, **f32) if gt is not None else None
+    unary = torch.empty(Pn, **f32) if gt is not None else None
+    with torch.cuda.device(dev):
+        _lib.call("skg_postprocess", _lib.ptr(run["logits"]), run["logits"].stride(0), nc, ctypes_byref(tables), Pn,
+                  1.0 if G.training else 2.8, _lib.ptr(gt), L, _lib.ptr(index), _lib.ptr(pred), _lib.ptr(scores),
+                  _lib.ptr(prior), _lib.ptr(weights), _lib.ptr(lab_e), _lib.ptr(unary), _lib.ptr(obj), _lib.stream_ptr(dev))
+    psz = seg.pair_off[1:] - seg.pair_off[:-1]
+    p2c = run["pair2cell"].long()
+    if Pn:
+        hbox = (run["cell_orow"].long() - run["y"] + run["x"])[p2c]; obox = run["cell_orow"].long()[p2c]
+    else:
+        hbox = obox = torch.zeros(0, **i64)
+    bh = _split(boxes_cat[hbox], psz); bo = _split(boxes_cat[obox], psz)
+    results = []
+    for b, (idx_b, pr_b, sc_b, pri_b, w_b, o_b) in enumerate(zip(_split(index, per_img), _split(pred, per_img),
+                                                                _split(scores, per_img), _split(prior, per_img, dim=1),
+                                                                _split(weights, psz), _split(obj, psz))):
+        r = dict(boxes_h=bh[b], boxes_o=bo[b], index=idx_b, prediction=pr_b, scores=sc_b, object=o_b, prior=pri_b,
+                 weights=w_b)
+        results.append(r)
+    if gt is not None:
+        for r, l_b, u_b in zip(results, _split(lab_e, per_img), _split(unary, psz)):
+            r["labels"] = l_b; r["unary_labels"] = u_b
+    ih.__dict__["_skg_last_run"] = run
+    if ih.training:
+        # losses (head.py:153-235); n_p averaged over ranks when distributed (one 2-float all-reduce, no barriers)
+        n_p = torch.stack([(lab_e != 0).sum(), (unary != 0).sum()]).float()
+        if ih.distributed:
+            import torch.distributed as dist
+            dist.all_reduce(n_p)
+            n_p = n_p / dist.get_world_size()
+        hoi = ops.binary_focal_loss(scores, lab_e, reduction="sum", gamma=0.2) / n_p[0]
+        inter = ops.binary_focal_loss(weights, unary, reduction="sum", gamma=2.0) / n_p[1]
+        pos, neg, eh, et, rl, rn = _transh_pos_neg(G, run, gt, targets)
+        ns = NegativeSampling(loss=MarginLoss(margin=1), batch_size=256).to(dev)
+        transh = ns(pos, neg, eh, rl, rn, et) / n_p[1]
+        results.append(dict(hoi_loss=hoi, interactiveness_loss=inter, transH_loss=transh))
+    return results
+
+
+def preprocess_detections(ih, detections: List[dict], targets, append_gt: Optional[bool] = None) -> List[dict]:
+    """InteractionHead.preprocess (head.py:92-151).  Stays on stock torch / torchvision ops (score filter,
+    class-wise NMS, sort, cap, humans first) -- it is outside the hot path."""
+    import torchvision.ops.boxes as box_ops
+    results = []
+    for b_idx, det in enumerate(detections):
+        boxes, labels, scores = det["boxes"], det["labels"], det["scores"]
+        if append_gt is None:
+            append_gt = ih.training
+        if append_gt:
+            tgt = targets[b_idx]
+            ng = tgt["boxes_h"].shape[0]
+            boxes = torch.cat([tgt["boxes_h"], tgt["boxes_o"], boxes])
+            scores = torch.cat([torch.ones(2 * ng, device=scores.device), scores])
+            labels = torch.cat([ih.human_idx * torch.ones(ng, device=labels.device).long(), tgt["object"], labels])
+        active = torch.nonzero(scores >= ih.box_score_thresh).squeeze(1)
+        keep = box_ops.batched_nms(boxes[active], scores[active], labels[active], ih.box_nms_thresh)
+        active = active[keep]
+        active = active[torch.argsort(scores[active], descending=True)]
+        h_idx = torch.nonzero(labels[active] == ih.human_idx).squeeze(1)[:ih.max_human]
+        o_idx = torch.nonzero(labels[active] != ih.human_idx).squeeze(1)[:ih.max_object]
+        active = active[torch.cat([h_idx, o_idx])]
+        results.append(dict(boxes=boxes[active].view(-1, 4), labels=labels[active].view(-1), scores=scores[active].view(-1)))
+    return results
+
+
+def interaction_head_forward(ih, features, detections, image_shapes, targets=None) -> List[dict]:
+    """InteractionHead.forward (head.py:341-429): stock preprocess + RoIAlign, then the CUDA hot path."""
+    if ih.training:
+        assert targets is not None, "Targets should be passed during training"
+    detections = preprocess_detections(ih, detections, targets)
+    coords = [d["boxes"] for d in detections]; labels = [d["labels"] for d in detections]
+    scores = [d["scores"] for d in detections]
+    box_features = ih.box_roi_pool(features, coords, image_shapes)                        # head.py:387
+    return interaction_head_from_pooled(ih, features, image_shapes, box_features, coords, labels, scores, targets)
