@@ -1,0 +1,380 @@
+#!/usr/bin/env python
+"""Benchmark of the interaction-head hot path (BASELINE.json metric: HOI-head human-object pairs/s).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference]
+
+One "step" = one pass of the interaction head (eval) over one batch of synthetic HICO-DET-shaped
+detections: BASELINE.json configs[1] = 8 images x (16 humans, 32 boxes) -> 4096 grid cells, 3968
+valid pairs, 117 verbs, from the pooled box features to the post-processed result dicts
+(reference head.py:389-427).  For N > 1 (torchrun, one rank per GPU) every rank processes its own
+batch -- images are independent, there is no data-path collective ("weak" scaling).
+
+JSON keys beyond the base contract:
+  value      pairs/s with the step's inputs already resident in HBM (CUDA events, per-step, L2
+             flushed between steps, max over ranks);
+  e2e        the same metric through the public module API with pinned HOST inputs: H2D of the
+             step's inputs and D2H of its results are inside the timed region;
+  roofline   the dominant kernel (the fused fc_2 GEMM of the four MBFs, M = cells, N = 4096, K = 1024)
+             timed alone with CUDA events; spatial / transh hold the two bandwidth kernels;
+  cpu_baseline  the CPU restatement of the reference head (oracle/head_oracle.py, kind "port")
+             timed on this box's host cores on a bounded sample (rank 0, N = 1 only).
+`--impl reference` times that CPU head alone (the reference is eager PyTorch; its own checkout is
+not on the GPU box, so the pinned op-for-op port stands in).
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = "hoi_head_pairs_per_sec"
+UNIT = "pairs/s"
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=50)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--images", type=int, default=8, help="images per step per GPU (configs[1]: 8)")
+    ap.add_argument("--humans", type=int, default=16)
+    ap.add_argument("--boxes", type=int, default=32)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-rooflines", action="store_true")
+    return ap.parse_args()
+
+
+def workload_config(args, extra=None):
+    cfg = {"workload": "HICO-DET-shaped inference, batch %d images x (%d humans, %d boxes), 117 verbs "
+                       "(BASELINE configs[1])" % (args.images, args.humans, args.boxes),
+           "images_per_step_per_gpu": args.images, "n_h": args.humans, "n": args.boxes,
+           "cells_per_step_per_gpu": args.images * args.humans * args.boxes,
+           "pairs_per_step_per_gpu": args.images * args.humans * (args.boxes - 1),
+           "boundary": "InteractionHead.forward_from_pooled (head.py:389-427; RoIAlign/NMS stay stock torchvision)",
+           "parallelism": "dp%d (images sharded, no data-path collective)" % args.gpus}
+    if extra:
+        cfg.update(extra)
+    return cfg
+
+
+# ------------------------------------------------------------------------------------------------
+# CPU reference arm / cpu_baseline  (the only place outside tests/ and smoke() that executes oracle/)
+# ------------------------------------------------------------------------------------------------
+def cpu_head_throughput(args, steps, warmup):
+    """Times the reference head's CPU restatement (reference-faithful per-row entity loop) on the
+    host cores; one step = ONE image of the workload (bounded sample).  Returns (pairs/s, cores, s/step)."""
+    import torch
+    from oracle import head_oracle as O
+    from skghoi_b200 import synthetic
+    from skghoi_b200.head import build_interaction_head
+    cores = len(os.sched_getaffinity(0))
+    torch.set_num_threads(cores)
+    otv = synthetic.hico_object_to_verb()
+    ih = build_interaction_head(otv, seed=42)
+    P = {k: v.detach().clone() for k, v in ih.state_dict().items()}
+    tables = synthetic.make_transh_tables(42)
+    batch = synthetic.make_batch([(args.humans, args.boxes)], seed=42)
+    pairs = args.humans * (args.boxes - 1)
+
+    def step():
+        with torch.no_grad():
+            O.interaction_head_forward(P, tables, batch["features"]["3"], batch["image_shapes"],
+                                       batch["box_features"], batch["box_coords"], batch["box_labels"],
+                                       batch["box_scores"], otv, row_pick="loop")
+    for _ in range(warmup):
+        step()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        step()
+    dt = time.perf_counter() - t0
+    return pairs * steps / dt, cores, dt / steps
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    steps = max(1, min(args.steps, 40)); warmup = max(1, min(args.warmup, 2))
+    v, cores, sps = cpu_head_throughput(args, steps, warmup)
+    sample = "1 image (%d humans x %d boxes = %d pairs) per step, %d timed steps, fp32 torch CPU, %d threads" % (
+        args.humans, args.boxes, args.humans * (args.boxes - 1), steps, cores)
+    line = {"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": steps,
+            "warmup": warmup, "ms_per_step": sps * 1e3, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": workload_config(args, {"sample": sample}),
+            "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+            "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line))
+
+
+# ------------------------------------------------------------------------------------------------
+# clocks
+# ------------------------------------------------------------------------------------------------
+class ClockSampler:
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index = index; self.proc = None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+        except OSError:
+            self.proc = None
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            out, _ = self.proc.communicate(timeout=5)
+        except subprocess.TimeoutExpired:
+            self.proc.kill(); out, _ = self.proc.communicate()
+        sm, mx, pw, reasons = [], [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in out.strip().splitlines():
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 7:
+                continue
+            try:
+                sm.append(float(f[0])); mx.append(float(f[1])); pw.append(float(f[2]))
+            except ValueError:
+                continue
+            for nm, v in zip(names, f[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no samples"]}
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": max(mx), "power_w_max": max(pw), "samples": len(sm),
+                "reasons": sorted(reasons)}
+
+
+# ------------------------------------------------------------------------------------------------
+# B200 arm
+# ------------------------------------------------------------------------------------------------
+def run_b200(args):
+    import torch
+    import torch.distributed as dist
+    from skghoi_b200 import _lib, engine, synthetic
+    from skghoi_b200.head import build_interaction_head
+
+    rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the product path has no CPU fallback")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    lib = _lib.lib()
+    peaks = {}
+    pk_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.isfile(pk_path):
+        peaks = json.load(open(pk_path))
+    hbm_peak = float(peaks.get("hbm_gbs", 6650.0)); tf_peak = float(peaks.get("bf16_tflops", 1590.0))
+    peak_src = "measured (MEASURED_PEAKS.json)" if peaks else "fallback (B200_PROFILING.md)"
+
+    otv = synthetic.hico_object_to_verb()
+    ih = build_interaction_head(otv, seed=42)
+    ih.box_pair_head.transh_head.set_tables(*synthetic.make_transh_tables(42))
+    ih = ih.to(dev).eval()
+    ih.box_pair_head.transh_head.transh.to(dev)
+    shapes = [(args.humans, args.boxes)] * args.images
+    batch = synthetic.make_batch(shapes, seed=42 + rank)
+    pairs_step = args.images * args.humans * (args.boxes - 1)
+    # host (pinned) and device copies of the step's inputs
+    host = dict(f3=batch["features"]["3"].pin_memory(), bf=batch["box_features"].pin_memory(),
+                boxes=[b.pin_memory() for b in batch["box_coords"]], labels=[l.pin_memory() for l in batch["box_labels"]],
+                scores=[s.pin_memory() for s in batch["box_scores"]])
+    d = dict(f3=host["f3"].to(dev), bf=host["bf"].to(dev), boxes=[b.to(dev) for b in host["boxes"]],
+             labels=[l.to(dev) for l in host["labels"]], scores=[s.to(dev) for s in host["scores"]])
+    meta = engine._host_meta(batch["box_labels"], batch["box_scores"], 49)   # host-side copy of the tiny label/score lists
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)          # > 126 MB L2
+
+    def step_resident():
+        with torch.no_grad():
+            return engine.interaction_head_from_pooled(ih, {"3": d["f3"]}, batch["image_shapes"], d["bf"], d["boxes"],
+                                                       d["labels"], d["scores"], meta=meta)
+
+    h2d_bytes = (host["f3"].numel() + host["bf"].numel()) * 4 + sum(b.numel() * 4 for b in host["boxes"]) + \
+        sum(l.numel() * 8 for l in host["labels"]) + sum(s.numel() * 4 for s in host["scores"])
+    d2h_holder = {}
+
+    def step_e2e():
+        with torch.no_grad():
+            f3 = host["f3"].to(dev, non_blocking=True); bf = host["bf"].to(dev, non_blocking=True)
+            boxes = [b.to(dev, non_blocking=True) for b in host["boxes"]]
+            labels = [l.to(dev, non_blocking=True) for l in host["labels"]]
+            scores = [s.to(dev, non_blocking=True) for s in host["scores"]]
+            res = ih.forward_from_pooled({"3": f3}, batch["image_shapes"], bf, boxes, labels, scores)
+            out, nbytes = [], 0
+            for r in res:
+                for k in ("index", "prediction", "scores", "weights", "object"):
+                    t = r[k].to("cpu", non_blocking=True); out.append(t); nbytes += t.numel() * t.element_size()
+            torch.cuda.synchronize(dev)
+            d2h_holder["bytes"] = nbytes
+            return out
+
+    def barrier():
+        torch.cuda.synchronize(dev)
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize(dev)
+
+    # ---- warm-up
+    for _ in range(max(args.warmup, 3)):
+        step_resident(); flush.zero_()
+    torch.cuda.synchronize(dev)
+    # ---- timed: device-resident inputs
+    sampler = ClockSampler(local)
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    l0 = lib.skg_launch_count()
+    barrier()
+    sampler.start()
+    for s, e in ev:
+        s.record(); step_resident(); e.record()
+        flush.zero_()
+    barrier()
+    launches = lib.skg_launch_count() - l0
+    t_ms = sum(s.elapsed_time(e) for s, e in ev)
+    # ---- timed: end to end from pinned host buffers
+    for _ in range(3):
+        step_e2e()
+    barrier()
+    e2e_s = 0.0
+    for _ in range(args.steps):
+        flush.zero_(); torch.cuda.synchronize(dev)
+        t0 = time.perf_counter(); step_e2e(); e2e_s += time.perf_counter() - t0
+    barrier()
+    clocks = sampler.stop()
+    tt = torch.tensor([t_ms, e2e_s * 1e3], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+    t_ms, e2e_ms = float(tt[0]), float(tt[1])
+    value = pairs_step * world * args.steps / (t_ms * 1e-3)
+    e2e_v = pairs_step * world * args.steps / (e2e_ms * 1e-3)
+
+    roof = None; extra_roofs = {}
+    if rank == 0 and not args.no_rooflines:
+        roof, extra_roofs = measure_rooflines(torch, _lib, engine, ih, dev, flush, hbm_peak, tf_peak, peak_src)
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        v, cores, sps = cpu_head_throughput(args, steps=20, warmup=1)
+        cpu = {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
+               "sample": "oracle/head_oracle.py (op-for-op fp32 restatement of the reference head), 20 steps of 1 image "
+                         "(%d pairs) each, %.3f s/step" % (args.humans * (args.boxes - 1), sps)}
+    if rank == 0:
+        line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+                "warmup": max(args.warmup, 3), "ms_per_step": t_ms / args.steps, "higher_is_better": True,
+                "scaling": "weak", "vs_baseline": None, "dtype": "bf16 (fp32 accumulate; fp32 spatial/TransH)",
+                "data": "synthetic", "impl": "b200",
+                "config": workload_config(args, {"l2": "256 MiB flush buffer written between timed steps",
+                                                 "timing": "CUDA events per step on the launch stream, summed, max over ranks"}),
+                "e2e": {"value": e2e_v, "unit": UNIT, "h2d_bytes_per_step": h2d_bytes,
+                        "d2h_bytes_per_step": d2h_holder.get("bytes", 0), "ms_per_step": e2e_ms / args.steps,
+                        "timing": "host wall clock around H2D + forward + D2H + sync, per step"},
+                "gpu_launches": int(launches), "clocks": clocks, "roofline": roof, "cpu_baseline": cpu}
+        line.update(extra_roofs)
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def _time_kernel(torch, fn, flush, reps=20):
+    fn(); torch.cuda.synchronize()
+    tot = 0.0
+    for _ in range(reps):
+        flush.zero_()
+        s = torch.cuda.Event(enable_timing=True); e = torch.cuda.Event(enable_timing=True)
+        s.record(); fn(); e.record(); torch.cuda.synchronize()
+        tot += s.elapsed_time(e)
+    return tot / reps * 1e-3
+
+
+def measure_rooflines(torch, _lib, engine, ih, dev, flush, hbm_peak, tf_peak, peak_src):
+    """Times the dominant kernels alone (CUDA events on the launch stream, L2 flushed before each launch)."""
+    run = ih.__dict__["_skg_last_run"]
+    g = engine.dominant_gemm_closure(ih, run)
+    sec = _time_kernel(torch, g["launch"], flush)
+    roof = {"kernel": "gemm_bf16_kernel<256> (fused fc_2 of attention_head|obj_to_sub|sub_to_obj|attention_head_g, "
+                      "M=%d N=%d K=%d, Hadamard+ReLU epilogue)" % (g["M"], g["N"], g["K"]),
+            "bound": "tensor", "achieved": g["flops"] / sec / 1e12, "peak": tf_peak, "unit": "TFLOP/s",
+            "frac": g["flops"] / sec / 1e12 / tf_peak, "traffic": None, "peak_source": peak_src + ", burst bf16",
+            "us_per_launch": sec * 1e6, "flops_per_launch": g["flops"]}
+    extra = {}
+    # spatial encoding at >= 2^20 cells: enc + x_keep/y_keep only
+    from skghoi_b200 import synthetic
+    B = 2048
+    gen = torch.Generator().manual_seed(1)
+    bx, _, _ = synthetic.make_detections([(16, 32)], [(800, 1216)], gen)
+    boxes = bx[0].repeat(B, 1).to(dev)
+    seg = engine.Segments([16] * B, [32] * B, [(800, 1216)] * B, dev)
+    C, Pn = seg.total_cells, seg.total_pairs
+    enc = torch.empty(C, 46, dtype=torch.float32, device=dev)
+    xk = torch.empty(Pn, dtype=torch.int64, device=dev); yk = torch.empty(Pn, dtype=torch.int64, device=dev)
+    nanf = torch.zeros(B, dtype=torch.int32, device=dev)
+    p = _lib.ptr
+
+    def sp_launch():
+        _lib.call("skg_pairs_spatial_encode", p(boxes), p(seg.d_box_off), p(seg.d_n_h), p(seg.d_cell_off), p(seg.d_pair_off),
+                  p(seg.d_hum_off), p(seg.d_hw), B, C, 23, 1e-10, 0, p(enc), None, None, p(xk), p(yk), None, None, None,
+                  None, None, p(nanf), _lib.stream_ptr(dev))
+    sec = _time_kernel(torch, sp_launch, flush)
+    nbytes = 184 * C + 16 * Pn + 16 * seg.total_boxes
+    extra["spatial_roofline"] = {"kernel": "pairs_spatial_kernel<23> (%d cells, enc + x_keep/y_keep)" % C, "bound": "hbm",
+                                 "achieved": nbytes / sec / 1e9, "peak": hbm_peak, "unit": "GB/s",
+                                 "frac": nbytes / sec / 1e9 / hbm_peak, "traffic": None, "bytes_per_launch": nbytes,
+                                 "us_per_launch": sec * 1e6, "peak_source": peak_src}
+    del enc, xk, yk
+    # TransH: score-only grid mode (4 B / triple) and API-faithful mode (804 B written / triple)
+    tr = ih.box_pair_head.transh_head.transh
+    e, r, w = tr.ent_embeddings.weight.detach(), tr.rel_embeddings.weight.detach(), tr.norm_vector.weight.detach()
+    cells = 1 << 20
+    tails = (torch.arange(cells, device=dev) % 32).to(torch.int64)
+    score = torch.empty(cells * 117, dtype=torch.float32, device=dev)
+
+    def th_score():
+        _lib.call("skg_transh_forward_grid", p(e), p(r), p(w), 80, 117, 50, 49, p(tails), cells, 2, 1, None, None, None, None,
+                  p(score), _lib.stream_ptr(dev))
+    sec = _time_kernel(torch, th_score, flush, reps=10)
+    nb = 4 * cells * 117 + 8 * cells
+    extra["transh_score_roofline"] = {"kernel": "transh_forward_kernel (grid mode, score only, %d triples)" % (cells * 117),
+                                      "bound": "hbm", "achieved": nb / sec / 1e9, "peak": hbm_peak, "unit": "GB/s",
+                                      "frac": nb / sec / 1e9 / hbm_peak, "traffic": None, "bytes_per_launch": nb,
+                                      "us_per_launch": sec * 1e6, "triples_per_s": cells * 117 / sec}
+    del score
+    cells2 = 8192
+    T = cells2 * 117
+    outs = [torch.empty(T, 50, dtype=torch.float32, device=dev) for _ in range(4)]
+    score = torch.empty(T, dtype=torch.float32, device=dev)
+
+    def th_full():
+        _lib.call("skg_transh_forward_grid", p(e), p(r), p(w), 80, 117, 50, 49, p(tails), cells2, 2, 1, p(outs[0]), p(outs[1]),
+                  p(outs[2]), p(outs[3]), p(score), _lib.stream_ptr(dev))
+    sec = _time_kernel(torch, th_full, flush, reps=10)
+    nb = 804 * T + 8 * cells2
+    extra["transh_rows_roofline"] = {"kernel": "transh_forward_kernel (grid mode, API-faithful h_/r/w/t_ rows + score, %d triples)" % T,
+                                     "bound": "hbm", "achieved": nb / sec / 1e9, "peak": hbm_peak, "unit": "GB/s",
+                                     "frac": nb / sec / 1e9 / hbm_peak, "traffic": None, "bytes_per_launch": nb,
+                                     "us_per_launch": sec * 1e6, "triples_per_s": T / sec}
+    return roof, extra
+
+
+if __name__ == "__main__":
+    a = parse_args()
+    if a.impl == "reference":
+        run_reference(a)
+    else:
+        run_b200(a)

@@ -32,6 +32,8 @@ typedef struct CUstream_st* cudaStream_t;
 const char* skg_last_error(void);
 int skg_abi_version(void);
 int skg_num_sms(void);
+/* number of kernel launches this library has enqueued in the process so far (bench.py "gpu_launches") */
+long long skg_launch_count(void);
 
 /* ---- pair enumeration + spatial encoding --------------------------------------------------
  * Replaces, for a whole batch in one launch: the meshgrid / nonzero(x != y) pair construction of

@@ -19,6 +19,7 @@ _SIGNATURES = {
     "skg_last_error": (c_char_p, []),
     "skg_abi_version": (I, []),
     "skg_num_sms": (I, []),
+    "skg_launch_count": (ctypes.c_longlong, []),
     "skg_pairs_spatial_encode": (I, [P, P, P, P, P, P, P, I, L, I, F, I, P, P, P, P, P, P, P, P, P, P, P, P]),
     "skg_spatial_encode_rows": (I, [P, P, P, P, I, L, I, F, P, P, P]),
     "skg_transh_forward": (I, [P, P, P, I, I, I, P, P, P, L, I, I, P, P, P, P, P, P]),

@@ -3,10 +3,12 @@
 #include "skghoi_b200.h"
 #include <stdarg.h>
 #include <string.h>
+#include <atomic>
 
 namespace skg {
 
 static thread_local char g_err[512] = "";
+static std::atomic<long long> g_launches{0};   // kernels enqueued through this library (skg_launch_count)
 
 void set_error(const char* fmt, ...) {
   va_list ap;
@@ -16,6 +18,7 @@ void set_error(const char* fmt, ...) {
 }
 
 int check_launch(const char* what) {
+  g_launches.fetch_add(1, std::memory_order_relaxed);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) {
     set_error("%s: launch failed: %s", what, cudaGetErrorString(e));
@@ -42,3 +45,4 @@ int num_sms() {
 extern "C" const char* skg_last_error(void) { return skg::g_err; }
 extern "C" int skg_abi_version(void) { return SKG_ABI_VERSION; }
 extern "C" int skg_num_sms(void) { return skg::num_sms(); }
+extern "C" long long skg_launch_count(void) { return skg::g_launches.load(std::memory_order_relaxed); }

@@ -408,8 +408,27 @@ def head_forward(ih, features3: Tensor, image_shapes, box_features: Tensor, boxe
         else:
             _lib.gemm_bf16(feat, pk.Wpred, [_g(bias=pk.bpred, out_f32=logits)], N=pk.n_logit)
     out.update(logits=logits, feat=feat, adjacency=adjacency, node16=node, hN32=hN32, oN32=oN32, enc32=enc32,
-               enc16=enc16, sp=sp, NH=NH, NB=NB)
+               enc16=enc16, sp=sp, NH=NH, NB=NB, hproj=hproj, oproj=oproj, Gt=Gt,
+               fc2_out=(H_att, S_raw, H_os, H_so, H_g))
     return out
+
+
+def dominant_gemm_closure(ih, run: dict) -> dict:
+    """Re-launchable closure of the step's dominant kernel -- the fused fc_2 GEMM of the four MBFs
+    (M = cells, N = 4R, K = 1024) on the operands of the last forward -- for bench.py's roofline leg."""
+    pk = packed_head(ih)
+    R = pk.R
+    sp, hproj, oproj, Gt = run["sp"], run["hproj"], run["oproj"], run["Gt"]
+    H_att, S_raw, H_os, H_so, H_g = run["fc2_out"]
+    hrow, orow, img = run["cell_hrow"], run["cell_orow"], run["cell_img"]
+    groups = [
+        _g(n_begin=0, relu=True, bias=pk.b2cat, mul_p=hproj[:, :R], row_p=hrow, mul_q=oproj[:, :R], row_q=orow,
+           out_bf16=H_att, raw_bf16=S_raw),
+        _g(n_begin=R, relu=True, bias=pk.b2cat, mul_p=oproj[:, R:], row_p=orow, out_bf16=H_os),
+        _g(n_begin=2 * R, relu=True, bias=pk.b2cat, mul_p=hproj[:, R:], row_p=hrow, out_bf16=H_so),
+        _g(n_begin=3 * R, relu=True, bias=pk.b2cat, mul_p=Gt, row_p=img, out_bf16=H_g)]
+    M, N, K = sp.shape[0], pk.W2cat.shape[0], pk.W2cat.shape[1]
+    return dict(launch=lambda: _lib.gemm_bf16(sp, pk.W2cat, groups), M=M, N=N, K=K, flops=2.0 * M * N * K)
 
 
 # =============================================================================================
