@@ -113,7 +113,8 @@ int skg_focal_loss(const float* x, const float* y, int64_t n, float alpha, float
  *     v *= mul_p[row_p[r]][lc] (+ mul_q[row_q[r]][lc])    (optional Hadamard with gathered fp32 tables)
  *     v = max(v, 0)                                       (flags & SKG_EPI_RELU)
  *     v += residual[row_r[r]][lc]                         (optional)
- *     dot_out[out_row[r]][tile] = sum_lc v * dot_w[lc]    (optional fused row-dot, one partial per N tile)
+ *     dot_out[out_row[r]][4*tile + h] = sum_lc v * dot_w[lc]  (optional fused row-dot; four partials per N tile,
+ *                                                          one per column quarter h, summed by the consumer)
  *     out_bf16 / out_f32 [out_row[r]][lc] = v             (optional; out_row NULL = r, < 0 = skip row)
  * row_* NULL means the identity map.  bias, dot_w and the gathered tables are read in 32-column
  * chunks, so they (and out_bf16 / raw_bf16 rows) must be padded to a multiple of 32 columns;
@@ -205,6 +206,17 @@ int skg_postprocess(const float* logits, int ld_logits, int num_cls, const skg_p
                     float prior_power, const float* gt_labels, int64_t total_entries, int64_t* out_index,
                     int64_t* out_pred, float* out_scores, float* out_prior, float* out_weights,
                     float* out_labels, float* out_unary, int64_t* out_object, cudaStream_t stream);
+
+/* Output offsets of skg_postprocess built on the device (no host round trip): box_cnt / box_prefix [boxes],
+ * hum_base [humans] (batch-global), img_entries [B] and img_base [B+1] (entries per image and their prefix) --
+ * the closed form of the per-image nonzero(prior[0]) ordering of head.py:315.  verb_off as in skg_post_tables. */
+int skg_post_offsets(const int32_t* verb_off, const int64_t* labels, const float* scores, const int32_t* box_off,
+                     const int32_t* hum_off, int num_images, int32_t* box_cnt, int32_t* box_prefix,
+                     int64_t* hum_base, int64_t* img_entries, int64_t* img_base, cudaStream_t stream);
+
+/* boxes_h / boxes_o [P, 4] of every valid pair (head.py:975-976: coords[x_keep], coords[y_keep]). */
+int skg_gather_pair_boxes(const float* boxes, const skg_post_tables* tables, int64_t pairs, float* boxes_h,
+                          float* boxes_o, cudaStream_t stream);
 
 /* compute_prior_scores (head.py:721-767): dense prior [2, P, num_cls]. */
 int skg_prior_dense(const skg_post_tables* tables, int64_t pairs, int num_cls, float prior_power, float* prior,

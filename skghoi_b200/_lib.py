@@ -121,6 +121,8 @@ class PostTables(ctypes.Structure):
 
 _SIGNATURES["skg_postprocess"] = (I, [P, I, I, ctypes.POINTER(PostTables), L, F, P, L, P, P, P, P, P, P, P, P, P])
 _SIGNATURES["skg_prior_dense"] = (I, [ctypes.POINTER(PostTables), L, I, F, P, P])
+_SIGNATURES["skg_post_offsets"] = (I, [P, P, P, P, P, I, P, P, P, P, P, P])
+_SIGNATURES["skg_gather_pair_boxes"] = (I, [P, ctypes.POINTER(PostTables), L, P, P, P])
 _SIGNATURES["skg_associate_gt"] = (I, [P, ctypes.POINTER(PostTables), L, I, P, P, P, P, F, P, P])
 
 EPI_RELU = 1

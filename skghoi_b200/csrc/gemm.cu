@@ -8,7 +8,7 @@
 //   warp 0      : TMA producer  (cp.async.bulk.tensor 2D, 128B swizzle, mbarrier complete_tx)
 //   warp 1      : MMA issuer    (one elected lane issues tcgen05.mma M=128 x N=BN x K=16, fp32 accum in TMEM)
 //   warp 2      : TMEM allocator (2 accumulator buffers so the epilogue of tile i overlaps the MMAs of tile i+1)
-//   warps 4..7  : epilogue      (tcgen05.ld 32x32b -> registers -> fused math -> global)
+//   warps 4..11 : epilogue      (tcgen05.ld 32x32b -> registers -> smem transpose -> fused math -> coalesced global)
 // The epilogue is described per column group (skg_epilogue_group): bias, Hadamard product with
 // row-gathered fp32 tables (the MBF "fc_1(app) * fc_2(sp)" branch product, gathered through the
 // cell -> human / box row maps so the [pairs, 1024] appearance term is never materialised), ReLU,
@@ -23,7 +23,10 @@ namespace skg {
 constexpr int BM = 128;            // UMMA M (cta_group::1)
 constexpr int BK = 64;             // 64 bf16 = 128 B = one swizzle-128B atom row
 constexpr int UMMA_K = 16;
-constexpr int kGemmThreads = 256;  // 8 warps: 0 TMA, 1 MMA, 2 TMEM alloc, 3 idle, 4..7 epilogue
+constexpr int kEpiWarps = 16;      // 4 per TMEM lane quadrant
+constexpr int kGemmThreads = 32 * (4 + kEpiWarps);  // warps: 0 TMA, 1 MMA, 2 TMEM alloc, 3 idle, 4..19 epilogue
+// epilogue features (compile-time mask FEAT of gemm_bf16_kernel; bias / ReLU / out_row are always available)
+enum : uint32_t { F_P = 1, F_Q = 2, F_RAW = 4, F_RES = 8, F_DOT = 16, F_OB = 32, F_OF = 64, F_LO = 128, F_ALL = 255 };
 constexpr int kEpiWarp0 = 4;
 constexpr int kMaxGroups = 4;
 
@@ -94,6 +97,16 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
   asm volatile("tcgen05.wait::ld.sync.aligned;\n" ::: "memory");
 }
 
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&r)[16]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];\n"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+        "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+      : "r"(taddr));
+  asm volatile("tcgen05.wait::ld.sync.aligned;\n" ::: "memory");
+}
+
 // K-major, 128B-swizzled operand tile: rows of 64 bf16 (128 B), 8-row groups 1024 B apart.
 // Descriptor fields (see cute/arch/mma_sm100_desc.hpp): start>>4 [0,14), LBO>>4 [16,30) (=1, unused for
 // swizzled K-major), SBO>>4 [32,46) (=64), version=1 [46,48), layout_type=2 (SWIZZLE_128B) [61,64).
@@ -125,10 +138,11 @@ struct GemmSmem {
   static constexpr int kABytes = BM * BK * 2;
   static constexpr int kBBytes = BN * BK * 2;
   static constexpr int kStageBytes = kABytes + kBBytes;
-  static constexpr int kTotal = kStages * kStageBytes + 1024 /*align slack*/ + 256 /*barriers*/;
+  static constexpr int kStagingBytes = kEpiWarps * 2048;   // one swizzled 32 x 16 fp32 patch per epilogue warp
+  static constexpr int kTotal = kStages * kStageBytes + 1024 /*align slack*/ + 256 /*barriers*/ + kStagingBytes;
 };
 
-template <int BN>
+template <int BN, uint32_t FEAT>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, int M, int N, int K,
                  const __grid_constant__ EpiGroups epi) {
@@ -142,6 +156,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   uint64_t* tmem_full = bars + 2 * kStages;      // [2]        MMA -> epilogue
   uint64_t* tmem_empty = bars + 2 * kStages + 2; // [2]        epilogue -> MMA
   uint32_t* tmem_base_slot = reinterpret_cast<uint32_t*>(bars + 2 * kStages + 4);
+  float* staging = reinterpret_cast<float*>(smem + kStages * S::kStageBytes + 256);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int num_m = (M + BM - 1) / BM, num_n = (N + BN - 1) / BN;
@@ -154,7 +169,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   }
   if (warp == 1 && lane == 0) {
     for (int s = 0; s < kStages; ++s) { mbar_init(full_bar + s, 1); mbar_init(empty_bar + s, 1); }
-    for (int a = 0; a < 2; ++a) { mbar_init(tmem_full + a, 1); mbar_init(tmem_empty + a, 4); }
+    for (int a = 0; a < 2; ++a) { mbar_init(tmem_full + a, 1); mbar_init(tmem_empty + a, kEpiWarps); }
     asm volatile("fence.mbarrier_init.release.cluster;\n" ::: "memory");
   }
   if (warp == 2) {   // 2 x BN fp32 accumulator columns (power of two >= 32)
@@ -213,7 +228,19 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     }
   } else if (warp >= kEpiWarp0) {
     // ===================== epilogue =====================
+    // TMEM hands every thread one accumulator ROW (lane = row).  Touching global memory in that layout makes
+    // each warp-wide access hit 32 different 128-byte lines, which the L1 serialises; so every 32x16 block is
+    // transposed through a private, XOR-swizzled 2 KB shared-memory patch and processed with
+    // lane = (row % 8, 4 columns): a warp-wide float4 access then covers 8 rows x 64 contiguous bytes.
+    // 16 epilogue warps (4 per TMEM lane quadrant, a quarter of the tile's columns each) keep four warps per
+    // scheduler in flight; FEAT removes at compile time every epilogue feature the launch does not use.
+    const int ew = warp - kEpiWarp0;
     const int quad = warp & 3;                            // TMEM lane quadrant this warp may access
+    const int part = ew >> 2;                             // which quarter of the tile's columns this warp drains
+    float4* patch = reinterpret_cast<float4*>(staging) + ew * 128;   // 32 rows x 4 float4
+    const int sub = lane >> 2;                            // row inside an 8-row group
+    const int cq = (lane & 3) * 4;                        // first of this lane's 4 columns inside a 16-column block
+    constexpr int kBlocks = BN / 64;                      // 16-column blocks per warp
     int acc = 0; uint32_t acc_phase = 0;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
       const int m_blk = tile / num_n, n_blk = tile % num_n;
@@ -221,110 +248,133 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       int gi = 0;
       for (int q = 1; q < epi.num; ++q) if (n0 >= epi.g[q].n_begin) gi = q;
       const skg_epilogue_group& G = epi.g[gi];
-      const int row = m0 + quad * 32 + lane;
-      const bool row_ok = row < M;
-      const int flags = G.flags;
-      int rp = row, rq = row, rr = row, ro = row;
-      if (row_ok) {
-        if (G.row_p) rp = __ldg(G.row_p + row);
-        if (G.row_q) rq = __ldg(G.row_q + row);
-        if (G.row_r) rr = __ldg(G.row_r + row);
-        if (G.out_row) ro = __ldg(G.out_row + row);
+      // hoist the group descriptor out of the inner loops (it lives in the indexed constant bank)
+      const bool relu = (G.flags & SKG_EPI_RELU) != 0;
+      const int n_begin = G.n_begin;
+      const float* __restrict__ g_bias = G.bias;
+      const float* __restrict__ g_p = (FEAT & F_P) ? G.mul_p : nullptr;
+      const float* __restrict__ g_q = (FEAT & F_Q) ? G.mul_q : nullptr;
+      const float* __restrict__ g_res = (FEAT & F_RES) ? G.residual : nullptr;
+      const float* __restrict__ g_dw = (FEAT & F_DOT) ? G.dot_w : nullptr;
+      __nv_bfloat16* g_ob = (FEAT & F_OB) ? reinterpret_cast<__nv_bfloat16*>(G.out_bf16) : nullptr;
+      __nv_bfloat16* g_raw = (FEAT & F_RAW) ? reinterpret_cast<__nv_bfloat16*>(G.raw_bf16) : nullptr;
+      __nv_bfloat16* g_lo = (FEAT & F_LO) ? reinterpret_cast<__nv_bfloat16*>(G.lo_bf16) : nullptr;
+      float* g_of = (FEAT & F_OF) ? G.out_f32 : nullptr;
+      const int ld_p = G.ld_p, ld_q = G.ld_q, ld_r = G.ld_r, ld_ob = G.ld_ob, ld_raw = G.ld_raw, ld_lo = G.ld_lo, ld_of = G.ld_of;
+      // per-row maps: loaded by the lane that owns the row, then handed to the lanes that process it
+      int rp_i[4], rq_i[4], rr_i[4], ro_i[4];
+      {
+        const int row = m0 + quad * 32 + lane;
+        const bool row_ok = row < M;
+        int rp = row, rq = row, rr = row, ro = row;
+        if (row_ok) {
+          if ((FEAT & F_P) && G.row_p) rp = __ldg(G.row_p + row);
+          if ((FEAT & F_Q) && G.row_q) rq = __ldg(G.row_q + row);
+          if ((FEAT & F_RES) && G.row_r) rr = __ldg(G.row_r + row);
+          if (G.out_row) ro = __ldg(G.out_row + row);
+        } else {
+          rp = rq = rr = 0; ro = -1;
+        }
+#pragma unroll
+        for (int it = 0; it < 4; ++it) {
+          const int src = it * 8 + sub;
+          rp_i[it] = __shfl_sync(0xffffffffu, rp, src); rq_i[it] = __shfl_sync(0xffffffffu, rq, src);
+          rr_i[it] = __shfl_sync(0xffffffffu, rr, src); ro_i[it] = __shfl_sync(0xffffffffu, ro, src);
+        }
       }
-      const bool store_ok = row_ok && ro >= 0;
-      float dot = 0.f;
-      mbar_wait(tmem_full + acc, acc_phase);
-      tcgen05_fence_after();
+      float dot[4] = {0.f, 0.f, 0.f, 0.f};
+      bool waited = false;
       const uint32_t t_row = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(acc * BN);
 #pragma unroll 1
-      for (int c0 = 0; c0 < BN; c0 += 32) {
-        uint32_t raw[32];
-        tmem_ld32(t_row + c0, raw);
-        const int col = n0 + c0;                 // global column of raw[0]
-        if (col >= N) break;                     // warp-uniform
-        const int lc = col - G.n_begin;          // column inside the group (table / output column)
-        float v[32];
+      for (int blk = 0; blk < kBlocks; ++blk) {
+        const int c0 = part * (BN / 4) + blk * 16;
+        if (n0 + c0 >= N) break;                     // warp-uniform
+        const int col = n0 + c0 + cq;                // global column of this lane's 4 values
+        const int lc = col - n_begin;                // column inside the group (table / output column)
+        // gathered tables first: they do not depend on the accumulator, so their latency overlaps the TMEM load
+        const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
+        float4 b4 = z4, w4 = z4, tp[4], tq[4], tr[4];
+        if (g_bias) b4 = __ldg(reinterpret_cast<const float4*>(g_bias + col));
+        if ((FEAT & F_DOT) && g_dw) w4 = __ldg(reinterpret_cast<const float4*>(g_dw + lc));
+        if ((FEAT & F_P) && g_p) {
 #pragma unroll
-        for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(raw[j]);
-        if (G.bias) {
+          for (int it = 0; it < 4; ++it) tp[it] = __ldg(reinterpret_cast<const float4*>(g_p + (int64_t)rp_i[it] * ld_p + lc));
+        }
+        if ((FEAT & F_Q) && g_q) {
 #pragma unroll
-          for (int j = 0; j < 32; j += 4) {
-            const float4 b = __ldg(reinterpret_cast<const float4*>(G.bias + col + j));
-            v[j] += b.x; v[j + 1] += b.y; v[j + 2] += b.z; v[j + 3] += b.w;
+          for (int it = 0; it < 4; ++it) tq[it] = __ldg(reinterpret_cast<const float4*>(g_q + (int64_t)rq_i[it] * ld_q + lc));
+        }
+        if ((FEAT & F_RES) && g_res) {
+#pragma unroll
+          for (int it = 0; it < 4; ++it) tr[it] = __ldg(reinterpret_cast<const float4*>(g_res + (int64_t)rr_i[it] * ld_r + lc));
+        }
+        if (!waited) {                               // first block of the tile: wait for the accumulator
+          mbar_wait(tmem_full + acc, acc_phase);
+          tcgen05_fence_after();
+          waited = true;
+        }
+        uint32_t raw[16];
+        tmem_ld16(t_row + c0, raw);
+        __syncwarp();                                // the patch's previous readers are done
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+          patch[lane * 4 + (j ^ ((lane >> 1) & 3))] =
+              make_float4(__uint_as_float(raw[4 * j]), __uint_as_float(raw[4 * j + 1]), __uint_as_float(raw[4 * j + 2]),
+                          __uint_as_float(raw[4 * j + 3]));
+        __syncwarp();
+#pragma unroll
+        for (int it = 0; it < 4; ++it) {
+          const int ro = ro_i[it];
+          const bool store_ok = ro >= 0;             // also false for rows beyond M
+          const int r = it * 8 + sub;
+          float4 v = patch[r * 4 + ((lane & 3) ^ ((r >> 1) & 3))];
+          v.x += b4.x; v.y += b4.y; v.z += b4.z; v.w += b4.w;
+          if ((FEAT & F_RAW) && g_raw && store_ok)
+            *reinterpret_cast<uint2*>(g_raw + (int64_t)ro * ld_raw + lc) = make_uint2(pack_bf16(v.x, v.y), pack_bf16(v.z, v.w));
+          if ((FEAT & F_P) && g_p) {
+            float4 a = tp[it];
+            if ((FEAT & F_Q) && g_q) { a.x += tq[it].x; a.y += tq[it].y; a.z += tq[it].z; a.w += tq[it].w; }
+            v.x *= a.x; v.y *= a.y; v.z *= a.z; v.w *= a.w;
           }
-        }
-        if (store_ok && G.raw_bf16) {
-          uint4* dst = reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(G.raw_bf16) + (int64_t)ro * G.ld_raw + lc);
-#pragma unroll
-          for (int j = 0; j < 32; j += 8)
-            dst[j >> 3] = make_uint4(pack_bf16(v[j], v[j + 1]), pack_bf16(v[j + 2], v[j + 3]), pack_bf16(v[j + 4], v[j + 5]),
-                                     pack_bf16(v[j + 6], v[j + 7]));
-        }
-        if (row_ok && G.mul_p) {
-          const float4* p = reinterpret_cast<const float4*>(G.mul_p + (int64_t)rp * G.ld_p + lc);
-          if (G.mul_q) {
-            const float4* q = reinterpret_cast<const float4*>(G.mul_q + (int64_t)rq * G.ld_q + lc);
-#pragma unroll
-            for (int j = 0; j < 32; j += 4) {
-              const float4 a = __ldg(p + (j >> 2)), b = __ldg(q + (j >> 2));
-              v[j] *= (a.x + b.x); v[j + 1] *= (a.y + b.y); v[j + 2] *= (a.z + b.z); v[j + 3] *= (a.w + b.w);
+          if (relu) { v.x = fmaxf(v.x, 0.f); v.y = fmaxf(v.y, 0.f); v.z = fmaxf(v.z, 0.f); v.w = fmaxf(v.w, 0.f); }
+          if ((FEAT & F_RES) && g_res) { v.x += tr[it].x; v.y += tr[it].y; v.z += tr[it].z; v.w += tr[it].w; }
+          if (FEAT & F_DOT) dot[it] += v.x * w4.x + v.y * w4.y + v.z * w4.z + v.w * w4.w;
+          if (store_ok) {
+            if ((FEAT & F_OB) && g_ob)
+              *reinterpret_cast<uint2*>(g_ob + (int64_t)ro * ld_ob + lc) = make_uint2(pack_bf16(v.x, v.y), pack_bf16(v.z, v.w));
+            if ((FEAT & F_LO) && g_lo) {   // residual of the bf16 rounding: v ~= hi + lo to ~16 mantissa bits
+              const float lx = v.x - __bfloat162float(__float2bfloat16(v.x)), ly = v.y - __bfloat162float(__float2bfloat16(v.y));
+              const float lz = v.z - __bfloat162float(__float2bfloat16(v.z)), lw = v.w - __bfloat162float(__float2bfloat16(v.w));
+              *reinterpret_cast<uint2*>(g_lo + (int64_t)ro * ld_lo + lc) = make_uint2(pack_bf16(lx, ly), pack_bf16(lz, lw));
             }
-          } else {
-#pragma unroll
-            for (int j = 0; j < 32; j += 4) {
-              const float4 a = __ldg(p + (j >> 2));
-              v[j] *= a.x; v[j + 1] *= a.y; v[j + 2] *= a.z; v[j + 3] *= a.w;
+            if ((FEAT & F_OF) && g_of) {
+              float* dst = g_of + (int64_t)ro * ld_of + lc;
+              if (col + 4 <= N && (ld_of & 3) == 0) {
+                *reinterpret_cast<float4*>(dst) = v;
+              } else {
+                if (col < N) dst[0] = v.x;
+                if (col + 1 < N) dst[1] = v.y;
+                if (col + 2 < N) dst[2] = v.z;
+                if (col + 3 < N) dst[3] = v.w;
+              }
             }
-          }
-        }
-        if (flags & SKG_EPI_RELU) {
-#pragma unroll
-          for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j], 0.f);
-        }
-        if (row_ok && G.residual) {
-          const float4* r4 = reinterpret_cast<const float4*>(G.residual + (int64_t)rr * G.ld_r + lc);
-#pragma unroll
-          for (int j = 0; j < 32; j += 4) {
-            const float4 a = __ldg(r4 + (j >> 2));
-            v[j] += a.x; v[j + 1] += a.y; v[j + 2] += a.z; v[j + 3] += a.w;
-          }
-        }
-        if (G.dot_w) {
-#pragma unroll
-          for (int j = 0; j < 32; j += 4) {
-            const float4 a = __ldg(reinterpret_cast<const float4*>(G.dot_w + lc + j));
-            dot += v[j] * a.x + v[j + 1] * a.y + v[j + 2] * a.z + v[j + 3] * a.w;
-          }
-        }
-        if (store_ok && G.out_bf16) {
-          uint4* dst = reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(G.out_bf16) + (int64_t)ro * G.ld_ob + lc);
-#pragma unroll
-          for (int j = 0; j < 32; j += 8)
-            dst[j >> 3] = make_uint4(pack_bf16(v[j], v[j + 1]), pack_bf16(v[j + 2], v[j + 3]), pack_bf16(v[j + 4], v[j + 5]),
-                                     pack_bf16(v[j + 6], v[j + 7]));
-        }
-        if (store_ok && G.lo_bf16) {   // residual of the bf16 rounding: v ~= hi + lo to ~16 mantissa bits
-          uint4* dst = reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(G.lo_bf16) + (int64_t)ro * G.ld_lo + lc);
-#pragma unroll
-          for (int j = 0; j < 32; j += 8) {
-            float l[8];
-#pragma unroll
-            for (int t = 0; t < 8; ++t) l[t] = v[j + t] - __bfloat162float(__float2bfloat16(v[j + t]));
-            dst[j >> 3] = make_uint4(pack_bf16(l[0], l[1]), pack_bf16(l[2], l[3]), pack_bf16(l[4], l[5]), pack_bf16(l[6], l[7]));
-          }
-        }
-        if (store_ok && G.out_f32) {
-          float* dst = G.out_f32 + (int64_t)ro * G.ld_of + lc;
-          if (col + 32 <= N && (G.ld_of & 3) == 0) {
-#pragma unroll
-            for (int j = 0; j < 32; j += 4) *reinterpret_cast<float4*>(dst + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
-          } else {
-#pragma unroll
-            for (int j = 0; j < 32; ++j) if (col + j < N) dst[j] = v[j];
           }
         }
       }
-      if (G.dot_out && store_ok) G.dot_out[(int64_t)ro * G.ld_dot + (n0 - G.n_begin) / BN] = dot;
+      if (!waited) {                                 // this warp's columns lie beyond N: still consume the phase
+        mbar_wait(tmem_full + acc, acc_phase);
+        tcgen05_fence_after();
+      }
+      if ((FEAT & F_DOT) && G.dot_out) {   // four partials per N tile (one per column quarter), summed by the consumer
+#pragma unroll
+        for (int it = 0; it < 4; ++it) {
+          float d = dot[it];
+          d += __shfl_xor_sync(0xffffffffu, d, 1);
+          d += __shfl_xor_sync(0xffffffffu, d, 2);
+          if ((lane & 3) == 0 && ro_i[it] >= 0)
+            G.dot_out[(int64_t)ro_i[it] * G.ld_dot + ((n0 - n_begin) / BN) * 4 + part] = d;
+        }
+      }
       // accumulator drained: hand the TMEM buffer back to the MMA warp
       tcgen05_fence_before();
       __syncwarp();
@@ -376,11 +426,11 @@ static int make_tmap(CUtensorMap* map, const void* ptr, int64_t rows, int64_t co
   return SKG_OK;
 }
 
-template <int BN>
+template <int BN, uint32_t FEAT>
 static int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, int M, int N, int K, const EpiGroups& epi,
                        int max_ctas, cudaStream_t stream) {
   using S = GemmSmem<BN>;
-  auto kern = gemm_bf16_kernel<BN>;
+  auto kern = gemm_bf16_kernel<BN, FEAT>;
   static bool attr_set = false;
   if (!attr_set) {
     SKG_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, S::kTotal));
@@ -428,6 +478,27 @@ extern "C" int skg_gemm_bf16(const void* A, int64_t lda, const void* B, int64_t 
   if (rc) return rc;
   rc = make_tmap(&tmB, B, N, K, ldb, block_n);
   if (rc) return rc;
-  if (block_n == 256) return launch_gemm<256>(tmA, tmB, M, N, K, epi, 0, stream);
-  return launch_gemm<128>(tmA, tmB, M, N, K, epi, 0, stream);
+  // pick the leanest compiled epilogue whose feature set covers what the groups ask for
+  uint32_t need = 0;
+  for (int i = 0; i < num_groups; ++i) {
+    const skg_epilogue_group& g = groups[i];
+    need |= (g.mul_p ? F_P : 0) | (g.mul_q ? F_Q : 0) | (g.raw_bf16 ? F_RAW : 0) | (g.residual ? F_RES : 0) |
+            ((g.dot_w || g.dot_out) ? F_DOT : 0) | (g.out_bf16 ? F_OB : 0) | (g.out_f32 ? F_OF : 0) | (g.lo_bf16 ? F_LO : 0);
+  }
+#define SKG_GEMM_CASE(F)                                                                   \
+  if ((need & ~(uint32_t)(F)) == 0) {                                                      \
+    if (block_n == 256) return launch_gemm<256, (F)>(tmA, tmB, M, N, K, epi, 0, stream);   \
+    return launch_gemm<128, (F)>(tmA, tmB, M, N, K, epi, 0, stream);                       \
+  }
+  SKG_GEMM_CASE(F_OB)                          // bias (+ReLU) -> bf16: spatial_head, box_head
+  SKG_GEMM_CASE(F_OF)                          // -> fp32: per-node projections
+  SKG_GEMM_CASE(F_OB | F_OF)                   // fc_head / fc_tail
+  SKG_GEMM_CASE(F_P | F_Q | F_RAW | F_OB)      // fused fc_2 of the MBFs (Hadamard with gathered tables)
+  SKG_GEMM_CASE(F_DOT)                         // attention weights -> adjacency row-dot
+  SKG_GEMM_CASE(F_RES | F_OF)                  // message fc_3 + residual, split-bf16 predictor second pass
+  SKG_GEMM_CASE(F_OB | F_LO)                   // final pair features with rounding residual
+  SKG_GEMM_CASE(F_ALL)
+#undef SKG_GEMM_CASE
+  set_error("no epilogue variant");
+  return SKG_ERR_UNSUPPORTED;
 }

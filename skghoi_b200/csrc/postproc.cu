@@ -121,6 +121,78 @@ __global__ void associate_gt_kernel(const float4* __restrict__ boxes, PostTables
   }
 }
 
+
+// Output offsets of the post-processing, built on the device so the whole batch needs no host round trip:
+//   box_cnt[k]    = number of valid verbs of box k's class
+//   box_prefix[k] = exclusive prefix of box_cnt inside the image
+//   row_tot[i]    = (score_i > 0) ? sum_j cnt_j - cnt_i : 0      entries emitted by human row i (head.py:315 nonzero)
+//   img_entries[b] = sum_i row_tot[i]
+// One CTA per image; the boxes of one image are scanned by warp 0 in chunks of 32.
+__global__ void post_counts_kernel(const int32_t* __restrict__ verb_off, const int64_t* __restrict__ labels,
+                                   const float* __restrict__ scores, const int32_t* __restrict__ box_off,
+                                   const int32_t* __restrict__ hum_off, int32_t* __restrict__ box_cnt,
+                                   int32_t* __restrict__ box_prefix, int64_t* __restrict__ hum_base,
+                                   int64_t* __restrict__ img_entries) {
+  if (threadIdx.x >= 32) return;
+  const int b = blockIdx.x, lane = threadIdx.x;
+  const int lo = __ldg(box_off + b), n = __ldg(box_off + b + 1) - lo;
+  const int h0 = __ldg(hum_off + b), nh = __ldg(hum_off + b + 1) - h0;
+  int run = 0;
+  for (int k0 = 0; k0 < n; k0 += 32) {
+    const int k = k0 + lane;
+    int c = 0;
+    if (k < n) { const int64_t l = __ldg(labels + lo + k); c = __ldg(verb_off + l + 1) - __ldg(verb_off + l); }
+    int inc = c;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { const int t = __shfl_up_sync(0xffffffffu, inc, o); if (lane >= o) inc += t; }
+    if (k < n) { box_cnt[lo + k] = c; box_prefix[lo + k] = run + inc - c; }
+    run += __shfl_sync(0xffffffffu, inc, 31);
+  }
+  __syncwarp();
+  const int S = run;
+  long long rrun = 0;
+  for (int i0 = 0; i0 < nh; i0 += 32) {
+    const int i = i0 + lane;
+    long long t = 0;
+    if (i < nh && __ldg(scores + lo + i) > 0.f) t = S - box_cnt[lo + i];
+    long long inc = t;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { const long long u = __shfl_up_sync(0xffffffffu, inc, o); if (lane >= o) inc += u; }
+    if (i < nh) hum_base[h0 + i] = rrun + inc - t;       // image-local for now; post_bases_kernel adds the image base
+    rrun += __shfl_sync(0xffffffffu, inc, 31);
+  }
+  if (lane == 0) img_entries[b] = rrun;
+}
+
+__global__ void post_bases_kernel(const int32_t* __restrict__ hum_off, int B, const int64_t* __restrict__ img_entries,
+                                  int64_t* __restrict__ img_base, int64_t* __restrict__ hum_base) {
+  __shared__ long long carry;
+  if (threadIdx.x == 0) {
+    long long run = 0;
+    for (int b = 0; b < B; ++b) { img_base[b] = run; run += img_entries[b]; }
+    img_base[B] = run;
+    carry = run;
+  }
+  __syncthreads();
+  const int total_h = __ldg(hum_off + B);
+  for (int h = threadIdx.x; h < total_h; h += blockDim.x) {
+    int lo = 0, hi = B;
+    while (hi - lo > 1) { const int mid = (lo + hi) >> 1; if (__ldg(hum_off + mid) <= h) lo = mid; else hi = mid; }
+    hum_base[h] += img_base[lo];
+  }
+}
+
+// boxes_h / boxes_o of every valid pair (head.py:975-976: coords[x_keep], coords[y_keep]).
+__global__ void gather_pair_boxes_kernel(const float4* __restrict__ boxes, PostTables t, int64_t pairs,
+                                         float4* __restrict__ boxes_h, float4* __restrict__ boxes_o) {
+  const int64_t p = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (p >= pairs) return;
+  const int cell = __ldg(t.pair2cell + p);
+  const int hr = __ldg(t.cell_hrow + cell), orow = __ldg(t.cell_orow + cell), b = __ldg(t.cell_img + cell);
+  boxes_h[p] = __ldg(boxes + __ldg(t.box_off + b) + (hr - __ldg(t.hum_off + b)));
+  boxes_o[p] = __ldg(boxes + orow);
+}
+
 }  // namespace skg
 
 using namespace skg;
@@ -179,4 +251,30 @@ extern "C" int skg_associate_gt(const float* boxes, const skg_post_tables* table
                                                                       (const float4*)gt_boxes_h, (const float4*)gt_boxes_o,
                                                                       gt_verb, fg_iou_thresh, labels);
   return check_launch("associate_gt_kernel");
+}
+
+extern "C" int skg_post_offsets(const int32_t* verb_off, const int64_t* labels, const float* scores, const int32_t* box_off,
+                                const int32_t* hum_off, int num_images, int32_t* box_cnt, int32_t* box_prefix,
+                                int64_t* hum_base, int64_t* img_entries, int64_t* img_base, cudaStream_t stream) {
+  if (num_images == 0) return SKG_OK;
+  SKG_REQUIRE(verb_off && labels && scores && box_off && hum_off && box_cnt && box_prefix && hum_base && img_entries && img_base,
+              "null pointer argument");
+  post_counts_kernel<<<num_images, 32, 0, stream>>>(verb_off, labels, scores, box_off, hum_off, box_cnt, box_prefix, hum_base,
+                                                    img_entries);
+  int rc = check_launch("post_counts_kernel");
+  if (rc) return rc;
+  post_bases_kernel<<<1, 256, 0, stream>>>(hum_off, num_images, img_entries, img_base, hum_base);
+  return check_launch("post_bases_kernel");
+}
+
+extern "C" int skg_gather_pair_boxes(const float* boxes, const skg_post_tables* tables, int64_t pairs, float* boxes_h,
+                                     float* boxes_o, cudaStream_t stream) {
+  if (pairs == 0) return SKG_OK;
+  PostTables t;
+  int rc = fill_tables(t, tables);
+  if (rc) return rc;
+  SKG_REQUIRE(boxes && boxes_h && boxes_o, "null pointer argument");
+  gather_pair_boxes_kernel<<<(int)ceil_div64(pairs, 256), 256, 0, stream>>>((const float4*)boxes, t, pairs, (float4*)boxes_h,
+                                                                           (float4*)boxes_o);
+  return check_launch("gather_pair_boxes_kernel");
 }

@@ -369,7 +369,7 @@ def head_forward(ih, features3: Tensor, image_shapes, box_features: Tensor, boxe
             _g(n_begin=2 * R, relu=True, bias=pk.b2cat, mul_p=hproj[:, R:], row_p=hrow, out_bf16=H_so),
             _g(n_begin=3 * R, relu=True, bias=pk.b2cat, mul_p=Gt, row_p=img, out_bf16=H_g)])
         # ---- attention weights -> adjacency (head.py:896-897); the two iterations of head.py:892 are identical
-        nt = R // 256
+        nt = 4 * (R // 256)      # four row-dot partials per 256-column tile
         dot_part = torch.empty(C, nt, **f32)
         _lib.gemm_bf16(H_att, pk.W3att, [_g(relu=True, bias=pk.b3att, dot_w=pk.w_adj, dot_out=dot_part)], block_n=256)
         # ---- messages (head.py:907-925)

@@ -68,7 +68,7 @@ def test_gemm_hadamard_groups_dot_residual():
     o0 = torch.zeros(M, R, dtype=torch.bfloat16, device=DEV); raw0 = torch.zeros(M, R, dtype=torch.bfloat16, device=DEV)
     o1 = torch.zeros(M, R, dtype=torch.bfloat16, device=DEV)
     o2 = torch.zeros(M, R, device=DEV)
-    dot = torch.zeros(M, R // 256, device=DEV)
+    dot = torch.zeros(M, 4 * (R // 256), device=DEV)      # four partials per 256-column tile
     o3 = torch.zeros(M, R, device=DEV)
     groups = [
         _lib.epilogue_group(0, relu=True, bias=bias, mul_p=P, row_p=rp, mul_q=Q, row_q=rq, out_bf16=o0, raw_bf16=raw0),
