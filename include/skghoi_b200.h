@@ -227,6 +227,73 @@ int skg_associate_gt(const float* boxes, const skg_post_tables* tables, int64_t 
                      const int32_t* gt_off, const float* gt_boxes_h, const float* gt_boxes_o,
                      const int64_t* gt_verb, float fg_iou_thresh, float* labels, cudaStream_t stream);
 
+
+/* ---- the whole pair path in one call (csrc/forward.cu) ------------------------------------------
+ * GraphHead.forward + predictor / suppressor for a batch (head.py:769-993, 408-411): pair
+ * enumeration + spatial encoding, spatial_head, box_head, fc_head / fc_tail on the distinct node rows
+ * with the TransH entity rows, the fused fc_2 GEMM of the four MBFs, adjacency, message aggregation,
+ * LayerNorm, the final attention heads on the valid pairs and the logits.  The host mirror packs
+ * the weights once (engine.PackedHead) and hands raw DEVICE pointers; the library owns no weights.
+ * All intermediates live in ONE caller-allocated workspace whose layout skg_head_plan reports
+ * (so the caller can read any tap: enc, x_keep, adjacency, ...); no allocation, no sync. */
+typedef struct skg_head_weights {
+  int32_t R, E, K0, pool_k, fc_k, Kg, Cg, num_cls, n_logit, n_logit_pad, human_idx, ent_tot, ent_dim, sp_in;
+  const void* Wb1; const float* bb1;          /* box_head.1  [E, K0] bf16 (K padded)   head.py:637 */
+  const void* Wb2; const float* bb2;          /* box_head.3  [E, E]                    head.py:639 */
+  const float* Wsp0; const float* bsp0;       /* spatial_head.0 [128, 46] fp32         head.py:663 */
+  const void* Wsp1; const float* bsp1;        /* spatial_head.2 [256, 128]             head.py:665 */
+  const void* Wsp2; const float* bsp2;        /* spatial_head.4 [R, 256]               head.py:667 */
+  const void* Wfh; const float* bfh;          /* fc_head.0 [R, fc_k]                   head.py:694 */
+  const void* Wft; const float* bft;          /* fc_tail.0 [R, fc_k]                   head.py:698 */
+  const void* W_hproj; const float* b_hproj;  /* [2R, R]: attention_head.fc_1[:, :E] | sub_to_obj.fc_1 */
+  const void* W_oproj; const float* b_oproj;  /* [2R, R]: attention_head.fc_1[:, E:] | obj_to_sub.fc_1 */
+  const void* Wg1; const float* bg1;          /* attention_head_g.fc_1 [R, Kg] */
+  const void* W2cat; const float* b2cat;      /* fc_2 of attention_head | obj_to_sub | sub_to_obj | attention_head_g  [4R, R] */
+  const void* W3att; const float* b3att;      /* fc_3 (branch-concatenated) [R, R] */
+  const void* W3os; const float* b3os;
+  const void* W3so; const float* b3so;
+  const void* W3g; const float* b3g;
+  const float* w_adj; float b_adj;            /* adjacency Linear(R -> 1) head.py:644 */
+  const float* ln_h_w; const float* ln_h_b; const float* ln_o_w; const float* ln_o_b; float ln_eps;
+  const void* Wpred; const float* bpred;      /* [n_logit_pad, 2R] predictor rows then the suppressor row (models.py:176-177) */
+  const void* Wpred_hh; const void* Wpred_lo; /* split-bf16 predictor operands ([hi | hi] and lo), NULL -> single bf16 pass */
+  const float* ent;                           /* TransH entity table [ent_tot, ent_dim] (head.py:574-578) */
+} skg_head_weights;
+
+typedef struct skg_head_batch {
+  int32_t num_images, total_boxes, total_humans, max_boxes_per_image, feat_hw;
+  int64_t total_cells, total_pairs;
+  const float* features3;     /* [B, Cg, feat_hw]  features['3'] (head.py:811) */
+  const float* box_features;  /* [boxes, pool_k]   pooled box features (head.py:387) */
+  const float* boxes;         /* [boxes, 4] */
+  const int32_t* box_off; const int32_t* n_h; const int32_t* hum_off;   /* segment table, as skg_pairs_spatial_encode */
+  const int64_t* cell_off; const int64_t* pair_off; const float* hw;
+} skg_head_batch;
+
+#define SKG_HEAD_NUM_BUFFERS 48
+typedef struct skg_head_plan_t {
+  int64_t total_bytes;
+  int32_t num_buffers;
+  int64_t offset[SKG_HEAD_NUM_BUFFERS];     /* byte offset inside the workspace (256-byte aligned) */
+  int64_t rows[SKG_HEAD_NUM_BUFFERS];
+  int64_t cols[SKG_HEAD_NUM_BUFFERS];       /* row pitch in elements */
+  int32_t elem_size[SKG_HEAD_NUM_BUFFERS];  /* 2 = bf16, 4 = fp32 / int32, 8 = int64 */
+} skg_head_plan_t;
+
+/* name of workspace buffer i ("enc", "x_keep", "logits", ...) or NULL past the end */
+const char* skg_head_buffer_name(int i);
+/* sizes only (pointers of `batch` are not read) */
+int skg_head_plan(const skg_head_weights* weights, const skg_head_batch* batch, int flags, skg_head_plan_t* plan);
+#define SKG_HEAD_PRECISE_LOGITS 1   /* split-bf16 predictor (3 bf16 passes, ~fp32 logits) */
+#define SKG_HEAD_WANT_TAPS 2        /* also keep fp32 copies of the refined node encodings */
+int skg_head_forward(const skg_head_weights* weights, const skg_head_batch* batch, int flags, void* workspace,
+                     int64_t workspace_bytes, cudaStream_t stream);
+
+/* Host-side closed form of the number of (pair, verb) entries postprocess emits per image
+ * (head.py:315 nonzero(prior[0])): all arrays are HOST pointers; returns the total, or -1. */
+int64_t skg_post_count_host(const int32_t* verb_len, int num_obj_cls, const int64_t* labels, const float* scores,
+                            const int64_t* box_off, const int64_t* n_h, int num_images, int64_t* img_entries);
+
 #ifdef __cplusplus
 }
 #endif

@@ -164,3 +164,66 @@ def gemm_bf16(A, B, groups, M=None, N=None, K=None, block_n=0):
     with torch.cuda.device(A.device):
         call("skg_gemm_bf16", ptr(A), A.stride(0), ptr(B), B.stride(0), M, N, K, arr, len(groups), block_n,
              stream_ptr(A.device))
+
+
+# ---- whole-path forward (csrc/forward.cu) -------------------------------------------------------
+_HW_INTS = ("R", "E", "K0", "pool_k", "fc_k", "Kg", "Cg", "num_cls", "n_logit", "n_logit_pad", "human_idx", "ent_tot",
+            "ent_dim", "sp_in")
+
+
+class HeadWeights(ctypes.Structure):
+    """Mirror of ``skg_head_weights``: raw device pointers of the packed operands."""
+    _fields_ = [(k, ctypes.c_int32) for k in _HW_INTS] + [
+        ("Wb1", c_void_p), ("bb1", c_void_p), ("Wb2", c_void_p), ("bb2", c_void_p),
+        ("Wsp0", c_void_p), ("bsp0", c_void_p), ("Wsp1", c_void_p), ("bsp1", c_void_p), ("Wsp2", c_void_p), ("bsp2", c_void_p),
+        ("Wfh", c_void_p), ("bfh", c_void_p), ("Wft", c_void_p), ("bft", c_void_p),
+        ("W_hproj", c_void_p), ("b_hproj", c_void_p), ("W_oproj", c_void_p), ("b_oproj", c_void_p),
+        ("Wg1", c_void_p), ("bg1", c_void_p), ("W2cat", c_void_p), ("b2cat", c_void_p),
+        ("W3att", c_void_p), ("b3att", c_void_p), ("W3os", c_void_p), ("b3os", c_void_p),
+        ("W3so", c_void_p), ("b3so", c_void_p), ("W3g", c_void_p), ("b3g", c_void_p),
+        ("w_adj", c_void_p), ("b_adj", c_float),
+        ("ln_h_w", c_void_p), ("ln_h_b", c_void_p), ("ln_o_w", c_void_p), ("ln_o_b", c_void_p), ("ln_eps", c_float),
+        ("Wpred", c_void_p), ("bpred", c_void_p), ("Wpred_hh", c_void_p), ("Wpred_lo", c_void_p),
+        ("ent", c_void_p)]
+
+
+class HeadBatch(ctypes.Structure):
+    """Mirror of ``skg_head_batch``."""
+    _fields_ = [(k, ctypes.c_int32) for k in ("num_images", "total_boxes", "total_humans", "max_boxes_per_image", "feat_hw")] + \
+               [("total_cells", c_int64), ("total_pairs", c_int64)] + \
+               [(k, c_void_p) for k in ("features3", "box_features", "boxes", "box_off", "n_h", "hum_off", "cell_off",
+                                        "pair_off", "hw")]
+
+
+HEAD_NUM_BUFFERS = 48
+
+
+class HeadPlan(ctypes.Structure):
+    """Mirror of ``skg_head_plan_t``."""
+    _fields_ = [("total_bytes", c_int64), ("num_buffers", ctypes.c_int32),
+                ("offset", c_int64 * HEAD_NUM_BUFFERS), ("rows", c_int64 * HEAD_NUM_BUFFERS),
+                ("cols", c_int64 * HEAD_NUM_BUFFERS), ("elem_size", ctypes.c_int32 * HEAD_NUM_BUFFERS)]
+
+
+HEAD_PRECISE_LOGITS = 1
+HEAD_WANT_TAPS = 2
+_SIGNATURES["skg_head_buffer_name"] = (c_char_p, [I])
+_SIGNATURES["skg_head_plan"] = (I, [ctypes.POINTER(HeadWeights), ctypes.POINTER(HeadBatch), I, ctypes.POINTER(HeadPlan)])
+_SIGNATURES["skg_head_forward"] = (I, [ctypes.POINTER(HeadWeights), ctypes.POINTER(HeadBatch), I, P, L, P])
+_SIGNATURES["skg_post_count_host"] = (c_int64, [P, I, P, P, P, P, I, P])
+
+_buffer_names = None
+
+
+def head_buffer_names():
+    global _buffer_names
+    if _buffer_names is None:
+        l = lib()
+        names, i = [], 0
+        while True:
+            s = l.skg_head_buffer_name(i)
+            if s is None:
+                break
+            names.append(s.decode()); i += 1
+        _buffer_names = names
+    return _buffer_names

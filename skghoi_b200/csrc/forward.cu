@@ -1,0 +1,297 @@
+// The whole pair path of the interaction head as ONE host call (reference GraphHead.forward head.py:769-993 and
+// the predictor / suppressor of InteractionHead.forward head.py:408-411), batched over every image of the step.
+//
+// Host-side orchestration only: it carves the caller's workspace, builds the epilogue descriptors and enqueues
+// the kernels of spatial.cu / headops.cu / gemm.cu.  Independent chains run on a second (library-owned,
+// per-thread) stream forked from and joined back into the caller's stream with events:
+//     main : pair enumeration + spatial encoding -> spatial_head (3 layers)
+//     side : box_head -> fc_head / fc_tail node rows -> per-node fc_1 projections ; global pooling -> fc_1 of attention_head_g
+//     join : fused fc_2 GEMM of the four MBFs (the dominant launch)
+//     main : adjacency row-dot GEMM -> softmax message sums -> message fc_3 + residual -> LayerNorm -> final attention head
+//     side : attention_head_g fc_3 on the valid pairs (independent of the message passing)
+//     join : predictor + suppressor logits
+// so the few-CTA node-row GEMMs overlap the wide cell-row ones instead of leaving 140 SMs idle.
+#include "common.cuh"
+#include "skghoi_b200.h"
+#include <string.h>
+
+namespace skg {
+
+enum Buf : int {
+  B_ENC = 0, B_X, B_Y, B_XKEEP, B_YKEEP, B_CELL2PAIR, B_CELL_HROW, B_CELL_OROW, B_CELL_IMG, B_PAIR2CELL, B_NANFLAG,
+  B_S1, B_S2, B_SP, B_XB, B_X1, B_NODE, B_HIN, B_OIN, B_HN32, B_HN16, B_ON32, B_ON16, B_HPROJ, B_OPROJ, B_GFEAT, B_G32,
+  B_GT, B_HATT, B_SRAW, B_HOS, B_HSO, B_HG, B_DOTPART, B_Z, B_ADJ, B_PRE, B_ENC16, B_ENC32, B_U2H, B_U2O, B_H2, B_FEAT,
+  B_TMP, B_LOGITS, B_COUNT
+};
+static_assert(B_COUNT <= SKG_HEAD_NUM_BUFFERS, "raise SKG_HEAD_NUM_BUFFERS");
+
+static const char* kBufNames[B_COUNT] = {
+  "enc", "x", "y", "x_keep", "y_keep", "cell2pair", "cell_hrow", "cell_orow", "cell_img", "pair2cell", "nan_flag",
+  "s1", "s2", "sp", "xb", "x1", "node16", "h_in", "o_in", "hN32", "hN16", "oN32", "oN16", "hproj", "oproj", "gfeat", "g32",
+  "Gt", "H_att", "S_raw", "H_os", "H_so", "H_g", "dot_part", "Z", "adjacency", "pre", "enc16", "enc32", "U2h", "U2o", "H2", "feat",
+  "tmp", "logits"};
+
+static inline int64_t align_up(int64_t v, int64_t a) { return (v + a - 1) / a * a; }
+
+static int make_plan(const skg_head_weights& w, const skg_head_batch& b, int flags, skg_head_plan_t* p) {
+  SKG_REQUIRE(w.R > 0 && w.R % 256 == 0, "representation_size must be a multiple of 256 for the tensor-core path, got %d", w.R);
+  SKG_REQUIRE(w.E > 0 && w.E % 128 == 0, "node_encoding_size must be a multiple of 128, got %d", w.E);
+  SKG_REQUIRE(w.K0 % 8 == 0 && w.fc_k % 8 == 0 && w.Kg % 8 == 0 && w.K0 >= w.pool_k && w.Kg >= w.Cg, "padded K sizes must be multiples of 8");
+  SKG_REQUIRE(w.fc_k >= w.E + w.ent_dim, "fc_k must cover node encoding + TransH dim");
+  SKG_REQUIRE(w.sp_in == 46, "spatial_head input must be 46 (2 x 23 ratio features, head.py:663)");
+  SKG_REQUIRE(w.n_logit == w.num_cls + 1 && w.n_logit_pad >= w.n_logit && w.n_logit_pad % 128 == 0, "bad logit sizes");
+  SKG_REQUIRE(b.num_images >= 0 && b.total_boxes >= 0 && b.total_humans >= 0 && b.total_cells >= 0 && b.total_pairs >= 0, "negative sizes");
+  const int64_t C = b.total_cells, P = b.total_pairs, NB = b.total_boxes, NH = b.total_humans, B = b.num_images;
+  const int R = w.R;
+  const bool precise = (flags & SKG_HEAD_PRECISE_LOGITS) != 0;
+  memset(p, 0, sizeof(*p));
+  p->num_buffers = B_COUNT;
+  auto set = [&](int i, int64_t rows, int64_t cols, int es) { p->rows[i] = rows; p->cols[i] = cols; p->elem_size[i] = es; };
+  set(B_ENC, C, 46, 4); set(B_X, C, 1, 8); set(B_Y, C, 1, 8); set(B_XKEEP, P, 1, 8); set(B_YKEEP, P, 1, 8);
+  set(B_CELL2PAIR, C, 1, 4); set(B_CELL_HROW, C, 1, 4); set(B_CELL_OROW, C, 1, 4); set(B_CELL_IMG, C, 1, 4);
+  set(B_PAIR2CELL, P, 1, 4); set(B_NANFLAG, B > 0 ? B : 1, 1, 4);
+  set(B_S1, C, 128, 2); set(B_S2, C, 256, 2); set(B_SP, C, R, 2);
+  set(B_XB, NB, w.K0, 2); set(B_X1, NB, w.E, 2); set(B_NODE, NB, w.E, 2);
+  set(B_HIN, NH, w.fc_k, 2); set(B_OIN, NB, w.fc_k, 2);
+  set(B_HN32, NH, R, 4); set(B_HN16, NH, R, 2); set(B_ON32, NB, R, 4); set(B_ON16, NB, R, 2);
+  set(B_HPROJ, NH, 2 * R, 4); set(B_OPROJ, NB, 2 * R, 4);
+  set(B_GFEAT, B, w.Kg, 2); set(B_G32, B, w.Cg, 4); set(B_GT, B, R, 4);
+  set(B_HATT, C, R, 2); set(B_SRAW, C, R, 2); set(B_HOS, C, R, 2); set(B_HSO, C, R, 2); set(B_HG, C, R, 2);
+  set(B_DOTPART, C, 4 * (R / 256), 4); set(B_Z, NH + NB, R, 2); set(B_ADJ, C, 1, 4); set(B_PRE, NH + NB, R, 4);
+  set(B_ENC16, NH + NB, R, 2); set(B_ENC32, (flags & SKG_HEAD_WANT_TAPS) ? NH + NB : 0, R, 4);
+  set(B_U2H, NH, R, 4); set(B_U2O, NB, R, 4); set(B_H2, C, R, 2);
+  set(B_FEAT, P, precise ? 4 * R : 2 * R, 2); set(B_TMP, precise ? P : 0, w.n_logit_pad, 4); set(B_LOGITS, P, w.n_logit, 4);
+  int64_t off = 0;
+  for (int i = 0; i < B_COUNT; ++i) {
+    p->offset[i] = off;
+    off = align_up(off + p->rows[i] * p->cols[i] * p->elem_size[i], 256);
+  }
+  p->total_bytes = off > 0 ? off : 256;
+  return SKG_OK;
+}
+
+// library-owned side stream + fork/join events (per host thread and device)
+struct SideStream {
+  int dev = -1;
+  cudaStream_t s = nullptr;
+  cudaEvent_t fork[2] = {nullptr, nullptr}, join[2] = {nullptr, nullptr};
+};
+static thread_local SideStream g_side;
+
+static int get_side(SideStream** out) {
+  int dev = 0;
+  SKG_CUDA(cudaGetDevice(&dev));
+  if (g_side.dev != dev) {
+    if (g_side.s) {   // device changed on this thread: drop the old objects (rare)
+      cudaStreamDestroy(g_side.s);
+      for (int i = 0; i < 2; ++i) { cudaEventDestroy(g_side.fork[i]); cudaEventDestroy(g_side.join[i]); }
+      g_side = SideStream();
+    }
+    SKG_CUDA(cudaStreamCreateWithFlags(&g_side.s, cudaStreamNonBlocking));
+    for (int i = 0; i < 2; ++i) {
+      SKG_CUDA(cudaEventCreateWithFlags(&g_side.fork[i], cudaEventDisableTiming));
+      SKG_CUDA(cudaEventCreateWithFlags(&g_side.join[i], cudaEventDisableTiming));
+    }
+    g_side.dev = dev;
+  }
+  *out = &g_side;
+  return SKG_OK;
+}
+
+static skg_epilogue_group group0() {
+  skg_epilogue_group g;
+  memset(&g, 0, sizeof(g));
+  return g;
+}
+
+#define SKG_TRY(call)        \
+  do {                       \
+    int rc__ = (call);       \
+    if (rc__) return rc__;   \
+  } while (0)
+
+}  // namespace skg
+
+using namespace skg;
+
+extern "C" const char* skg_head_buffer_name(int i) { return (i >= 0 && i < B_COUNT) ? kBufNames[i] : nullptr; }
+
+extern "C" int skg_head_plan(const skg_head_weights* weights, const skg_head_batch* batch, int flags, skg_head_plan_t* plan) {
+  SKG_REQUIRE(weights && batch && plan, "null pointer argument");
+  return make_plan(*weights, *batch, flags, plan);
+}
+
+extern "C" int skg_head_forward(const skg_head_weights* wp, const skg_head_batch* bp, int flags, void* workspace,
+                                int64_t workspace_bytes, cudaStream_t st) {
+  SKG_REQUIRE(wp && bp && workspace, "null pointer argument");
+  const skg_head_weights& w = *wp;
+  const skg_head_batch& b = *bp;
+  skg_head_plan_t plan;
+  SKG_TRY(make_plan(w, b, flags, &plan));
+  SKG_REQUIRE(workspace_bytes >= plan.total_bytes, "workspace too small: %lld < %lld bytes", (long long)workspace_bytes,
+              (long long)plan.total_bytes);
+  SKG_REQUIRE((reinterpret_cast<uintptr_t>(workspace) & 255u) == 0, "workspace must be 256-byte aligned");
+  const int64_t C = b.total_cells, P = b.total_pairs;
+  const int NB = b.total_boxes, NH = b.total_humans, B = b.num_images, R = w.R, E = w.E;
+  if (C == 0 || B == 0) return SKG_OK;
+  SKG_REQUIRE(C < (int64_t)1 << 31, "too many grid cells in one batch");
+  SKG_REQUIRE(b.features3 && b.box_features && b.boxes && b.box_off && b.n_h && b.hum_off && b.cell_off && b.pair_off && b.hw,
+              "null batch pointer");
+  SKG_REQUIRE(b.max_boxes_per_image <= w.ent_tot, "index out of range in self: a box index addresses the %d-row entity table (head.py:572)",
+              w.ent_tot);
+  const bool precise = (flags & SKG_HEAD_PRECISE_LOGITS) != 0 && w.Wpred_hh && w.Wpred_lo;
+  SKG_REQUIRE(precise || w.Wpred, "missing predictor weights");
+  uint8_t* base = reinterpret_cast<uint8_t*>(workspace);
+  auto F = [&](int i) { return reinterpret_cast<float*>(base + plan.offset[i]); };
+  auto H = [&](int i) { return reinterpret_cast<void*>(base + plan.offset[i]); };
+  auto I32 = [&](int i) { return reinterpret_cast<int32_t*>(base + plan.offset[i]); };
+  auto I64 = [&](int i) { return reinterpret_cast<int64_t*>(base + plan.offset[i]); };
+  auto HR = [&](int i, int64_t row) { return reinterpret_cast<void*>(base + plan.offset[i] + row * plan.cols[i] * 2); };
+  auto FR = [&](int i, int64_t row) { return reinterpret_cast<float*>(base + plan.offset[i] + row * plan.cols[i] * 4); };
+  SideStream* side = nullptr;
+  SKG_TRY(get_side(&side));
+  cudaStream_t ss = side->s;
+
+  // ---------------- fork: node-row chain on the side stream
+  SKG_CUDA(cudaEventRecord(side->fork[0], st));
+  SKG_CUDA(cudaStreamWaitEvent(ss, side->fork[0], 0));
+  {
+    // box head (head.py:635-641, 812)
+    SKG_TRY(skg_cast_pad_bf16(b.box_features, w.pool_k, nullptr, 0, NB, w.pool_k, H(B_XB), w.K0, w.K0, ss));
+    skg_epilogue_group g = group0();
+    g.flags = SKG_EPI_RELU; g.bias = w.bb1; g.out_bf16 = H(B_X1); g.ld_ob = E;
+    SKG_TRY(skg_gemm_bf16(H(B_XB), w.K0, w.Wb1, w.K0, NB, E, w.K0, &g, 1, 0, ss));
+    g = group0(); g.flags = SKG_EPI_RELU; g.bias = w.bb2; g.out_bf16 = H(B_NODE); g.ld_ob = E;
+    SKG_TRY(skg_gemm_bf16(H(B_X1), E, w.Wb2, E, NB, E, E, &g, 1, 0, ss));
+    // fc_head / fc_tail on the n_h (resp. n) DISTINCT rows (head.py:875-885)
+    SKG_TRY(skg_node_inputs(H(B_NODE), E, w.ent, w.ent_dim, w.ent_tot, w.human_idx, b.box_off, b.hum_off, B, NB, NH, H(B_HIN),
+                            H(B_OIN), w.fc_k, ss));
+    g = group0(); g.flags = SKG_EPI_RELU; g.bias = w.bfh; g.out_f32 = F(B_HN32); g.ld_of = R; g.out_bf16 = H(B_HN16); g.ld_ob = R;
+    SKG_TRY(skg_gemm_bf16(H(B_HIN), w.fc_k, w.Wfh, w.fc_k, NH, R, w.fc_k, &g, 1, 0, ss));
+    g = group0(); g.flags = SKG_EPI_RELU; g.bias = w.bft; g.out_f32 = F(B_ON32); g.ld_of = R; g.out_bf16 = H(B_ON16); g.ld_ob = R;
+    SKG_TRY(skg_gemm_bf16(H(B_OIN), w.fc_k, w.Wft, w.fc_k, NB, R, w.fc_k, &g, 1, 0, ss));
+    // per-node halves of the MBF appearance terms: humans -> [U_h | V_so], boxes -> [U_o | V_os]
+    g = group0(); g.bias = w.b_hproj; g.out_f32 = F(B_HPROJ); g.ld_of = 2 * R;
+    SKG_TRY(skg_gemm_bf16(H(B_HN16), R, w.W_hproj, R, NH, 2 * R, R, &g, 1, 0, ss));
+    g = group0(); g.bias = w.b_oproj; g.out_f32 = F(B_OPROJ); g.ld_of = 2 * R;
+    SKG_TRY(skg_gemm_bf16(H(B_ON16), R, w.W_oproj, R, NB, 2 * R, R, &g, 1, 0, ss));
+    // global feature term of attention_head_g (head.py:811, 971)
+    if (w.Kg == w.Cg) {
+      SKG_TRY(skg_global_pool(b.features3, (int64_t)B * w.Cg, b.feat_hw, H(B_GFEAT), nullptr, ss));
+    } else {
+      SKG_TRY(skg_global_pool(b.features3, (int64_t)B * w.Cg, b.feat_hw, nullptr, F(B_G32), ss));
+      SKG_TRY(skg_cast_pad_bf16(F(B_G32), w.Cg, nullptr, 0, B, w.Cg, H(B_GFEAT), w.Kg, w.Kg, ss));
+    }
+    g = group0(); g.bias = w.bg1; g.out_f32 = F(B_GT); g.ld_of = R;
+    SKG_TRY(skg_gemm_bf16(H(B_GFEAT), w.Kg, w.Wg1, w.Kg, B, R, w.Kg, &g, 1, 0, ss));
+  }
+  SKG_CUDA(cudaEventRecord(side->join[0], ss));
+
+  // ---------------- main: pairs + spatial head (head.py:847-868, 662-669, 888)
+  SKG_TRY(skg_pairs_spatial_encode(b.boxes, b.box_off, b.n_h, b.cell_off, b.pair_off, b.hum_off, b.hw, B, C, 23, 1e-10f, 1,
+                                   F(B_ENC), I64(B_X), I64(B_Y), I64(B_XKEEP), I64(B_YKEEP), I32(B_CELL2PAIR), I32(B_CELL_HROW),
+                                   I32(B_CELL_OROW), I32(B_CELL_IMG), I32(B_PAIR2CELL), I32(B_NANFLAG), st));
+  SKG_TRY(skg_spatial_fc1(F(B_ENC), w.Wsp0, w.bsp0, C, 46, 128, H(B_S1), st));
+  {
+    skg_epilogue_group g = group0();
+    g.flags = SKG_EPI_RELU; g.bias = w.bsp1; g.out_bf16 = H(B_S2); g.ld_ob = 256;
+    SKG_TRY(skg_gemm_bf16(H(B_S1), 128, w.Wsp1, 128, (int)C, 256, 128, &g, 1, 0, st));
+    g = group0(); g.flags = SKG_EPI_RELU; g.bias = w.bsp2; g.out_bf16 = H(B_SP); g.ld_ob = R;
+    SKG_TRY(skg_gemm_bf16(H(B_S2), 256, w.Wsp2, 256, (int)C, R, 256, &g, 1, 0, st));
+  }
+  SKG_CUDA(cudaStreamWaitEvent(st, side->join[0], 0));
+
+  // ---------------- fused fc_2 GEMM of the four MBFs that read the spatial features (N = 4R)
+  {
+    skg_epilogue_group g[4];
+    for (int i = 0; i < 4; ++i) { g[i] = group0(); g[i].n_begin = i * R; g[i].flags = SKG_EPI_RELU; g[i].bias = w.b2cat; g[i].ld_ob = R; }
+    g[0].mul_p = F(B_HPROJ); g[0].row_p = I32(B_CELL_HROW); g[0].ld_p = 2 * R;
+    g[0].mul_q = F(B_OPROJ); g[0].row_q = I32(B_CELL_OROW); g[0].ld_q = 2 * R;
+    g[0].out_bf16 = H(B_HATT); g[0].raw_bf16 = H(B_SRAW); g[0].ld_raw = R;
+    g[1].mul_p = F(B_OPROJ) + R; g[1].row_p = I32(B_CELL_OROW); g[1].ld_p = 2 * R; g[1].out_bf16 = H(B_HOS);
+    g[2].mul_p = F(B_HPROJ) + R; g[2].row_p = I32(B_CELL_HROW); g[2].ld_p = 2 * R; g[2].out_bf16 = H(B_HSO);
+    g[3].mul_p = F(B_GT); g[3].row_p = I32(B_CELL_IMG); g[3].ld_p = R; g[3].out_bf16 = H(B_HG);
+    SKG_TRY(skg_gemm_bf16(H(B_SP), R, w.W2cat, R, (int)C, 4 * R, R, g, 4, 0, st));
+  }
+  // ---------------- fork: attention_head_g fc_3 on the valid pairs (head.py:971) does not depend on the messages
+  const int feat_ld = (int)plan.cols[B_FEAT];
+  SKG_CUDA(cudaEventRecord(side->fork[1], st));
+  SKG_CUDA(cudaStreamWaitEvent(ss, side->fork[1], 0));
+  {
+    skg_epilogue_group g = group0();
+    g.flags = SKG_EPI_RELU; g.bias = w.b3g; g.out_bf16 = reinterpret_cast<__nv_bfloat16*>(H(B_FEAT)) + R; g.ld_ob = feat_ld;
+    g.out_row = I32(B_CELL2PAIR);
+    if (precise) { g.lo_bf16 = reinterpret_cast<__nv_bfloat16*>(H(B_FEAT)) + 3 * R; g.ld_lo = feat_ld; }
+    SKG_TRY(skg_gemm_bf16(H(B_HG), R, w.W3g, R, (int)C, R, R, &g, 1, 0, ss));
+  }
+  SKG_CUDA(cudaEventRecord(side->join[1], ss));
+  // ---------------- attention weights -> adjacency (head.py:896-897); the two iterations of head.py:892 are identical
+  const int nt = 4 * (R / 256);
+  {
+    skg_epilogue_group g = group0();
+    g.flags = SKG_EPI_RELU; g.bias = w.b3att; g.dot_w = w.w_adj; g.dot_out = F(B_DOTPART); g.ld_dot = nt;
+    SKG_TRY(skg_gemm_bf16(H(B_HATT), R, w.W3att, R, (int)C, R, R, &g, 1, 256, st));
+  }
+  // ---------------- messages (head.py:907-925)
+  SKG_TRY(skg_message_aggregate(F(B_DOTPART), nt, w.b_adj, H(B_HOS), H(B_HSO), R, b.box_off, b.hum_off, b.cell_off, B, NB, NH,
+                                b.max_boxes_per_image, R, HR(B_Z, 0), HR(B_Z, NH), F(B_ADJ), st));
+  {
+    skg_epilogue_group g = group0();
+    g.flags = SKG_EPI_RELU; g.bias = w.b3os; g.residual = F(B_HN32); g.ld_r = R; g.out_f32 = FR(B_PRE, 0); g.ld_of = R;
+    SKG_TRY(skg_gemm_bf16(HR(B_Z, 0), R, w.W3os, R, NH, R, R, &g, 1, 0, st));
+    g = group0(); g.flags = SKG_EPI_RELU; g.bias = w.b3so; g.residual = F(B_ON32); g.ld_r = R; g.out_f32 = FR(B_PRE, NH); g.ld_of = R;
+    SKG_TRY(skg_gemm_bf16(HR(B_Z, NH), R, w.W3so, R, NB, R, R, &g, 1, 0, st));
+  }
+  SKG_TRY(skg_layernorm(F(B_PRE), NH + NB, NH, R, w.ln_h_w, w.ln_h_b, w.ln_o_w, w.ln_o_b, w.ln_eps,
+                        (flags & SKG_HEAD_WANT_TAPS) ? F(B_ENC32) : nullptr, H(B_ENC16), st));
+  // ---------------- final attention head on the valid pairs (head.py:966-970)
+  {
+    skg_epilogue_group g = group0();
+    g.out_f32 = F(B_U2H); g.ld_of = R;
+    SKG_TRY(skg_gemm_bf16(HR(B_ENC16, 0), R, w.W_hproj, R, NH, R, R, &g, 1, 0, st));
+    g = group0(); g.bias = w.b_oproj; g.out_f32 = F(B_U2O); g.ld_of = R;
+    SKG_TRY(skg_gemm_bf16(HR(B_ENC16, NH), R, w.W_oproj, R, NB, R, R, &g, 1, 0, st));
+  }
+  SKG_TRY(skg_hadamard_cells(H(B_SRAW), R, F(B_U2H), R, F(B_U2O), R, I32(B_CELL_HROW), I32(B_CELL_OROW), C, R, H(B_H2), R, st));
+  {
+    skg_epilogue_group g = group0();
+    g.flags = SKG_EPI_RELU; g.bias = w.b3att; g.out_bf16 = H(B_FEAT); g.ld_ob = feat_ld; g.out_row = I32(B_CELL2PAIR);
+    if (precise) { g.lo_bf16 = reinterpret_cast<__nv_bfloat16*>(H(B_FEAT)) + 2 * R; g.ld_lo = feat_ld; }
+    SKG_TRY(skg_gemm_bf16(H(B_H2), R, w.W3att, R, (int)C, R, R, &g, 1, 0, st));
+  }
+  SKG_CUDA(cudaStreamWaitEvent(st, side->join[1], 0));
+  // ---------------- predictor + suppressor (head.py:410-411) as one N = num_cls + 1 GEMM
+  if (P > 0) {
+    skg_epilogue_group g = group0();
+    if (precise) {   // split bf16: logits = [hi | lo] x [W_hi | W_hi]^T + hi x W_lo^T   (3 bf16 passes ~ fp32 product)
+      g.bias = w.bpred; g.out_f32 = F(B_TMP); g.ld_of = w.n_logit_pad;
+      SKG_TRY(skg_gemm_bf16(H(B_FEAT), feat_ld, w.Wpred_hh, 4 * R, (int)P, w.n_logit, 4 * R, &g, 1, 0, st));
+      g = group0(); g.residual = F(B_TMP); g.ld_r = w.n_logit_pad; g.out_f32 = F(B_LOGITS); g.ld_of = w.n_logit;
+      SKG_TRY(skg_gemm_bf16(H(B_FEAT), feat_ld, w.Wpred_lo, 2 * R, (int)P, w.n_logit, 2 * R, &g, 1, 0, st));
+    } else {
+      g.bias = w.bpred; g.out_f32 = F(B_LOGITS); g.ld_of = w.n_logit;
+      SKG_TRY(skg_gemm_bf16(H(B_FEAT), feat_ld, w.Wpred, 2 * R, (int)P, w.n_logit, 2 * R, &g, 1, 0, st));
+    }
+  }
+  return SKG_OK;
+}
+
+extern "C" int64_t skg_post_count_host(const int32_t* verb_len, int num_obj_cls, const int64_t* labels, const float* scores,
+                                       const int64_t* box_off, const int64_t* n_h, int num_images, int64_t* img_entries) {
+  if (!verb_len || !labels || !scores || !box_off || !n_h) { set_error("null pointer argument"); return -1; }
+  int64_t total = 0;
+  for (int b = 0; b < num_images; ++b) {
+    const int64_t lo = box_off[b], hi = box_off[b + 1];
+    int64_t S = 0;
+    for (int64_t k = lo; k < hi; ++k) {
+      if (labels[k] < 0 || labels[k] >= num_obj_cls) { set_error("object class %lld out of range", (long long)labels[k]); return -1; }
+      S += verb_len[labels[k]];
+    }
+    int64_t e = 0;
+    for (int64_t i = 0; i < n_h[b]; ++i)
+      if (scores[lo + i] > 0.f) e += S - verb_len[labels[lo + i]];
+    if (img_entries) img_entries[b] = e;
+    total += e;
+  }
+  return total;
+}

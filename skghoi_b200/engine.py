@@ -248,6 +248,24 @@ class PackedHead:
         hi = Wp.to(torch.bfloat16); lo = (Wp - hi.float()).to(torch.bfloat16)
         self.Wpred_hh = _bf16(torch.cat([hi.float(), hi.float()], 1), pad_rows=128)     # [128, 2*2R] against [hi | lo]
         self.Wpred_lo = _bf16(lo.float(), pad_rows=128)                                 # [128, 2R]   against hi
+        self.cw = self._c_struct(G)
+
+    def _c_struct(self, G):
+        """skg_head_weights: raw device pointers of the packed operands (this object keeps them alive)."""
+        w = _lib.HeadWeights()
+        w.R, w.E, w.K0, w.pool_k = self.R, self.E, self.Wb1.shape[1], G.box_head[1].weight.shape[1]
+        w.fc_k, w.Kg, w.Cg = self.fc_k, self.Wg1.shape[1], G.attention_head_g.fc_1[0].weight.shape[1]
+        w.num_cls, w.n_logit, w.n_logit_pad = self.num_cls, self.n_logit, self.Wpred.shape[0]
+        w.human_idx, w.ent_tot, w.ent_dim = G.human_idx, G.transh_head.num_object, G.transh_head.transh_dim
+        w.sp_in = G.spatial_head[0].weight.shape[1]
+        for name in ("Wb1", "bb1", "Wb2", "bb2", "Wsp0", "bsp0", "Wsp1", "bsp1", "Wsp2", "bsp2", "Wfh", "bfh", "Wft", "bft",
+                     "W_hproj", "b_hproj", "W_oproj", "b_oproj", "Wg1", "bg1", "W2cat", "b2cat", "W3att", "b3att",
+                     "W3os", "b3os", "W3so", "b3so", "W3g", "b3g", "w_adj", "Wpred", "bpred", "Wpred_hh", "Wpred_lo"):
+            setattr(w, name, getattr(self, name).data_ptr())
+        w.b_adj = self.b_adj
+        w.ln_h_w, w.ln_h_b, w.ln_o_w, w.ln_o_b = (t.data_ptr() for t in self.ln)
+        w.ln_eps = self.ln_eps
+        return w
 
 
 def packed_head(ih) -> PackedHead:
@@ -287,130 +305,96 @@ def _host_meta(box_labels: List[Tensor], box_scores: Optional[List[Tensor]], hum
     return dict(n=n, n_h=n_h, labels=labels, scores=scores)
 
 
+_INT64_BUFS = {"x", "y", "x_keep", "y_keep"}
+_INT32_BUFS = {"cell2pair", "cell_hrow", "cell_orow", "cell_img", "pair2cell", "nan_flag"}
+_workspaces = {}
+
+
+def _workspace(dev, nbytes: int) -> Tensor:
+    """One growing scratch buffer per (device, stream): every intermediate of the step lives in it."""
+    key = (dev.index, torch.cuda.current_stream(dev).cuda_stream)
+    ws = _workspaces.get(key)
+    if ws is None or ws.numel() < nbytes:
+        ws = torch.empty(int(nbytes * 1.25) + 256, dtype=torch.uint8, device=dev)
+        _workspaces[key] = ws
+    return ws
+
+
+class _Run(dict):
+    """Result of ``head_forward``: named views into the step's workspace, created on first access.
+    The views alias scratch memory that the next step on the same stream overwrites."""
+
+    def __init__(self, ws: Tensor, plan, **kw):
+        super().__init__(**kw)
+        self._ws, self._plan = ws, plan
+        self._index = {n: i for i, n in enumerate(_lib.head_buffer_names())}
+
+    def __missing__(self, name):
+        i = self._index[name]                      # KeyError for unknown names
+        p = self._plan
+        rows, cols, es, off = int(p.rows[i]), int(p.cols[i]), int(p.elem_size[i]), int(p.offset[i])
+        dt = torch.int64 if name in _INT64_BUFS else torch.int32 if name in _INT32_BUFS else \
+            torch.bfloat16 if es == 2 else torch.float32
+        t = self._ws[off:off + rows * cols * es].view(dt)
+        t = t.view(rows) if cols == 1 and (name in _INT64_BUFS or name in _INT32_BUFS or name == "adjacency") else t.view(rows, cols)
+        self[name] = t
+        return t
+
+    def get(self, name, default=None):
+        try:
+            return self[name]
+        except KeyError:
+            return default
+
+
 def head_forward(ih, features3: Tensor, image_shapes, box_features: Tensor, boxes_cat: Tensor, meta: dict,
                  want_taps: bool = False, precise_logits: bool = True) -> dict:
-    """Runs the whole pair path for a batch.  Inputs: features['3'] [B,256,h,w] fp32, pooled box
-    features [sum n, 256, 7, 7] fp32, concatenated boxes [sum n, 4] fp32 (all CUDA), host ``meta``.
-    Returns a dict of device tensors: logits [P,118] fp32 (117 verb logits + suppressor logit),
-    feat (bf16 [P, 2*R] hi part, and lo part when precise_logits), pair indices, encodings, etc."""
+    """Runs the whole pair path for a batch through ONE C-ABI call (skg_head_forward, csrc/forward.cu).
+    Inputs: features['3'] [B,256,h,w] fp32, pooled box features [sum n, 256, 7, 7] fp32, concatenated boxes
+    [sum n, 4] fp32 (all CUDA), host ``meta``.  Returns named views into the step's workspace: logits [P,118]
+    fp32 (117 verb logits + suppressor logit), feat (bf16 [P, 2R] hi part, + lo part when precise_logits),
+    pair indices, encodings, row maps and every intermediate."""
     pk = packed_head(ih)
     G = ih.box_pair_head
     dev = pk.device
-    R, E = pk.R, pk.E
     n, n_h = meta["n"], meta["n_h"]
     if any(k > G.transh_head.num_object for k in n):
         raise IndexError("index out of range in self")   # head.py:572: box index addresses the 80-row entity table
     # images the reference skips (head.py:829-839) contribute no cells: treat them as n_h = 0
     n_h_eff = [0 if (h == 0 or k <= 1) else h for h, k in zip(n_h, n)]
     seg = Segments(n_h_eff, n, image_shapes, dev)
-    B, NB, NH, C, Pn = seg.B, seg.total_boxes, seg.total_humans, seg.total_cells, seg.total_pairs
-    out = dict(seg=seg)
-    f32 = dict(dtype=torch.float32, device=dev); b16 = dict(dtype=torch.bfloat16, device=dev)
-    st = _lib.stream_ptr(dev)
+    tr = G.transh_head.transh
+    if tr.ent_embeddings.weight.device != dev:
+        tr.to(dev)
+    ent = tr.ent_embeddings.weight.detach()
+    f3 = features3.contiguous()
+    bf = box_features.reshape(seg.total_boxes, -1)
+    if not bf.is_contiguous():
+        bf = bf.contiguous()
+    _lib.require_cuda(f3, bf, boxes_cat)
+    w = pk.cw
+    w.ent = ent.data_ptr()
+    b = _lib.HeadBatch()
+    b.num_images, b.total_boxes, b.total_humans = seg.B, seg.total_boxes, seg.total_humans
+    b.max_boxes_per_image = int(max(n)) if len(n) else 0
+    b.feat_hw = int(f3.shape[2] * f3.shape[3]) if f3.dim() == 4 else 0
+    b.total_cells, b.total_pairs = seg.total_cells, seg.total_pairs
+    b.features3, b.box_features, b.boxes = f3.data_ptr(), bf.data_ptr(), boxes_cat.data_ptr()
+    b.box_off, b.n_h, b.hum_off = seg.d_box_off.data_ptr(), seg.d_n_h.data_ptr(), seg.d_hum_off.data_ptr()
+    b.cell_off, b.pair_off, b.hw = seg.d_cell_off.data_ptr(), seg.d_pair_off.data_ptr(), seg.d_hw.data_ptr()
+    flags = (_lib.HEAD_PRECISE_LOGITS if precise_logits else 0) | (_lib.HEAD_WANT_TAPS if want_taps else 0)
+    plan = _lib.HeadPlan()
+    import ctypes
+    _lib.call("skg_head_plan", ctypes.byref(w), ctypes.byref(b), flags, ctypes.byref(plan))
     with torch.cuda.device(dev):
-        pe = enumerate_pairs(None, n_h_eff, image_shapes, seg=seg, boxes_cat=boxes_cat)
-        out.update(pe)
-        if C == 0:
-            out.update(logits=torch.zeros(0, pk.n_logit, **f32), feat=torch.zeros(0, 2 * R, **b16))
-            return out
-        # ---- spatial head (head.py:662-669, 888): fp32 layer 0, then two tensor-core layers
-        s1 = torch.empty(C, 128, **b16)
-        _lib.call("skg_spatial_fc1", _lib.ptr(pe["enc"]), _lib.ptr(pk.Wsp0), _lib.ptr(pk.bsp0), C, 46, 128, _lib.ptr(s1), st)
-        s2 = torch.empty(C, 256, **b16)
-        _lib.gemm_bf16(s1, pk.Wsp1, [_g(relu=True, bias=pk.bsp1, out_bf16=s2)])
-        sp = torch.empty(C, R, **b16)
-        _lib.gemm_bf16(s2, pk.Wsp2, [_g(relu=True, bias=pk.bsp2, out_bf16=sp)])
-        # ---- box head (head.py:635-641, 812)
-        K0 = pk.Wb1.shape[1]
-        bf = box_features.reshape(NB, -1)
-        xb = torch.empty(NB, K0, **b16)
-        _lib.call("skg_cast_pad_bf16", _lib.ptr(bf), bf.stride(0), None, 0, NB, bf.shape[1], _lib.ptr(xb), K0, K0, st)
-        x1 = torch.empty(NB, E, **b16)
-        _lib.gemm_bf16(xb, pk.Wb1, [_g(relu=True, bias=pk.bb1, out_bf16=x1)])
-        node = torch.empty(NB, E, **b16)
-        _lib.gemm_bf16(x1, pk.Wb2, [_g(relu=True, bias=pk.bb2, out_bf16=node)])
-        # ---- fc_head / fc_tail on the n_h (resp. n) DISTINCT rows (head.py:875-885)
-        tr = G.transh_head.transh
-        if tr.ent_embeddings.weight.device != dev:
-            tr.to(dev)
-        ent = tr.ent_embeddings.weight.detach()
-        h_in = torch.empty(NH, pk.fc_k, **b16); o_in = torch.empty(NB, pk.fc_k, **b16)
-        _lib.call("skg_node_inputs", _lib.ptr(node), E, _lib.ptr(ent), ent.shape[1], ent.shape[0], G.human_idx,
-                  _lib.ptr(seg.d_box_off), _lib.ptr(seg.d_hum_off), B, NB, NH, _lib.ptr(h_in), _lib.ptr(o_in), pk.fc_k, st)
-        hN32 = torch.empty(NH, R, **f32); hN16 = torch.empty(NH, R, **b16)
-        oN32 = torch.empty(NB, R, **f32); oN16 = torch.empty(NB, R, **b16)
-        _lib.gemm_bf16(h_in, pk.Wfh, [_g(relu=True, bias=pk.bfh, out_f32=hN32, out_bf16=hN16)])
-        _lib.gemm_bf16(o_in, pk.Wft, [_g(relu=True, bias=pk.bft, out_f32=oN32, out_bf16=oN16)])
-        # ---- per-node halves of the MBF appearance terms
-        hproj = torch.empty(NH, 2 * R, **f32); oproj = torch.empty(NB, 2 * R, **f32)
-        _lib.gemm_bf16(hN16, pk.W_hproj, [_g(bias=pk.b_hproj, out_f32=hproj)])
-        _lib.gemm_bf16(oN16, pk.W_oproj, [_g(bias=pk.b_oproj, out_f32=oproj)])
-        # ---- global feature term of attention_head_g (head.py:811, 971)
-        Cg = features3.shape[1]
-        f3 = features3.contiguous()
-        Kg = pk.Wg1.shape[1]
-        gfeat = torch.zeros(B, Kg, **b16)
-        if Kg == Cg:
-            _lib.call("skg_global_pool", _lib.ptr(f3), B * Cg, f3.shape[2] * f3.shape[3], _lib.ptr(gfeat), None, st)
-        else:
-            g32 = torch.empty(B, Cg, **f32)
-            _lib.call("skg_global_pool", _lib.ptr(f3), B * Cg, f3.shape[2] * f3.shape[3], None, _lib.ptr(g32), st)
-            _lib.call("skg_cast_pad_bf16", _lib.ptr(g32), Cg, None, 0, B, Cg, _lib.ptr(gfeat), Kg, Kg, st)
-        Gt = torch.empty(B, R, **f32)
-        _lib.gemm_bf16(gfeat, pk.Wg1, [_g(bias=pk.bg1, out_f32=Gt)])
-        # ---- fused fc_2 GEMM of the four MBFs that read the spatial features (N = 4R)
-        H_att = torch.empty(C, R, **b16); S_raw = torch.empty(C, R, **b16)
-        H_os = torch.empty(C, R, **b16); H_so = torch.empty(C, R, **b16); H_g = torch.empty(C, R, **b16)
-        hrow, orow, img = pe["cell_hrow"], pe["cell_orow"], pe["cell_img"]
-        _lib.gemm_bf16(sp, pk.W2cat, [
-            _g(n_begin=0, relu=True, bias=pk.b2cat, mul_p=hproj[:, :R], row_p=hrow, mul_q=oproj[:, :R], row_q=orow,
-               out_bf16=H_att, raw_bf16=S_raw),
-            _g(n_begin=R, relu=True, bias=pk.b2cat, mul_p=oproj[:, R:], row_p=orow, out_bf16=H_os),
-            _g(n_begin=2 * R, relu=True, bias=pk.b2cat, mul_p=hproj[:, R:], row_p=hrow, out_bf16=H_so),
-            _g(n_begin=3 * R, relu=True, bias=pk.b2cat, mul_p=Gt, row_p=img, out_bf16=H_g)])
-        # ---- attention weights -> adjacency (head.py:896-897); the two iterations of head.py:892 are identical
-        nt = 4 * (R // 256)      # four row-dot partials per 256-column tile
-        dot_part = torch.empty(C, nt, **f32)
-        _lib.gemm_bf16(H_att, pk.W3att, [_g(relu=True, bias=pk.b3att, dot_w=pk.w_adj, dot_out=dot_part)], block_n=256)
-        # ---- messages (head.py:907-925)
-        Z = torch.empty(NH + NB, R, **b16)
-        adjacency = torch.empty(C, **f32)
-        _lib.call("skg_message_aggregate", _lib.ptr(dot_part), nt, pk.b_adj, _lib.ptr(H_os), _lib.ptr(H_so), R,
-                  _lib.ptr(seg.d_box_off), _lib.ptr(seg.d_hum_off), _lib.ptr(seg.d_cell_off), B, NB, NH, int(max(n)), R,
-                  _lib.ptr(Z[:NH]), _lib.ptr(Z[NH:]), _lib.ptr(adjacency), st)
-        pre = torch.empty(NH + NB, R, **f32)
-        _lib.gemm_bf16(Z[:NH], pk.W3os, [_g(relu=True, bias=pk.b3os, residual=hN32, out_f32=pre[:NH])])
-        _lib.gemm_bf16(Z[NH:], pk.W3so, [_g(relu=True, bias=pk.b3so, residual=oN32, out_f32=pre[NH:])])
-        enc16 = torch.empty(NH + NB, R, **b16)
-        enc32 = torch.empty(NH + NB, R, **f32) if want_taps else None
-        _lib.call("skg_layernorm", _lib.ptr(pre), NH + NB, NH, R, _lib.ptr(pk.ln[0]), _lib.ptr(pk.ln[1]), _lib.ptr(pk.ln[2]),
-                  _lib.ptr(pk.ln[3]), pk.ln_eps, _lib.ptr(enc32), _lib.ptr(enc16), st)
-        # ---- final attention heads on the valid pairs (head.py:966-973)
-        U2h = torch.empty(NH, R, **f32); U2o = torch.empty(NB, R, **f32)
-        _lib.gemm_bf16(enc16[:NH], pk.W_hproj, [_g(out_f32=U2h)], N=R)
-        _lib.gemm_bf16(enc16[NH:], pk.W_oproj, [_g(bias=pk.b_oproj, out_f32=U2o)], N=R)
-        H2 = torch.empty(C, R, **b16)
-        _lib.call("skg_hadamard_cells", _lib.ptr(S_raw), R, _lib.ptr(U2h), R, _lib.ptr(U2o), R, _lib.ptr(hrow), _lib.ptr(orow),
-                  C, R, _lib.ptr(H2), R, st)
-        # feat rows are the valid pairs (cell2pair scatter); columns [hi(att1) hi(att2) | lo(att1) lo(att2)]
-        feat = torch.empty(Pn, 4 * R if precise_logits else 2 * R, **b16)
-        c2p = pe["cell2pair"]
-        lo1 = feat[:, 2 * R:3 * R] if precise_logits else None
-        lo2 = feat[:, 3 * R:] if precise_logits else None
-        _lib.gemm_bf16(H2, pk.W3att, [_g(relu=True, bias=pk.b3att, out_bf16=feat[:, :R], out_row=c2p, lo_bf16=lo1)])
-        _lib.gemm_bf16(H_g, pk.W3g, [_g(relu=True, bias=pk.b3g, out_bf16=feat[:, R:2 * R], out_row=c2p, lo_bf16=lo2)])
-        # ---- predictor + suppressor (head.py:410-411) as one N = num_cls + 1 GEMM
-        logits = torch.empty(Pn, pk.n_logit, **f32)
-        if precise_logits:
-            tmp = torch.empty(Pn, pk.Wpred.shape[0], **f32)       # pitch padded to 128 (read back as residual)
-            _lib.gemm_bf16(feat, pk.Wpred_hh, [_g(bias=pk.bpred, out_f32=tmp)], N=pk.n_logit)
-            _lib.gemm_bf16(feat[:, :2 * R], pk.Wpred_lo, [_g(residual=tmp, out_f32=logits)], N=pk.n_logit, K=2 * R)
-        else:
-            _lib.gemm_bf16(feat, pk.Wpred, [_g(bias=pk.bpred, out_f32=logits)], N=pk.n_logit)
-    out.update(logits=logits, feat=feat, adjacency=adjacency, node16=node, hN32=hN32, oN32=oN32, enc32=enc32,
-               enc16=enc16, sp=sp, NH=NH, NB=NB, hproj=hproj, oproj=oproj, Gt=Gt,
-               fc2_out=(H_att, S_raw, H_os, H_so, H_g))
-    return out
+        ws = _workspace(dev, int(plan.total_bytes))
+        _lib.call("skg_head_forward", ctypes.byref(w), ctypes.byref(b), flags, _lib.ptr(ws), ws.numel(), _lib.stream_ptr(dev))
+    run = _Run(ws, plan, seg=seg, NH=seg.total_humans, NB=seg.total_boxes, _keep=(f3, bf, boxes_cat, ent))
+    if want_taps:
+        run["enc32"]
+    else:
+        run["enc32"] = None
+    return run
 
 
 def dominant_gemm_closure(ih, run: dict) -> dict:
@@ -419,7 +403,7 @@ def dominant_gemm_closure(ih, run: dict) -> dict:
     pk = packed_head(ih)
     R = pk.R
     sp, hproj, oproj, Gt = run["sp"], run["hproj"], run["oproj"], run["Gt"]
-    H_att, S_raw, H_os, H_so, H_g = run["fc2_out"]
+    H_att, S_raw, H_os, H_so, H_g = run["H_att"], run["S_raw"], run["H_os"], run["H_so"], run["H_g"]
     hrow, orow, img = run["cell_hrow"], run["cell_orow"], run["cell_img"]
     groups = [
         _g(n_begin=0, relu=True, bias=pk.b2cat, mul_p=hproj[:, :R], row_p=hrow, mul_q=oproj[:, :R], row_q=orow,
@@ -444,6 +428,7 @@ class VerbTable:
             v = sorted(set(int(t) for t in verbs))
             lens.append(len(v)); flat.extend(v)
         self.lens = np.asarray(lens, dtype=np.int64)
+        self.lens32 = np.ascontiguousarray(self.lens, dtype=np.int32)
         off = np.concatenate([[0], np.cumsum(self.lens)]).astype(np.int32)
         self.d_off = torch.from_numpy(off).to(device)
         self.d_idx = torch.tensor(flat if flat else [0], dtype=torch.int32).to(device)
@@ -459,7 +444,10 @@ def _verb_table(G, device) -> VerbTable:
 
 
 def _post_tables(G, run: dict, meta: dict, labels_dev: Tensor, scores_dev: Tensor, with_counts: bool):
-    """Builds the skg_post_tables struct; with_counts adds the closed-form output offsets."""
+    """Builds the skg_post_tables struct.  with_counts adds the closed-form output offsets: the per-image
+    entry counts come from a host helper (they size the outputs), the per-box / per-human offsets are built
+    on the device by skg_post_offsets -- no numpy loops, no extra host->device copies."""
+    import ctypes
     seg: Segments = run["seg"]
     dev = seg.device
     vt = _verb_table(G, dev)
@@ -472,30 +460,38 @@ def _post_tables(G, run: dict, meta: dict, labels_dev: Tensor, scores_dev: Tenso
     t.labels, t.scores = labels_dev.data_ptr(), scores_dev.data_ptr()
     entries_per_image = None
     if with_counts:
-        labels = meta["labels"]; scores = meta["scores"]
-        cnt = vt.lens[labels] if len(labels) else np.zeros(0, np.int64)
-        prefix = np.zeros_like(cnt); hum_base = np.zeros(seg.total_humans, dtype=np.int64)
-        entries_per_image = np.zeros(seg.B, dtype=np.int64)
-        total = 0
-        for b in range(seg.B):
-            lo, hi = int(seg.box_off[b]), int(seg.box_off[b + 1])
-            c = cnt[lo:hi]
-            prefix[lo:hi] = np.cumsum(c) - c
-            nh = int(seg.n_h[b])
-            if nh:
-                S = int(c.sum())
-                live = scores[lo:lo + nh] > 0
-                row_tot = np.where(live, S - c[:nh], 0)
-                h0 = int(seg.hum_off[b])
-                hum_base[h0:h0 + nh] = total + np.cumsum(row_tot) - row_tot
-                entries_per_image[b] = int(row_tot.sum())
-                total += int(row_tot.sum())
-        d_cnt = torch.from_numpy(cnt.astype(np.int32)).to(dev)
-        d_prefix = torch.from_numpy(prefix.astype(np.int32)).to(dev)
-        d_hbase = torch.from_numpy(hum_base).to(dev)
-        keep += [d_cnt, d_prefix, d_hbase]
+        labels = np.ascontiguousarray(meta["labels"], dtype=np.int64)
+        scores = np.ascontiguousarray(meta["scores"], dtype=np.float32)
+        entries_per_image = np.zeros(max(seg.B, 1), dtype=np.int64)
+        total = _lib.lib().skg_post_count_host(vt.lens32.ctypes.data, len(vt.lens32), labels.ctypes.data, scores.ctypes.data,
+                                               seg.box_off.ctypes.data, seg.n_h.ctypes.data, seg.B,
+                                               entries_per_image.ctypes.data)
+        if total < 0:
+            raise _lib.SkgError("skg_post_count_host: " + _lib.lib().skg_last_error().decode())
+        entries_per_image = entries_per_image[:seg.B]
+        NB, NHm = max(seg.total_boxes, 1), max(seg.total_humans, 1)
+        i32 = torch.empty(2 * NB, dtype=torch.int32, device=dev)
+        i64 = torch.empty(NHm + 2 * seg.B + 1, dtype=torch.int64, device=dev)
+        d_cnt, d_prefix = i32[:NB], i32[NB:]
+        d_hbase, d_ient, d_ibase = i64[:NHm], i64[NHm:NHm + seg.B], i64[NHm + seg.B:]
+        with torch.cuda.device(dev):
+            _lib.call("skg_post_offsets", _lib.ptr(vt.d_off), _lib.ptr(labels_dev), _lib.ptr(scores_dev), _lib.ptr(seg.d_box_off),
+                      _lib.ptr(seg.d_hum_off), seg.B, _lib.ptr(d_cnt), _lib.ptr(d_prefix), _lib.ptr(d_hbase), _lib.ptr(d_ient),
+                      _lib.ptr(d_ibase), _lib.stream_ptr(dev))
+        keep += [i32, i64]
         t.box_cnt, t.box_prefix, t.hum_base = d_cnt.data_ptr(), d_prefix.data_ptr(), d_hbase.data_ptr()
     return t, keep, entries_per_image
+
+
+def _pair_boxes(run: dict, tables, boxes_cat: Tensor):
+    """boxes_h / boxes_o [P, 4] of every valid pair (head.py:975-976)."""
+    seg: Segments = run["seg"]
+    Pn = seg.total_pairs
+    out = torch.empty(2, Pn, 4, dtype=torch.float32, device=seg.device)
+    with torch.cuda.device(seg.device):
+        _lib.call("skg_gather_pair_boxes", _lib.ptr(boxes_cat), ctypes_byref(tables), Pn, _lib.ptr(out[0]), _lib.ptr(out[1]),
+                  _lib.stream_ptr(seg.device))
+    return out[0], out[1]
 
 
 def _gt_labels(G, run: dict, tables, boxes_cat: Tensor, targets: List[dict]) -> Tensor:
@@ -589,10 +585,9 @@ def graph_head_forward(G, features, image_shapes, box_features, box_coords, box_
         _lib.call("skg_prior_dense", ctypes_byref(tables), Pn, G.num_cls, 1.0 if G.training else 2.8, _lib.ptr(prior),
                   _lib.stream_ptr(dev))
     priors = _split(prior, psz, dim=1)
-    p2c = run["pair2cell"].long()
-    hrow_box = (run["cell_orow"].long() - run["y"] + run["x"])[p2c] if Pn else torch.zeros(0, dtype=torch.int64, device=dev)
-    orow = run["cell_orow"].long()[p2c] if Pn else hrow_box
-    boxes_h = _split(boxes_cat[hrow_box], psz); boxes_o = _split(boxes_cat[orow], psz)
+    bh_all, bo_all = _pair_boxes(run, tables, boxes_cat)
+    boxes_h = _split(bh_all, psz); boxes_o = _split(bo_all, psz)
+    orow = run["cell_orow"].long()[run["pair2cell"].long()] if Pn else torch.zeros(0, dtype=torch.int64, device=dev)
     obj = _split(labels_dev[orow], psz)
     all_labels, pos, neg, eh, et, rl, rn = [], [], [], [], [], [], []
     if targets is not None:
@@ -644,12 +639,8 @@ def interaction_head_from_pooled(ih, features, image_shapes, box_features, box_c
                   1.0 if G.training else 2.8, _lib.ptr(gt), L, _lib.ptr(index), _lib.ptr(pred), _lib.ptr(scores),
                   _lib.ptr(prior), _lib.ptr(weights), _lib.ptr(lab_e), _lib.ptr(unary), _lib.ptr(obj), _lib.stream_ptr(dev))
     psz = seg.pair_off[1:] - seg.pair_off[:-1]
-    p2c = run["pair2cell"].long()
-    if Pn:
-        hbox = (run["cell_orow"].long() - run["y"] + run["x"])[p2c]; obox = run["cell_orow"].long()[p2c]
-    else:
-        hbox = obox = torch.zeros(0, **i64)
-    bh = _split(boxes_cat[hbox], psz); bo = _split(boxes_cat[obox], psz)
+    bh_all, bo_all = _pair_boxes(run, tables, boxes_cat)
+    bh = _split(bh_all, psz); bo = _split(bo_all, psz)
     results = []
     for b, (idx_b, pr_b, sc_b, pri_b, w_b, o_b) in enumerate(zip(_split(index, per_img), _split(pred, per_img),
                                                                 _split(scores, per_img), _split(prior, per_img, dim=1),
