@@ -140,6 +140,16 @@ typedef struct skg_epilogue_group {
 int skg_gemm_bf16(const void* A, int64_t lda, const void* B, int64_t ldb, int M, int N, int K,
                   const skg_epilogue_group* groups, int num_groups, int block_n, cudaStream_t stream);
 
+/* Same GEMM with split-K for shapes whose tiles alone leave most SMs idle (M = node rows of a batch):
+ * `scratch` is a caller-owned region of at least skg_gemm_splitk_scratch_bytes() bytes that must be ZERO on
+ * entry and is left zero on exit (partial tiles are reduced with fp32 red.global.add; the last split to arrive
+ * runs the epilogue and re-zeroes its tile).  One scratch region may serve successive launches of ONE stream.
+ * scratch NULL (or too small) -> no split, identical to skg_gemm_bf16. */
+int skg_gemm_bf16_splitk(const void* A, int64_t lda, const void* B, int64_t ldb, int M, int N, int K,
+                         const skg_epilogue_group* groups, int num_groups, int block_n, void* scratch,
+                         int64_t scratch_bytes, cudaStream_t stream);
+int64_t skg_gemm_splitk_scratch_bytes(int max_tiles_m, int max_n);
+
 /* ---- glue kernels between the GEMMs (csrc/headops.cu) ---------------------------------------- */
 
 /* dst[r, 0:cols_pad] = bf16(relu?(src[r, 0:cols] + bias)), zero padded (operand packing for the GEMMs). */
@@ -155,6 +165,13 @@ int skg_spatial_fc1(const float* enc, const float* weight, const float* bias, in
 int skg_node_inputs(const void* node_enc_bf16, int enc_dim, const float* ent, int ent_dim, int ent_tot,
                     int human_idx, const int32_t* box_off, const int32_t* hum_off, int num_images,
                     int total_boxes, int total_humans, void* h_in, void* o_in, int ld, cudaStream_t stream);
+
+/* Fused-fc variant of skg_node_inputs: fills only the TransH entity columns o_in[box, enc_dim:ld] = bf16(E[index of the
+ * box inside its image]) (tail_stack == E[y], head.py:572; the node encoding columns are written by the box_head GEMM)
+ * and box2hum[boxes] = human row of the box (first n_h boxes of every image) or -1. */
+int skg_node_prep(const float* ent, int ent_dim, int ent_tot, const int32_t* box_off, const int32_t* n_h,
+                  const int32_t* hum_off, int num_images, int total_boxes, void* o_in, int ld, int enc_dim,
+                  int32_t* box2hum, cudaStream_t stream);
 
 /* avg_pool(features['3']).flatten(1) (head.py:811): planes = B*C, hw = H*W. */
 int skg_global_pool(const float* features, int64_t planes, int hw, void* out_bf16, float* out_f32,
@@ -235,7 +252,10 @@ int skg_associate_gt(const float* boxes, const skg_post_tables* tables, int64_t 
  * LayerNorm, the final attention heads on the valid pairs and the logits.  The host mirror packs
  * the weights once (engine.PackedHead) and hands raw DEVICE pointers; the library owns no weights.
  * All intermediates live in ONE caller-allocated workspace whose layout skg_head_plan reports
- * (so the caller can read any tap: enc, x_keep, adjacency, ...); no allocation, no sync. */
+ * (so the caller can read any tap: enc, x_keep, adjacency, ...); no allocation, no sync.
+ * The first two buffers ("splitk_main", "splitk_side", fixed size, at the start of the workspace) are the
+ * split-K scratch of the two streams: they must be ZERO before the first call on a workspace and every call
+ * leaves them zero (see skg_gemm_bf16_splitk). */
 typedef struct skg_head_weights {
   int32_t R, E, K0, pool_k, fc_k, Kg, Cg, num_cls, n_logit, n_logit_pad, human_idx, ent_tot, ent_dim, sp_in;
   const void* Wb1; const float* bb1;          /* box_head.1  [E, K0] bf16 (K padded)   head.py:637 */
@@ -245,6 +265,8 @@ typedef struct skg_head_weights {
   const void* Wsp2; const float* bsp2;        /* spatial_head.4 [R, 256]               head.py:667 */
   const void* Wfh; const float* bfh;          /* fc_head.0 [R, fc_k]                   head.py:694 */
   const void* Wft; const float* bft;          /* fc_tail.0 [R, fc_k]                   head.py:698 */
+  const void* Wfc; const float* bfc;          /* fused [2R, fc_k]: fc_head rows (entity columns zeroed, their constant
+                                                 E[human_idx] term folded into bfc) then fc_tail rows */
   const void* W_hproj; const float* b_hproj;  /* [2R, R]: attention_head.fc_1[:, :E] | sub_to_obj.fc_1 */
   const void* W_oproj; const float* b_oproj;  /* [2R, R]: attention_head.fc_1[:, E:] | obj_to_sub.fc_1 */
   const void* Wg1; const float* bg1;          /* attention_head_g.fc_1 [R, Kg] */
@@ -286,6 +308,10 @@ const char* skg_head_buffer_name(int i);
 int skg_head_plan(const skg_head_weights* weights, const skg_head_batch* batch, int flags, skg_head_plan_t* plan);
 #define SKG_HEAD_PRECISE_LOGITS 1   /* split-bf16 predictor (3 bf16 passes, ~fp32 logits) */
 #define SKG_HEAD_WANT_TAPS 2        /* also keep fp32 copies of the refined node encodings */
+#define SKG_HEAD_PROFILE 4          /* record an event after every launch and SYNCHRONISE at the end (diagnostics only) */
+/* launch i of the last profiled skg_head_forward on this thread: label, stream (0 caller's, 1 side), microseconds since
+ * the previous event on that stream; returns -1 past the end */
+int skg_head_profile_get(int i, const char** name, int* stream_id, float* us);
 int skg_head_forward(const skg_head_weights* weights, const skg_head_batch* batch, int flags, void* workspace,
                      int64_t workspace_bytes, cudaStream_t stream);
 

@@ -31,6 +31,7 @@ _SIGNATURES = {
     "skg_spatial_fc1": (I, [P, P, P, L, I, I, P, P]),
     "skg_node_inputs": (I, [P, I, P, I, I, I, P, P, I, I, I, P, P, I, P]),
     "skg_global_pool": (I, [P, L, I, P, P, P]),
+    "skg_node_prep": (I, [P, I, I, P, P, P, I, I, P, I, I, P, P]),
     "skg_message_aggregate": (I, [P, I, F, P, P, L, P, P, P, I, I, I, I, I, P, P, P, P]),
     "skg_layernorm": (I, [P, L, L, I, P, P, P, P, F, P, P, P]),
     "skg_hadamard_cells": (I, [P, L, P, L, P, L, P, P, L, I, P, L, P]),
@@ -153,8 +154,13 @@ def epilogue_group(n_begin=0, relu=False, bias=None, mul_p=None, row_p=None, mul
     return g
 
 
-def gemm_bf16(A, B, groups, M=None, N=None, K=None, block_n=0):
-    """C = epilogue(A[M,K] @ B[N,K]^T); A, B bf16 CUDA tensors with unit inner stride."""
+_SIGNATURES["skg_gemm_bf16_splitk"] = (I, [P, L, P, L, I, I, I, ctypes.POINTER(EpilogueGroup), I, I, P, L, P])
+_SIGNATURES["skg_gemm_splitk_scratch_bytes"] = (c_int64, [I, I])
+
+
+def gemm_bf16(A, B, groups, M=None, N=None, K=None, block_n=0, scratch=None):
+    """C = epilogue(A[M,K] @ B[N,K]^T); A, B bf16 CUDA tensors with unit inner stride.  ``scratch`` (a zeroed
+    uint8 CUDA tensor of skg_gemm_splitk_scratch_bytes) enables split-K for few-tile shapes."""
     require_cuda(A, B)
     assert A.dtype == torch.bfloat16 and B.dtype == torch.bfloat16 and A.stride(1) == 1 and B.stride(1) == 1
     M = A.shape[0] if M is None else M
@@ -162,8 +168,12 @@ def gemm_bf16(A, B, groups, M=None, N=None, K=None, block_n=0):
     K = A.shape[1] if K is None else K
     arr = (EpilogueGroup * len(groups))(*groups)
     with torch.cuda.device(A.device):
-        call("skg_gemm_bf16", ptr(A), A.stride(0), ptr(B), B.stride(0), M, N, K, arr, len(groups), block_n,
-             stream_ptr(A.device))
+        if scratch is not None:
+            call("skg_gemm_bf16_splitk", ptr(A), A.stride(0), ptr(B), B.stride(0), M, N, K, arr, len(groups), block_n,
+                 ptr(scratch), scratch.numel(), stream_ptr(A.device))
+        else:
+            call("skg_gemm_bf16", ptr(A), A.stride(0), ptr(B), B.stride(0), M, N, K, arr, len(groups), block_n,
+                 stream_ptr(A.device))
 
 
 # ---- whole-path forward (csrc/forward.cu) -------------------------------------------------------
@@ -177,6 +187,7 @@ class HeadWeights(ctypes.Structure):
         ("Wb1", c_void_p), ("bb1", c_void_p), ("Wb2", c_void_p), ("bb2", c_void_p),
         ("Wsp0", c_void_p), ("bsp0", c_void_p), ("Wsp1", c_void_p), ("bsp1", c_void_p), ("Wsp2", c_void_p), ("bsp2", c_void_p),
         ("Wfh", c_void_p), ("bfh", c_void_p), ("Wft", c_void_p), ("bft", c_void_p),
+        ("Wfc", c_void_p), ("bfc", c_void_p),
         ("W_hproj", c_void_p), ("b_hproj", c_void_p), ("W_oproj", c_void_p), ("b_oproj", c_void_p),
         ("Wg1", c_void_p), ("bg1", c_void_p), ("W2cat", c_void_p), ("b2cat", c_void_p),
         ("W3att", c_void_p), ("b3att", c_void_p), ("W3os", c_void_p), ("b3os", c_void_p),
@@ -207,6 +218,8 @@ class HeadPlan(ctypes.Structure):
 
 HEAD_PRECISE_LOGITS = 1
 HEAD_WANT_TAPS = 2
+HEAD_PROFILE = 4
+_SIGNATURES["skg_head_profile_get"] = (I, [I, ctypes.POINTER(c_char_p), ctypes.POINTER(I), ctypes.POINTER(c_float)])
 _SIGNATURES["skg_head_buffer_name"] = (c_char_p, [I])
 _SIGNATURES["skg_head_plan"] = (I, [ctypes.POINTER(HeadWeights), ctypes.POINTER(HeadBatch), I, ctypes.POINTER(HeadPlan)])
 _SIGNATURES["skg_head_forward"] = (I, [ctypes.POINTER(HeadWeights), ctypes.POINTER(HeadBatch), I, P, L, P])

@@ -18,16 +18,16 @@
 namespace skg {
 
 enum Buf : int {
-  B_ENC = 0, B_X, B_Y, B_XKEEP, B_YKEEP, B_CELL2PAIR, B_CELL_HROW, B_CELL_OROW, B_CELL_IMG, B_PAIR2CELL, B_NANFLAG,
-  B_S1, B_S2, B_SP, B_XB, B_X1, B_NODE, B_HIN, B_OIN, B_HN32, B_HN16, B_ON32, B_ON16, B_HPROJ, B_OPROJ, B_GFEAT, B_G32,
+  B_SPLITK0 = 0, B_SPLITK1, B_ENC, B_X, B_Y, B_XKEEP, B_YKEEP, B_CELL2PAIR, B_CELL_HROW, B_CELL_OROW, B_CELL_IMG, B_PAIR2CELL, B_NANFLAG,
+  B_S1, B_S2, B_SP, B_XB, B_X1, B_BOX2HUM, B_OIN, B_HN32, B_HN16, B_ON32, B_ON16, B_HPROJ, B_OPROJ, B_GFEAT, B_G32,
   B_GT, B_HATT, B_SRAW, B_HOS, B_HSO, B_HG, B_DOTPART, B_Z, B_ADJ, B_PRE, B_ENC16, B_ENC32, B_U2H, B_U2O, B_H2, B_FEAT,
   B_TMP, B_LOGITS, B_COUNT
 };
 static_assert(B_COUNT <= SKG_HEAD_NUM_BUFFERS, "raise SKG_HEAD_NUM_BUFFERS");
 
 static const char* kBufNames[B_COUNT] = {
-  "enc", "x", "y", "x_keep", "y_keep", "cell2pair", "cell_hrow", "cell_orow", "cell_img", "pair2cell", "nan_flag",
-  "s1", "s2", "sp", "xb", "x1", "node16", "h_in", "o_in", "hN32", "hN16", "oN32", "oN16", "hproj", "oproj", "gfeat", "g32",
+  "splitk_main", "splitk_side", "enc", "x", "y", "x_keep", "y_keep", "cell2pair", "cell_hrow", "cell_orow", "cell_img", "pair2cell", "nan_flag",
+  "s1", "s2", "sp", "xb", "x1", "box2hum", "o_in", "hN32", "hN16", "oN32", "oN16", "hproj", "oproj", "gfeat", "g32",
   "Gt", "H_att", "S_raw", "H_os", "H_so", "H_g", "dot_part", "Z", "adjacency", "pre", "enc16", "enc32", "U2h", "U2o", "H2", "feat",
   "tmp", "logits"};
 
@@ -47,12 +47,15 @@ static int make_plan(const skg_head_weights& w, const skg_head_batch& b, int fla
   memset(p, 0, sizeof(*p));
   p->num_buffers = B_COUNT;
   auto set = [&](int i, int64_t rows, int64_t cols, int es) { p->rows[i] = rows; p->cols[i] = cols; p->elem_size[i] = es; };
+  // split-K scratch of the two streams: FIRST in the layout so their position does not depend on the batch shape;
+  // must be zero before the first call on a workspace and are left zero by every call (skg_gemm_bf16_splitk)
+  const int64_t sk_elems = skg_gemm_splitk_scratch_bytes(0, 0) / 4;
+  set(B_SPLITK0, 1, sk_elems, 4); set(B_SPLITK1, 1, sk_elems, 4);
   set(B_ENC, C, 46, 4); set(B_X, C, 1, 8); set(B_Y, C, 1, 8); set(B_XKEEP, P, 1, 8); set(B_YKEEP, P, 1, 8);
   set(B_CELL2PAIR, C, 1, 4); set(B_CELL_HROW, C, 1, 4); set(B_CELL_OROW, C, 1, 4); set(B_CELL_IMG, C, 1, 4);
   set(B_PAIR2CELL, P, 1, 4); set(B_NANFLAG, B > 0 ? B : 1, 1, 4);
   set(B_S1, C, 128, 2); set(B_S2, C, 256, 2); set(B_SP, C, R, 2);
-  set(B_XB, NB, w.K0, 2); set(B_X1, NB, w.E, 2); set(B_NODE, NB, w.E, 2);
-  set(B_HIN, NH, w.fc_k, 2); set(B_OIN, NB, w.fc_k, 2);
+  set(B_XB, NB, w.K0, 2); set(B_X1, NB, w.E, 2); set(B_BOX2HUM, NB, 1, 4); set(B_OIN, NB, w.fc_k, 2);
   set(B_HN32, NH, R, 4); set(B_HN16, NH, R, 2); set(B_ON32, NB, R, 4); set(B_ON16, NB, R, 2);
   set(B_HPROJ, NH, 2 * R, 4); set(B_OPROJ, NB, 2 * R, 4);
   set(B_GFEAT, B, w.Kg, 2); set(B_G32, B, w.Cg, 4); set(B_GT, B, R, 4);
@@ -70,11 +73,13 @@ static int make_plan(const skg_head_weights& w, const skg_head_batch& b, int fla
   return SKG_OK;
 }
 
-// library-owned side stream + fork/join events (per host thread and device)
+// library-owned side streams + an event pool for fork / join (per host thread and device)
 struct SideStream {
+  static constexpr int kStreams = 3, kEvents = 16;
   int dev = -1;
-  cudaStream_t s = nullptr;
-  cudaEvent_t fork[2] = {nullptr, nullptr}, join[2] = {nullptr, nullptr};
+  cudaStream_t s[kStreams] = {};
+  cudaEvent_t ev[kEvents] = {};
+  int next = 0;
 };
 static thread_local SideStream g_side;
 
@@ -82,21 +87,49 @@ static int get_side(SideStream** out) {
   int dev = 0;
   SKG_CUDA(cudaGetDevice(&dev));
   if (g_side.dev != dev) {
-    if (g_side.s) {   // device changed on this thread: drop the old objects (rare)
-      cudaStreamDestroy(g_side.s);
-      for (int i = 0; i < 2; ++i) { cudaEventDestroy(g_side.fork[i]); cudaEventDestroy(g_side.join[i]); }
+    if (g_side.dev >= 0) {   // device changed on this thread: drop the old objects (rare)
+      for (auto& x : g_side.s) if (x) cudaStreamDestroy(x);
+      for (auto& e : g_side.ev) if (e) cudaEventDestroy(e);
       g_side = SideStream();
     }
-    SKG_CUDA(cudaStreamCreateWithFlags(&g_side.s, cudaStreamNonBlocking));
-    for (int i = 0; i < 2; ++i) {
-      SKG_CUDA(cudaEventCreateWithFlags(&g_side.fork[i], cudaEventDisableTiming));
-      SKG_CUDA(cudaEventCreateWithFlags(&g_side.join[i], cudaEventDisableTiming));
-    }
+    for (auto& x : g_side.s) SKG_CUDA(cudaStreamCreateWithFlags(&x, cudaStreamNonBlocking));
+    for (auto& e : g_side.ev) SKG_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
     g_side.dev = dev;
   }
+  g_side.next = 0;
   *out = &g_side;
   return SKG_OK;
 }
+
+// `to` waits for everything enqueued on `from` so far
+static int stream_dep(SideStream* sd, cudaStream_t from, cudaStream_t to) {
+  SKG_REQUIRE(sd->next < SideStream::kEvents, "event pool exhausted");
+  cudaEvent_t e = sd->ev[sd->next++];
+  SKG_CUDA(cudaEventRecord(e, from));
+  SKG_CUDA(cudaStreamWaitEvent(to, e, 0));
+  return SKG_OK;
+}
+
+// optional per-launch timing (SKG_HEAD_PROFILE): one event after every launch, read back after a stream sync
+struct Prof {
+  static constexpr int kMax = 96;
+  bool on = false;
+  int n = 0;
+  cudaEvent_t ev[kMax] = {};
+  const char* name[kMax] = {};
+  int sid[kMax] = {};
+  float us[kMax] = {};
+};
+static thread_local Prof g_prof;
+
+static void prof_mark(const char* name, int sid, cudaStream_t s) {
+  Prof& p = g_prof;
+  if (!p.on || p.n >= Prof::kMax) return;
+  if (!p.ev[p.n]) cudaEventCreate(&p.ev[p.n]);
+  cudaEventRecord(p.ev[p.n], s);
+  p.name[p.n] = name; p.sid[p.n] = sid; p.n++;
+}
+#define MARK(name, s) prof_mark(name, (s) == st ? 0 : (s) == sa ? 1 : (s) == sb ? 2 : 3, (s))
 
 static skg_epilogue_group group0() {
   skg_epilogue_group g;
@@ -148,132 +181,176 @@ extern "C" int skg_head_forward(const skg_head_weights* wp, const skg_head_batch
   auto I64 = [&](int i) { return reinterpret_cast<int64_t*>(base + plan.offset[i]); };
   auto HR = [&](int i, int64_t row) { return reinterpret_cast<void*>(base + plan.offset[i] + row * plan.cols[i] * 2); };
   auto FR = [&](int i, int64_t row) { return reinterpret_cast<float*>(base + plan.offset[i] + row * plan.cols[i] * 4); };
+  const int64_t sk_bytes = plan.cols[B_SPLITK0] * 4;
   SideStream* side = nullptr;
   SKG_TRY(get_side(&side));
-  cudaStream_t ss = side->s;
+  cudaStream_t sa = side->s[0], sb = side->s[1], sc = side->s[2];
+  skg_epilogue_group g;
 
-  // ---------------- fork: node-row chain on the side stream
-  SKG_CUDA(cudaEventRecord(side->fork[0], st));
-  SKG_CUDA(cudaStreamWaitEvent(ss, side->fork[0], 0));
+  g_prof.on = (flags & SKG_HEAD_PROFILE) != 0; g_prof.n = 0;
+  MARK("start", st);
+  // ================= fork: node-row chain on sa, global-feature chain on sb
+  SKG_TRY(stream_dep(side, st, sa));
+  SKG_TRY(stream_dep(side, st, sb));
+  MARK("start", sa); MARK("start", sb);
+  // ---- sa: box head (head.py:635-641, 812); its second layer writes straight into the fc input rows
+  SKG_TRY(skg_node_prep(w.ent, w.ent_dim, w.ent_tot, b.box_off, b.n_h, b.hum_off, B, NB, H(B_OIN), w.fc_k, E, I32(B_BOX2HUM), sa));
+  MARK("node_prep", sa);
+  SKG_TRY(skg_cast_pad_bf16(b.box_features, w.pool_k, nullptr, 0, NB, w.pool_k, H(B_XB), w.K0, w.K0, sa));
+  MARK("cast box_features", sa);
+  g = group0(); g.flags = SKG_EPI_RELU; g.bias = w.bb1; g.out_bf16 = H(B_X1); g.ld_ob = E;
+  SKG_TRY(skg_gemm_bf16_splitk(H(B_XB), w.K0, w.Wb1, w.K0, NB, E, w.K0, &g, 1, 0, H(B_SPLITK1), sk_bytes, sa));
+  MARK("gemm box_head.1", sa);
+  g = group0(); g.flags = SKG_EPI_RELU; g.bias = w.bb2; g.out_bf16 = H(B_OIN); g.ld_ob = w.fc_k;
+  SKG_TRY(skg_gemm_bf16(H(B_X1), E, w.Wb2, E, NB, E, E, &g, 1, 0, sa));
+  MARK("gemm box_head.3", sa);
+  // ---- sa: fc_head and fc_tail as ONE GEMM over all boxes with stacked weights (head.py:875-885): only n_h (resp. n)
+  //      rows of the reference's [N2, 1074] inputs are distinct; human rows are compacted through box2hum
   {
-    // box head (head.py:635-641, 812)
-    SKG_TRY(skg_cast_pad_bf16(b.box_features, w.pool_k, nullptr, 0, NB, w.pool_k, H(B_XB), w.K0, w.K0, ss));
-    skg_epilogue_group g = group0();
-    g.flags = SKG_EPI_RELU; g.bias = w.bb1; g.out_bf16 = H(B_X1); g.ld_ob = E;
-    SKG_TRY(skg_gemm_bf16(H(B_XB), w.K0, w.Wb1, w.K0, NB, E, w.K0, &g, 1, 0, ss));
-    g = group0(); g.flags = SKG_EPI_RELU; g.bias = w.bb2; g.out_bf16 = H(B_NODE); g.ld_ob = E;
-    SKG_TRY(skg_gemm_bf16(H(B_X1), E, w.Wb2, E, NB, E, E, &g, 1, 0, ss));
-    // fc_head / fc_tail on the n_h (resp. n) DISTINCT rows (head.py:875-885)
-    SKG_TRY(skg_node_inputs(H(B_NODE), E, w.ent, w.ent_dim, w.ent_tot, w.human_idx, b.box_off, b.hum_off, B, NB, NH, H(B_HIN),
-                            H(B_OIN), w.fc_k, ss));
-    g = group0(); g.flags = SKG_EPI_RELU; g.bias = w.bfh; g.out_f32 = F(B_HN32); g.ld_of = R; g.out_bf16 = H(B_HN16); g.ld_ob = R;
-    SKG_TRY(skg_gemm_bf16(H(B_HIN), w.fc_k, w.Wfh, w.fc_k, NH, R, w.fc_k, &g, 1, 0, ss));
-    g = group0(); g.flags = SKG_EPI_RELU; g.bias = w.bft; g.out_f32 = F(B_ON32); g.ld_of = R; g.out_bf16 = H(B_ON16); g.ld_ob = R;
-    SKG_TRY(skg_gemm_bf16(H(B_OIN), w.fc_k, w.Wft, w.fc_k, NB, R, w.fc_k, &g, 1, 0, ss));
-    // per-node halves of the MBF appearance terms: humans -> [U_h | V_so], boxes -> [U_o | V_os]
-    g = group0(); g.bias = w.b_hproj; g.out_f32 = F(B_HPROJ); g.ld_of = 2 * R;
-    SKG_TRY(skg_gemm_bf16(H(B_HN16), R, w.W_hproj, R, NH, 2 * R, R, &g, 1, 0, ss));
-    g = group0(); g.bias = w.b_oproj; g.out_f32 = F(B_OPROJ); g.ld_of = 2 * R;
-    SKG_TRY(skg_gemm_bf16(H(B_ON16), R, w.W_oproj, R, NB, 2 * R, R, &g, 1, 0, ss));
-    // global feature term of attention_head_g (head.py:811, 971)
-    if (w.Kg == w.Cg) {
-      SKG_TRY(skg_global_pool(b.features3, (int64_t)B * w.Cg, b.feat_hw, H(B_GFEAT), nullptr, ss));
-    } else {
-      SKG_TRY(skg_global_pool(b.features3, (int64_t)B * w.Cg, b.feat_hw, nullptr, F(B_G32), ss));
-      SKG_TRY(skg_cast_pad_bf16(F(B_G32), w.Cg, nullptr, 0, B, w.Cg, H(B_GFEAT), w.Kg, w.Kg, ss));
-    }
-    g = group0(); g.bias = w.bg1; g.out_f32 = F(B_GT); g.ld_of = R;
-    SKG_TRY(skg_gemm_bf16(H(B_GFEAT), w.Kg, w.Wg1, w.Kg, B, R, w.Kg, &g, 1, 0, ss));
+    skg_epilogue_group gg[2];
+    gg[0] = group0(); gg[0].flags = SKG_EPI_RELU; gg[0].bias = w.bfc; gg[0].out_f32 = F(B_HN32); gg[0].ld_of = R;
+    gg[0].out_bf16 = H(B_HN16); gg[0].ld_ob = R; gg[0].out_row = I32(B_BOX2HUM);
+    gg[1] = group0(); gg[1].n_begin = R; gg[1].flags = SKG_EPI_RELU; gg[1].bias = w.bfc; gg[1].out_f32 = F(B_ON32); gg[1].ld_of = R;
+    gg[1].out_bf16 = H(B_ON16); gg[1].ld_ob = R;
+    SKG_TRY(skg_gemm_bf16(H(B_OIN), w.fc_k, w.Wfc, w.fc_k, NB, 2 * R, w.fc_k, gg, 2, 0, sa));
+    MARK("gemm fc_head|fc_tail", sa);
   }
-  SKG_CUDA(cudaEventRecord(side->join[0], ss));
+  // ---- per-node halves of the MBF appearance terms: humans -> [U_h | V_so] (sc), boxes -> [U_o | V_os] (sa)
+  SKG_TRY(stream_dep(side, sa, sc));
+  MARK("start", sc);
+  g = group0(); g.bias = w.b_hproj; g.out_f32 = F(B_HPROJ); g.ld_of = 2 * R;
+  SKG_TRY(skg_gemm_bf16(H(B_HN16), R, w.W_hproj, R, NH, 2 * R, R, &g, 1, 0, sc));
+  MARK("gemm hproj", sc);
+  g = group0(); g.bias = w.b_oproj; g.out_f32 = F(B_OPROJ); g.ld_of = 2 * R;
+  SKG_TRY(skg_gemm_bf16(H(B_ON16), R, w.W_oproj, R, NB, 2 * R, R, &g, 1, 0, sa));
+  MARK("gemm oproj", sa);
+  // ---- sb: global feature term of attention_head_g (head.py:811, 971)
+  if (w.Kg == w.Cg) {
+    SKG_TRY(skg_global_pool(b.features3, (int64_t)B * w.Cg, b.feat_hw, H(B_GFEAT), nullptr, sb));
+  } else {
+    SKG_TRY(skg_global_pool(b.features3, (int64_t)B * w.Cg, b.feat_hw, nullptr, F(B_G32), sb));
+    SKG_TRY(skg_cast_pad_bf16(F(B_G32), w.Cg, nullptr, 0, B, w.Cg, H(B_GFEAT), w.Kg, w.Kg, sb));
+  }
+  MARK("global_pool", sb);
+  g = group0(); g.bias = w.bg1; g.out_f32 = F(B_GT); g.ld_of = R;
+  SKG_TRY(skg_gemm_bf16(H(B_GFEAT), w.Kg, w.Wg1, w.Kg, B, R, w.Kg, &g, 1, 0, sb));
+  MARK("gemm attention_head_g.fc_1", sb);
 
-  // ---------------- main: pairs + spatial head (head.py:847-868, 662-669, 888)
+  // ================= main: pairs + spatial head (head.py:847-868, 662-669, 888)
   SKG_TRY(skg_pairs_spatial_encode(b.boxes, b.box_off, b.n_h, b.cell_off, b.pair_off, b.hum_off, b.hw, B, C, 23, 1e-10f, 1,
                                    F(B_ENC), I64(B_X), I64(B_Y), I64(B_XKEEP), I64(B_YKEEP), I32(B_CELL2PAIR), I32(B_CELL_HROW),
                                    I32(B_CELL_OROW), I32(B_CELL_IMG), I32(B_PAIR2CELL), I32(B_NANFLAG), st));
+  MARK("pairs_spatial_encode", st);
   SKG_TRY(skg_spatial_fc1(F(B_ENC), w.Wsp0, w.bsp0, C, 46, 128, H(B_S1), st));
+  MARK("spatial_fc1", st);
+  g = group0(); g.flags = SKG_EPI_RELU; g.bias = w.bsp1; g.out_bf16 = H(B_S2); g.ld_ob = 256;
+  SKG_TRY(skg_gemm_bf16(H(B_S1), 128, w.Wsp1, 128, (int)C, 256, 128, &g, 1, 0, st));
+  MARK("gemm spatial_head.2", st);
+  g = group0(); g.flags = SKG_EPI_RELU; g.bias = w.bsp2; g.out_bf16 = H(B_SP); g.ld_ob = R;
+  SKG_TRY(skg_gemm_bf16(H(B_S2), 256, w.Wsp2, 256, (int)C, R, 256, &g, 1, 0, st));
+  MARK("gemm spatial_head.4", st);
+  // ================= join, then the fused fc_2 GEMM of the four MBFs that read the spatial features (N = 4R)
+  SKG_TRY(stream_dep(side, sa, st));
+  SKG_TRY(stream_dep(side, sb, st));
+  SKG_TRY(stream_dep(side, sc, st));
   {
-    skg_epilogue_group g = group0();
-    g.flags = SKG_EPI_RELU; g.bias = w.bsp1; g.out_bf16 = H(B_S2); g.ld_ob = 256;
-    SKG_TRY(skg_gemm_bf16(H(B_S1), 128, w.Wsp1, 128, (int)C, 256, 128, &g, 1, 0, st));
-    g = group0(); g.flags = SKG_EPI_RELU; g.bias = w.bsp2; g.out_bf16 = H(B_SP); g.ld_ob = R;
-    SKG_TRY(skg_gemm_bf16(H(B_S2), 256, w.Wsp2, 256, (int)C, R, 256, &g, 1, 0, st));
+    skg_epilogue_group gq[4];
+    for (int i = 0; i < 4; ++i) { gq[i] = group0(); gq[i].n_begin = i * R; gq[i].flags = SKG_EPI_RELU; gq[i].bias = w.b2cat; gq[i].ld_ob = R; }
+    gq[0].mul_p = F(B_HPROJ); gq[0].row_p = I32(B_CELL_HROW); gq[0].ld_p = 2 * R;
+    gq[0].mul_q = F(B_OPROJ); gq[0].row_q = I32(B_CELL_OROW); gq[0].ld_q = 2 * R;
+    gq[0].out_bf16 = H(B_HATT); gq[0].raw_bf16 = H(B_SRAW); gq[0].ld_raw = R;
+    gq[1].mul_p = F(B_OPROJ) + R; gq[1].row_p = I32(B_CELL_OROW); gq[1].ld_p = 2 * R; gq[1].out_bf16 = H(B_HOS);
+    gq[2].mul_p = F(B_HPROJ) + R; gq[2].row_p = I32(B_CELL_HROW); gq[2].ld_p = 2 * R; gq[2].out_bf16 = H(B_HSO);
+    gq[3].mul_p = F(B_GT); gq[3].row_p = I32(B_CELL_IMG); gq[3].ld_p = R; gq[3].out_bf16 = H(B_HG);
+    SKG_TRY(skg_gemm_bf16(H(B_SP), R, w.W2cat, R, (int)C, 4 * R, R, gq, 4, 0, st));
+    MARK("gemm fused fc_2 x4", st);
   }
-  SKG_CUDA(cudaStreamWaitEvent(st, side->join[0], 0));
-
-  // ---------------- fused fc_2 GEMM of the four MBFs that read the spatial features (N = 4R)
-  {
-    skg_epilogue_group g[4];
-    for (int i = 0; i < 4; ++i) { g[i] = group0(); g[i].n_begin = i * R; g[i].flags = SKG_EPI_RELU; g[i].bias = w.b2cat; g[i].ld_ob = R; }
-    g[0].mul_p = F(B_HPROJ); g[0].row_p = I32(B_CELL_HROW); g[0].ld_p = 2 * R;
-    g[0].mul_q = F(B_OPROJ); g[0].row_q = I32(B_CELL_OROW); g[0].ld_q = 2 * R;
-    g[0].out_bf16 = H(B_HATT); g[0].raw_bf16 = H(B_SRAW); g[0].ld_raw = R;
-    g[1].mul_p = F(B_OPROJ) + R; g[1].row_p = I32(B_CELL_OROW); g[1].ld_p = 2 * R; g[1].out_bf16 = H(B_HOS);
-    g[2].mul_p = F(B_HPROJ) + R; g[2].row_p = I32(B_CELL_HROW); g[2].ld_p = 2 * R; g[2].out_bf16 = H(B_HSO);
-    g[3].mul_p = F(B_GT); g[3].row_p = I32(B_CELL_IMG); g[3].ld_p = R; g[3].out_bf16 = H(B_HG);
-    SKG_TRY(skg_gemm_bf16(H(B_SP), R, w.W2cat, R, (int)C, 4 * R, R, g, 4, 0, st));
-  }
-  // ---------------- fork: attention_head_g fc_3 on the valid pairs (head.py:971) does not depend on the messages
+  // ================= fork sb: attention_head_g fc_3 on the valid pairs (head.py:971) does not depend on the messages
   const int feat_ld = (int)plan.cols[B_FEAT];
-  SKG_CUDA(cudaEventRecord(side->fork[1], st));
-  SKG_CUDA(cudaStreamWaitEvent(ss, side->fork[1], 0));
-  {
-    skg_epilogue_group g = group0();
-    g.flags = SKG_EPI_RELU; g.bias = w.b3g; g.out_bf16 = reinterpret_cast<__nv_bfloat16*>(H(B_FEAT)) + R; g.ld_ob = feat_ld;
-    g.out_row = I32(B_CELL2PAIR);
-    if (precise) { g.lo_bf16 = reinterpret_cast<__nv_bfloat16*>(H(B_FEAT)) + 3 * R; g.ld_lo = feat_ld; }
-    SKG_TRY(skg_gemm_bf16(H(B_HG), R, w.W3g, R, (int)C, R, R, &g, 1, 0, ss));
-  }
-  SKG_CUDA(cudaEventRecord(side->join[1], ss));
-  // ---------------- attention weights -> adjacency (head.py:896-897); the two iterations of head.py:892 are identical
+  SKG_TRY(stream_dep(side, st, sb));
+  MARK("start", sb);
+  g = group0(); g.flags = SKG_EPI_RELU; g.bias = w.b3g; g.out_bf16 = reinterpret_cast<__nv_bfloat16*>(H(B_FEAT)) + R; g.ld_ob = feat_ld;
+  g.out_row = I32(B_CELL2PAIR);
+  if (precise) { g.lo_bf16 = reinterpret_cast<__nv_bfloat16*>(H(B_FEAT)) + 3 * R; g.ld_lo = feat_ld; }
+  SKG_TRY(skg_gemm_bf16(H(B_HG), R, w.W3g, R, (int)C, R, R, &g, 1, 0, sb));
+  MARK("gemm attention_head_g.fc_3", sb);
+  // ---- attention weights -> adjacency (head.py:896-897); the two iterations of head.py:892 are identical
   const int nt = 4 * (R / 256);
-  {
-    skg_epilogue_group g = group0();
-    g.flags = SKG_EPI_RELU; g.bias = w.b3att; g.dot_w = w.w_adj; g.dot_out = F(B_DOTPART); g.ld_dot = nt;
-    SKG_TRY(skg_gemm_bf16(H(B_HATT), R, w.W3att, R, (int)C, R, R, &g, 1, 256, st));
-  }
-  // ---------------- messages (head.py:907-925)
+  g = group0(); g.flags = SKG_EPI_RELU; g.bias = w.b3att; g.dot_w = w.w_adj; g.dot_out = F(B_DOTPART); g.ld_dot = nt;
+  SKG_TRY(skg_gemm_bf16(H(B_HATT), R, w.W3att, R, (int)C, R, R, &g, 1, 256, st));
+  MARK("gemm attention_head.fc_3 + adjacency dot", st);
+  // ---- messages (head.py:907-925)
   SKG_TRY(skg_message_aggregate(F(B_DOTPART), nt, w.b_adj, H(B_HOS), H(B_HSO), R, b.box_off, b.hum_off, b.cell_off, B, NB, NH,
                                 b.max_boxes_per_image, R, HR(B_Z, 0), HR(B_Z, NH), F(B_ADJ), st));
-  {
-    skg_epilogue_group g = group0();
-    g.flags = SKG_EPI_RELU; g.bias = w.b3os; g.residual = F(B_HN32); g.ld_r = R; g.out_f32 = FR(B_PRE, 0); g.ld_of = R;
-    SKG_TRY(skg_gemm_bf16(HR(B_Z, 0), R, w.W3os, R, NH, R, R, &g, 1, 0, st));
-    g = group0(); g.flags = SKG_EPI_RELU; g.bias = w.b3so; g.residual = F(B_ON32); g.ld_r = R; g.out_f32 = FR(B_PRE, NH); g.ld_of = R;
-    SKG_TRY(skg_gemm_bf16(HR(B_Z, NH), R, w.W3so, R, NB, R, R, &g, 1, 0, st));
-  }
+  MARK("message_aggregate", st);
+  SKG_TRY(stream_dep(side, st, sc));
+  MARK("start", sc);
+  g = group0(); g.flags = SKG_EPI_RELU; g.bias = w.b3os; g.residual = F(B_HN32); g.ld_r = R; g.out_f32 = FR(B_PRE, 0); g.ld_of = R;
+  SKG_TRY(skg_gemm_bf16(HR(B_Z, 0), R, w.W3os, R, NH, R, R, &g, 1, 0, sc));
+  MARK("gemm obj_to_sub.fc_3", sc);
+  g = group0(); g.flags = SKG_EPI_RELU; g.bias = w.b3so; g.residual = F(B_ON32); g.ld_r = R; g.out_f32 = FR(B_PRE, NH); g.ld_of = R;
+  SKG_TRY(skg_gemm_bf16(HR(B_Z, NH), R, w.W3so, R, NB, R, R, &g, 1, 0, st));
+  MARK("gemm sub_to_obj.fc_3", st);
+  SKG_TRY(stream_dep(side, sc, st));
   SKG_TRY(skg_layernorm(F(B_PRE), NH + NB, NH, R, w.ln_h_w, w.ln_h_b, w.ln_o_w, w.ln_o_b, w.ln_eps,
                         (flags & SKG_HEAD_WANT_TAPS) ? F(B_ENC32) : nullptr, H(B_ENC16), st));
-  // ---------------- final attention head on the valid pairs (head.py:966-970)
-  {
-    skg_epilogue_group g = group0();
-    g.out_f32 = F(B_U2H); g.ld_of = R;
-    SKG_TRY(skg_gemm_bf16(HR(B_ENC16, 0), R, w.W_hproj, R, NH, R, R, &g, 1, 0, st));
-    g = group0(); g.bias = w.b_oproj; g.out_f32 = F(B_U2O); g.ld_of = R;
-    SKG_TRY(skg_gemm_bf16(HR(B_ENC16, NH), R, w.W_oproj, R, NB, R, R, &g, 1, 0, st));
-  }
+  MARK("layernorm", st);
+  // ---- final attention head on the valid pairs (head.py:966-970)
+  SKG_TRY(stream_dep(side, st, sc));
+  MARK("start", sc);
+  g = group0(); g.out_f32 = F(B_U2H); g.ld_of = R;
+  SKG_TRY(skg_gemm_bf16(HR(B_ENC16, 0), R, w.W_hproj, R, NH, R, R, &g, 1, 0, sc));
+  MARK("gemm U2h", sc);
+  g = group0(); g.bias = w.b_oproj; g.out_f32 = F(B_U2O); g.ld_of = R;
+  SKG_TRY(skg_gemm_bf16(HR(B_ENC16, NH), R, w.W_oproj, R, NB, R, R, &g, 1, 0, st));
+  MARK("gemm U2o", st);
+  SKG_TRY(stream_dep(side, sc, st));
   SKG_TRY(skg_hadamard_cells(H(B_SRAW), R, F(B_U2H), R, F(B_U2O), R, I32(B_CELL_HROW), I32(B_CELL_OROW), C, R, H(B_H2), R, st));
-  {
-    skg_epilogue_group g = group0();
-    g.flags = SKG_EPI_RELU; g.bias = w.b3att; g.out_bf16 = H(B_FEAT); g.ld_ob = feat_ld; g.out_row = I32(B_CELL2PAIR);
-    if (precise) { g.lo_bf16 = reinterpret_cast<__nv_bfloat16*>(H(B_FEAT)) + 2 * R; g.ld_lo = feat_ld; }
-    SKG_TRY(skg_gemm_bf16(H(B_H2), R, w.W3att, R, (int)C, R, R, &g, 1, 0, st));
-  }
-  SKG_CUDA(cudaStreamWaitEvent(st, side->join[1], 0));
-  // ---------------- predictor + suppressor (head.py:410-411) as one N = num_cls + 1 GEMM
+  MARK("hadamard_cells", st);
+  g = group0(); g.flags = SKG_EPI_RELU; g.bias = w.b3att; g.out_bf16 = H(B_FEAT); g.ld_ob = feat_ld; g.out_row = I32(B_CELL2PAIR);
+  if (precise) { g.lo_bf16 = reinterpret_cast<__nv_bfloat16*>(H(B_FEAT)) + 2 * R; g.ld_lo = feat_ld; }
+  SKG_TRY(skg_gemm_bf16(H(B_H2), R, w.W3att, R, (int)C, R, R, &g, 1, 0, st));
+  MARK("gemm attention_head.fc_3 (pairs)", st);
+  SKG_TRY(stream_dep(side, sb, st));
+  // ================= predictor + suppressor (head.py:410-411) as one N = num_cls + 1 GEMM
   if (P > 0) {
-    skg_epilogue_group g = group0();
+    g = group0();
     if (precise) {   // split bf16: logits = [hi | lo] x [W_hi | W_hi]^T + hi x W_lo^T   (3 bf16 passes ~ fp32 product)
       g.bias = w.bpred; g.out_f32 = F(B_TMP); g.ld_of = w.n_logit_pad;
       SKG_TRY(skg_gemm_bf16(H(B_FEAT), feat_ld, w.Wpred_hh, 4 * R, (int)P, w.n_logit, 4 * R, &g, 1, 0, st));
+      MARK("gemm predictor [hi|lo]x[Whi|Whi]", st);
       g = group0(); g.residual = F(B_TMP); g.ld_r = w.n_logit_pad; g.out_f32 = F(B_LOGITS); g.ld_of = w.n_logit;
       SKG_TRY(skg_gemm_bf16(H(B_FEAT), feat_ld, w.Wpred_lo, 2 * R, (int)P, w.n_logit, 2 * R, &g, 1, 0, st));
+      MARK("gemm predictor hi x Wlo", st);
     } else {
       g.bias = w.bpred; g.out_f32 = F(B_LOGITS); g.ld_of = w.n_logit;
       SKG_TRY(skg_gemm_bf16(H(B_FEAT), feat_ld, w.Wpred, 2 * R, (int)P, w.n_logit, 2 * R, &g, 1, 0, st));
+      MARK("gemm predictor", st);
     }
   }
+  if (g_prof.on) {   // profiling mode synchronises: per-launch time = gap to the previous event on the same stream
+    SKG_CUDA(cudaStreamSynchronize(st));
+    SKG_CUDA(cudaStreamSynchronize(sa)); SKG_CUDA(cudaStreamSynchronize(sb)); SKG_CUDA(cudaStreamSynchronize(sc));
+    Prof& p = g_prof;
+    int last[4] = {-1, -1, -1, -1};
+    for (int i = 0; i < p.n; ++i) {
+      float ms = 0.f;
+      if (last[p.sid[i]] >= 0) cudaEventElapsedTime(&ms, p.ev[last[p.sid[i]]], p.ev[i]);
+      p.us[i] = ms * 1e3f;
+      last[p.sid[i]] = i;
+    }
+    p.on = false;
+  }
   return SKG_OK;
+}
+
+extern "C" int skg_head_profile_get(int i, const char** name, int* stream_id, float* us) {
+  const Prof& p = g_prof;
+  if (i < 0 || i >= p.n) return -1;
+  if (name) *name = p.name[i];
+  if (stream_id) *stream_id = p.sid[i];
+  if (us) *us = p.us[i];
+  return 0;
 }
 
 extern "C" int64_t skg_post_count_host(const int32_t* verb_len, int num_obj_cls, const int64_t* labels, const float* scores,

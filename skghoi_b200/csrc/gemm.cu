@@ -134,7 +134,7 @@ __device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
 // ---------------------------------------------------------------------------------------------
 template <int BN>
 struct GemmSmem {
-  static constexpr int kStages = (BN == 256) ? 4 : 6;
+  static constexpr int kStages = (BN == 256) ? 4 : (BN == 128 ? 6 : 7);
   static constexpr int kABytes = BM * BK * 2;
   static constexpr int kBBytes = BN * BK * 2;
   static constexpr int kStageBytes = kABytes + kBBytes;
@@ -142,10 +142,10 @@ struct GemmSmem {
   static constexpr int kTotal = kStages * kStageBytes + 1024 /*align slack*/ + 256 /*barriers*/ + kStagingBytes;
 };
 
-template <int BN, uint32_t FEAT>
+template <int BN, uint32_t FEAT, bool SK>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, int M, int N, int K,
-                 const __grid_constant__ EpiGroups epi) {
+                 const __grid_constant__ EpiGroups epi, int splits, float* __restrict__ sk_ws, int* __restrict__ sk_cnt) {
   using S = GemmSmem<BN>;
   constexpr int kStages = S::kStages;
   extern __shared__ uint8_t smem_raw[];
@@ -157,11 +157,15 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   uint64_t* tmem_empty = bars + 2 * kStages + 2; // [2]        epilogue -> MMA
   uint32_t* tmem_base_slot = reinterpret_cast<uint32_t*>(bars + 2 * kStages + 4);
   float* staging = reinterpret_cast<float*>(smem + kStages * S::kStageBytes + 256);
+  volatile int* sk_flag = reinterpret_cast<volatile int*>(tmem_base_slot + 1);   // split-K: 'this CTA owns the epilogue'
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int num_m = (M + BM - 1) / BM, num_n = (N + BN - 1) / BN;
   const int num_tiles = num_m * num_n;
   const int num_k = (K + BK - 1) / BK;
+  // split-K: work item = (tile, split); the splits of one tile sit on adjacent CTAs and reduce through fp32
+  // red.global.add into a zeroed scratch tile; the last split to arrive runs the epilogue and re-zeroes it.
+  const int num_items = num_tiles * splits;
 
   if (warp == 0 && lane == 0) {
     asm volatile("prefetch.tensormap [%0];\n" ::"l"(&tmA) : "memory");
@@ -185,9 +189,11 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     // ===================== TMA producer =====================
     if (lane == 0) {
       int stage = 0; uint32_t phase = 0;
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      for (int item = blockIdx.x; item < num_items; item += gridDim.x) {
+        const int tile = item / splits, split = item - tile * splits;
         const int m0 = (tile / num_n) * BM, n0 = (tile % num_n) * BN;
-        for (int kb = 0; kb < num_k; ++kb) {
+        const int kb0 = (int)((long long)split * num_k / splits), kb1 = (int)((long long)(split + 1) * num_k / splits);
+        for (int kb = kb0; kb < kb1; ++kb) {
           mbar_wait(empty_bar + stage, phase ^ 1);
           uint8_t* sa = smem + stage * S::kStageBytes;
           uint8_t* sb = sa + S::kABytes;
@@ -204,11 +210,13 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       constexpr uint32_t idesc = make_idesc(BM, BN);
       int stage = 0; uint32_t phase = 0;
       int acc = 0; uint32_t acc_phase = 0;
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      for (int item = blockIdx.x; item < num_items; item += gridDim.x) {
+        const int split = item % splits;
+        const int kb0 = (int)((long long)split * num_k / splits), kb1 = (int)((long long)(split + 1) * num_k / splits);
         mbar_wait(tmem_empty + acc, acc_phase ^ 1);      // epilogue has drained this accumulator
         tcgen05_fence_after();
         const uint32_t d_tmem = tmem_base + (uint32_t)(acc * BN);
-        for (int kb = 0; kb < num_k; ++kb) {
+        for (int kb = kb0; kb < kb1; ++kb) {
           mbar_wait(full_bar + stage, phase);
           tcgen05_fence_after();
           const uint32_t sa = smem_u32(smem + stage * S::kStageBytes);
@@ -217,7 +225,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           for (int k = 0; k < BK / UMMA_K; ++k) {
             const uint64_t da = make_smem_desc(sa + k * UMMA_K * 2);
             const uint64_t db = make_smem_desc(sb + k * UMMA_K * 2);
-            umma_bf16(d_tmem, da, db, idesc, (kb | k) != 0 ? 1u : 0u);
+            umma_bf16(d_tmem, da, db, idesc, (kb > kb0 || k != 0) ? 1u : 0u);
           }
           tcgen05_commit(empty_bar + stage);              // smem slot free once these MMAs retire
           if (++stage == kStages) { stage = 0; phase ^= 1; }
@@ -242,7 +250,8 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     const int cq = (lane & 3) * 4;                        // first of this lane's 4 columns inside a 16-column block
     constexpr int kBlocks = BN / 64;                      // 16-column blocks per warp
     int acc = 0; uint32_t acc_phase = 0;
-    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+    for (int item = blockIdx.x; item < num_items; item += gridDim.x) {
+      const int tile = item / splits;
       const int m_blk = tile / num_n, n_blk = tile % num_n;
       const int m0 = m_blk * BM, n0 = n_blk * BN;
       int gi = 0;
@@ -282,103 +291,148 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           rr_i[it] = __shfl_sync(0xffffffffu, rr, src); ro_i[it] = __shfl_sync(0xffffffffu, ro, src);
         }
       }
-      float dot[4] = {0.f, 0.f, 0.f, 0.f};
-      bool waited = false;
       const uint32_t t_row = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(acc * BN);
+      const bool split_mode = SK && splits > 1;
+      float* ws_rows = split_mode ? sk_ws + (size_t)tile * (BM * BN) + (size_t)(quad * 32 + sub) * BN : nullptr;
+      bool is_last = false;
+      // pass 0 reads the accumulator from TMEM: without split-K it runs the fused epilogue; with split-K it only adds
+      // the partial tile into the scratch tile.  pass 1 (last-arriving split only) runs the epilogue from the scratch tile.
 #pragma unroll 1
-      for (int blk = 0; blk < kBlocks; ++blk) {
-        const int c0 = part * (BN / 4) + blk * 16;
-        if (n0 + c0 >= N) break;                     // warp-uniform
-        const int col = n0 + c0 + cq;                // global column of this lane's 4 values
-        const int lc = col - n_begin;                // column inside the group (table / output column)
-        // gathered tables first: they do not depend on the accumulator, so their latency overlaps the TMEM load
-        const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
-        float4 b4 = z4, w4 = z4, tp[4], tq[4], tr[4];
-        if (g_bias) b4 = __ldg(reinterpret_cast<const float4*>(g_bias + col));
-        if ((FEAT & F_DOT) && g_dw) w4 = __ldg(reinterpret_cast<const float4*>(g_dw + lc));
-        if ((FEAT & F_P) && g_p) {
+      for (int pass = 0; pass < (SK ? 2 : 1); ++pass) {
+        if (pass == 1 && !is_last) break;
+        const bool do_math = (pass == 1) || !split_mode;
+        float dot[4] = {0.f, 0.f, 0.f, 0.f};
+        bool waited = false;
+#pragma unroll 1
+        for (int blk = 0; blk < kBlocks; ++blk) {
+          const int c0 = part * (BN / 4) + blk * 16;
+          if (n0 + c0 >= N) break;                     // warp-uniform
+          const int col = n0 + c0 + cq;                // global column of this lane's 4 values
+          const int lc = col - n_begin;                // column inside the group (table / output column)
+          // gathered tables first: they do not depend on the accumulator, so their latency overlaps the TMEM load
+          const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
+          float4 b4 = z4, w4 = z4, tp[4], tq[4], tr[4];
+          if (do_math) {
+            if (g_bias) b4 = __ldg(reinterpret_cast<const float4*>(g_bias + col));
+            if ((FEAT & F_DOT) && g_dw) w4 = __ldg(reinterpret_cast<const float4*>(g_dw + lc));
+            if ((FEAT & F_P) && g_p) {
 #pragma unroll
-          for (int it = 0; it < 4; ++it) tp[it] = __ldg(reinterpret_cast<const float4*>(g_p + (int64_t)rp_i[it] * ld_p + lc));
-        }
-        if ((FEAT & F_Q) && g_q) {
-#pragma unroll
-          for (int it = 0; it < 4; ++it) tq[it] = __ldg(reinterpret_cast<const float4*>(g_q + (int64_t)rq_i[it] * ld_q + lc));
-        }
-        if ((FEAT & F_RES) && g_res) {
-#pragma unroll
-          for (int it = 0; it < 4; ++it) tr[it] = __ldg(reinterpret_cast<const float4*>(g_res + (int64_t)rr_i[it] * ld_r + lc));
-        }
-        if (!waited) {                               // first block of the tile: wait for the accumulator
-          mbar_wait(tmem_full + acc, acc_phase);
-          tcgen05_fence_after();
-          waited = true;
-        }
-        uint32_t raw[16];
-        tmem_ld16(t_row + c0, raw);
-        __syncwarp();                                // the patch's previous readers are done
-#pragma unroll
-        for (int j = 0; j < 4; ++j)
-          patch[lane * 4 + (j ^ ((lane >> 1) & 3))] =
-              make_float4(__uint_as_float(raw[4 * j]), __uint_as_float(raw[4 * j + 1]), __uint_as_float(raw[4 * j + 2]),
-                          __uint_as_float(raw[4 * j + 3]));
-        __syncwarp();
-#pragma unroll
-        for (int it = 0; it < 4; ++it) {
-          const int ro = ro_i[it];
-          const bool store_ok = ro >= 0;             // also false for rows beyond M
-          const int r = it * 8 + sub;
-          float4 v = patch[r * 4 + ((lane & 3) ^ ((r >> 1) & 3))];
-          v.x += b4.x; v.y += b4.y; v.z += b4.z; v.w += b4.w;
-          if ((FEAT & F_RAW) && g_raw && store_ok)
-            *reinterpret_cast<uint2*>(g_raw + (int64_t)ro * ld_raw + lc) = make_uint2(pack_bf16(v.x, v.y), pack_bf16(v.z, v.w));
-          if ((FEAT & F_P) && g_p) {
-            float4 a = tp[it];
-            if ((FEAT & F_Q) && g_q) { a.x += tq[it].x; a.y += tq[it].y; a.z += tq[it].z; a.w += tq[it].w; }
-            v.x *= a.x; v.y *= a.y; v.z *= a.z; v.w *= a.w;
-          }
-          if (relu) { v.x = fmaxf(v.x, 0.f); v.y = fmaxf(v.y, 0.f); v.z = fmaxf(v.z, 0.f); v.w = fmaxf(v.w, 0.f); }
-          if ((FEAT & F_RES) && g_res) { v.x += tr[it].x; v.y += tr[it].y; v.z += tr[it].z; v.w += tr[it].w; }
-          if (FEAT & F_DOT) dot[it] += v.x * w4.x + v.y * w4.y + v.z * w4.z + v.w * w4.w;
-          if (store_ok) {
-            if ((FEAT & F_OB) && g_ob)
-              *reinterpret_cast<uint2*>(g_ob + (int64_t)ro * ld_ob + lc) = make_uint2(pack_bf16(v.x, v.y), pack_bf16(v.z, v.w));
-            if ((FEAT & F_LO) && g_lo) {   // residual of the bf16 rounding: v ~= hi + lo to ~16 mantissa bits
-              const float lx = v.x - __bfloat162float(__float2bfloat16(v.x)), ly = v.y - __bfloat162float(__float2bfloat16(v.y));
-              const float lz = v.z - __bfloat162float(__float2bfloat16(v.z)), lw = v.w - __bfloat162float(__float2bfloat16(v.w));
-              *reinterpret_cast<uint2*>(g_lo + (int64_t)ro * ld_lo + lc) = make_uint2(pack_bf16(lx, ly), pack_bf16(lz, lw));
+              for (int it = 0; it < 4; ++it) tp[it] = __ldg(reinterpret_cast<const float4*>(g_p + (int64_t)rp_i[it] * ld_p + lc));
             }
-            if ((FEAT & F_OF) && g_of) {
-              float* dst = g_of + (int64_t)ro * ld_of + lc;
-              if (col + 4 <= N && (ld_of & 3) == 0) {
-                *reinterpret_cast<float4*>(dst) = v;
-              } else {
-                if (col < N) dst[0] = v.x;
-                if (col + 1 < N) dst[1] = v.y;
-                if (col + 2 < N) dst[2] = v.z;
-                if (col + 3 < N) dst[3] = v.w;
+            if ((FEAT & F_Q) && g_q) {
+#pragma unroll
+              for (int it = 0; it < 4; ++it) tq[it] = __ldg(reinterpret_cast<const float4*>(g_q + (int64_t)rq_i[it] * ld_q + lc));
+            }
+            if ((FEAT & F_RES) && g_res) {
+#pragma unroll
+              for (int it = 0; it < 4; ++it) tr[it] = __ldg(reinterpret_cast<const float4*>(g_res + (int64_t)rr_i[it] * ld_r + lc));
+            }
+          }
+          if (pass == 0) {
+            if (!waited) {                             // first block of the tile: wait for the accumulator
+              mbar_wait(tmem_full + acc, acc_phase);
+              tcgen05_fence_after();
+              waited = true;
+            }
+            uint32_t raw[16];
+            tmem_ld16(t_row + c0, raw);
+            __syncwarp();                              // the patch's previous readers are done
+#pragma unroll
+            for (int j = 0; j < 4; ++j)
+              patch[lane * 4 + (j ^ ((lane >> 1) & 3))] =
+                  make_float4(__uint_as_float(raw[4 * j]), __uint_as_float(raw[4 * j + 1]), __uint_as_float(raw[4 * j + 2]),
+                              __uint_as_float(raw[4 * j + 3]));
+            __syncwarp();
+          }
+#pragma unroll
+          for (int it = 0; it < 4; ++it) {
+            const int r = it * 8 + sub;
+            float4 v;
+            if (pass == 0) {
+              v = patch[r * 4 + ((lane & 3) ^ ((r >> 1) & 3))];
+              if (split_mode) {                        // partial sum -> scratch tile (fp32 reduction in L2)
+                if (m0 + quad * 32 + r < M) {
+                  float* dst = ws_rows + (size_t)(it * 8) * BN + c0 + cq;
+                  asm volatile("red.relaxed.gpu.global.add.v4.f32 [%0], {%1, %2, %3, %4};\n" ::"l"(dst), "f"(v.x), "f"(v.y),
+                               "f"(v.z), "f"(v.w)
+                               : "memory");
+                }
+                continue;
+              }
+            } else {                                   // complete sum from the scratch tile; leave it zeroed
+              float4* src = reinterpret_cast<float4*>(ws_rows + (size_t)(it * 8) * BN + c0 + cq);
+              if (m0 + quad * 32 + r < M) { v = __ldcg(src); __stcg(src, z4); } else v = z4;
+            }
+            const int ro = ro_i[it];
+            const bool store_ok = ro >= 0;             // also false for rows beyond M
+            v.x += b4.x; v.y += b4.y; v.z += b4.z; v.w += b4.w;
+            if ((FEAT & F_RAW) && g_raw && store_ok)
+              *reinterpret_cast<uint2*>(g_raw + (int64_t)ro * ld_raw + lc) = make_uint2(pack_bf16(v.x, v.y), pack_bf16(v.z, v.w));
+            if ((FEAT & F_P) && g_p) {
+              float4 a = tp[it];
+              if ((FEAT & F_Q) && g_q) { a.x += tq[it].x; a.y += tq[it].y; a.z += tq[it].z; a.w += tq[it].w; }
+              v.x *= a.x; v.y *= a.y; v.z *= a.z; v.w *= a.w;
+            }
+            if (relu) { v.x = fmaxf(v.x, 0.f); v.y = fmaxf(v.y, 0.f); v.z = fmaxf(v.z, 0.f); v.w = fmaxf(v.w, 0.f); }
+            if ((FEAT & F_RES) && g_res) { v.x += tr[it].x; v.y += tr[it].y; v.z += tr[it].z; v.w += tr[it].w; }
+            if (FEAT & F_DOT) dot[it] += v.x * w4.x + v.y * w4.y + v.z * w4.z + v.w * w4.w;
+            if (store_ok) {
+              if ((FEAT & F_OB) && g_ob)
+                *reinterpret_cast<uint2*>(g_ob + (int64_t)ro * ld_ob + lc) = make_uint2(pack_bf16(v.x, v.y), pack_bf16(v.z, v.w));
+              if ((FEAT & F_LO) && g_lo) {   // residual of the bf16 rounding: v ~= hi + lo to ~16 mantissa bits
+                const float lx = v.x - __bfloat162float(__float2bfloat16(v.x)), ly = v.y - __bfloat162float(__float2bfloat16(v.y));
+                const float lz = v.z - __bfloat162float(__float2bfloat16(v.z)), lw = v.w - __bfloat162float(__float2bfloat16(v.w));
+                *reinterpret_cast<uint2*>(g_lo + (int64_t)ro * ld_lo + lc) = make_uint2(pack_bf16(lx, ly), pack_bf16(lz, lw));
+              }
+              if ((FEAT & F_OF) && g_of) {
+                float* dst = g_of + (int64_t)ro * ld_of + lc;
+                if (col + 4 <= N && (ld_of & 3) == 0) {
+                  *reinterpret_cast<float4*>(dst) = v;
+                } else {
+                  if (col < N) dst[0] = v.x;
+                  if (col + 1 < N) dst[1] = v.y;
+                  if (col + 2 < N) dst[2] = v.z;
+                  if (col + 3 < N) dst[3] = v.w;
+                }
               }
             }
           }
         }
-      }
-      if (!waited) {                                 // this warp's columns lie beyond N: still consume the phase
-        mbar_wait(tmem_full + acc, acc_phase);
-        tcgen05_fence_after();
-      }
-      if ((FEAT & F_DOT) && G.dot_out) {   // four partials per N tile (one per column quarter), summed by the consumer
+        if (pass == 0) {
+          if (!waited) {                               // this warp's columns lie beyond N: still consume the phase
+            mbar_wait(tmem_full + acc, acc_phase);
+            tcgen05_fence_after();
+          }
+          // accumulator drained: hand the TMEM buffer back to the MMA warp
+          tcgen05_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(tmem_empty + acc);
+          if (split_mode) {                            // threadfence-reduction: who adds the last partial owns the epilogue
+            __threadfence();
+            asm volatile("bar.sync 1, %0;\n" ::"n"(kEpiWarps * 32) : "memory");
+            if (ew == 0 && lane == 0) {
+              const int prev = atomicAdd(sk_cnt + tile, 1);
+              const int last = (prev == splits - 1) ? 1 : 0;
+              if (last) sk_cnt[tile] = 0;              // self-resetting: the next launch finds zeroed counters
+              *sk_flag = last;
+            }
+            asm volatile("bar.sync 1, %0;\n" ::"n"(kEpiWarps * 32) : "memory");
+            is_last = (*sk_flag != 0);
+            __threadfence();
+          }
+        }
+        if (do_math && (FEAT & F_DOT) && G.dot_out) {   // four partials per N tile (one per column quarter), summed by the consumer
 #pragma unroll
-        for (int it = 0; it < 4; ++it) {
-          float d = dot[it];
-          d += __shfl_xor_sync(0xffffffffu, d, 1);
-          d += __shfl_xor_sync(0xffffffffu, d, 2);
-          if ((lane & 3) == 0 && ro_i[it] >= 0)
-            G.dot_out[(int64_t)ro_i[it] * G.ld_dot + ((n0 - n_begin) / BN) * 4 + part] = d;
+          for (int it = 0; it < 4; ++it) {
+            float d = dot[it];
+            d += __shfl_xor_sync(0xffffffffu, d, 1);
+            d += __shfl_xor_sync(0xffffffffu, d, 2);
+            if ((lane & 3) == 0 && ro_i[it] >= 0)
+              G.dot_out[(int64_t)ro_i[it] * G.ld_dot + ((n0 - n_begin) / BN) * 4 + part] = d;
+          }
         }
       }
-      // accumulator drained: hand the TMEM buffer back to the MMA warp
-      tcgen05_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(tmem_empty + acc);
+      if (split_mode) asm volatile("bar.sync 1, %0;\n" ::"n"(kEpiWarps * 32) : "memory");   // sk_flag is rewritten by the next item
       if (++acc == 2) { acc = 0; acc_phase ^= 1; }
     }
   }
@@ -426,20 +480,25 @@ static int make_tmap(CUtensorMap* map, const void* ptr, int64_t rows, int64_t co
   return SKG_OK;
 }
 
-template <int BN, uint32_t FEAT>
+struct SplitK {
+  int splits;
+  float* ws;
+  int* cnt;
+};
+
+template <int BN, uint32_t FEAT, bool SK>
 static int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, int M, int N, int K, const EpiGroups& epi,
-                       int max_ctas, cudaStream_t stream) {
+                       const SplitK& sk, cudaStream_t stream) {
   using S = GemmSmem<BN>;
-  auto kern = gemm_bf16_kernel<BN, FEAT>;
+  auto kern = gemm_bf16_kernel<BN, FEAT, SK>;
   static bool attr_set = false;
   if (!attr_set) {
     SKG_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, S::kTotal));
     attr_set = true;
   }
-  const int tiles = ceil_div(M, BM) * ceil_div(N, BN);
-  int grid = tiles < num_sms() ? tiles : num_sms();
-  if (max_ctas > 0 && grid > max_ctas) grid = max_ctas;
-  kern<<<grid, kGemmThreads, S::kTotal, stream>>>(tmA, tmB, M, N, K, epi);
+  const int items = ceil_div(M, BM) * ceil_div(N, BN) * sk.splits;
+  const int grid = items < num_sms() ? items : num_sms();
+  kern<<<grid, kGemmThreads, S::kTotal, stream>>>(tmA, tmB, M, N, K, epi, sk.splits, sk.ws, sk.cnt);
   return check_launch("gemm_bf16_kernel");
 }
 
@@ -447,16 +506,53 @@ static int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, int M, in
 
 using namespace skg;
 
+constexpr int kSplitKCounters = 1024;   // ints at the head of the split-K scratch
+
+// split-K pays when the tiles alone leave most SMs idle (node-row GEMMs: M = humans / boxes of the batch)
+static int choose_splits(int M, int N, int K, int block_n, int64_t ws_bytes) {
+  const int tiles = ceil_div(M, BM) * ceil_div(N, block_n);
+  const int num_k = ceil_div(K, BK);
+  // the fp32 reduction through L2 costs ~10 us: it only pays for long-K problems (box_head: K = 12544)
+  if (tiles * 2 > num_sms() || tiles > kSplitKCounters || num_k < 64) return 1;
+  if (ws_bytes < (int64_t)kSplitKCounters * 4 + (int64_t)tiles * BM * block_n * 4) return 1;
+  int splits = num_sms() / tiles;
+  if (splits > num_k / 16) splits = num_k / 16;   // at least 16 k-blocks (K = 1024) per split
+  return splits < 1 ? 1 : splits;
+}
+
+extern "C" int64_t skg_gemm_splitk_scratch_bytes(int max_tiles_m, int max_n) {
+  // enough for any GEMM the split-K heuristic accepts: tiles * 2 <= SMs, 128 x 256 fp32 scratch tile each
+  (void)max_tiles_m; (void)max_n;
+  return (int64_t)kSplitKCounters * 4 + (int64_t)(num_sms() / 2 + 1) * BM * 256 * 4;
+}
+
 extern "C" int skg_gemm_bf16(const void* A, int64_t lda, const void* B, int64_t ldb, int M, int N, int K,
                              const skg_epilogue_group* groups, int num_groups, int block_n, cudaStream_t stream) {
+  return skg_gemm_bf16_splitk(A, lda, B, ldb, M, N, K, groups, num_groups, block_n, nullptr, 0, stream);
+}
+
+extern "C" int skg_gemm_bf16_splitk(const void* A, int64_t lda, const void* B, int64_t ldb, int M, int N, int K,
+                                    const skg_epilogue_group* groups, int num_groups, int block_n, void* scratch,
+                                    int64_t scratch_bytes, cudaStream_t stream) {
   SKG_REQUIRE(M >= 0 && N > 0 && K > 0, "bad GEMM shape M=%d N=%d K=%d", M, N, K);
   if (M == 0) return SKG_OK;
   SKG_REQUIRE(A && B && groups, "null pointer argument");
   SKG_REQUIRE(num_groups >= 1 && num_groups <= kMaxGroups, "num_groups must be in [1, %d]", kMaxGroups);
   SKG_REQUIRE((lda % 8) == 0 && (ldb % 8) == 0 && lda >= K && ldb >= K, "lda/ldb must be >= K and multiples of 8 elements");
   SKG_REQUIRE(((reinterpret_cast<uintptr_t>(A) | reinterpret_cast<uintptr_t>(B)) & 15u) == 0, "A and B must be 16-byte aligned");
-  if (block_n == 0) block_n = (N % 256 == 0) ? 256 : 128;
-  SKG_REQUIRE(block_n == 128 || block_n == 256, "block_n must be 128 or 256");
+  if (block_n == 0) {
+    // widest tile that still spreads the problem over the SMs: node-row GEMMs (M = humans / boxes of the batch,
+    // one or two M tiles) are bound by how fast ONE SM can stream its weight slab, so they get narrow N tiles
+    const int mt = ceil_div(M, BM);
+    block_n = (N % 256 == 0) ? 256 : 128;
+    bool has_dot = false;   // the row-dot partial layout depends on block_n: never narrow those launches
+    for (int i = 0; i < num_groups; ++i) has_dot |= (groups[i].dot_out != nullptr);
+    if (!has_dot) {
+    if (block_n == 256 && mt * (N / 256) < num_sms() / 2) block_n = 128;
+    if (block_n == 128 && (N % 64 == 0 || N < 128) && mt * ceil_div(N, 128) < num_sms() / 2) block_n = 64;
+    }
+  }
+  SKG_REQUIRE(block_n == 64 || block_n == 128 || block_n == 256, "block_n must be 64, 128 or 256");
   EpiGroups epi;
   epi.num = num_groups;
   for (int i = 0; i < num_groups; ++i) {
@@ -478,6 +574,15 @@ extern "C" int skg_gemm_bf16(const void* A, int64_t lda, const void* B, int64_t 
   if (rc) return rc;
   rc = make_tmap(&tmB, B, N, K, ldb, block_n);
   if (rc) return rc;
+  SplitK sk{1, nullptr, nullptr};
+  if (scratch) {
+    SKG_REQUIRE((reinterpret_cast<uintptr_t>(scratch) & 15u) == 0, "split-K scratch must be 16-byte aligned");
+    sk.splits = block_n == 64 ? 1 : choose_splits(M, N, K, block_n, scratch_bytes);
+    if (sk.splits > 1) {
+      sk.cnt = reinterpret_cast<int*>(scratch);
+      sk.ws = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(scratch) + kSplitKCounters * 4);
+    }
+  }
   // pick the leanest compiled epilogue whose feature set covers what the groups ask for
   uint32_t need = 0;
   for (int i = 0; i < num_groups; ++i) {
@@ -485,19 +590,35 @@ extern "C" int skg_gemm_bf16(const void* A, int64_t lda, const void* B, int64_t 
     need |= (g.mul_p ? F_P : 0) | (g.mul_q ? F_Q : 0) | (g.raw_bf16 ? F_RAW : 0) | (g.residual ? F_RES : 0) |
             ((g.dot_w || g.dot_out) ? F_DOT : 0) | (g.out_bf16 ? F_OB : 0) | (g.out_f32 ? F_OF : 0) | (g.lo_bf16 ? F_LO : 0);
   }
-#define SKG_GEMM_CASE(F)                                                                   \
-  if ((need & ~(uint32_t)(F)) == 0) {                                                      \
-    if (block_n == 256) return launch_gemm<256, (F)>(tmA, tmB, M, N, K, epi, 0, stream);   \
-    return launch_gemm<128, (F)>(tmA, tmB, M, N, K, epi, 0, stream);                       \
+#define SKG_GEMM_CASE64(F)                                                                        \
+  if (block_n == 64 && (need & ~(uint32_t)(F)) == 0) {                                            \
+    sk.splits = 1;                                                                                \
+    return launch_gemm<64, (F), false>(tmA, tmB, M, N, K, epi, sk, stream);                       \
   }
-  SKG_GEMM_CASE(F_OB)                          // bias (+ReLU) -> bf16: spatial_head, box_head
-  SKG_GEMM_CASE(F_OF)                          // -> fp32: per-node projections
-  SKG_GEMM_CASE(F_OB | F_OF)                   // fc_head / fc_tail
-  SKG_GEMM_CASE(F_P | F_Q | F_RAW | F_OB)      // fused fc_2 of the MBFs (Hadamard with gathered tables)
-  SKG_GEMM_CASE(F_DOT)                         // attention weights -> adjacency row-dot
-  SKG_GEMM_CASE(F_RES | F_OF)                  // message fc_3 + residual, split-bf16 predictor second pass
-  SKG_GEMM_CASE(F_OB | F_LO)                   // final pair features with rounding residual
-  SKG_GEMM_CASE(F_ALL)
+  SKG_GEMM_CASE64(F_OB)
+  SKG_GEMM_CASE64(F_OF)
+  SKG_GEMM_CASE64(F_OB | F_OF)
+  SKG_GEMM_CASE64(F_RES | F_OF)
+  SKG_GEMM_CASE64(F_ALL)
+#undef SKG_GEMM_CASE64
+#define SKG_GEMM_CASE(F, SKV)                                                                 \
+  if ((need & ~(uint32_t)(F)) == 0) {                                                      \
+    if (SKV && sk.splits > 1) {                                                                   \
+      if (block_n == 256) return launch_gemm<256, (F), SKV>(tmA, tmB, M, N, K, epi, sk, stream);  \
+      return launch_gemm<128, (F), SKV>(tmA, tmB, M, N, K, epi, sk, stream);                      \
+    }                                                                                             \
+    sk.splits = 1;                                                                                \
+    if (block_n == 256) return launch_gemm<256, (F), false>(tmA, tmB, M, N, K, epi, sk, stream);  \
+    return launch_gemm<128, (F), false>(tmA, tmB, M, N, K, epi, sk, stream);                      \
+  }
+  SKG_GEMM_CASE(F_OB, true)                    // bias (+ReLU) -> bf16: spatial_head, box_head
+  SKG_GEMM_CASE(F_OF, true)                    // -> fp32: per-node projections
+  SKG_GEMM_CASE(F_OB | F_OF, true)                // fc_head / fc_tail
+  SKG_GEMM_CASE(F_P | F_Q | F_RAW | F_OB, false)    // fused fc_2 of the MBFs (Hadamard with gathered tables)
+  SKG_GEMM_CASE(F_DOT, false)                  // attention weights -> adjacency row-dot
+  SKG_GEMM_CASE(F_RES | F_OF, true)                // message fc_3 + residual, split-bf16 predictor second pass
+  SKG_GEMM_CASE(F_OB | F_LO, false)                // final pair features with rounding residual
+  SKG_GEMM_CASE(F_ALL, true)
 #undef SKG_GEMM_CASE
   set_error("no epilogue variant");
   return SKG_ERR_UNSUPPORTED;

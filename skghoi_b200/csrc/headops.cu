@@ -100,6 +100,23 @@ __global__ void node_inputs_kernel(const __nv_bfloat16* __restrict__ node_enc, i
   }
 }
 
+// Per-box preparation for the fused fc_head / fc_tail GEMM (head.py:875-885): the TransH entity columns of the
+// node input, o_in[row, enc_dim : ld] = bf16(E[index of the box inside its image]) zero padded (tail_stack == E[y],
+// head.py:572; the human side's constant E[human_idx] term is folded into the bias by the host), and the
+// box -> human-row map (human rows are the first n_h boxes of every image, -1 otherwise).
+__global__ void node_prep_kernel(const float* __restrict__ ent, int ent_dim, int ent_tot, const int32_t* __restrict__ box_off,
+                                 const int32_t* __restrict__ n_h, const int32_t* __restrict__ hum_off, int B,
+                                 __nv_bfloat16* __restrict__ o_in, int ld, int enc_dim, int32_t* __restrict__ box2hum) {
+  const int row = blockIdx.x;
+  int lo = 0, hi = B;
+  while (hi - lo > 1) { const int mid = (lo + hi) >> 1; if (__ldg(box_off + mid) <= row) lo = mid; else hi = mid; }
+  const int idx = row - __ldg(box_off + lo);
+  int entity = idx < ent_tot ? idx : ent_tot - 1;     // host rejects n > ent_tot (reference raises IndexError)
+  for (int c = enc_dim + threadIdx.x; c < ld; c += blockDim.x)
+    o_in[(int64_t)row * ld + c] = __float2bfloat16(c < enc_dim + ent_dim ? __ldg(ent + (int64_t)entity * ent_dim + (c - enc_dim)) : 0.f);
+  if (threadIdx.x == 0 && box2hum) box2hum[row] = idx < __ldg(n_h + lo) ? __ldg(hum_off + lo) + idx : -1;
+}
+
 // global_features = avg_pool(features['3']).flatten(1) (head.py:811): one warp per (image, channel)
 __global__ void global_pool_kernel(const float* __restrict__ f, int64_t planes, int hw, __nv_bfloat16* __restrict__ out_bf16,
                                    float* __restrict__ out_f32) {
@@ -278,6 +295,17 @@ extern "C" int skg_node_inputs(const void* node_enc_bf16, int enc_dim, const flo
                                                                    total_boxes, total_humans, (__nv_bfloat16*)h_in,
                                                                    (__nv_bfloat16*)o_in, ld);
   return check_launch("node_inputs_kernel");
+}
+
+extern "C" int skg_node_prep(const float* ent, int ent_dim, int ent_tot, const int32_t* box_off, const int32_t* n_h,
+                             const int32_t* hum_off, int num_images, int total_boxes, void* o_in, int ld, int enc_dim,
+                             int32_t* box2hum, cudaStream_t stream) {
+  if (total_boxes == 0) return SKG_OK;
+  SKG_REQUIRE(ent && box_off && n_h && hum_off && o_in, "null pointer argument");
+  SKG_REQUIRE(ld >= enc_dim + ent_dim && ent_tot > 0, "bad node_prep sizes");
+  node_prep_kernel<<<total_boxes, 64, 0, stream>>>(ent, ent_dim, ent_tot, box_off, n_h, hum_off, num_images,
+                                                   (__nv_bfloat16*)o_in, ld, enc_dim, box2hum);
+  return check_launch("node_prep_kernel");
 }
 
 extern "C" int skg_global_pool(const float* features, int64_t planes, int hw, void* out_bf16, float* out_f32,

@@ -119,6 +119,12 @@ def _versions(module) -> tuple:
     return tuple((p.data_ptr(), p._version) for p in module.parameters())
 
 
+def _version_sum(params) -> int:
+    """Cheap change detector for in-place parameter updates (optimizer steps, load_state_dict copies);
+    re-homing the parameters (.to / .cuda / .float) invalidates the cache through ``_apply`` (head.py)."""
+    return sum(p._version for p in params)
+
+
 class PackedMBF:
     """Concatenated-branch bf16 operands of one MultiBranchFusion / MessageMBF (head.py:446-474)."""
 
@@ -210,7 +216,9 @@ class PackedHead:
         if dev.type != "cuda":
             raise _lib.SkgError("the interaction head must live on a CUDA device (no CPU fallback)")
         self.device = dev
-        self.key = _versions(ih)
+        self.params = list(ih.parameters())
+        self.vsum = _version_sum(self.params)
+        self.ptr0 = (self.params[0].data_ptr(), self.params[-1].data_ptr())
         R = G.representation_size; E = G.node_encoding_size
         self.R, self.E = R, E
         self.Wb1, self.bb1 = _bf16(G.box_head[1].weight, pad_k=64), _f32(G.box_head[1].bias)
@@ -221,6 +229,14 @@ class PackedHead:
         self.Wfh, self.bfh = _bf16(G.fc_head[0].weight, pad_k=64), _f32(G.fc_head[0].bias)
         self.Wft, self.bft = _bf16(G.fc_tail[0].weight, pad_k=64), _f32(G.fc_tail[0].bias)
         self.fc_k = self.Wfh.shape[1]
+        # fused fc_head | fc_tail over all boxes: the human side's entity columns multiply the CONSTANT row E[human_idx]
+        # (head.py:571, 877-882), so they are zeroed here and folded into the bias by ``fc_bias`` below
+        Wfh_node = G.fc_head[0].weight.detach().float().clone()
+        self.Wfh_ent = Wfh_node[:, E:].clone().contiguous()          # [R, transh_dim] fp32
+        Wfh_node[:, E:] = 0
+        self.Wfc = _bf16(torch.cat([Wfh_node, G.fc_tail[0].weight.detach().float()], 0), pad_k=64)
+        self.bfc = torch.cat([self.bfh, self.bft]).contiguous()
+        self.ent_key = None
         att = G.attention_head.packed(); os_ = G.obj_to_sub.packed(); so = G.sub_to_obj.packed()
         gg = G.attention_head_g.packed()
         z = torch.zeros(R, device=dev)
@@ -250,6 +266,13 @@ class PackedHead:
         self.Wpred_lo = _bf16(lo.float(), pad_rows=128)                                 # [128, 2R]   against hi
         self.cw = self._c_struct(G)
 
+    def fc_bias(self, ent: Tensor, human_idx: int) -> None:
+        """bfc[:R] = fc_head bias + W_head[:, E:] @ E[human_idx]; refreshed only when the TransH entity table changes."""
+        key = (ent.data_ptr(), ent._version)
+        if key != self.ent_key:
+            self.bfc[:self.R] = self.bfh[:self.R] + self.Wfh_ent @ ent[human_idx].float()
+            self.ent_key = key
+
     def _c_struct(self, G):
         """skg_head_weights: raw device pointers of the packed operands (this object keeps them alive)."""
         w = _lib.HeadWeights()
@@ -259,6 +282,7 @@ class PackedHead:
         w.human_idx, w.ent_tot, w.ent_dim = G.human_idx, G.transh_head.num_object, G.transh_head.transh_dim
         w.sp_in = G.spatial_head[0].weight.shape[1]
         for name in ("Wb1", "bb1", "Wb2", "bb2", "Wsp0", "bsp0", "Wsp1", "bsp1", "Wsp2", "bsp2", "Wfh", "bfh", "Wft", "bft",
+                     "Wfc", "bfc",
                      "W_hproj", "b_hproj", "W_oproj", "b_oproj", "Wg1", "bg1", "W2cat", "b2cat", "W3att", "b3att",
                      "W3os", "b3os", "W3so", "b3so", "W3g", "b3g", "w_adj", "Wpred", "bpred", "Wpred_hh", "Wpred_lo"):
             setattr(w, name, getattr(self, name).data_ptr())
@@ -270,7 +294,7 @@ class PackedHead:
 
 def packed_head(ih) -> PackedHead:
     pk = ih.__dict__.get("_skg_packed")
-    if pk is None or pk.key != _versions(ih):
+    if pk is None or pk.vsum != _version_sum(pk.params) or pk.ptr0 != (pk.params[0].data_ptr(), pk.params[-1].data_ptr()):
         pk = PackedHead(ih)
         ih.__dict__["_skg_packed"] = pk
     return pk
@@ -306,7 +330,7 @@ def _host_meta(box_labels: List[Tensor], box_scores: Optional[List[Tensor]], hum
 
 
 _INT64_BUFS = {"x", "y", "x_keep", "y_keep"}
-_INT32_BUFS = {"cell2pair", "cell_hrow", "cell_orow", "cell_img", "pair2cell", "nan_flag"}
+_INT32_BUFS = {"cell2pair", "cell_hrow", "cell_orow", "cell_img", "pair2cell", "nan_flag", "box2hum"}
 _workspaces = {}
 
 
@@ -315,7 +339,7 @@ def _workspace(dev, nbytes: int) -> Tensor:
     key = (dev.index, torch.cuda.current_stream(dev).cuda_stream)
     ws = _workspaces.get(key)
     if ws is None or ws.numel() < nbytes:
-        ws = torch.empty(int(nbytes * 1.25) + 256, dtype=torch.uint8, device=dev)
+        ws = torch.zeros(int(nbytes * 1.25) + 256, dtype=torch.uint8, device=dev)   # split-K scratch must start zeroed
         _workspaces[key] = ws
     return ws
 
@@ -348,7 +372,7 @@ class _Run(dict):
 
 
 def head_forward(ih, features3: Tensor, image_shapes, box_features: Tensor, boxes_cat: Tensor, meta: dict,
-                 want_taps: bool = False, precise_logits: bool = True) -> dict:
+                 want_taps: bool = False, precise_logits: bool = True, profile: bool = False) -> dict:
     """Runs the whole pair path for a batch through ONE C-ABI call (skg_head_forward, csrc/forward.cu).
     Inputs: features['3'] [B,256,h,w] fp32, pooled box features [sum n, 256, 7, 7] fp32, concatenated boxes
     [sum n, 4] fp32 (all CUDA), host ``meta``.  Returns named views into the step's workspace: logits [P,118]
@@ -374,6 +398,7 @@ def head_forward(ih, features3: Tensor, image_shapes, box_features: Tensor, boxe
     _lib.require_cuda(f3, bf, boxes_cat)
     w = pk.cw
     w.ent = ent.data_ptr()
+    pk.fc_bias(ent, G.human_idx)
     b = _lib.HeadBatch()
     b.num_images, b.total_boxes, b.total_humans = seg.B, seg.total_boxes, seg.total_humans
     b.max_boxes_per_image = int(max(n)) if len(n) else 0
@@ -383,13 +408,25 @@ def head_forward(ih, features3: Tensor, image_shapes, box_features: Tensor, boxe
     b.box_off, b.n_h, b.hum_off = seg.d_box_off.data_ptr(), seg.d_n_h.data_ptr(), seg.d_hum_off.data_ptr()
     b.cell_off, b.pair_off, b.hw = seg.d_cell_off.data_ptr(), seg.d_pair_off.data_ptr(), seg.d_hw.data_ptr()
     flags = (_lib.HEAD_PRECISE_LOGITS if precise_logits else 0) | (_lib.HEAD_WANT_TAPS if want_taps else 0)
+    if profile:
+        flags |= _lib.HEAD_PROFILE
     plan = _lib.HeadPlan()
     import ctypes
     _lib.call("skg_head_plan", ctypes.byref(w), ctypes.byref(b), flags, ctypes.byref(plan))
     with torch.cuda.device(dev):
         ws = _workspace(dev, int(plan.total_bytes))
-        _lib.call("skg_head_forward", ctypes.byref(w), ctypes.byref(b), flags, _lib.ptr(ws), ws.numel(), _lib.stream_ptr(dev))
+        try:
+            _lib.call("skg_head_forward", ctypes.byref(w), ctypes.byref(b), flags, _lib.ptr(ws), ws.numel(), _lib.stream_ptr(dev))
+        except Exception:
+            _workspaces.clear()          # a failed step may leave the split-K scratch dirty: start from a fresh one
+            raise
     run = _Run(ws, plan, seg=seg, NH=seg.total_humans, NB=seg.total_boxes, _keep=(f3, bf, boxes_cat, ent))
+    if profile:
+        prof, i = [], 0
+        nm, sid, us = _lib.c_char_p(), _lib.c_int(), _lib.c_float()
+        while _lib.lib().skg_head_profile_get(i, ctypes.byref(nm), ctypes.byref(sid), ctypes.byref(us)) == 0:
+            prof.append((nm.value.decode(), sid.value, us.value)); i += 1
+        run["profile"] = prof
     if want_taps:
         run["enc32"]
     else:

@@ -191,6 +191,11 @@ class InteractionHead(Module):
         self.max_object = max_object
         self.distributed = distributed
 
+    def _apply(self, fn, *args, **kwargs):
+        # .to() / .cuda() / .float() re-home the parameters: drop the packed bf16 operands
+        self.__dict__.pop("_skg_packed", None)
+        return super()._apply(fn, *args, **kwargs)
+
     def preprocess(self, detections: List[dict], targets: List[dict], append_gt: Optional[bool] = None):
         from .engine import preprocess_detections
         return preprocess_detections(self, detections, targets, append_gt)

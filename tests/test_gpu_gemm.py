@@ -93,3 +93,40 @@ def test_gemm_rejects_bad_arguments():
         _lib.gemm_bf16(A, B, [_lib.epilogue_group(n_begin=64)])
     with pytest.raises(_lib.SkgError):
         _lib.gemm_bf16(A[:, :60].contiguous(), B[:, :60].contiguous(), [_lib.epilogue_group()])   # pitch 60 % 8 != 0
+
+
+@pytest.mark.parametrize("M,N,K,kind", [(256, 1024, 12544, "ob"), (128, 1024, 1088, "obof"), (130, 2048, 1024, "of"),
+                                        (256, 1024, 1024, "res"), (3968, 118, 4096, "of")])
+def test_gemm_split_k(M, N, K, kind):
+    """Few-tile shapes (node-row GEMMs of the head) run split-K through a zeroed scratch region that the kernel
+    must leave zeroed; results equal the unsplit product up to fp32 summation order."""
+    Np = (N + 127) // 128 * 128
+    A, B = _ops(M, Np, K, seed=M + N)
+    B[N:] = 0
+    bias = torch.zeros(Np, device=DEV); bias[:N] = torch.randn(N, device=DEV)
+    nbytes = int(_lib.lib().skg_gemm_splitk_scratch_bytes(0, 0))
+    scratch = torch.zeros(nbytes, dtype=torch.uint8, device=DEV)
+    ref = A.float() @ B[:N].float().t() + bias[:N]
+    out32 = torch.full((M, N), float("nan"), device=DEV)
+    out16 = torch.zeros(M, Np, dtype=torch.bfloat16, device=DEV)
+    res = torch.randn(M, Np, device=DEV)
+    for rep in range(2):                     # second launch re-uses the self-cleaned scratch
+        out32.fill_(float("nan"))
+        if kind == "ob":
+            g = _lib.epilogue_group(relu=True, bias=bias, out_bf16=out16)
+            _lib.gemm_bf16(A, B, [g], N=N, scratch=scratch)
+            torch.testing.assert_close(out16[:, :N].float(), torch.relu(ref), rtol=1e-2, atol=1e-2)
+        elif kind == "obof":
+            g = _lib.epilogue_group(relu=True, bias=bias, out_bf16=out16, out_f32=out32)
+            _lib.gemm_bf16(A, B, [g], N=N, scratch=scratch)
+            torch.testing.assert_close(out32, torch.relu(ref), rtol=2e-3, atol=2e-3)
+            torch.testing.assert_close(out16[:, :N].float(), torch.relu(ref), rtol=1e-2, atol=1e-2)
+        elif kind == "of":
+            g = _lib.epilogue_group(bias=bias, out_f32=out32)
+            _lib.gemm_bf16(A, B, [g], N=N, scratch=scratch)
+            torch.testing.assert_close(out32, ref, rtol=2e-3, atol=3e-3)
+        else:
+            g = _lib.epilogue_group(relu=True, bias=bias, residual=res, out_f32=out32)
+            _lib.gemm_bf16(A, B, [g], N=N, scratch=scratch)
+            torch.testing.assert_close(out32, torch.relu(ref) + res[:, :N], rtol=2e-3, atol=3e-3)
+        assert int(scratch.count_nonzero()) == 0, "split-K scratch not left zeroed"
