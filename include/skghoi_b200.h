@@ -285,6 +285,7 @@ typedef struct skg_head_weights {
 typedef struct skg_head_batch {
   int32_t num_images, total_boxes, total_humans, max_boxes_per_image, feat_hw;
   int64_t total_cells, total_pairs;
+  int64_t seg_bytes;          /* room to reserve in the workspace for the packed segment table (buffer "seg"; may be 0) */
   const float* features3;     /* [B, Cg, feat_hw]  features['3'] (head.py:811) */
   const float* box_features;  /* [boxes, pool_k]   pooled box features (head.py:387) */
   const float* boxes;         /* [boxes, 4] */
@@ -308,12 +309,24 @@ const char* skg_head_buffer_name(int i);
 int skg_head_plan(const skg_head_weights* weights, const skg_head_batch* batch, int flags, skg_head_plan_t* plan);
 #define SKG_HEAD_PRECISE_LOGITS 1   /* split-bf16 predictor (3 bf16 passes, ~fp32 logits) */
 #define SKG_HEAD_WANT_TAPS 2        /* also keep fp32 copies of the refined node encodings */
+#define SKG_HEAD_GRAPH 8            /* replay the step as a CUDA graph when the same (weights, batch incl. input pointers,
+                                       workspace) key repeats; any change falls back to plain launches */
 #define SKG_HEAD_PROFILE 4          /* record an event after every launch and SYNCHRONISE at the end (diagnostics only) */
 /* launch i of the last profiled skg_head_forward on this thread: label, stream (0 caller's, 1 side), microseconds since
  * the previous event on that stream; returns -1 past the end */
 int skg_head_profile_get(int i, const char** name, int* stream_id, float* us);
+/* graph-cache counters of this thread: replays, captures, first-sighting plain launches */
+void skg_head_graph_stats(long long* replays, long long* captures, long long* plain);
 int skg_head_forward(const skg_head_weights* weights, const skg_head_batch* batch, int flags, void* workspace,
                      int64_t workspace_bytes, cudaStream_t stream);
+
+/* Host-side packing of the per-batch segment table every batched kernel consumes (all HOST pointers): n / n_h [B]
+ * boxes and humans per image, hw [B,2] = (h, w) as doubles.  `out` receives
+ *   cell_off i64[B+1] | pair_off i64[B+1] | box_off i32[B+1] | n_h i32[B] | hum_off i32[B+1] | hw f32[3B] (h, w, h*w)
+ * (n_h forced to 0 for images the reference skips, head.py:829-839); offsets[6] = byte offsets of the six arrays,
+ * totals[5] = boxes, humans, cells, pairs, max boxes per image.  Returns the bytes used (multiple of 16) or -1. */
+int64_t skg_segments_pack(const int64_t* n, const int64_t* n_h, const double* hw, int num_images, void* out,
+                          int64_t out_bytes, int64_t* offsets, int64_t* totals);
 
 /* Host-side closed form of the number of (pair, verb) entries postprocess emits per image
  * (head.py:315 nonzero(prior[0])): all arrays are HOST pointers; returns the total, or -1. */

@@ -201,7 +201,7 @@ class HeadWeights(ctypes.Structure):
 class HeadBatch(ctypes.Structure):
     """Mirror of ``skg_head_batch``."""
     _fields_ = [(k, ctypes.c_int32) for k in ("num_images", "total_boxes", "total_humans", "max_boxes_per_image", "feat_hw")] + \
-               [("total_cells", c_int64), ("total_pairs", c_int64)] + \
+               [("total_cells", c_int64), ("total_pairs", c_int64), ("seg_bytes", c_int64)] + \
                [(k, c_void_p) for k in ("features3", "box_features", "boxes", "box_off", "n_h", "hum_off", "cell_off",
                                         "pair_off", "hw")]
 
@@ -219,10 +219,13 @@ class HeadPlan(ctypes.Structure):
 HEAD_PRECISE_LOGITS = 1
 HEAD_WANT_TAPS = 2
 HEAD_PROFILE = 4
+HEAD_GRAPH = 8
 _SIGNATURES["skg_head_profile_get"] = (I, [I, ctypes.POINTER(c_char_p), ctypes.POINTER(I), ctypes.POINTER(c_float)])
 _SIGNATURES["skg_head_buffer_name"] = (c_char_p, [I])
 _SIGNATURES["skg_head_plan"] = (I, [ctypes.POINTER(HeadWeights), ctypes.POINTER(HeadBatch), I, ctypes.POINTER(HeadPlan)])
 _SIGNATURES["skg_head_forward"] = (I, [ctypes.POINTER(HeadWeights), ctypes.POINTER(HeadBatch), I, P, L, P])
+_SIGNATURES["skg_head_graph_stats"] = (None, [ctypes.POINTER(ctypes.c_longlong)] * 3)
+_SIGNATURES["skg_segments_pack"] = (c_int64, [P, P, P, I, P, L, P, P])
 _SIGNATURES["skg_post_count_host"] = (c_int64, [P, I, P, P, P, P, I, P])
 
 _buffer_names = None
@@ -240,3 +243,10 @@ def head_buffer_names():
             names.append(s.decode()); i += 1
         _buffer_names = names
     return _buffer_names
+
+
+def graph_stats():
+    """(replays, captures, plain launches) of the skg_head_forward graph cache on this thread."""
+    a, b, c = ctypes.c_longlong(), ctypes.c_longlong(), ctypes.c_longlong()
+    lib().skg_head_graph_stats(ctypes.byref(a), ctypes.byref(b), ctypes.byref(c))
+    return a.value, b.value, c.value

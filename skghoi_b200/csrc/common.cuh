@@ -15,6 +15,7 @@ namespace skg {
 // last error text, retrievable through skg_last_error() (no exceptions cross the C boundary)
 void set_error(const char* fmt, ...);
 int check_launch(const char* what);
+void add_launches(long long n);   // adjusts skg_launch_count (graph capture / replay)
 
 #define SKG_REQUIRE(cond, ...)                                  \
   do {                                                          \

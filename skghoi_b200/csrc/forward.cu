@@ -18,7 +18,7 @@
 namespace skg {
 
 enum Buf : int {
-  B_SPLITK0 = 0, B_SPLITK1, B_ENC, B_X, B_Y, B_XKEEP, B_YKEEP, B_CELL2PAIR, B_CELL_HROW, B_CELL_OROW, B_CELL_IMG, B_PAIR2CELL, B_NANFLAG,
+  B_SPLITK0 = 0, B_SPLITK1, B_SEG, B_ENC, B_X, B_Y, B_XKEEP, B_YKEEP, B_CELL2PAIR, B_CELL_HROW, B_CELL_OROW, B_CELL_IMG, B_PAIR2CELL, B_NANFLAG,
   B_S1, B_S2, B_SP, B_XB, B_X1, B_BOX2HUM, B_OIN, B_HN32, B_HN16, B_ON32, B_ON16, B_HPROJ, B_OPROJ, B_GFEAT, B_G32,
   B_GT, B_HATT, B_SRAW, B_HOS, B_HSO, B_HG, B_DOTPART, B_Z, B_ADJ, B_PRE, B_ENC16, B_ENC32, B_U2H, B_U2O, B_H2, B_FEAT,
   B_TMP, B_LOGITS, B_COUNT
@@ -26,7 +26,7 @@ enum Buf : int {
 static_assert(B_COUNT <= SKG_HEAD_NUM_BUFFERS, "raise SKG_HEAD_NUM_BUFFERS");
 
 static const char* kBufNames[B_COUNT] = {
-  "splitk_main", "splitk_side", "enc", "x", "y", "x_keep", "y_keep", "cell2pair", "cell_hrow", "cell_orow", "cell_img", "pair2cell", "nan_flag",
+  "splitk_main", "splitk_side", "seg", "enc", "x", "y", "x_keep", "y_keep", "cell2pair", "cell_hrow", "cell_orow", "cell_img", "pair2cell", "nan_flag",
   "s1", "s2", "sp", "xb", "x1", "box2hum", "o_in", "hN32", "hN16", "oN32", "oN16", "hproj", "oproj", "gfeat", "g32",
   "Gt", "H_att", "S_raw", "H_os", "H_so", "H_g", "dot_part", "Z", "adjacency", "pre", "enc16", "enc32", "U2h", "U2o", "H2", "feat",
   "tmp", "logits"};
@@ -51,6 +51,7 @@ static int make_plan(const skg_head_weights& w, const skg_head_batch& b, int fla
   // must be zero before the first call on a workspace and are left zero by every call (skg_gemm_bf16_splitk)
   const int64_t sk_elems = skg_gemm_splitk_scratch_bytes(0, 0) / 4;
   set(B_SPLITK0, 1, sk_elems, 4); set(B_SPLITK1, 1, sk_elems, 4);
+  set(B_SEG, 1, b.seg_bytes > 0 ? b.seg_bytes : 0, 1);
   set(B_ENC, C, 46, 4); set(B_X, C, 1, 8); set(B_Y, C, 1, 8); set(B_XKEEP, P, 1, 8); set(B_YKEEP, P, 1, 8);
   set(B_CELL2PAIR, C, 1, 4); set(B_CELL_HROW, C, 1, 4); set(B_CELL_OROW, C, 1, 4); set(B_CELL_IMG, C, 1, 4);
   set(B_PAIR2CELL, P, 1, 4); set(B_NANFLAG, B > 0 ? B : 1, 1, 4);
@@ -75,7 +76,7 @@ static int make_plan(const skg_head_weights& w, const skg_head_batch& b, int fla
 
 // library-owned side streams + an event pool for fork / join (per host thread and device)
 struct SideStream {
-  static constexpr int kStreams = 3, kEvents = 16;
+  static constexpr int kStreams = 4, kEvents = 18;   // s[3] stands in for the legacy default stream (cannot be captured)
   int dev = -1;
   cudaStream_t s[kStreams] = {};
   cudaEvent_t ev[kEvents] = {};
@@ -96,7 +97,7 @@ static int get_side(SideStream** out) {
     for (auto& e : g_side.ev) SKG_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
     g_side.dev = dev;
   }
-  g_side.next = 0;
+  g_side.next = 2;                                    // ev[0], ev[1] belong to the graph wrapper's fork / join
   *out = &g_side;
   return SKG_OK;
 }
@@ -154,9 +155,107 @@ extern "C" int skg_head_plan(const skg_head_weights* weights, const skg_head_bat
   return make_plan(*weights, *batch, flags, plan);
 }
 
+static int enqueue_forward(const skg_head_weights* wp, const skg_head_batch* bp, int flags, void* workspace,
+                           int64_t workspace_bytes, cudaStream_t st);
+
+// ---- CUDA-graph cache -------------------------------------------------------------------------------------------
+// A step is ~35 small launches on four streams; replaying it as a graph removes the per-launch host cost and the
+// inter-kernel launch gaps.  Key = every byte that reaches a launch (weights struct, batch struct incl. the input
+// pointers, flags, workspace): the second call with an identical key captures the graph, later calls replay it.
+// Any difference (new shapes, inputs at other addresses) falls back to plain stream launches.
+struct GraphEntry {
+  skg_head_weights w; skg_head_batch b; int flags; void* ws; int64_t ws_bytes; int dev;
+  int seen = 0;
+  cudaGraphExec_t exec = nullptr;
+  long long launches = 0;
+  unsigned long long stamp = 0;
+};
+static thread_local GraphEntry g_graphs[8];
+static thread_local unsigned long long g_graph_clock = 0;
+static thread_local long long g_graph_stats[3] = {0, 0, 0};   // replays, captures, plain launches
+
+static bool same_key(const GraphEntry& e, const skg_head_weights& w, const skg_head_batch& b, int flags, void* ws, int64_t wsb, int dev) {
+  return e.seen > 0 && e.flags == flags && e.ws == ws && e.ws_bytes == wsb && e.dev == dev && memcmp(&e.w, &w, sizeof(w)) == 0 &&
+         memcmp(&e.b, &b, sizeof(b)) == 0;
+}
+
 extern "C" int skg_head_forward(const skg_head_weights* wp, const skg_head_batch* bp, int flags, void* workspace,
                                 int64_t workspace_bytes, cudaStream_t st) {
   SKG_REQUIRE(wp && bp && workspace, "null pointer argument");
+  if (!(flags & SKG_HEAD_GRAPH) || (flags & SKG_HEAD_PROFILE)) return enqueue_forward(wp, bp, flags, workspace, workspace_bytes, st);
+  cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
+  if (cudaStreamIsCapturing(st, &cs) != cudaSuccess || cs != cudaStreamCaptureStatusNone)
+    return enqueue_forward(wp, bp, flags, workspace, workspace_bytes, st);   // the caller is capturing: just enqueue
+  int dev = 0;
+  SKG_CUDA(cudaGetDevice(&dev));
+  if (st == nullptr || st == cudaStreamLegacy) {
+    // the legacy default stream cannot be captured: run the step on a library stream forked from / joined into it
+    SideStream* sd = nullptr;
+    SKG_TRY(get_side(&sd));
+    cudaStream_t run = sd->s[3];
+    cudaEvent_t e0 = sd->ev[0], e1 = sd->ev[1];
+    SKG_CUDA(cudaEventRecord(e0, st));
+    SKG_CUDA(cudaStreamWaitEvent(run, e0, 0));
+    const int rc = skg_head_forward(wp, bp, flags, workspace, workspace_bytes, run);
+    SKG_CUDA(cudaEventRecord(e1, run));
+    SKG_CUDA(cudaStreamWaitEvent(st, e1, 0));
+    return rc;
+  }
+  GraphEntry* hit = nullptr; GraphEntry* victim = &g_graphs[0];
+  for (auto& e : g_graphs) {
+    if (same_key(e, *wp, *bp, flags, workspace, workspace_bytes, dev)) { hit = &e; break; }
+    if (e.stamp < victim->stamp) victim = &e;
+  }
+  if (hit && hit->exec) {
+    hit->stamp = ++g_graph_clock;
+    SKG_CUDA(cudaGraphLaunch(hit->exec, st));
+    add_launches(hit->launches);
+    g_graph_stats[0]++;
+    return SKG_OK;
+  }
+  if (!hit) {   // first sighting: plain launches (also sets the kernels' function attributes outside any capture)
+    if (victim->exec) { cudaGraphExecDestroy(victim->exec); victim->exec = nullptr; }
+    victim->w = *wp; victim->b = *bp; victim->flags = flags; victim->ws = workspace; victim->ws_bytes = workspace_bytes;
+    victim->dev = dev; victim->seen = 1; victim->stamp = ++g_graph_clock;
+    g_graph_stats[2]++;
+    return enqueue_forward(wp, bp, flags, workspace, workspace_bytes, st);
+  }
+  // second sighting: capture, instantiate, launch
+  hit->stamp = ++g_graph_clock;
+  const long long l0 = skg_launch_count();
+  if (cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal) != cudaSuccess) {
+    cudaGetLastError();
+    return enqueue_forward(wp, bp, flags, workspace, workspace_bytes, st);
+  }
+  const int rc = enqueue_forward(wp, bp, flags, workspace, workspace_bytes, st);
+  cudaGraph_t graph = nullptr;
+  const cudaError_t ce = cudaStreamEndCapture(st, &graph);
+  const long long captured = skg_launch_count() - l0;
+  add_launches(-captured);                       // nothing ran yet: count launches when the graph is launched
+  if (rc != SKG_OK || ce != cudaSuccess || !graph) {
+    cudaGetLastError();
+    if (graph) cudaGraphDestroy(graph);
+    hit->seen = 0;
+    if (rc != SKG_OK) return rc;
+    return enqueue_forward(wp, bp, flags, workspace, workspace_bytes, st);
+  }
+  cudaGraphExec_t exec = nullptr;
+  const cudaError_t ie = cudaGraphInstantiate(&exec, graph, 0);
+  cudaGraphDestroy(graph);
+  if (ie != cudaSuccess || !exec) {
+    cudaGetLastError();
+    hit->seen = 0;
+    return enqueue_forward(wp, bp, flags, workspace, workspace_bytes, st);
+  }
+  hit->exec = exec; hit->launches = captured;
+  g_graph_stats[1]++;
+  SKG_CUDA(cudaGraphLaunch(exec, st));
+  add_launches(captured);
+  return SKG_OK;
+}
+
+static int enqueue_forward(const skg_head_weights* wp, const skg_head_batch* bp, int flags, void* workspace,
+                           int64_t workspace_bytes, cudaStream_t st) {
   const skg_head_weights& w = *wp;
   const skg_head_batch& b = *bp;
   skg_head_plan_t plan;
@@ -344,6 +443,12 @@ extern "C" int skg_head_forward(const skg_head_weights* wp, const skg_head_batch
   return SKG_OK;
 }
 
+extern "C" void skg_head_graph_stats(long long* replays, long long* captures, long long* plain) {
+  if (replays) *replays = g_graph_stats[0];
+  if (captures) *captures = g_graph_stats[1];
+  if (plain) *plain = g_graph_stats[2];
+}
+
 extern "C" int skg_head_profile_get(int i, const char** name, int* stream_id, float* us) {
   const Prof& p = g_prof;
   if (i < 0 || i >= p.n) return -1;
@@ -371,4 +476,41 @@ extern "C" int64_t skg_post_count_host(const int32_t* verb_len, int num_obj_cls,
     total += e;
   }
   return total;
+}
+
+// Host-side packing of the per-batch segment table (engine.Segments): one buffer, one H2D copy.
+//   layout: cell_off i64[B+1] | pair_off i64[B+1] | box_off i32[B+1] | n_h i32[B] | hum_off i32[B+1] | hw f32[3B] | pad to 16
+// n_h_eff[b] = 0 for images the reference skips (n_h == 0 or n <= 1, head.py:829-839).  offsets[6] receive the byte offsets
+// of the six arrays, totals[5] = boxes, humans, cells, pairs, max boxes per image.  Returns the bytes used or -1.
+extern "C" int64_t skg_segments_pack(const int64_t* n, const int64_t* n_h, const double* hw, int num_images, void* out,
+                                     int64_t out_bytes, int64_t* offsets, int64_t* totals) {
+  const int64_t B = num_images;
+  if (B < 0 || !out || !offsets || !totals || (B > 0 && (!n || !n_h || !hw))) { set_error("null pointer argument"); return -1; }
+  const int64_t o_cell = 0, o_pair = o_cell + 8 * (B + 1), o_box = o_pair + 8 * (B + 1), o_nh = o_box + 4 * (B + 1),
+                o_hum = o_nh + 4 * B, o_hw = o_hum + 4 * (B + 1);
+  const int64_t used = (o_hw + 12 * B + 15) / 16 * 16;
+  if (out_bytes < used) { set_error("segment buffer too small: %lld < %lld", (long long)out_bytes, (long long)used); return -1; }
+  uint8_t* base = reinterpret_cast<uint8_t*>(out);
+  int64_t* cell_off = reinterpret_cast<int64_t*>(base + o_cell);
+  int64_t* pair_off = reinterpret_cast<int64_t*>(base + o_pair);
+  int32_t* box_off = reinterpret_cast<int32_t*>(base + o_box);
+  int32_t* nh = reinterpret_cast<int32_t*>(base + o_nh);
+  int32_t* hum_off = reinterpret_cast<int32_t*>(base + o_hum);
+  float* hwf = reinterpret_cast<float*>(base + o_hw);
+  int64_t boxes = 0, humans = 0, cells = 0, pairs = 0, max_n = 0;
+  for (int64_t b = 0; b < B; ++b) {
+    if (n_h[b] < 0 || n_h[b] > n[b]) { set_error("n_h must satisfy 0 <= n_h <= n"); return -1; }
+    cell_off[b] = cells; pair_off[b] = pairs; box_off[b] = (int32_t)boxes; hum_off[b] = (int32_t)humans;
+    const int64_t h = (n_h[b] == 0 || n[b] <= 1) ? 0 : n_h[b];
+    nh[b] = (int32_t)h;
+    boxes += n[b]; humans += h; cells += h * n[b]; pairs += h * (n[b] > 0 ? n[b] - 1 : 0);
+    if (n[b] > max_n) max_n = n[b];
+    hwf[3 * b] = (float)hw[2 * b]; hwf[3 * b + 1] = (float)hw[2 * b + 1]; hwf[3 * b + 2] = (float)(hw[2 * b] * hw[2 * b + 1]);
+  }
+  if (boxes >= ((int64_t)1 << 31) || cells >= ((int64_t)1 << 31)) { set_error("too many boxes / grid cells in one batch"); return -1; }
+  cell_off[B] = cells; pair_off[B] = pairs; box_off[B] = (int32_t)boxes; hum_off[B] = (int32_t)humans;
+  for (int64_t i = o_hw + 12 * B; i < used; ++i) base[i] = 0;
+  offsets[0] = o_cell; offsets[1] = o_pair; offsets[2] = o_box; offsets[3] = o_nh; offsets[4] = o_hum; offsets[5] = o_hw;
+  totals[0] = boxes; totals[1] = humans; totals[2] = cells; totals[3] = pairs; totals[4] = max_n;
+  return used;
 }

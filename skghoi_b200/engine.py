@@ -16,41 +16,51 @@ from . import _lib
 
 class Segments:
     """Per-batch segment table.  For image b with n boxes (n_h humans first):
-    cells N2 = n_h*n (row-major human x box grid), valid pairs P = n_h*(n-1)."""
+    cells N2 = n_h*n (row-major human x box grid), valid pairs P = n_h*(n-1).
+    Packed on the host by skg_segments_pack into ONE buffer (one H2D copy); ``device=None`` defers the copy
+    (``upload``) so the table can live at a fixed place inside the step's workspace."""
 
-    def __init__(self, n_h: Sequence[int], n: Sequence[int], image_shapes: Sequence[Tuple[int, int]], device):
+    def __init__(self, n_h: Sequence[int], n: Sequence[int], image_shapes: Sequence[Tuple[int, int]], device=None):
         B = len(n)
         assert len(n_h) == B and len(image_shapes) == B
-        nh = np.asarray(n_h, dtype=np.int64); nn_ = np.asarray(n, dtype=np.int64)
-        if B and (np.any(nh > nn_) or np.any(nh < 0)):
-            raise ValueError("n_h must satisfy 0 <= n_h <= n")
+        nn_ = np.ascontiguousarray(n, dtype=np.int64); nh = np.ascontiguousarray(n_h, dtype=np.int64)
+        hw = np.ascontiguousarray(image_shapes, dtype=np.float64).reshape(B, 2)
+        nbytes = (40 * B + 24 + 15) // 16 * 16
+        # pinned: the H2D copy is then truly asynchronous (a pageable source makes torch synchronise the stream);
+        # torch's caching host allocator keeps the block alive until the copy has executed
+        self.host = torch.empty(nbytes, dtype=torch.uint8, pin_memory=torch.cuda.is_available())
+        raw = self.host.numpy()
+        offs = np.empty(6, dtype=np.int64); tot = np.empty(5, dtype=np.int64)
+        used = _lib.lib().skg_segments_pack(nn_.ctypes.data, nh.ctypes.data, hw.ctypes.data, B, raw.ctypes.data, nbytes,
+                                            offs.ctypes.data, tot.ctypes.data)
+        if used < 0:
+            raise ValueError(_lib.lib().skg_last_error().decode())
         self.B = B
-        self.n_h = nh; self.n = nn_
-        self.box_off = np.concatenate([[0], np.cumsum(nn_)]).astype(np.int64)
-        self.hum_off = np.concatenate([[0], np.cumsum(nh)]).astype(np.int64)
-        self.cell_off = np.concatenate([[0], np.cumsum(nh * nn_)]).astype(np.int64)
-        self.pair_off = np.concatenate([[0], np.cumsum(nh * np.maximum(nn_ - 1, 0))]).astype(np.int64)
-        self.total_boxes = int(self.box_off[-1]); self.total_humans = int(self.hum_off[-1])
-        self.total_cells = int(self.cell_off[-1]); self.total_pairs = int(self.pair_off[-1])
-        if self.total_cells >= 2 ** 31:
-            raise ValueError("too many grid cells in one batch")
-        hw = np.asarray([[float(h), float(w), float(h * w)] for h, w in image_shapes], dtype=np.float32).reshape(B, 3)
-        # one packed host buffer -> one H2D copy
-        i32 = np.concatenate([self.box_off, nh, self.hum_off]).astype(np.int32)
-        i64 = np.concatenate([self.cell_off, self.pair_off]).astype(np.int64)
-        raw = np.concatenate([i64.view(np.uint8), i32.view(np.uint8), hw.reshape(-1).view(np.uint8)])
-        pad = (-len(raw)) % 16
-        raw = np.concatenate([raw, np.zeros(pad, dtype=np.uint8)])
-        self.host = torch.from_numpy(raw)
-        self.dev = self.host.to(device, non_blocking=False)
-        o = 0
-        self.d_cell_off = self.dev[o:o + 8 * (B + 1)].view(torch.int64); o += 8 * (B + 1)
-        self.d_pair_off = self.dev[o:o + 8 * (B + 1)].view(torch.int64); o += 8 * (B + 1)
-        self.d_box_off = self.dev[o:o + 4 * (B + 1)].view(torch.int32); o += 4 * (B + 1)
-        self.d_n_h = self.dev[o:o + 4 * B].view(torch.int32); o += 4 * B
-        self.d_hum_off = self.dev[o:o + 4 * (B + 1)].view(torch.int32); o += 4 * (B + 1)
-        self.d_hw = self.dev[o:o + 12 * B].view(torch.float32)
-        self.device = self.dev.device
+        self.n = nn_
+        self.offs = [int(o) for o in offs]
+        o = self.offs
+        self.cell_off = np.frombuffer(raw, np.int64, B + 1, o[0]); self.pair_off = np.frombuffer(raw, np.int64, B + 1, o[1])
+        self.box_off = np.frombuffer(raw, np.int32, B + 1, o[2]).astype(np.int64)
+        self.n_h = np.frombuffer(raw, np.int32, B, o[3]).astype(np.int64)
+        self.hum_off = np.frombuffer(raw, np.int32, B + 1, o[4]).astype(np.int64)
+        self.total_boxes, self.total_humans, self.total_cells, self.total_pairs, self.max_n = (int(t) for t in tot)
+        self.nbytes = int(used)
+        self.dev = None
+        if device is not None:
+            self.upload(torch.empty(self.nbytes, dtype=torch.uint8, device=device))
+
+    def upload(self, dst: Tensor) -> None:
+        """Copies the packed table into ``dst`` (uint8 CUDA tensor of ``nbytes``) on the current stream."""
+        B, o = self.B, self.offs
+        dst.copy_(self.host, non_blocking=True)
+        self.dev = dst
+        self.d_cell_off = dst[o[0]:o[0] + 8 * (B + 1)].view(torch.int64)
+        self.d_pair_off = dst[o[1]:o[1] + 8 * (B + 1)].view(torch.int64)
+        self.d_box_off = dst[o[2]:o[2] + 4 * (B + 1)].view(torch.int32)
+        self.d_n_h = dst[o[3]:o[3] + 4 * B].view(torch.int32)
+        self.d_hum_off = dst[o[4]:o[4] + 4 * (B + 1)].view(torch.int32)
+        self.d_hw = dst[o[5]:o[5] + 12 * B].view(torch.float32)
+        self.device = dst.device
 
 
 def enumerate_pairs(box_coords: List[Tensor], n_h: Sequence[int], image_shapes: Sequence[Tuple[int, int]],
@@ -358,7 +368,7 @@ class _Run(dict):
         p = self._plan
         rows, cols, es, off = int(p.rows[i]), int(p.cols[i]), int(p.elem_size[i]), int(p.offset[i])
         dt = torch.int64 if name in _INT64_BUFS else torch.int32 if name in _INT32_BUFS else \
-            torch.bfloat16 if es == 2 else torch.float32
+            torch.bfloat16 if es == 2 else torch.uint8 if es == 1 else torch.float32
         t = self._ws[off:off + rows * cols * es].view(dt)
         t = t.view(rows) if cols == 1 and (name in _INT64_BUFS or name in _INT32_BUFS or name == "adjacency") else t.view(rows, cols)
         self[name] = t
@@ -372,7 +382,7 @@ class _Run(dict):
 
 
 def head_forward(ih, features3: Tensor, image_shapes, box_features: Tensor, boxes_cat: Tensor, meta: dict,
-                 want_taps: bool = False, precise_logits: bool = True, profile: bool = False) -> dict:
+                 want_taps: bool = False, precise_logits: bool = True, profile: bool = False, graph: bool = True) -> dict:
     """Runs the whole pair path for a batch through ONE C-ABI call (skg_head_forward, csrc/forward.cu).
     Inputs: features['3'] [B,256,h,w] fp32, pooled box features [sum n, 256, 7, 7] fp32, concatenated boxes
     [sum n, 4] fp32 (all CUDA), host ``meta``.  Returns named views into the step's workspace: logits [P,118]
@@ -386,7 +396,7 @@ def head_forward(ih, features3: Tensor, image_shapes, box_features: Tensor, boxe
         raise IndexError("index out of range in self")   # head.py:572: box index addresses the 80-row entity table
     # images the reference skips (head.py:829-839) contribute no cells: treat them as n_h = 0
     n_h_eff = [0 if (h == 0 or k <= 1) else h for h, k in zip(n_h, n)]
-    seg = Segments(n_h_eff, n, image_shapes, dev)
+    seg = Segments(n_h_eff, n, image_shapes)
     tr = G.transh_head.transh
     if tr.ent_embeddings.weight.device != dev:
         tr.to(dev)
@@ -401,20 +411,25 @@ def head_forward(ih, features3: Tensor, image_shapes, box_features: Tensor, boxe
     pk.fc_bias(ent, G.human_idx)
     b = _lib.HeadBatch()
     b.num_images, b.total_boxes, b.total_humans = seg.B, seg.total_boxes, seg.total_humans
-    b.max_boxes_per_image = int(max(n)) if len(n) else 0
+    b.max_boxes_per_image = seg.max_n
+    b.seg_bytes = seg.nbytes
     b.feat_hw = int(f3.shape[2] * f3.shape[3]) if f3.dim() == 4 else 0
     b.total_cells, b.total_pairs = seg.total_cells, seg.total_pairs
     b.features3, b.box_features, b.boxes = f3.data_ptr(), bf.data_ptr(), boxes_cat.data_ptr()
-    b.box_off, b.n_h, b.hum_off = seg.d_box_off.data_ptr(), seg.d_n_h.data_ptr(), seg.d_hum_off.data_ptr()
-    b.cell_off, b.pair_off, b.hw = seg.d_cell_off.data_ptr(), seg.d_pair_off.data_ptr(), seg.d_hw.data_ptr()
     flags = (_lib.HEAD_PRECISE_LOGITS if precise_logits else 0) | (_lib.HEAD_WANT_TAPS if want_taps else 0)
     if profile:
         flags |= _lib.HEAD_PROFILE
+    elif graph:
+        flags |= _lib.HEAD_GRAPH
     plan = _lib.HeadPlan()
     import ctypes
     _lib.call("skg_head_plan", ctypes.byref(w), ctypes.byref(b), flags, ctypes.byref(plan))
     with torch.cuda.device(dev):
         ws = _workspace(dev, int(plan.total_bytes))
+        so = int(plan.offset[_lib.head_buffer_names().index("seg")])
+        seg.upload(ws[so:so + seg.nbytes])          # fixed place in the workspace: stable pointers for the graph cache
+        b.box_off, b.n_h, b.hum_off = seg.d_box_off.data_ptr(), seg.d_n_h.data_ptr(), seg.d_hum_off.data_ptr()
+        b.cell_off, b.pair_off, b.hw = seg.d_cell_off.data_ptr(), seg.d_pair_off.data_ptr(), seg.d_hw.data_ptr()
         try:
             _lib.call("skg_head_forward", ctypes.byref(w), ctypes.byref(b), flags, _lib.ptr(ws), ws.numel(), _lib.stream_ptr(dev))
         except Exception:

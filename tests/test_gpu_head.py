@@ -60,3 +60,25 @@ def test_head_core_logits_vs_reference(case, precise):
     assert st_s["max_abs"] <= 1e-2 * st_s["ref_max"]
     if precise:
         assert ok_p and ok_s, (st_p, st_s)      # SURVEY 8(d) per-element form
+
+
+def test_graph_replay_matches_plain_launches():
+    """The CUDA-graph cache of skg_head_forward (second identical call captures, later ones replay) must give the
+    same logits as plain stream launches, and must pick up new input CONTENTS at unchanged addresses."""
+    from skghoi_b200 import engine
+    ih = gpu_head()
+    batch = synthetic.make_batch([(3, 7), (2, 5), (4, 4)], seed=11)
+    meta = engine._host_meta(batch["box_labels"], batch["box_scores"], 49)
+    boxes_cat = torch.cat(batch["box_coords"]).to(DEV)
+    f3 = batch["features"]["3"].to(DEV); bf = batch["box_features"].to(DEV)
+    with torch.no_grad():
+        plain = engine.head_forward(ih, f3, batch["image_shapes"], bf, boxes_cat, meta, graph=False)["logits"].clone()
+        outs = [engine.head_forward(ih, f3, batch["image_shapes"], bf, boxes_cat, meta, graph=True)["logits"].clone()
+                for _ in range(4)]
+        for o in outs:
+            torch.testing.assert_close(o, plain, rtol=1e-5, atol=1e-5)     # split-K reduction order may differ in the last bit
+        bf.mul_(0.5)                                                        # same address, new contents
+        replay = engine.head_forward(ih, f3, batch["image_shapes"], bf, boxes_cat, meta, graph=True)["logits"].clone()
+        direct = engine.head_forward(ih, f3, batch["image_shapes"], bf, boxes_cat, meta, graph=False)["logits"].clone()
+    torch.testing.assert_close(replay, direct, rtol=1e-5, atol=1e-5)
+    assert float((replay - plain).abs().max()) > 1e-3

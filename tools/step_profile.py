@@ -55,13 +55,14 @@ for fn, name in ((step, "interaction_head_from_pooled"), (core, "head_forward on
     torch.cuda.synchronize(); b2b = (time.perf_counter() - t0) / N
     print("%-32s host enqueue %.3f ms | events (idle start) %.3f ms | back-to-back %.3f ms/step" % (name, host / N * 1e3, dev_ms / N, b2b * 1e3))
 
+print("graph cache (replays, captures, plain):", _lib.graph_stats())
 pr = cProfile.Profile()
 pr.enable()
 for _ in range(50):
     step()
 torch.cuda.synchronize()
 pr.disable()
-pstats.Stats(pr).sort_stats("cumulative").print_stats(28)
+pstats.Stats(pr).sort_stats("tottime").print_stats(45)
 
 # per-launch device timeline of skg_head_forward inside the real pipeline (events after each launch; warm caches)
 boxes_cat = torch.cat(d["boxes"])
