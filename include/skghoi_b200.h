@@ -235,6 +235,16 @@ int skg_post_offsets(const int32_t* verb_off, const int64_t* labels, const float
 int skg_gather_pair_boxes(const float* boxes, const skg_post_tables* tables, int64_t pairs, float* boxes_h,
                           float* boxes_o, cudaStream_t stream);
 
+/* skg_post_offsets + skg_postprocess + skg_gather_pair_boxes as ONE host call (InteractionHead.postprocess for a batch,
+ * head.py:291-337, 975-976).  tables->box_cnt / box_prefix / hum_base are ignored and built into the caller's scratch:
+ * scratch_i32 [2 * total_boxes], scratch_i64 [total_humans + 2 * num_images + 1]. */
+int skg_head_post(const float* logits, int ld_logits, int num_cls, const skg_post_tables* tables, const float* boxes,
+                  int num_images, int total_boxes, int total_humans, int64_t pairs, float prior_power,
+                  const float* gt_labels, int64_t total_entries, int32_t* scratch_i32, int64_t* scratch_i64,
+                  int64_t* out_index, int64_t* out_pred, float* out_scores, float* out_prior, float* out_weights,
+                  float* out_labels, float* out_unary, int64_t* out_object, float* boxes_h, float* boxes_o,
+                  cudaStream_t stream);
+
 /* compute_prior_scores (head.py:721-767): dense prior [2, P, num_cls]. */
 int skg_prior_dense(const skg_post_tables* tables, int64_t pairs, int num_cls, float prior_power, float* prior,
                     cudaStream_t stream);
@@ -293,7 +303,7 @@ typedef struct skg_head_batch {
   const int64_t* cell_off; const int64_t* pair_off; const float* hw;
 } skg_head_batch;
 
-#define SKG_HEAD_NUM_BUFFERS 48
+#define SKG_HEAD_NUM_BUFFERS 64
 typedef struct skg_head_plan_t {
   int64_t total_bytes;
   int32_t num_buffers;

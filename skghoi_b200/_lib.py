@@ -121,6 +121,7 @@ class PostTables(ctypes.Structure):
 
 
 _SIGNATURES["skg_postprocess"] = (I, [P, I, I, ctypes.POINTER(PostTables), L, F, P, L, P, P, P, P, P, P, P, P, P])
+_SIGNATURES["skg_head_post"] = (I, [P, I, I, ctypes.POINTER(PostTables), P, I, I, I, L, F, P, L, P, P, P, P, P, P, P, P, P, P, P, P, P])
 _SIGNATURES["skg_prior_dense"] = (I, [ctypes.POINTER(PostTables), L, I, F, P, P])
 _SIGNATURES["skg_post_offsets"] = (I, [P, P, P, P, P, I, P, P, P, P, P, P])
 _SIGNATURES["skg_gather_pair_boxes"] = (I, [P, ctypes.POINTER(PostTables), L, P, P, P])
@@ -206,7 +207,7 @@ class HeadBatch(ctypes.Structure):
                                         "pair_off", "hw")]
 
 
-HEAD_NUM_BUFFERS = 48
+HEAD_NUM_BUFFERS = 64
 
 
 class HeadPlan(ctypes.Structure):

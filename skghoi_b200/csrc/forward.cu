@@ -21,7 +21,7 @@ enum Buf : int {
   B_SPLITK0 = 0, B_SPLITK1, B_SEG, B_ENC, B_X, B_Y, B_XKEEP, B_YKEEP, B_CELL2PAIR, B_CELL_HROW, B_CELL_OROW, B_CELL_IMG, B_PAIR2CELL, B_NANFLAG,
   B_S1, B_S2, B_SP, B_XB, B_X1, B_BOX2HUM, B_OIN, B_HN32, B_HN16, B_ON32, B_ON16, B_HPROJ, B_OPROJ, B_GFEAT, B_G32,
   B_GT, B_HATT, B_SRAW, B_HOS, B_HSO, B_HG, B_DOTPART, B_Z, B_ADJ, B_PRE, B_ENC16, B_ENC32, B_U2H, B_U2O, B_H2, B_FEAT,
-  B_TMP, B_LOGITS, B_COUNT
+  B_TMP, B_LOGITS, B_POST32, B_POST64, B_COUNT
 };
 static_assert(B_COUNT <= SKG_HEAD_NUM_BUFFERS, "raise SKG_HEAD_NUM_BUFFERS");
 
@@ -29,7 +29,7 @@ static const char* kBufNames[B_COUNT] = {
   "splitk_main", "splitk_side", "seg", "enc", "x", "y", "x_keep", "y_keep", "cell2pair", "cell_hrow", "cell_orow", "cell_img", "pair2cell", "nan_flag",
   "s1", "s2", "sp", "xb", "x1", "box2hum", "o_in", "hN32", "hN16", "oN32", "oN16", "hproj", "oproj", "gfeat", "g32",
   "Gt", "H_att", "S_raw", "H_os", "H_so", "H_g", "dot_part", "Z", "adjacency", "pre", "enc16", "enc32", "U2h", "U2o", "H2", "feat",
-  "tmp", "logits"};
+  "tmp", "logits", "post_i32", "post_i64"};
 
 static inline int64_t align_up(int64_t v, int64_t a) { return (v + a - 1) / a * a; }
 
@@ -65,6 +65,7 @@ static int make_plan(const skg_head_weights& w, const skg_head_batch& b, int fla
   set(B_ENC16, NH + NB, R, 2); set(B_ENC32, (flags & SKG_HEAD_WANT_TAPS) ? NH + NB : 0, R, 4);
   set(B_U2H, NH, R, 4); set(B_U2O, NB, R, 4); set(B_H2, C, R, 2);
   set(B_FEAT, P, precise ? 4 * R : 2 * R, 2); set(B_TMP, precise ? P : 0, w.n_logit_pad, 4); set(B_LOGITS, P, w.n_logit, 4);
+  set(B_POST32, 2 * NB, 1, 4); set(B_POST64, NH + 2 * B + 1, 1, 8);   // scratch of skg_head_post
   int64_t off = 0;
   for (int i = 0; i < B_COUNT; ++i) {
     p->offset[i] = off;

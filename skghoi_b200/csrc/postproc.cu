@@ -278,3 +278,27 @@ extern "C" int skg_gather_pair_boxes(const float* boxes, const skg_post_tables* 
                                                                            (float4*)boxes_o);
   return check_launch("gather_pair_boxes_kernel");
 }
+
+// The whole post-processing of a batch as one host call: output offsets (device), per-entry / per-pair outputs, pair boxes.
+// scratch_i32 [2 * boxes], scratch_i64 [humans + 2 * B + 1] are caller-owned (the forward workspace has room for them).
+extern "C" int skg_head_post(const float* logits, int ld_logits, int num_cls, const skg_post_tables* tables, const float* boxes,
+                             int num_images, int total_boxes, int total_humans, int64_t pairs, float prior_power,
+                             const float* gt_labels, int64_t total_entries, int32_t* scratch_i32, int64_t* scratch_i64,
+                             int64_t* out_index, int64_t* out_pred, float* out_scores, float* out_prior, float* out_weights,
+                             float* out_labels, float* out_unary, int64_t* out_object, float* boxes_h, float* boxes_o,
+                             cudaStream_t stream) {
+  if (pairs == 0 || num_images == 0) return SKG_OK;
+  SKG_REQUIRE(tables && scratch_i32 && scratch_i64, "null pointer argument");
+  skg_post_tables t = *tables;
+  int32_t* box_cnt = scratch_i32; int32_t* box_prefix = scratch_i32 + total_boxes;
+  int64_t* hum_base = scratch_i64; int64_t* img_entries = scratch_i64 + total_humans; int64_t* img_base = img_entries + num_images;
+  int rc = skg_post_offsets(t.verb_off, t.labels, t.scores, t.box_off, t.hum_off, num_images, box_cnt, box_prefix, hum_base,
+                            img_entries, img_base, stream);
+  if (rc) return rc;
+  t.box_cnt = box_cnt; t.box_prefix = box_prefix; t.hum_base = hum_base;
+  rc = skg_postprocess(logits, ld_logits, num_cls, &t, pairs, prior_power, gt_labels, total_entries, out_index, out_pred,
+                       out_scores, out_prior, out_weights, out_labels, out_unary, out_object, stream);
+  if (rc) return rc;
+  if (boxes_h && boxes_o) rc = skg_gather_pair_boxes(boxes, &t, pairs, boxes_h, boxes_o, stream);
+  return rc;
+}

@@ -339,8 +339,8 @@ def _host_meta(box_labels: List[Tensor], box_scores: Optional[List[Tensor]], hum
     return dict(n=n, n_h=n_h, labels=labels, scores=scores)
 
 
-_INT64_BUFS = {"x", "y", "x_keep", "y_keep"}
-_INT32_BUFS = {"cell2pair", "cell_hrow", "cell_orow", "cell_img", "pair2cell", "nan_flag", "box2hum"}
+_INT64_BUFS = {"x", "y", "x_keep", "y_keep", "post_i64"}
+_INT32_BUFS = {"cell2pair", "cell_hrow", "cell_orow", "cell_img", "pair2cell", "nan_flag", "box2hum", "post_i32"}
 _workspaces = {}
 
 
@@ -571,13 +571,38 @@ def ctypes_byref(x):
     return ctypes.byref(x)
 
 
+def _cat_rows(parts, dtype, dev, width=None) -> Tensor:
+    """Concatenation of a per-image list along dim 0.  When the parts already are consecutive slices of ONE buffer
+    (a caller that uploads the batch in one copy and hands out per-image views) the buffer is used as is."""
+    parts = list(parts)
+    if not parts:
+        return torch.zeros((0, width) if width else (0,), dtype=dtype, device=dev)
+    first = parts[0]
+    if first.dtype == dtype and first.is_contiguous():
+        ptr, es, ok, rows = first.data_ptr(), first.element_size(), True, 0
+        for t in parts:
+            if t.dtype != dtype or not t.is_contiguous() or t.data_ptr() != ptr:
+                ok = False
+                break
+            ptr += t.numel() * es; rows += t.shape[0]
+        if ok and first._base is not None and first._base.is_contiguous():
+            base = first._base.view(-1)
+            off = (first.data_ptr() - base.data_ptr()) // es
+            n_el = (ptr - first.data_ptr()) // es
+            if base.dtype == dtype and 0 <= off and off + n_el <= base.numel():
+                flat = base[off:off + n_el]
+                return flat.view(rows, width) if width else flat
+    out = torch.cat(parts)
+    return out if out.dtype == dtype else out.to(dtype)
+
+
 def _prep_inputs(G, features, box_features, box_coords, box_labels, box_scores, meta):
     dev = box_features.device
     _lib.require_cuda(box_features, features["3"], *box_coords)
     meta = _host_meta(box_labels, box_scores, G.human_idx, meta)
-    boxes_cat = (torch.cat(list(box_coords)) if len(box_coords) else torch.zeros(0, 4, device=dev)).to(torch.float32).contiguous()
-    labels_dev = (torch.cat(list(box_labels)) if len(box_labels) else torch.zeros(0, device=dev)).to(torch.int64).contiguous()
-    scores_dev = (torch.cat(list(box_scores)) if len(box_scores) else torch.zeros(0, device=dev)).to(torch.float32).contiguous()
+    boxes_cat = _cat_rows(box_coords, torch.float32, dev, 4)
+    labels_dev = _cat_rows(box_labels, torch.int64, dev)
+    scores_dev = _cat_rows(box_scores, torch.float32, dev)
     return meta, boxes_cat, labels_dev, scores_dev
 
 
@@ -678,31 +703,50 @@ def interaction_head_from_pooled(ih, features, image_shapes, box_features, box_c
     dev = seg.device
     Pn = seg.total_pairs
     nc = G.num_cls
-    tables, keep, per_img = _post_tables(G, run, meta, labels_dev, scores_dev, with_counts=True)
-    L = int(per_img.sum())
+    vt = _verb_table(G, dev)
+    tables = _lib.PostTables()
+    tables.verb_off, tables.verb_idx = vt.d_off.data_ptr(), vt.d_idx.data_ptr()
+    tables.pair2cell, tables.cell_hrow = run["pair2cell"].data_ptr(), run["cell_hrow"].data_ptr()
+    tables.cell_orow, tables.cell_img = run["cell_orow"].data_ptr(), run["cell_img"].data_ptr()
+    tables.hum_off, tables.box_off, tables.pair_off = seg.d_hum_off.data_ptr(), seg.d_box_off.data_ptr(), seg.d_pair_off.data_ptr()
+    tables.labels, tables.scores = labels_dev.data_ptr(), scores_dev.data_ptr()
+    # entries per image (sizes the outputs): closed form on the host, no device round trip
+    lab_h = np.ascontiguousarray(meta["labels"], dtype=np.int64); sc_h = np.ascontiguousarray(meta["scores"], dtype=np.float32)
+    per_img = np.zeros(max(seg.B, 1), dtype=np.int64)
+    L = int(_lib.lib().skg_post_count_host(vt.lens32.ctypes.data, len(vt.lens32), lab_h.ctypes.data, sc_h.ctypes.data,
+                                           seg.box_off.ctypes.data, seg.n_h.ctypes.data, seg.B, per_img.ctypes.data))
+    if L < 0:
+        raise _lib.SkgError("skg_post_count_host: " + _lib.lib().skg_last_error().decode())
+    per_img = per_img[:seg.B]
     gt = _gt_labels(G, run, tables, boxes_cat, targets) if targets is not None else None
-    i64 = dict(dtype=torch.int64, device=dev); f32 = dict(dtype=torch.float32, device=dev)
-    index = torch.empty(L, **i64); pred = torch.empty(L, **i64); scores = torch.empty(L, **f32)
-    prior = torch.empty(2, L, **f32); weights = torch.empty(Pn, **f32); obj = torch.empty(Pn, **i64)
-    lab_e = torch.empty(L, **f32) if gt is not None else None
-    unary = torch.empty(Pn, **f32) if gt is not None else None
+    # two allocations hold every output of the batch; the per-image results are views into them
+    n_f = 3 * L + 9 * Pn + ((L + Pn) if gt is not None else 0)
+    out_i = torch.empty(2 * L + Pn, dtype=torch.int64, device=dev)
+    out_f = torch.empty(n_f, dtype=torch.float32, device=dev)
+    index, pred, obj = out_i[:L], out_i[L:2 * L], out_i[2 * L:]
+    scores, prior, weights = out_f[:L], out_f[L:3 * L].view(2, L), out_f[3 * L:3 * L + Pn]
+    o = 3 * L + Pn
+    bh_all, bo_all = out_f[o:o + 4 * Pn].view(Pn, 4), out_f[o + 4 * Pn:o + 8 * Pn].view(Pn, 4)
+    o += 8 * Pn
+    lab_e = out_f[o:o + L] if gt is not None else None
+    unary = out_f[o + L:o + L + Pn] if gt is not None else None
     with torch.cuda.device(dev):
-        _lib.call("skg_postprocess", _lib.ptr(run["logits"]), run["logits"].stride(0), nc, ctypes_byref(tables), Pn,
-                  1.0 if G.training else 2.8, _lib.ptr(gt), L, _lib.ptr(index), _lib.ptr(pred), _lib.ptr(scores),
-                  _lib.ptr(prior), _lib.ptr(weights), _lib.ptr(lab_e), _lib.ptr(unary), _lib.ptr(obj), _lib.stream_ptr(dev))
-    psz = seg.pair_off[1:] - seg.pair_off[:-1]
-    bh_all, bo_all = _pair_boxes(run, tables, boxes_cat)
-    bh = _split(bh_all, psz); bo = _split(bo_all, psz)
-    results = []
-    for b, (idx_b, pr_b, sc_b, pri_b, w_b, o_b) in enumerate(zip(_split(index, per_img), _split(pred, per_img),
-                                                                _split(scores, per_img), _split(prior, per_img, dim=1),
-                                                                _split(weights, psz), _split(obj, psz))):
-        r = dict(boxes_h=bh[b], boxes_o=bo[b], index=idx_b, prediction=pr_b, scores=sc_b, object=o_b, prior=pri_b,
-                 weights=w_b)
-        results.append(r)
+        _lib.call("skg_head_post", _lib.ptr(run["logits"]), run["logits"].stride(0), nc, ctypes_byref(tables), _lib.ptr(boxes_cat),
+                  seg.B, seg.total_boxes, seg.total_humans, Pn, 1.0 if G.training else 2.8, _lib.ptr(gt), L,
+                  _lib.ptr(run["post_i32"]), _lib.ptr(run["post_i64"]), _lib.ptr(index), _lib.ptr(pred), _lib.ptr(scores),
+                  _lib.ptr(prior), _lib.ptr(weights), _lib.ptr(lab_e), _lib.ptr(unary), _lib.ptr(obj), _lib.ptr(bh_all),
+                  _lib.ptr(bo_all), _lib.stream_ptr(dev))
+    psz = [int(v) for v in (seg.pair_off[1:] - seg.pair_off[:-1])]
+    esz = [int(v) for v in per_img]
+    flat = dict(out_i=out_i, out_f=out_f, L=L, P=Pn, psz=psz, esz=esz, train=gt is not None)
+    results = [dict(boxes_h=a, boxes_o=b_, index=c, prediction=d_, scores=e, object=f, prior=g, weights=h)
+               for a, b_, c, d_, e, f, g, h in zip(bh_all.split(psz), bo_all.split(psz), index.split(esz), pred.split(esz),
+                                                   scores.split(esz), obj.split(psz), prior.split(esz, dim=1),
+                                                   weights.split(psz))]
     if gt is not None:
-        for r, l_b, u_b in zip(results, _split(lab_e, per_img), _split(unary, psz)):
+        for r, l_b, u_b in zip(results, lab_e.split(esz), unary.split(psz)):
             r["labels"] = l_b; r["unary_labels"] = u_b
+    ih.__dict__["_skg_last_flat"] = flat
     ih.__dict__["_skg_last_run"] = run
     if ih.training:
         # losses (head.py:153-235); n_p averaged over ranks when distributed (one 2-float all-reduce, no barriers)
@@ -718,6 +762,55 @@ def interaction_head_from_pooled(ih, features, image_shapes, box_features, box_c
         transh = ns(pos, neg, eh, rl, rn, et) / n_p[1]
         results.append(dict(hoi_loss=hoi, interactiveness_loss=inter, transH_loss=transh))
     return results
+
+
+class PendingResults:
+    """Results on their way to pinned host memory (``results_to_host(..., wait=False)``); ``get()`` waits for the
+    copies of THIS step only (an event), so the next step can be enqueued before the previous one is read."""
+
+    def __init__(self, finish, event):
+        self._finish, self._event, self._out = finish, event, None
+
+    def get(self) -> List[dict]:
+        if self._out is None:
+            if self._event is not None:
+                self._event.synchronize()
+            self._out = self._finish()
+        return self._out
+
+
+def results_to_host(ih, results: List[dict], wait: bool = True):
+    """Host copies of the result dicts ``forward`` just returned: the per-image tensors are views into two flat
+    device buffers, so the whole batch comes back with TWO pinned device->host copies and one synchronise instead of
+    eight small copies per image."""
+    flat = ih.__dict__.get("_skg_last_flat")
+    if flat is None or not results or results[0]["index"].untyped_storage().data_ptr() != flat["out_i"].untyped_storage().data_ptr():
+        out = [{k: v.cpu() for k, v in r.items()} for r in results]
+        return out if wait else PendingResults(lambda: out, None)
+    hi = torch.empty(flat["out_i"].shape, dtype=torch.int64, pin_memory=True)
+    hf = torch.empty(flat["out_f"].shape, dtype=torch.float32, pin_memory=True)
+    hi.copy_(flat["out_i"], non_blocking=True); hf.copy_(flat["out_f"], non_blocking=True)
+    ev = torch.cuda.Event()
+    ev.record(torch.cuda.current_stream(flat["out_i"].device))
+    pending = PendingResults(lambda: _split_host_results(flat, hi, hf, results), ev)
+    return pending.get() if wait else pending
+
+
+def _split_host_results(flat, hi, hf, results):
+    L, Pn, psz, esz = flat["L"], flat["P"], flat["psz"], flat["esz"]
+    index, pred, obj = hi[:L], hi[L:2 * L], hi[2 * L:]
+    scores, prior, weights = hf[:L], hf[L:3 * L].view(2, L), hf[3 * L:3 * L + Pn]
+    o = 3 * L + Pn
+    bh, bo = hf[o:o + 4 * Pn].view(Pn, 4), hf[o + 4 * Pn:o + 8 * Pn].view(Pn, 4)
+    out = [dict(boxes_h=a, boxes_o=b_, index=c, prediction=d_, scores=e, object=f, prior=g, weights=h)
+           for a, b_, c, d_, e, f, g, h in zip(bh.split(psz), bo.split(psz), index.split(esz), pred.split(esz), scores.split(esz),
+                                               obj.split(psz), prior.split(esz, dim=1), weights.split(psz))]
+    if flat["train"]:
+        o += 8 * Pn
+        for r, l_b, u_b in zip(out, hf[o:o + L].split(esz), hf[o + L:o + L + Pn].split(psz)):
+            r["labels"] = l_b; r["unary_labels"] = u_b
+    out.extend(results[len(out):])            # the trailing loss dict (training) stays where it is
+    return out
 
 
 def preprocess_detections(ih, detections: List[dict], targets, append_gt: Optional[bool] = None) -> List[dict]:

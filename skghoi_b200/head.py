@@ -207,12 +207,25 @@ class InteractionHead(Module):
         return interaction_head_forward(self, features, detections, image_shapes, targets)
 
     def forward_from_pooled(self, features: OrderedDict, image_shapes, box_features: Tensor, box_coords,
-                            box_labels, box_scores, targets=None) -> List[dict]:
+                            box_labels, box_scores, targets=None, meta=None) -> List[dict]:
         """The hot path proper: head.py:389-427 given already-preprocessed detections and pooled
         box features (what remains of ``forward`` after the stock torchvision NMS / RoIAlign steps)."""
         from .engine import interaction_head_from_pooled
         return interaction_head_from_pooled(self, features, image_shapes, box_features, box_coords, box_labels,
-                                            box_scores, targets)
+                                            box_scores, targets, meta=meta)
+
+    def host_meta(self, box_labels, box_scores):
+        """Host-side summary of a batch's detections (boxes / humans per image, labels, scores) that sizes the launch
+        and the outputs.  Build it from HOST copies of the labels / scores (the reference reads its detections from a
+        host-side cache) and pass it as ``meta=`` to skip the device->host read ``forward`` otherwise needs."""
+        from .engine import _host_meta
+        return _host_meta(box_labels, box_scores, self.human_idx)
+
+    def results_to_host(self, results: List[dict], wait: bool = True):
+        """Host copies of the dicts ``forward`` just returned (two pinned copies for the whole batch).  ``wait=False``
+        returns a handle whose ``get()`` waits only for this step's copies."""
+        from .engine import results_to_host
+        return results_to_host(self, results, wait)
 
 
 def build_interaction_head(object_to_verb: List[list], human_idx: int = 49, num_classes: int = 117,
