@@ -391,7 +391,7 @@ def measure_rooflines(torch, _lib, engine, ih, dev, flush, hbm_peak, tf_peak, pe
                   p(score), _lib.stream_ptr(dev))
     sec = _time_kernel(torch, th_score, flush, reps=10)
     nb = 4 * cells * 117 + 8 * cells
-    extra["transh_score_roofline"] = {"kernel": "transh_forward_kernel (grid mode, score only, %d triples)" % (cells * 117),
+    extra["transh_score_roofline"] = {"kernel": "transh_grid_kernel<false> (grid mode, score only: [80,117] score table broadcast, %d triples)" % (cells * 117),
                                       "bound": "hbm", "achieved": nb / sec / 1e9, "peak": hbm_peak, "unit": "GB/s",
                                       "frac": nb / sec / 1e9 / hbm_peak, "traffic": None, "bytes_per_launch": nb,
                                       "us_per_launch": sec * 1e6, "triples_per_s": cells * 117 / sec}
@@ -406,10 +406,35 @@ def measure_rooflines(torch, _lib, engine, ih, dev, flush, hbm_peak, tf_peak, pe
                   p(outs[2]), p(outs[3]), p(score), _lib.stream_ptr(dev))
     sec = _time_kernel(torch, th_full, flush, reps=10)
     nb = 804 * T + 8 * cells2
-    extra["transh_rows_roofline"] = {"kernel": "transh_forward_kernel (grid mode, API-faithful h_/r/w/t_ rows + score, %d triples)" % T,
+    extra["transh_rows_roofline"] = {"kernel": "transh_grid_kernel<true> (grid mode, API-faithful h_/r/w/t_ rows + score, %d triples)" % T,
                                      "bound": "hbm", "achieved": nb / sec / 1e9, "peak": hbm_peak, "unit": "GB/s",
                                      "frac": nb / sec / 1e9 / hbm_peak, "traffic": None, "bytes_per_launch": nb,
                                      "us_per_launch": sec * 1e6, "triples_per_s": T / sec}
+    del outs, score
+    # general kernel, explicit int64 index arrays, API-faithful rows: 804 B written + 24 B read per triple
+    T2 = 1 << 20
+    g2 = torch.Generator(device=dev).manual_seed(3)
+    hd = torch.randint(0, 80, (T2,), device=dev, generator=g2); rl = torch.randint(0, 117, (T2,), device=dev, generator=g2)
+    tt_ = torch.randint(0, 80, (T2,), device=dev, generator=g2)
+    outs = [torch.empty(T2, 50, dtype=torch.float32, device=dev) for _ in range(4)]
+    score = torch.empty(T2, dtype=torch.float32, device=dev)
+
+    def th_explicit():
+        _lib.call("skg_transh_forward", p(e), p(r), p(w), 80, 117, 50, p(hd), p(rl), p(tt_), T2, 2, 1, p(outs[0]), p(outs[1]),
+                  p(outs[2]), p(outs[3]), p(score), _lib.stream_ptr(dev))
+    sec = _time_kernel(torch, th_explicit, flush, reps=10)
+    nb = 828 * T2
+    extra["transh_explicit_rows_roofline"] = {"kernel": "transh_forward_kernel (explicit int64 indices, h_/r/w/t_ rows + score, %d triples)" % T2,
+                                              "bound": "hbm", "achieved": nb / sec / 1e9, "peak": hbm_peak, "unit": "GB/s",
+                                              "frac": nb / sec / 1e9 / hbm_peak, "traffic": None, "bytes_per_launch": nb,
+                                              "us_per_launch": sec * 1e6, "triples_per_s": T2 / sec}
+
+    def th_explicit_score():
+        _lib.call("skg_transh_forward", p(e), p(r), p(w), 80, 117, 50, p(hd), p(rl), p(tt_), T2, 2, 1, None, None, None, None,
+                  p(score), _lib.stream_ptr(dev))
+    sec = _time_kernel(torch, th_explicit_score, flush, reps=10)
+    extra["transh_explicit_score"] = {"kernel": "transh_forward_kernel (explicit indices, score only: issue-bound, 28 B / triple)",
+                                      "triples_per_s": T2 / sec, "us_per_launch": sec * 1e6, "achieved_gbs": 28 * T2 / sec / 1e9}
     return roof, extra
 
 

@@ -12,8 +12,12 @@
 // dropped (i < n_h <= n), so the row-major rank of a kept cell is p = i*(n-1) + j - (j > i):
 // bit-exact with nonzero() ordering, no scan and no host sync.
 //
-// Compiled with -fmad=false: the reference materialises every intermediate in fp32, so products
-// must not be contracted into FMAs.
+// Arithmetic: the reference computes 22 fp32 divisions and 23 logs per pair; with IEEE division and libm logf
+// that is ~1000 instructions per cell and the kernel is issue-bound at a third of the HBM roofline.  Parity for
+// the encodings is 1e-5 relative, so divisions use MUFU.RCP (__fdividef, 2 ulp) and logs
+// MUFU.LG2 (__logf, |err| < 2^-21 near 1): ~45 MUFU per cell, well under the store time.  NaN / inf placement is
+// unchanged (0/0 -> NaN, x/0 -> inf, log(<0) -> NaN, log(0 + eps) finite).  Compiled with -fmad=false so the
+// products keep the reference's separate rounding.
 #include "common.cuh"
 #include "skghoi_b200.h"
 
@@ -42,50 +46,52 @@ __device__ __forceinline__ int find_segment(const int64_t* __restrict__ off, int
 
 // Writes 2*F floats for one (b1, b2) pair.  F == 23: compute_spatial_ratio_encodings (ops.py:107-155),
 // F == 18: compute_spatial_encodings (ops.py:46-79).  Returns true when any value is NaN.
+__device__ __forceinline__ float fdiv(float a, float b) { return __fdividef(a, b); }
+
 template <int F>
 __device__ __forceinline__ bool encode_pair(float4 b1, float4 b2, float h, float w, float hw, float eps,
                                             float* __restrict__ out) {
-  const float c1_x = (b1.x + b1.z) / 2.f, c1_y = (b1.y + b1.w) / 2.f;
-  const float c2_x = (b2.x + b2.z) / 2.f, c2_y = (b2.y + b2.w) / 2.f;
+  const float c1_x = (b1.x + b1.z) * 0.5f, c1_y = (b1.y + b1.w) * 0.5f;     // exact: /2 == *0.5
+  const float c2_x = (b2.x + b2.z) * 0.5f, c2_y = (b2.y + b2.w) * 0.5f;
   const float b1_w = b1.z - b1.x, b1_h = b1.w - b1.y;
   const float b2_w = b2.z - b2.x, b2_h = b2.w - b2.y;
-  const float d_x = fabsf(c2_x - c1_x) / (b1_w + eps);
-  const float d_y = fabsf(c2_y - c1_y) / (b1_h + eps);
+  const float d_x = fdiv(fabsf(c2_x - c1_x), b1_w + eps);
+  const float d_y = fdiv(fabsf(c2_y - c1_y), b1_h + eps);
   // torchvision box_iou diagonal: no eps, 0/0 -> NaN
   const float area1 = b1_w * b1_h, area2 = b2_w * b2_h;
   const float iw = fmaxf(fminf(b1.z, b2.z) - fmaxf(b1.x, b2.x), 0.f);
   const float ih = fmaxf(fminf(b1.w, b2.w) - fmaxf(b1.y, b2.y), 0.f);
   const float inter = iw * ih;
-  const float iou = inter / ((area1 + area2) - inter);
+  const float iou = fdiv(inter, (area1 + area2) - inter);
   const float gx = (c2_x > c1_x) ? 1.f : 0.f, lx = (c2_x < c1_x) ? 1.f : 0.f;
   const float gy = (c2_y > c1_y) ? 1.f : 0.f, ly = (c2_y < c1_y) ? 1.f : 0.f;
   float f[F];
   if (F == 23) {
-    const float c1_xw = c1_x / w, c1_yh = c1_y / h, c2_xw = c2_x / w, c2_yh = c2_y / h;
-    const float b1_ww = b1_w / w, b1_hh = b1_h / h, b2_ww = b2_w / w, b2_hh = b2_h / h;
-    const float a1 = area1 / hw, a2 = area2 / hw;
+    const float c1_xw = fdiv(c1_x, w), c1_yh = fdiv(c1_y, h), c2_xw = fdiv(c2_x, w), c2_yh = fdiv(c2_y, h);
+    const float b1_ww = fdiv(b1_w, w), b1_hh = fdiv(b1_h, h), b2_ww = fdiv(b2_w, w), b2_hh = fdiv(b2_h, h);
+    const float a1 = fdiv(area1, hw), a2 = fdiv(area2, hw);
     f[0] = c1_xw; f[1] = c1_yh; f[2] = c2_xw; f[3] = c2_yh;
-    f[4] = c1_xw / (c2_xw + eps); f[5] = c1_yh / (c2_yh + eps);
+    f[4] = fdiv(c1_xw, c2_xw + eps); f[5] = fdiv(c1_yh, c2_yh + eps);
     f[6] = b1_ww; f[7] = b1_hh; f[8] = b2_ww; f[9] = b2_hh;
-    f[10] = b1_ww / (b2_ww + eps); f[11] = b1_hh / (b2_hh + eps);
-    f[12] = a1; f[13] = a2; f[14] = a1 / (a2 + eps);
-    f[15] = area2 / (area1 + eps);
-    f[16] = b1_w / (b1_h + eps); f[17] = b2_w / (b2_h + eps);
+    f[10] = fdiv(b1_ww, b2_ww + eps); f[11] = fdiv(b1_hh, b2_hh + eps);
+    f[12] = a1; f[13] = a2; f[14] = fdiv(a1, a2 + eps);
+    f[15] = fdiv(area2, area1 + eps);
+    f[16] = fdiv(b1_w, b1_h + eps); f[17] = fdiv(b2_w, b2_h + eps);
     f[18] = iou;
     f[19] = gx * d_x; f[20] = lx * d_x; f[21] = gy * d_y; f[22] = ly * d_y;
   } else {
-    f[0] = c1_x / w; f[1] = c1_y / h; f[2] = c2_x / w; f[3] = c2_y / h;
-    f[4] = b1_w / w; f[5] = b1_h / h; f[6] = b2_w / w; f[7] = b2_h / h;
-    f[8] = area1 / hw; f[9] = area2 / hw;
-    f[10] = area2 / (area1 + eps);
-    f[11] = b1_w / (b1_h + eps); f[12] = b2_w / (b2_h + eps);
+    f[0] = fdiv(c1_x, w); f[1] = fdiv(c1_y, h); f[2] = fdiv(c2_x, w); f[3] = fdiv(c2_y, h);
+    f[4] = fdiv(b1_w, w); f[5] = fdiv(b1_h, h); f[6] = fdiv(b2_w, w); f[7] = fdiv(b2_h, h);
+    f[8] = fdiv(area1, hw); f[9] = fdiv(area2, hw);
+    f[10] = fdiv(area2, area1 + eps);
+    f[11] = fdiv(b1_w, b1_h + eps); f[12] = fdiv(b2_w, b2_h + eps);
     f[13] = iou;
     f[14] = gx * d_x; f[15] = lx * d_x; f[16] = gy * d_y; f[17] = ly * d_y;
   }
   bool has_nan = false;
 #pragma unroll
   for (int k = 0; k < F; ++k) {
-    const float l = logf(f[k] + eps);
+    const float l = __logf(f[k] + eps);
     out[k] = f[k];
     out[F + k] = l;
     has_nan |= (f[k] != f[k]) | (l != l);
@@ -115,30 +121,32 @@ struct PairOutputs {
 };
 
 template <int F>
-__global__ void __launch_bounds__(kTileCells) pairs_spatial_kernel(const float4* __restrict__ boxes, SegTable seg,
-                                                                   int64_t total_cells, float eps, PairOutputs o) {
+__global__ void __launch_bounds__(kTileCells, 8) pairs_spatial_kernel(const float4* __restrict__ boxes, SegTable seg,
+                                                                      int64_t total_cells, float eps, PairOutputs o) {
+  // One 128-cell tile per CTA iteration, staged in shared memory in the exact output layout (23.5 KB) and drained by one
+  // bulk asynchronous copy; 8 CTAs per SM (188 KB of shared memory, <= 64 registers) keep 32 warps of MUFU / store
+  // work in flight, so the drain of one CTA's tile overlaps the arithmetic of the seven others.
   constexpr int W = 2 * F;
-  __shared__ __align__(128) float tile[2][kTileCells * W];
+  __shared__ __align__(128) float tile[kTileCells * W];
   const int tid = threadIdx.x;
   const int64_t num_tiles = (total_cells + kTileCells - 1) / kTileCells;
-  int buf = 0;
-  for (int64_t t = blockIdx.x; t < num_tiles; t += gridDim.x, buf ^= 1) {
+  for (int64_t t = blockIdx.x; t < num_tiles; t += gridDim.x) {
     const int64_t r0 = t * kTileCells;
     const int64_t r = r0 + tid;
-    // the bulk store that last read tile[buf] (two iterations ago) must have finished reading smem
-    if (tid == 0) asm volatile("cp.async.bulk.wait_group.read 1;\n" ::: "memory");
-    __syncthreads();
-    if (r < total_cells) {
-      const int b = find_segment(seg.cell_off, seg.B, r);
-      const int boff = __ldg(seg.box_off + b);
-      const int n = __ldg(seg.box_off + b + 1) - boff;
+    // index work first: it does not touch the tile, so it overlaps the previous bulk store
+    int b = 0, boff = 0, n = 1, i = 0, j = 0;
+    float4 b1 = make_float4(0.f, 0.f, 0.f, 0.f), b2 = b1;
+    float h = 1.f, w = 1.f, hw = 1.f;
+    const bool live = r < total_cells;
+    if (live) {
+      b = find_segment(seg.cell_off, seg.B, r);
+      boff = __ldg(seg.box_off + b);
+      n = __ldg(seg.box_off + b + 1) - boff;
       const int64_t c = r - __ldg(seg.cell_off + b);
-      const int i = (int)(c / n), j = (int)(c - (int64_t)i * n);
-      const float4 b1 = __ldg(boxes + boff + i);
-      const float4 b2 = __ldg(boxes + boff + j);
-      const float h = __ldg(seg.hw + 3 * b), w = __ldg(seg.hw + 3 * b + 1), hw = __ldg(seg.hw + 3 * b + 2);
-      const bool has_nan = encode_pair<F>(b1, b2, h, w, hw, eps, &tile[buf][tid * W]);
-      if (has_nan && o.nan_flag) atomicOr(o.nan_flag + b, 1);
+      i = (int)(c / n); j = (int)(c - (int64_t)i * n);
+      b1 = __ldg(boxes + boff + i);
+      b2 = __ldg(boxes + boff + j);
+      h = __ldg(seg.hw + 3 * b); w = __ldg(seg.hw + 3 * b + 1); hw = __ldg(seg.hw + 3 * b + 2);
       if (o.x) o.x[r] = i;
       if (o.y) o.y[r] = j;
       if (o.cell_hrow) o.cell_hrow[r] = __ldg(seg.hum_off + b) + i;
@@ -153,6 +161,13 @@ __global__ void __launch_bounds__(kTileCells) pairs_spatial_kernel(const float4*
         if (o.pair2cell) o.pair2cell[p] = (int32_t)r;
       }
     }
+    // the bulk store of the previous iteration must have finished READING the tile
+    if (tid == 0) asm volatile("cp.async.bulk.wait_group.read 0;\n" ::: "memory");
+    __syncthreads();
+    if (live) {
+      const bool has_nan = encode_pair<F>(b1, b2, h, w, hw, eps, &tile[tid * W]);
+      if (has_nan && o.nan_flag) atomicOr(o.nan_flag + b, 1);
+    }
     // make the generic-proxy smem writes visible to the async (TMA) proxy, then drain the tile
     asm volatile("fence.proxy.async.shared::cta;\n" ::: "memory");
     __syncthreads();
@@ -160,9 +175,10 @@ __global__ void __launch_bounds__(kTileCells) pairs_spatial_kernel(const float4*
     float* gdst = o.enc + r0 * W;
     const uint32_t bytes = (uint32_t)(cells_here * W * sizeof(float));
     if ((bytes & 15u) == 0 && ((reinterpret_cast<uintptr_t>(gdst) & 15u) == 0)) {
-      if (tid == 0) bulk_store_tile(gdst, tile[buf], bytes);
+      if (tid == 0) bulk_store_tile(gdst, tile, bytes);
     } else {  // ragged tail: plain coalesced stores
-      for (int e = tid; e < cells_here * W; e += kTileCells) gdst[e] = tile[buf][e];
+      for (int e = tid; e < cells_here * W; e += kTileCells) gdst[e] = tile[e];
+      __syncthreads();
     }
   }
   if (tid == 0) asm volatile("cp.async.bulk.wait_group 0;\n" ::: "memory");
@@ -231,7 +247,7 @@ extern "C" int skg_pairs_spatial_encode(const float* boxes, const int32_t* box_o
   PairOutputs o{enc, x, y, x_keep, y_keep, cell2pair, cell_hrow, cell_orow, cell_img, pair2cell, nan_flag};
   if (nan_flag) SKG_CUDA(cudaMemsetAsync(nan_flag, 0, sizeof(int32_t) * num_images, stream));
   const int64_t tiles = ceil_div64(total_cells, kTileCells);
-  // 4 resident 128-thread CTAs per SM (2 x 23.5 KB smem each); grid is a multiple of the SM count
+  // 8 resident 128-thread CTAs per SM (23.5 KB smem each); grid is a multiple of the SM count
   const int grid = (int)(tiles < (int64_t)num_sms() * 8 ? tiles : (int64_t)num_sms() * 8);
   if (num_features == 23)
     pairs_spatial_kernel<23><<<grid, kTileCells, 0, stream>>>((const float4*)boxes, seg, total_cells, eps, o);

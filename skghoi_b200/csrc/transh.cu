@@ -9,33 +9,12 @@
 // (large public KGs) are read through L2 instead.
 #include "common.cuh"
 #include "skghoi_b200.h"
+#include "transh.cuh"
 
 namespace skg {
 
 constexpr int kTranshThreads = 256;
 constexpr int kTranshWarps = kTranshThreads / 32;
-
-struct TripleIndex {
-  // explicit mode: head/relation/tail arrays.  implicit (grid) mode (head.py:570-572):
-  //   head = head_const, relation = t % rel_tot, tail = cell_tail ? cell_tail[t / rel_tot] : t / rel_tot
-  const int64_t* head;
-  const int64_t* relation;
-  const int64_t* tail;
-  const int64_t* cell_tail;
-  int64_t head_const;
-  int rel_tot;
-  int implicit;
-  __device__ __forceinline__ void get(int64_t t, int64_t& h, int64_t& r, int64_t& tl) const {
-    if (implicit) {
-      const int64_t c = t / rel_tot;
-      h = head_const;
-      r = t - c * rel_tot;
-      tl = cell_tail ? __ldg(cell_tail + c) : c;
-    } else {
-      h = __ldg(head + t); r = __ldg(relation + t); tl = __ldg(tail + t);
-    }
-  }
-};
 
 struct TranshTriple {   // per-lane slice of one triple's intermediate state
   float inv_w, a_h, a_t, inv_h, inv_t, inv_r, nrm_s;
@@ -76,50 +55,6 @@ __device__ __forceinline__ float transh_triple_fwd(const float (&h)[EPL], const 
   const float score = (p_norm == 1) ? acc : sqrtf(acc);      // torch.norm(score, p, -1)  TransH.py:70
   st.inv_w = inv_w; st.a_h = a_h; st.a_t = a_t; st.inv_h = inv_h; st.inv_t = inv_t; st.inv_r = inv_r; st.nrm_s = score;
   return score;
-}
-
-template <int EPL, bool SMEM_TABLES>
-__global__ void __launch_bounds__(kTranshThreads) transh_forward_kernel(
-    const float* __restrict__ ent, const float* __restrict__ rel, const float* __restrict__ nrm, int ent_tot, int rel_tot,
-    int dim, TripleIndex idx, int64_t T, int p_norm, int norm_flag, float* __restrict__ h_out, float* __restrict__ r_out,
-    float* __restrict__ w_out, float* __restrict__ t_out, float* __restrict__ score_out) {
-  extern __shared__ __align__(16) float smem[];
-  const float* E = ent; const float* R = rel; const float* W = nrm;
-  if (SMEM_TABLES) {
-    float* sE = smem; float* sR = sE + (size_t)ent_tot * dim; float* sW = sR + (size_t)rel_tot * dim;
-    for (int e = threadIdx.x; e < ent_tot * dim; e += blockDim.x) sE[e] = __ldg(ent + e);
-    for (int e = threadIdx.x; e < rel_tot * dim; e += blockDim.x) { sR[e] = __ldg(rel + e); sW[e] = __ldg(nrm + e); }
-    __syncthreads();
-    E = sE; R = sR; W = sW;
-  }
-  const int lane = threadIdx.x & 31;
-  const int64_t warp = (int64_t)blockIdx.x * kTranshWarps + (threadIdx.x >> 5);
-  const int64_t nwarps = (int64_t)gridDim.x * kTranshWarps;
-  for (int64_t t = warp; t < T; t += nwarps) {
-    int64_t hi, ri, ti;
-    idx.get(t, hi, ri, ti);
-    float h[EPL], tl[EPL], r[EPL], w[EPL], s[EPL];
-#pragma unroll
-    for (int e = 0; e < EPL; ++e) {
-      const int d = lane + 32 * e;
-      const bool in = d < dim;
-      h[e] = in ? E[hi * dim + d] : 0.f; tl[e] = in ? E[ti * dim + d] : 0.f;
-      r[e] = in ? R[ri * dim + d] : 0.f; w[e] = in ? W[ri * dim + d] : 0.f;
-    }
-    TranshTriple st;
-    const float score = transh_triple_fwd<EPL>(h, tl, r, w, p_norm, norm_flag, s, st);
-    if (h_out) {   // API-faithful mode: the fork returns the RAW gathered rows (TransH.py:106)
-#pragma unroll
-      for (int e = 0; e < EPL; ++e) {
-        const int d = lane + 32 * e;
-        if (d < dim) {
-          const int64_t o = t * dim + d;
-          __stcs(h_out + o, h[e]); __stcs(r_out + o, r[e]); __stcs(w_out + o, w[e]); __stcs(t_out + o, tl[e]);
-        }
-      }
-    }
-    if (lane == 0) score_out[t] = score;
-  }
 }
 
 // d(tables) += d(score) * d score / d tables.  Gradients accumulate into fp32 tables with atomics;
@@ -293,19 +228,6 @@ static int launch_transh(bool backward, const float* ent, const float* rel, cons
   const int per_sm = fits ? (table_bytes > 48 * 1024 ? 2 : 4) : 8;
   int grid = (int)(want < (int64_t)num_sms() * per_sm ? want : (int64_t)num_sms() * per_sm);
   if (grid < 1) grid = 1;
-  if (!backward) {
-    if (fits) {
-      auto k = transh_forward_kernel<EPL, true>;
-      SKG_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)table_bytes));
-      k<<<grid, kTranshThreads, table_bytes, stream>>>(ent, rel, nrm, ent_tot, rel_tot, dim, idx, T, p_norm, norm_flag,
-                                                       h_out, r_out, w_out, t_out, score);
-    } else {
-      transh_forward_kernel<EPL, false><<<grid, kTranshThreads, 0, stream>>>(ent, rel, nrm, ent_tot, rel_tot, dim, idx, T,
-                                                                             p_norm, norm_flag, h_out, r_out, w_out,
-                                                                             t_out, score);
-    }
-    return check_launch("transh_forward_kernel");
-  }
   if (fits) {
     auto k = transh_backward_kernel<EPL, true>;
     SKG_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)table_bytes));
@@ -340,33 +262,6 @@ static int dispatch_transh(bool backward, const float* ent, const float* rel, co
 }  // namespace skg
 
 using namespace skg;
-
-extern "C" int skg_transh_forward(const float* ent, const float* rel, const float* nrm, int ent_tot, int rel_tot,
-                                  int dim, const int64_t* head, const int64_t* relation, const int64_t* tail,
-                                  int64_t num_triples, int p_norm, int norm_flag, float* h_out, float* r_out,
-                                  float* w_out, float* t_out, float* score, cudaStream_t stream) {
-  SKG_REQUIRE(num_triples == 0 || (head && relation && tail && score), "null index/score pointer");
-  SKG_REQUIRE((h_out != nullptr) == (r_out != nullptr) && (h_out != nullptr) == (w_out != nullptr) &&
-                  (h_out != nullptr) == (t_out != nullptr),
-              "h_out, r_out, w_out, t_out must be all set or all null");
-  TripleIndex idx{head, relation, tail, nullptr, 0, rel_tot, 0};
-  return dispatch_transh(false, ent, rel, nrm, ent_tot, rel_tot, dim, idx, num_triples, p_norm, norm_flag, h_out, r_out,
-                         w_out, t_out, score, nullptr, nullptr, nullptr, nullptr, stream);
-}
-
-extern "C" int skg_transh_forward_grid(const float* ent, const float* rel, const float* nrm, int ent_tot, int rel_tot,
-                                       int dim, int64_t head_const, const int64_t* cell_tail, int64_t num_cells,
-                                       int p_norm, int norm_flag, float* h_out, float* r_out, float* w_out,
-                                       float* t_out, float* score, cudaStream_t stream) {
-  SKG_REQUIRE(num_cells == 0 || score, "null score pointer");
-  SKG_REQUIRE(head_const >= 0 && head_const < ent_tot, "head_const out of range");
-  SKG_REQUIRE((h_out != nullptr) == (r_out != nullptr) && (h_out != nullptr) == (w_out != nullptr) &&
-                  (h_out != nullptr) == (t_out != nullptr),
-              "h_out, r_out, w_out, t_out must be all set or all null");
-  TripleIndex idx{nullptr, nullptr, nullptr, cell_tail, head_const, rel_tot, 1};
-  return dispatch_transh(false, ent, rel, nrm, ent_tot, rel_tot, dim, idx, num_cells * rel_tot, p_norm, norm_flag, h_out,
-                         r_out, w_out, t_out, score, nullptr, nullptr, nullptr, nullptr, stream);
-}
 
 extern "C" int skg_transh_backward(const float* ent, const float* rel, const float* nrm, int ent_tot, int rel_tot,
                                    int dim, const int64_t* head, const int64_t* relation, const int64_t* tail,

@@ -1,0 +1,344 @@
+// TransH forward scoring (reference heads/TransH/TransH.py:56-106 and transH_head.forward head.py:558-582).
+//
+// Two kernels, both staged through shared memory and bound by their global stores:
+//
+//  transh_forward_kernel<EPL>  general triples (explicit head / relation / tail index arrays, or the implicit grid
+//      numbering).  The three tables (80x50 + 2x117x50 fp32 = 62.8 KB for the HOI label graph) and the per-relation
+//      inverse norms 1/||w||, 1/||r|| live in shared memory.  A warp scores FOUR consecutive triples at a time, one
+//      per 8-lane group (dim <= 8*EPL elements per triple, EPL per lane), so a reduction is three shuffle steps and
+//      four triples share every instruction.  The optional API-faithful outputs (the RAW gathered rows h_, r, w, t_
+//      the fork returns, TransH.py:106) are a second phase: the 4 x dim floats the warp owes each output array are
+//      contiguous in global memory, so the warp copies them table -> global as full 128-byte coalesced stores.
+//
+//  transh_grid_kernel  the in-head form (head.py:570-572): head = human_idx, relation = 0..rel_tot-1, tail = box
+//      index, for every grid cell.  score(cell, r) depends only on (tail, r): the [ent_tot, rel_tot] score table is
+//      computed ONCE by the general kernel (9 360 triples) and this kernel broadcasts it -- one warp per cell, pure
+//      shared-memory -> global copies (4 B / triple score-only, 804 B / triple with the four row outputs).
+#include "common.cuh"
+#include "skghoi_b200.h"
+#include "transh.cuh"
+
+namespace skg {
+
+constexpr int kFwdThreads = 256;
+constexpr int kFwdWarps = kFwdThreads / 32;
+
+__device__ __forceinline__ float group8_sum(float v) {
+  v += __shfl_xor_sync(0xffffffffu, v, 1);
+  v += __shfl_xor_sync(0xffffffffu, v, 2);
+  v += __shfl_xor_sync(0xffffffffu, v, 4);
+  return v;
+}
+
+// global -> shared staging of a table with 16-byte loads and eight of them in flight per thread (a scalar loop leaves one
+// L2 round trip per element on the critical path of every CTA)
+__device__ __forceinline__ void stage_table(float* __restrict__ dst, const float* __restrict__ src, int n) {
+  if (((reinterpret_cast<uintptr_t>(src) | reinterpret_cast<uintptr_t>(dst)) & 15u) == 0) {
+    const int n4 = n >> 2;
+    const float4* s4 = reinterpret_cast<const float4*>(src);
+    float4* d4 = reinterpret_cast<float4*>(dst);
+#pragma unroll 8
+    for (int e = threadIdx.x; e < n4; e += blockDim.x) d4[e] = __ldg(s4 + e);
+    for (int e = (n4 << 2) + threadIdx.x; e < n; e += blockDim.x) dst[e] = __ldg(src + e);
+  } else {
+#pragma unroll 8
+    for (int e = threadIdx.x; e < n; e += blockDim.x) dst[e] = __ldg(src + e);
+  }
+}
+
+// F.normalize(x, 2, -1): x / max(||x||, 1e-12)   (TransH.py:57-60, 76)
+__device__ __forceinline__ float inv_norm(float sq) { return 1.f / fmaxf(sqrtf(sq), 1e-12f); }
+
+template <int EPL, bool SMEM_TABLES>
+__global__ void __launch_bounds__(kFwdThreads, (EPL <= 8 ? 3 : 1)) transh_forward_kernel(
+    const float* __restrict__ ent, const float* __restrict__ rel, const float* __restrict__ nrm, int ent_tot, int rel_tot,
+    int dim, TripleIndex idx, int64_t T, int p_norm, int norm_flag, float* __restrict__ h_out, float* __restrict__ r_out,
+    float* __restrict__ w_out, float* __restrict__ t_out, float* __restrict__ score_out) {
+  extern __shared__ __align__(16) float smem[];
+  const float* E = ent; const float* R = rel; const float* W = nrm;
+  const float* inv_w_tab = nullptr; const float* inv_r_tab = nullptr;
+  if (SMEM_TABLES) {
+    const int aE = (ent_tot * dim + 3) & ~3, aR = (rel_tot * dim + 3) & ~3;     // 16-byte aligned sub-tables
+    float* sE = smem; float* sR = sE + aE; float* sW = sR + aR;
+    float* s_iw = sW + aR; float* s_ir = s_iw + rel_tot;
+    stage_table(sE, ent, ent_tot * dim); stage_table(sR, rel, rel_tot * dim); stage_table(sW, nrm, rel_tot * dim);
+    __syncthreads();
+    for (int r = threadIdx.x; r < rel_tot; r += blockDim.x) {   // per-relation inverse norms, once per CTA
+      float ww = 0.f, rr = 0.f;
+      for (int d = 0; d < dim; ++d) { const float a = sW[r * dim + d], b = sR[r * dim + d]; ww += a * a; rr += b * b; }
+      s_iw[r] = inv_norm(ww); s_ir[r] = inv_norm(rr);
+    }
+    __syncthreads();
+    E = sE; R = sR; W = sW; inv_w_tab = s_iw; inv_r_tab = s_ir;
+  }
+  const int lane = threadIdx.x & 31, grp = lane >> 3, l8 = lane & 7;
+  const int64_t warp = (int64_t)blockIdx.x * kFwdWarps + (threadIdx.x >> 5);
+  const int64_t nwarps = (int64_t)gridDim.x * kFwdWarps;
+  for (int64_t t0 = warp * 4; t0 < T; t0 += nwarps * 4) {
+    const int64_t t = t0 + grp;
+    const bool live = t < T;
+    int64_t hi = 0, ri = 0, ti = 0;
+    if (live) idx.get(t, hi, ri, ti);
+    float h[EPL], tl[EPL], r[EPL], w[EPL];
+    float hw = 0.f, tw = 0.f, ww = 0.f, rr = 0.f;
+#pragma unroll
+    for (int k = 0; k < EPL; ++k) {
+      const int d = l8 + 8 * k;
+      const bool in = d < dim;
+      h[k] = in ? E[hi * dim + d] : 0.f; tl[k] = in ? E[ti * dim + d] : 0.f;
+      r[k] = in ? R[ri * dim + d] : 0.f; w[k] = in ? W[ri * dim + d] : 0.f;
+      hw += h[k] * w[k]; tw += tl[k] * w[k];
+      if (!SMEM_TABLES) { ww += w[k] * w[k]; rr += r[k] * r[k]; }
+    }
+    hw = group8_sum(hw); tw = group8_sum(tw);
+    float inv_w, inv_r;
+    if (SMEM_TABLES) { inv_w = inv_w_tab[ri]; inv_r = inv_r_tab[ri]; }
+    else { inv_w = inv_norm(group8_sum(ww)); inv_r = inv_norm(group8_sum(rr)); }
+    const float a_h = hw * inv_w, a_t = tw * inv_w;          // sum(e * w_hat)   TransH.py:85
+    float hp[EPL], tp[EPL];
+    float hh = 0.f, tt = 0.f;
+#pragma unroll
+    for (int k = 0; k < EPL; ++k) {
+      const float wn = w[k] * inv_w;
+      hp[k] = h[k] - a_h * wn; tp[k] = tl[k] - a_t * wn;
+      hh += hp[k] * hp[k]; tt += tp[k] * tp[k];
+    }
+    float inv_h = 1.f, inv_t = 1.f;
+    if (norm_flag) { inv_h = inv_norm(group8_sum(hh)); inv_t = inv_norm(group8_sum(tt)); } else inv_r = 1.f;
+    float acc = 0.f;
+#pragma unroll
+    for (int k = 0; k < EPL; ++k) {
+      const float s = (hp[k] * inv_h + r[k] * inv_r) - tp[k] * inv_t;   // (h + r) - t   TransH.py:68
+      acc += (p_norm == 1) ? fabsf(s) : s * s;
+    }
+    acc = group8_sum(acc);
+    if (live && l8 == 0) score_out[t] = (p_norm == 1) ? acc : sqrtf(acc);   // torch.norm(score, p, -1)  TransH.py:70
+    if (h_out) {
+      // phase 2: the whole warp copies the rows of triples t0 .. t0+3, one triple at a time (coalesced, dim floats each)
+#pragma unroll
+      for (int g = 0; g < 4; ++g) {
+        if (t0 + g >= T) break;                          // warp-uniform
+        const int64_t hq = __shfl_sync(0xffffffffu, hi, g * 8), rq = __shfl_sync(0xffffffffu, ri, g * 8),
+                      tq = __shfl_sync(0xffffffffu, ti, g * 8);
+        const float* eh = E + hq * dim; const float* er = R + rq * dim; const float* ew = W + rq * dim; const float* et = E + tq * dim;
+        const int64_t base = (t0 + g) * dim;
+        for (int d = lane; d < dim; d += 32) {
+          __stcs(h_out + base + d, eh[d]); __stcs(r_out + base + d, er[d]);
+          __stcs(w_out + base + d, ew[d]); __stcs(t_out + base + d, et[d]);
+        }
+      }
+    }
+  }
+}
+
+
+// Broadcast of the [ent_tot, rel_tot] score table over the grid cells (+ the four row outputs): one warp per cell.
+constexpr int kGridThreads = 512;
+constexpr int kGridWarps = kGridThreads / 32;
+
+template <bool ROWS>
+__global__ void __launch_bounds__(kGridThreads) transh_grid_kernel(
+    const float* __restrict__ S, const float* __restrict__ ent, const float* __restrict__ rel, const float* __restrict__ nrm,
+    int ent_tot, int rel_tot, int dim, int head_const, const int64_t* __restrict__ cell_tail, int64_t num_cells,
+    float* __restrict__ h_out, float* __restrict__ r_out, float* __restrict__ w_out, float* __restrict__ t_out,
+    float* __restrict__ score) {
+  extern __shared__ __align__(16) float smem[];
+  float* sS = smem;
+  const int nS = ent_tot * rel_tot, nE = ent_tot * dim, nR = rel_tot * dim;
+  // rows mode: sS | sE | sR | sW ; score-only mode: sS | s_tail (the table pointers then collapse onto the end of sS)
+  float* sE = sS + ((nS + 3) & ~3); float* sR = sE + (ROWS ? ((nE + 3) & ~3) : 0); float* sW = sR + (ROWS ? ((nR + 3) & ~3) : 0);
+  stage_table(sS, S, nS);
+  if (ROWS) { stage_table(sE, ent, nE); stage_table(sR, rel, nR); stage_table(sW, nrm, nR); }
+  __syncthreads();
+  const int lane = threadIdx.x & 31;
+  const int64_t warp = (int64_t)blockIdx.x * kGridWarps + (threadIdx.x >> 5);
+  const int64_t nwarps = (int64_t)gridDim.x * kGridWarps;
+  const bool vec2 = ROWS && (dim & 1) == 0 && (((uintptr_t)h_out | (uintptr_t)r_out | (uintptr_t)w_out | (uintptr_t)t_out) & 7u) == 0;
+  const int step = (vec2 ? 64 : 32) % dim;
+  if (!ROWS) {
+    // score only: a CTA owns chunks of kGridThreads consecutive cells = one contiguous, 16-byte aligned slab of the output.
+    // The chunk's tails are staged in shared memory (one coalesced load), then every thread writes whole float4s:
+    // element q of the slab is relation q % rel_tot of cell q / rel_tot.
+    int* s_tail = reinterpret_cast<int*>(sW);
+    const float inv_rel = 1.f / (float)rel_tot;
+    const bool aligned = (reinterpret_cast<uintptr_t>(score) & 15u) == 0;
+    for (int64_t c0 = (int64_t)blockIdx.x * kGridThreads; c0 < num_cells; c0 += (int64_t)gridDim.x * kGridThreads) {
+      const int64_t cl = c0 + threadIdx.x;
+      int tv = 0;
+      if (cl < num_cells) {
+        const int64_t t64 = cell_tail ? __ldg(cell_tail + cl) : cl;
+        tv = (int)(t64 >= ent_tot ? ent_tot - 1 : (t64 < 0 ? 0 : t64));     // host rejects out-of-range tails (IndexError)
+      }
+      __syncthreads();                                   // previous chunk's readers are done
+      s_tail[threadIdx.x] = tv * rel_tot;
+      __syncthreads();
+      const int cells_here = (int)(num_cells - c0 < kGridThreads ? num_cells - c0 : kGridThreads);
+      const int n_el = cells_here * rel_tot;
+      float* dst = score + c0 * rel_tot;                 // c0 is a multiple of 4: 16-byte aligned when `score` is
+      for (int q = 4 * threadIdx.x; q < n_el; q += 4 * kGridThreads) {
+        int cell = (int)(((float)q + 0.5f) * inv_rel);
+        if (cell * rel_tot > q) --cell;
+        int r = q - cell * rel_tot;
+        if (r >= rel_tot) { r -= rel_tot; ++cell; }
+        float v[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          v[j] = (q + j < n_el) ? sS[s_tail[cell] + r] : 0.f;
+          if (++r == rel_tot) { r = 0; ++cell; }
+        }
+        if (aligned && q + 4 <= n_el) {
+          __stcs(reinterpret_cast<float4*>(dst + q), make_float4(v[0], v[1], v[2], v[3]));
+        } else {
+#pragma unroll
+          for (int j = 0; j < 4; ++j) if (q + j < n_el) dst[q + j] = v[j];
+        }
+      }
+    }
+    return;
+  }
+  // rows mode: one warp per cell -- 4 x rel_tot x dim floats of pure shared-memory -> global copy per cell
+  for (int64_t c = warp; c < num_cells; c += nwarps) {
+    int64_t t64 = cell_tail ? __ldg(cell_tail + c) : c;
+    const int tl = (int)(t64 >= ent_tot ? ent_tot - 1 : (t64 < 0 ? 0 : t64));
+    const float* srow = sS + tl * rel_tot;
+    float* dst = score + c * rel_tot;
+    for (int r = lane; r < rel_tot; r += 32) __stcs(dst + r, srow[r]);
+    const int64_t base = c * nR;
+    const float* eh = sE + head_const * dim; const float* et = sE + tl * dim;
+    if (vec2) {                                       // nR even, base even: 8-byte aligned float2 stores
+      int d = (2 * lane) % dim;
+      for (int q = 2 * lane; q < nR; q += 64) {
+        const float2 vh = *reinterpret_cast<const float2*>(eh + d), vt = *reinterpret_cast<const float2*>(et + d);
+        const float2 vr = *reinterpret_cast<const float2*>(sR + q), vw = *reinterpret_cast<const float2*>(sW + q);
+        __stcs(reinterpret_cast<float2*>(h_out + base + q), vh); __stcs(reinterpret_cast<float2*>(r_out + base + q), vr);
+        __stcs(reinterpret_cast<float2*>(w_out + base + q), vw); __stcs(reinterpret_cast<float2*>(t_out + base + q), vt);
+        d += step; if (d >= dim) d -= dim;
+      }
+    } else {
+      int d = lane % dim;
+      for (int q = lane; q < nR; q += 32) {
+        __stcs(h_out + base + q, eh[d]); __stcs(r_out + base + q, sR[q]);
+        __stcs(w_out + base + q, sW[q]); __stcs(t_out + base + q, et[d]);
+        d += step; if (d >= dim) d -= dim;
+      }
+    }
+  }
+}
+
+template <int EPL>
+static int launch_forward(const float* ent, const float* rel, const float* nrm, int ent_tot, int rel_tot, int dim,
+                          const TripleIndex& idx, int64_t T, int p_norm, int norm_flag, float* h_out, float* r_out,
+                          float* w_out, float* t_out, float* score, cudaStream_t stream) {
+  const size_t table_bytes = ((((size_t)ent_tot * dim + 3) & ~(size_t)3) + 2 * (((size_t)rel_tot * dim + 3) & ~(size_t)3) + 2 * (size_t)rel_tot) * sizeof(float);
+  const bool fits = table_bytes <= 100 * 1024;
+  const int64_t want = ceil_div64(T, kFwdWarps * 4 * 4);
+  const int per_sm = fits ? (table_bytes > 72 * 1024 ? 2 : 3) : 8;
+  int grid = (int)(want < (int64_t)num_sms() * per_sm ? want : (int64_t)num_sms() * per_sm);
+  if (grid < 1) grid = 1;
+  if (fits) {
+    auto k = transh_forward_kernel<EPL, true>;
+    SKG_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)table_bytes));
+    k<<<grid, kFwdThreads, table_bytes, stream>>>(ent, rel, nrm, ent_tot, rel_tot, dim, idx, T, p_norm, norm_flag, h_out,
+                                                  r_out, w_out, t_out, score);
+  } else {
+    transh_forward_kernel<EPL, false><<<grid, kFwdThreads, 0, stream>>>(ent, rel, nrm, ent_tot, rel_tot, dim, idx, T, p_norm,
+                                                                        norm_flag, h_out, r_out, w_out, t_out, score);
+  }
+  return check_launch("transh_forward_kernel");
+}
+
+static int dispatch_forward(const float* ent, const float* rel, const float* nrm, int ent_tot, int rel_tot, int dim,
+                            const TripleIndex& idx, int64_t T, int p_norm, int norm_flag, float* h_out, float* r_out,
+                            float* w_out, float* t_out, float* score, cudaStream_t stream) {
+  SKG_REQUIRE(dim >= 1 && dim <= 256, "TransH dim must be in [1, 256], got %d", dim);
+  SKG_REQUIRE(p_norm == 1 || p_norm == 2, "p_norm must be 1 or 2, got %d", p_norm);
+  SKG_REQUIRE(ent_tot > 0 && rel_tot > 0 && T >= 0, "bad table sizes");
+  if (T == 0) return SKG_OK;
+  SKG_REQUIRE(ent && rel && nrm && score, "null table / score pointer");
+  SKG_REQUIRE((h_out != nullptr) == (r_out != nullptr) && (h_out != nullptr) == (w_out != nullptr) &&
+                  (h_out != nullptr) == (t_out != nullptr),
+              "h_out, r_out, w_out, t_out must be all set or all null");
+#define SKG_FWD_CASE(E) \
+  return launch_forward<E>(ent, rel, nrm, ent_tot, rel_tot, dim, idx, T, p_norm, norm_flag, h_out, r_out, w_out, t_out, score, stream)
+  if (dim <= 32) SKG_FWD_CASE(4);
+  if (dim <= 64) SKG_FWD_CASE(8);
+  if (dim <= 128) SKG_FWD_CASE(16);
+  SKG_FWD_CASE(32);
+#undef SKG_FWD_CASE
+}
+
+}  // namespace skg
+
+using namespace skg;
+
+extern "C" int skg_transh_forward(const float* ent, const float* rel, const float* nrm, int ent_tot, int rel_tot,
+                                  int dim, const int64_t* head, const int64_t* relation, const int64_t* tail,
+                                  int64_t num_triples, int p_norm, int norm_flag, float* h_out, float* r_out,
+                                  float* w_out, float* t_out, float* score, cudaStream_t stream) {
+  SKG_REQUIRE(num_triples == 0 || (head && relation && tail && score), "null index/score pointer");
+  TripleIndex idx{head, relation, tail, nullptr, 0, rel_tot, 0};
+  return dispatch_forward(ent, rel, nrm, ent_tot, rel_tot, dim, idx, num_triples, p_norm, norm_flag, h_out, r_out, w_out,
+                          t_out, score, stream);
+}
+
+extern "C" int skg_transh_forward_grid(const float* ent, const float* rel, const float* nrm, int ent_tot, int rel_tot,
+                                       int dim, int64_t head_const, const int64_t* cell_tail, int64_t num_cells,
+                                       int p_norm, int norm_flag, float* h_out, float* r_out, float* w_out,
+                                       float* t_out, float* score, cudaStream_t stream) {
+  SKG_REQUIRE(num_cells == 0 || score, "null score pointer");
+  SKG_REQUIRE(head_const >= 0 && head_const < ent_tot, "head_const out of range");
+  SKG_REQUIRE((h_out != nullptr) == (r_out != nullptr) && (h_out != nullptr) == (w_out != nullptr) &&
+                  (h_out != nullptr) == (t_out != nullptr),
+              "h_out, r_out, w_out, t_out must be all set or all null");
+  if (num_cells == 0) return SKG_OK;
+  const bool rows = h_out != nullptr;
+  const size_t nS = (size_t)ent_tot * rel_tot, nE = (size_t)ent_tot * dim, nR = (size_t)rel_tot * dim;
+  const size_t smem_bytes = (((nS + 3) & ~(size_t)3) + (rows ? ((nE + 3) & ~(size_t)3) + 2 * ((nR + 3) & ~(size_t)3) : (size_t)kGridThreads)) * sizeof(float);
+  const bool implicit_tail_ok = cell_tail != nullptr || num_cells <= ent_tot;
+  if (smem_bytes > 200 * 1024 || num_cells < 4 * (int64_t)ent_tot || !implicit_tail_ok) {
+    // big tables or few cells: score every triple directly
+    TripleIndex idx{nullptr, nullptr, nullptr, cell_tail, head_const, rel_tot, 1};
+    return dispatch_forward(ent, rel, nrm, ent_tot, rel_tot, dim, idx, num_cells * rel_tot, p_norm, norm_flag, h_out, r_out,
+                            w_out, t_out, score, stream);
+  }
+  // 1) score table S[tail, r] = score(head_const, r, tail) for every entity: ent_tot * rel_tot triples, once
+  float* S = nullptr;
+  {   // keep freed pool memory cached: without a release threshold every cudaFreeAsync hands the block back to the OS
+    static thread_local int pool_dev = -1;
+    int dev = 0;
+    SKG_CUDA(cudaGetDevice(&dev));
+    if (pool_dev != dev) {
+      cudaMemPool_t pool;
+      SKG_CUDA(cudaDeviceGetDefaultMemPool(&pool, dev));
+      unsigned long long thr = 64ull << 20;
+      unsigned long long cur = 0;
+      cudaMemPoolGetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &cur);
+      if (cur < thr) SKG_CUDA(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &thr));
+      pool_dev = dev;
+    }
+  }
+  SKG_CUDA(cudaMallocAsync(&S, nS * sizeof(float), stream));     // stream-ordered pool allocation: no synchronisation
+  TripleIndex idx{nullptr, nullptr, nullptr, nullptr, head_const, rel_tot, 1};
+  int rc = dispatch_forward(ent, rel, nrm, ent_tot, rel_tot, dim, idx, (int64_t)nS, p_norm, norm_flag, nullptr, nullptr, nullptr,
+                            nullptr, S, stream);
+  if (rc == SKG_OK) {
+    // 2) broadcast over the cells
+    const int per_sm = smem_bytes > 110 * 1024 ? 1 : (smem_bytes > 72 * 1024 ? 2 : 3);
+    const int64_t want = rows ? ceil_div64(num_cells, kGridWarps) : ceil_div64(num_cells, kGridThreads);
+    const int grid = (int)(want < (int64_t)num_sms() * per_sm ? want : (int64_t)num_sms() * per_sm);
+    if (rows) {
+      auto k = transh_grid_kernel<true>;
+      cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes);
+      k<<<grid, kGridThreads, smem_bytes, stream>>>(S, ent, rel, nrm, ent_tot, rel_tot, dim, (int)head_const, cell_tail, num_cells,
+                                                   h_out, r_out, w_out, t_out, score);
+    } else {
+      auto k = transh_grid_kernel<false>;
+      cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes);
+      k<<<grid, kGridThreads, smem_bytes, stream>>>(S, ent, rel, nrm, ent_tot, rel_tot, dim, (int)head_const, cell_tail, num_cells,
+                                                   h_out, r_out, w_out, t_out, score);
+    }
+    rc = check_launch("transh_grid_kernel");
+  }
+  cudaFreeAsync(S, stream);
+  return rc;
+}
