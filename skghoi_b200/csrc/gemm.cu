@@ -23,7 +23,8 @@ namespace skg {
 constexpr int BM = 128;            // UMMA M (cta_group::1)
 constexpr int BK = 64;             // 64 bf16 = 128 B = one swizzle-128B atom row
 constexpr int UMMA_K = 16;
-constexpr int kEpiWarps = 16;      // 4 per TMEM lane quadrant
+constexpr int kEpiWarps = 8;       // kEpiParts per TMEM lane quadrant
+constexpr int kEpiParts = kEpiWarps / 4;   // column parts of a tile, one epilogue warp each per quadrant
 constexpr int kGemmThreads = 32 * (4 + kEpiWarps);  // warps: 0 TMA, 1 MMA, 2 TMEM alloc, 3 idle, 4..19 epilogue
 // epilogue features (compile-time mask FEAT of gemm_bf16_kernel; bias / ReLU / out_row are always available)
 enum : uint32_t { F_P = 1, F_Q = 2, F_RAW = 4, F_RES = 8, F_DOT = 16, F_OB = 32, F_OF = 64, F_LO = 128, F_ALL = 255 };
@@ -248,7 +249,8 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     float4* patch = reinterpret_cast<float4*>(staging) + ew * 128;   // 32 rows x 4 float4
     const int sub = lane >> 2;                            // row inside an 8-row group
     const int cq = (lane & 3) * 4;                        // first of this lane's 4 columns inside a 16-column block
-    constexpr int kBlocks = BN / 64;                      // 16-column blocks per warp
+    constexpr int kBlocks = BN / (16 * kEpiParts);        // 16-column blocks per warp (even, or 1)
+    static_assert(kBlocks == 1 || kBlocks % 2 == 0, "the pipelined epilogue walks the blocks in pairs");
     int acc = 0; uint32_t acc_phase = 0;
     for (int item = blockIdx.x; item < num_items; item += gridDim.x) {
       const int tile = item / splits;
@@ -303,31 +305,39 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         const bool do_math = (pass == 1) || !split_mode;
         float dot[4] = {0.f, 0.f, 0.f, 0.f};
         bool waited = false;
-#pragma unroll 1
-        for (int blk = 0; blk < kBlocks; ++blk) {
-          const int c0 = part * (BN / 4) + blk * 16;
-          if (n0 + c0 >= N) break;                     // warp-uniform
+        // The gathered operands of a 16-column block (bias, dot weights, Hadamard / residual table rows) do not depend on
+        // the accumulator.  They are software-pipelined one block ahead in registers: with one warp per scheduler
+        // quadrant-part there is no other work to hide an L2 round trip behind, and shared memory is full of pipeline
+        // stages, so the L1 that would otherwise catch these re-reads is down to a few KB.
+        struct Tabs { float4 b4, w4, tp[4], tq[4], tr[4]; };
+        auto load_tabs = [&](int blk, Tabs& T) {
+          const int c0 = part * (BN / kEpiParts) + blk * 16;
+          const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
+          T.b4 = z4; T.w4 = z4;
+          if (!do_math || n0 + c0 >= N) return;
+          const int col = n0 + c0 + cq, lc = col - n_begin;
+          if (g_bias) T.b4 = __ldg(reinterpret_cast<const float4*>(g_bias + col));
+          if ((FEAT & F_DOT) && g_dw) T.w4 = __ldg(reinterpret_cast<const float4*>(g_dw + lc));
+          if ((FEAT & F_P) && g_p) {
+#pragma unroll
+            for (int it = 0; it < 4; ++it) T.tp[it] = __ldg(reinterpret_cast<const float4*>(g_p + (int64_t)rp_i[it] * ld_p + lc));
+          }
+          if ((FEAT & F_Q) && g_q) {
+#pragma unroll
+            for (int it = 0; it < 4; ++it) T.tq[it] = __ldg(reinterpret_cast<const float4*>(g_q + (int64_t)rq_i[it] * ld_q + lc));
+          }
+          if ((FEAT & F_RES) && g_res) {
+#pragma unroll
+            for (int it = 0; it < 4; ++it) T.tr[it] = __ldg(reinterpret_cast<const float4*>(g_res + (int64_t)rr_i[it] * ld_r + lc));
+          }
+        };
+        auto process = [&](int blk, const Tabs& T) {
+          const int c0 = part * (BN / kEpiParts) + blk * 16;
+          if (n0 + c0 >= N) return;                    // warp-uniform
           const int col = n0 + c0 + cq;                // global column of this lane's 4 values
           const int lc = col - n_begin;                // column inside the group (table / output column)
-          // gathered tables first: they do not depend on the accumulator, so their latency overlaps the TMEM load
           const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
-          float4 b4 = z4, w4 = z4, tp[4], tq[4], tr[4];
-          if (do_math) {
-            if (g_bias) b4 = __ldg(reinterpret_cast<const float4*>(g_bias + col));
-            if ((FEAT & F_DOT) && g_dw) w4 = __ldg(reinterpret_cast<const float4*>(g_dw + lc));
-            if ((FEAT & F_P) && g_p) {
-#pragma unroll
-              for (int it = 0; it < 4; ++it) tp[it] = __ldg(reinterpret_cast<const float4*>(g_p + (int64_t)rp_i[it] * ld_p + lc));
-            }
-            if ((FEAT & F_Q) && g_q) {
-#pragma unroll
-              for (int it = 0; it < 4; ++it) tq[it] = __ldg(reinterpret_cast<const float4*>(g_q + (int64_t)rq_i[it] * ld_q + lc));
-            }
-            if ((FEAT & F_RES) && g_res) {
-#pragma unroll
-              for (int it = 0; it < 4; ++it) tr[it] = __ldg(reinterpret_cast<const float4*>(g_res + (int64_t)rr_i[it] * ld_r + lc));
-            }
-          }
+          const float4 b4 = T.b4, w4 = T.w4;
           if (pass == 0) {
             if (!waited) {                             // first block of the tile: wait for the accumulator
               mbar_wait(tmem_full + acc, acc_phase);
@@ -369,12 +379,12 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             if ((FEAT & F_RAW) && g_raw && store_ok)
               *reinterpret_cast<uint2*>(g_raw + (int64_t)ro * ld_raw + lc) = make_uint2(pack_bf16(v.x, v.y), pack_bf16(v.z, v.w));
             if ((FEAT & F_P) && g_p) {
-              float4 a = tp[it];
-              if ((FEAT & F_Q) && g_q) { a.x += tq[it].x; a.y += tq[it].y; a.z += tq[it].z; a.w += tq[it].w; }
+              float4 a = T.tp[it];
+              if ((FEAT & F_Q) && g_q) { a.x += T.tq[it].x; a.y += T.tq[it].y; a.z += T.tq[it].z; a.w += T.tq[it].w; }
               v.x *= a.x; v.y *= a.y; v.z *= a.z; v.w *= a.w;
             }
             if (relu) { v.x = fmaxf(v.x, 0.f); v.y = fmaxf(v.y, 0.f); v.z = fmaxf(v.z, 0.f); v.w = fmaxf(v.w, 0.f); }
-            if ((FEAT & F_RES) && g_res) { v.x += tr[it].x; v.y += tr[it].y; v.z += tr[it].z; v.w += tr[it].w; }
+            if ((FEAT & F_RES) && g_res) { v.x += T.tr[it].x; v.y += T.tr[it].y; v.z += T.tr[it].z; v.w += T.tr[it].w; }
             if (FEAT & F_DOT) dot[it] += v.x * w4.x + v.y * w4.y + v.z * w4.z + v.w * w4.w;
             if (store_ok) {
               if ((FEAT & F_OB) && g_ob)
@@ -396,6 +406,21 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                 }
               }
             }
+          }
+        };
+        if (kBlocks == 1) {
+          Tabs T0;
+          load_tabs(0, T0);
+          process(0, T0);
+        } else {
+          Tabs T0, T1;
+          load_tabs(0, T0);
+#pragma unroll 1
+          for (int blk = 0; blk < kBlocks; blk += 2) {
+            load_tabs(blk + 1, T1);
+            process(blk, T0);
+            if (blk + 2 < kBlocks) load_tabs(blk + 2, T0);
+            process(blk + 1, T1);
           }
         }
         if (pass == 0) {
@@ -427,8 +452,12 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             float d = dot[it];
             d += __shfl_xor_sync(0xffffffffu, d, 1);
             d += __shfl_xor_sync(0xffffffffu, d, 2);
-            if ((lane & 3) == 0 && ro_i[it] >= 0)
-              G.dot_out[(int64_t)ro_i[it] * G.ld_dot + ((n0 - n_begin) / BN) * 4 + part] = d;
+            if ((lane & 3) == 0 && ro_i[it] >= 0) {       // ABI: four partial slots per N tile; unused ones are written as 0
+              float* slot = G.dot_out + (int64_t)ro_i[it] * G.ld_dot + ((n0 - n_begin) / BN) * 4 + part * (4 / kEpiParts);
+              slot[0] = d;
+#pragma unroll
+              for (int z = 1; z < 4 / kEpiParts; ++z) slot[z] = 0.f;
+            }
           }
         }
       }
