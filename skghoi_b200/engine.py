@@ -752,9 +752,8 @@ def interaction_head_from_pooled(ih, features, image_shapes, box_features, box_c
         # losses (head.py:153-235); n_p averaged over ranks when distributed (one 2-float all-reduce, no barriers)
         n_p = torch.stack([(lab_e != 0).sum(), (unary != 0).sum()]).float()
         if ih.distributed:
-            import torch.distributed as dist
-            dist.all_reduce(n_p)
-            n_p = n_p / dist.get_world_size()
+            from .shard import average_normalisers
+            n_p = average_normalisers(n_p)
         hoi = ops.binary_focal_loss(scores, lab_e, reduction="sum", gamma=0.2) / n_p[0]
         inter = ops.binary_focal_loss(weights, unary, reduction="sum", gamma=2.0) / n_p[1]
         pos, neg, eh, et, rl, rn = _transh_pos_neg(G, run, gt, targets)

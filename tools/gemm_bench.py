@@ -55,6 +55,34 @@ def run(M, N, K, kind, bn=0):
         print("        cuBLAS same shape            : %8.2f us  %7.1f TFLOP/s" % (sec * 1e6, 2.0 * M * N * K / sec / 1e12))
 
 
+def anatomy():
+    """Per-CTA timeline T = setup + ML + (t-1)*max(EP, ML) + EP from launches with t tiles per CTA (N = 256, M = t*148*128)
+    at K = 64 (ML ~ 0 -> EP) and K = 1024, for the plain and the fused (P+Q+RAW+OB, P+OB) epilogues."""
+    for kind in ("plain", "fusedA", "fusedP"):
+        for K in (64, 1024, 2048):
+            for t in (1, 2, 4):
+                M, N = t * 148 * 128, 256
+                A = (torch.randn(M, K, device=dev) * 0.5).to(torch.bfloat16)
+                B = (torch.randn(N, K, device=dev) * 0.1).to(torch.bfloat16)
+                bias = torch.randn(N, device=dev)
+                o0 = torch.empty(M, N, dtype=torch.bfloat16, device=dev); o1 = torch.empty_like(o0)
+                ar = torch.arange(M, device=dev)
+                hrow = (ar // 32).int(); orow = ((ar // 512) * 32 + ar % 32).int()
+                hp = torch.randn(M // 32, N, device=dev); op = torch.randn(M // 16, N, device=dev)
+                g = _lib.epilogue_group
+                if kind == "plain":
+                    groups = [g(relu=True, bias=bias, out_bf16=o0)]
+                elif kind == "fusedA":
+                    groups = [g(relu=True, bias=bias, mul_p=hp, row_p=hrow, mul_q=op, row_q=orow, out_bf16=o0, raw_bf16=o1)]
+                else:
+                    groups = [g(relu=True, bias=bias, mul_p=op, row_p=orow, out_bf16=o0)]
+                sec = timeit(lambda: _lib.gemm_bf16(A, B, groups, block_n=256))
+                print("anatomy %-6s K=%4d tiles/CTA=%d : %7.2f us" % (kind, K, t, sec * 1e6))
+
+
+if "--anatomy" in sys.argv:
+    anatomy()
+    sys.exit(0)
 if "--fused-only" in sys.argv:
     run(4096, 4096, 1024, "fused4")
     sys.exit(0)
