@@ -246,6 +246,8 @@ extern "C" int skg_associate_gt(const float* boxes, const skg_post_tables* table
   int rc = fill_tables(t, tables);
   if (rc) return rc;
   SKG_REQUIRE(boxes && gt_off && labels, "null pointer argument");
+  SKG_REQUIRE(((reinterpret_cast<uintptr_t>(boxes) | reinterpret_cast<uintptr_t>(gt_boxes_h) | reinterpret_cast<uintptr_t>(gt_boxes_o)) & 15u) == 0,
+              "boxes and GT boxes must be 16-byte aligned (rows are read as float4)");
   SKG_CUDA(cudaMemsetAsync(labels, 0, sizeof(float) * pairs * num_cls, stream));
   associate_gt_kernel<<<(int)ceil_div64(pairs, 128), 128, 0, stream>>>((const float4*)boxes, t, pairs, num_cls, gt_off,
                                                                       (const float4*)gt_boxes_h, (const float4*)gt_boxes_o,
@@ -274,6 +276,8 @@ extern "C" int skg_gather_pair_boxes(const float* boxes, const skg_post_tables* 
   int rc = fill_tables(t, tables);
   if (rc) return rc;
   SKG_REQUIRE(boxes && boxes_h && boxes_o, "null pointer argument");
+  SKG_REQUIRE(((reinterpret_cast<uintptr_t>(boxes) | reinterpret_cast<uintptr_t>(boxes_h) | reinterpret_cast<uintptr_t>(boxes_o)) & 15u) == 0,
+              "boxes, boxes_h and boxes_o must be 16-byte aligned (rows are read / written as float4)");
   gather_pair_boxes_kernel<<<(int)ceil_div64(pairs, 256), 256, 0, stream>>>((const float4*)boxes, t, pairs, (float4*)boxes_h,
                                                                            (float4*)boxes_o);
   return check_launch("gather_pair_boxes_kernel");

@@ -720,16 +720,10 @@ def interaction_head_from_pooled(ih, features, image_shapes, box_features, box_c
     per_img = per_img[:seg.B]
     gt = _gt_labels(G, run, tables, boxes_cat, targets) if targets is not None else None
     # two allocations hold every output of the batch; the per-image results are views into them
-    n_f = 3 * L + 9 * Pn + ((L + Pn) if gt is not None else 0)
     out_i = torch.empty(2 * L + Pn, dtype=torch.int64, device=dev)
-    out_f = torch.empty(n_f, dtype=torch.float32, device=dev)
+    out_f = torch.empty(_flat_f_size(L, Pn, gt is not None), dtype=torch.float32, device=dev)
     index, pred, obj = out_i[:L], out_i[L:2 * L], out_i[2 * L:]
-    scores, prior, weights = out_f[:L], out_f[L:3 * L].view(2, L), out_f[3 * L:3 * L + Pn]
-    o = 3 * L + Pn
-    bh_all, bo_all = out_f[o:o + 4 * Pn].view(Pn, 4), out_f[o + 4 * Pn:o + 8 * Pn].view(Pn, 4)
-    o += 8 * Pn
-    lab_e = out_f[o:o + L] if gt is not None else None
-    unary = out_f[o + L:o + L + Pn] if gt is not None else None
+    bh_all, bo_all, scores, prior, weights, lab_e, unary = _flat_f_views(out_f, L, Pn, gt is not None)
     with torch.cuda.device(dev):
         _lib.call("skg_head_post", _lib.ptr(run["logits"]), run["logits"].stride(0), nc, ctypes_byref(tables), _lib.ptr(boxes_cat),
                   seg.B, seg.total_boxes, seg.total_humans, Pn, 1.0 if G.training else 2.8, _lib.ptr(gt), L,
@@ -761,6 +755,22 @@ def interaction_head_from_pooled(ih, features, image_shapes, box_features, box_c
         transh = ns(pos, neg, eh, rl, rn, et) / n_p[1]
         results.append(dict(hoi_loss=hoi, interactiveness_loss=inter, transH_loss=transh))
     return results
+
+
+def _flat_f_size(L: int, Pn: int, train: bool) -> int:
+    return 9 * Pn + 3 * L + ((L + Pn) if train else 0)
+
+
+def _flat_f_views(buf: Tensor, L: int, Pn: int, train: bool):
+    """Views into the flat fp32 output buffer of a batch.  The two [P, 4] box blocks come FIRST: the kernels write them as
+    float4, so they must start 16-byte aligned whatever L and P are."""
+    bh, bo = buf[:4 * Pn].view(Pn, 4), buf[4 * Pn:8 * Pn].view(Pn, 4)
+    o = 8 * Pn
+    scores, prior, weights = buf[o:o + L], buf[o + L:o + 3 * L].view(2, L), buf[o + 3 * L:o + 3 * L + Pn]
+    o += 3 * L + Pn
+    lab_e = buf[o:o + L] if train else None
+    unary = buf[o + L:o + L + Pn] if train else None
+    return bh, bo, scores, prior, weights, lab_e, unary
 
 
 class PendingResults:
@@ -798,15 +808,12 @@ def results_to_host(ih, results: List[dict], wait: bool = True):
 def _split_host_results(flat, hi, hf, results):
     L, Pn, psz, esz = flat["L"], flat["P"], flat["psz"], flat["esz"]
     index, pred, obj = hi[:L], hi[L:2 * L], hi[2 * L:]
-    scores, prior, weights = hf[:L], hf[L:3 * L].view(2, L), hf[3 * L:3 * L + Pn]
-    o = 3 * L + Pn
-    bh, bo = hf[o:o + 4 * Pn].view(Pn, 4), hf[o + 4 * Pn:o + 8 * Pn].view(Pn, 4)
+    bh, bo, scores, prior, weights, lab_e, unary = _flat_f_views(hf, L, Pn, flat["train"])
     out = [dict(boxes_h=a, boxes_o=b_, index=c, prediction=d_, scores=e, object=f, prior=g, weights=h)
            for a, b_, c, d_, e, f, g, h in zip(bh.split(psz), bo.split(psz), index.split(esz), pred.split(esz), scores.split(esz),
                                                obj.split(psz), prior.split(esz, dim=1), weights.split(psz))]
     if flat["train"]:
-        o += 8 * Pn
-        for r, l_b, u_b in zip(out, hf[o:o + L].split(esz), hf[o + L:o + L + Pn].split(psz)):
+        for r, l_b, u_b in zip(out, lab_e.split(esz), unary.split(psz)):
             r["labels"] = l_b; r["unary_labels"] = u_b
     out.extend(results[len(out):])            # the trailing loss dict (training) stays where it is
     return out

@@ -210,6 +210,10 @@ class InteractionHead(Module):
                             box_labels, box_scores, targets=None, meta=None) -> List[dict]:
         """The hot path proper: head.py:389-427 given already-preprocessed detections and pooled
         box features (what remains of ``forward`` after the stock torchvision NMS / RoIAlign steps)."""
+        if self.training and torch.is_grad_enabled():
+            from .train import training_forward      # losses differentiable w.r.t. the head parameters
+            return training_forward(self, features, image_shapes, box_features, box_coords, box_labels, box_scores,
+                                    targets, meta=meta)
         from .engine import interaction_head_from_pooled
         return interaction_head_from_pooled(self, features, image_shapes, box_features, box_coords, box_labels,
                                             box_scores, targets, meta=meta)
