@@ -47,6 +47,9 @@ def parse_args():
     ap.add_argument("--boxes", type=int, default=32)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-rooflines", action="store_true")
+    ap.add_argument("--no-train", action="store_true", help="skip the supplementary training-step line (configs[2])")
+    ap.add_argument("--train-images", type=int, default=16, help="images per training step per GPU (configs[2]: 16)")
+    ap.add_argument("--train-steps", type=int, default=10)
     return ap.parse_args()
 
 
@@ -309,6 +312,9 @@ def run_b200(args):
     roof = None; extra_roofs = {}
     if rank == 0 and not args.no_rooflines:
         roof, extra_roofs = measure_rooflines(torch, _lib, engine, ih, dev, flush, hbm_peak, tf_peak, peak_src)
+    train = None
+    if not args.no_train:
+        train = measure_training(torch, dist, args, dev, rank, world, flush)
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         v, cores, sps = cpu_head_throughput(args, steps=20, warmup=1)
@@ -328,9 +334,66 @@ def run_b200(args):
                         "timing": "host wall clock over all K steps; per step: H2D of its inputs from pinned memory (copy stream, one step ahead), forward through InteractionHead.forward_from_pooled, 256 MiB L2 flush write, D2H of its results to pinned memory, read on the host one step later (event wait)"},
                 "gpu_launches": int(launches), "clocks": clocks, "roofline": roof, "cpu_baseline": cpu}
         line.update(extra_roofs)
+        if train is not None:
+            line["training"] = train
         print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
+
+
+def measure_training(torch, dist, args, dev, rank, world, flush):
+    """BASELINE configs[2]: interaction-head training step, batch 16 images / GPU, data-parallel.  One step = zero_grad,
+    forward (train mode, targets), backward of the three losses, bucketed gradient all-reduce (NCCL when world > 1) and
+    an SGD update.  Device-resident inputs, CUDA events per step, L2 flushed between steps, max over ranks."""
+    from skghoi_b200 import shard, synthetic
+    from skghoi_b200.head import build_interaction_head
+    otv = synthetic.hico_object_to_verb()
+    ih = build_interaction_head(otv, seed=42, distributed=world > 1)
+    ih.box_pair_head.transh_head.set_tables(*synthetic.make_transh_tables(42))
+    ih = ih.to(dev).train()
+    ih.box_pair_head.transh_head.transh.to(dev)
+    n_img = args.train_images
+    batch = synthetic.make_batch([(args.humans, args.boxes)] * n_img, seed=1042 + rank, with_targets=True)
+    d = dict(f={"3": batch["features"]["3"].to(dev)}, bf=batch["box_features"].to(dev),
+             boxes=[b.to(dev) for b in batch["box_coords"]], labels=[l.to(dev) for l in batch["box_labels"]],
+             scores=[s_.to(dev) for s_ in batch["box_scores"]],
+             targets=[{k: v.to(dev) for k, v in t.items()} for t in batch["targets"]])
+    from skghoi_b200 import engine
+    meta = engine._host_meta(batch["box_labels"], batch["box_scores"], 49)
+    params = [p for p in ih.parameters() if p.requires_grad]
+    opt = torch.optim.SGD(params, lr=1e-4, momentum=0.9)
+    buckets = shard.GradBuckets(params)
+
+    def step():
+        opt.zero_grad(set_to_none=True)
+        res = ih.forward_from_pooled(d["f"], batch["image_shapes"], d["bf"], d["boxes"], d["labels"], d["scores"],
+                                     d["targets"], meta=meta)
+        ls = res[-1]
+        (ls["hoi_loss"] + ls["interactiveness_loss"] + ls["transH_loss"].sum()).backward()
+        buckets.allreduce()
+        opt.step()
+        return ls
+    for _ in range(3):
+        ls = step(); flush.zero_()
+    torch.cuda.synchronize(dev)
+    if world > 1:
+        dist.barrier()
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.train_steps)]
+    for s_, e in ev:
+        s_.record(); ls = step(); e.record(); flush.zero_()
+    torch.cuda.synchronize(dev)
+    if world > 1:
+        dist.barrier()
+    t_ms = shard.max_over_ranks([sum(s_.elapsed_time(e) for s_, e in ev)], device=dev)[0]
+    pairs = n_img * args.humans * (args.boxes - 1)
+    return {"workload": "interaction-head training step, batch %d images/GPU x (%d humans, %d boxes), data-parallel "
+                        "(BASELINE configs[2])" % (n_img, args.humans, args.boxes),
+            "value": pairs * world * args.train_steps / (t_ms * 1e-3), "unit": UNIT, "ms_per_step": t_ms / args.train_steps,
+            "steps": args.train_steps, "n_gpus": world, "pairs_per_step_per_gpu": pairs,
+            "step": "zero_grad + forward + backward (y, dx, dW of every dense layer on the tcgen05 GEMM) + %s + SGD update"
+                    % ("bucketed NCCL gradient all-reduce (%d buckets)" % len(buckets.buckets) if world > 1 else "no all-reduce (1 GPU)"),
+            "grad_bytes": sum(p.numel() * 4 for p in params),
+            "final_losses": {k: float(v.detach().reshape(-1)[0]) for k, v in ls.items()}}
 
 
 def _time_kernel(torch, fn, flush, reps=20):
@@ -438,9 +501,21 @@ def measure_rooflines(torch, _lib, engine, ih, dev, flush, hbm_peak, tf_peak, pe
     return roof, extra
 
 
+def _quiet_stdout():
+    """Libraries (NCCL's version banner, torchrun notices) write to fd 1; the contract is ONE JSON line on stdout.
+    Point fd 1 at stderr for the run and hand back a file object on the real stdout for the final line."""
+    sys.stdout.flush()
+    real = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
+    return real
+
+
 if __name__ == "__main__":
     a = parse_args()
+    _real_stdout = _quiet_stdout()
+    sys.stdout = _real_stdout
     if a.impl == "reference":
         run_reference(a)
     else:
         run_b200(a)
+    sys.stdout.flush()
