@@ -125,6 +125,17 @@ __host__ __device__ constexpr uint32_t make_idesc(int m, int n) {
   return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(m >> 4) << 24);
 }
 
+// explicit shared-space accesses: the 1024-byte re-alignment of the dynamic smem base goes through uintptr_t, after which
+// the compiler no longer knows the address space and would emit generic LD / ST (long-scoreboard, behind the global queue)
+__device__ __forceinline__ void sts_f4(uint32_t addr, float4 v) {
+  asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};\n" ::"r"(addr), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
+__device__ __forceinline__ float4 lds_f4(uint32_t addr) {
+  float4 v;
+  asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];\n" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr) : "memory");
+  return v;
+}
+
 __device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
   __nv_bfloat162 v = __floats2bfloat162_rn(a, b);
   return *reinterpret_cast<uint32_t*>(&v);
@@ -246,7 +257,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     const int ew = warp - kEpiWarp0;
     const int quad = warp & 3;                            // TMEM lane quadrant this warp may access
     const int part = ew >> 2;                             // which quarter of the tile's columns this warp drains
-    float4* patch = reinterpret_cast<float4*>(staging) + ew * 128;   // 32 rows x 4 float4
+    const uint32_t patch = smem_u32(staging) + (uint32_t)ew * 2048u;   // 32 rows x 4 float4 (shared-space address)
     const int sub = lane >> 2;                            // row inside an 8-row group
     const int cq = (lane & 3) * 4;                        // first of this lane's 4 columns inside a 16-column block
     constexpr int kBlocks = BN / (16 * kEpiParts);        // 16-column blocks per warp (even, or 1)
@@ -349,9 +360,9 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             __syncwarp();                              // the patch's previous readers are done
 #pragma unroll
             for (int j = 0; j < 4; ++j)
-              patch[lane * 4 + (j ^ ((lane >> 1) & 3))] =
-                  make_float4(__uint_as_float(raw[4 * j]), __uint_as_float(raw[4 * j + 1]), __uint_as_float(raw[4 * j + 2]),
-                              __uint_as_float(raw[4 * j + 3]));
+              sts_f4(patch + (uint32_t)(lane * 4 + (j ^ ((lane >> 1) & 3))) * 16u,
+                     make_float4(__uint_as_float(raw[4 * j]), __uint_as_float(raw[4 * j + 1]), __uint_as_float(raw[4 * j + 2]),
+                                 __uint_as_float(raw[4 * j + 3])));
             __syncwarp();
           }
 #pragma unroll
@@ -359,7 +370,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             const int r = it * 8 + sub;
             float4 v;
             if (pass == 0) {
-              v = patch[r * 4 + ((lane & 3) ^ ((r >> 1) & 3))];
+              v = lds_f4(patch + (uint32_t)(r * 4 + ((lane & 3) ^ ((r >> 1) & 3))) * 16u);
               if (split_mode) {                        // partial sum -> scratch tile (fp32 reduction in L2)
                 if (m0 + quad * 32 + r < M) {
                   float* dst = ws_rows + (size_t)(it * 8) * BN + c0 + cq;

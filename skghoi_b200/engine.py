@@ -449,22 +449,27 @@ def head_forward(ih, features3: Tensor, image_shapes, box_features: Tensor, boxe
     return run
 
 
-def dominant_gemm_closure(ih, run: dict) -> dict:
+def dominant_gemm_closure(ih, run: dict, private_copy: bool = False) -> dict:
     """Re-launchable closure of the step's dominant kernel -- the fused fc_2 GEMM of the four MBFs
-    (M = cells, N = 4R, K = 1024) on the operands of the last forward -- for bench.py's roofline leg."""
+    (M = cells, N = 4R, K = 1024) on the operands of the last forward -- for bench.py's roofline leg.
+    ``private_copy`` gives the closure its own copies of every operand and output (bench.py rotates several such
+    sets so that consecutive launches never find their operands in L2)."""
     pk = packed_head(ih)
     R = pk.R
-    sp, hproj, oproj, Gt = run["sp"], run["hproj"], run["oproj"], run["Gt"]
-    H_att, S_raw, H_os, H_so, H_g = run["H_att"], run["S_raw"], run["H_os"], run["H_so"], run["H_g"]
-    hrow, orow, img = run["cell_hrow"], run["cell_orow"], run["cell_img"]
+    c = (lambda t: t.clone()) if private_copy else (lambda t: t)
+    sp, hproj, oproj, Gt = c(run["sp"]), c(run["hproj"]), c(run["oproj"]), c(run["Gt"])
+    H_att, S_raw, H_os, H_so, H_g = c(run["H_att"]), c(run["S_raw"]), c(run["H_os"]), c(run["H_so"]), c(run["H_g"])
+    hrow, orow, img = c(run["cell_hrow"]), c(run["cell_orow"]), c(run["cell_img"])
+    W2cat, b2cat = c(pk.W2cat), c(pk.b2cat)
     groups = [
-        _g(n_begin=0, relu=True, bias=pk.b2cat, mul_p=hproj[:, :R], row_p=hrow, mul_q=oproj[:, :R], row_q=orow,
+        _g(n_begin=0, relu=True, bias=b2cat, mul_p=hproj[:, :R], row_p=hrow, mul_q=oproj[:, :R], row_q=orow,
            out_bf16=H_att, raw_bf16=S_raw),
-        _g(n_begin=R, relu=True, bias=pk.b2cat, mul_p=oproj[:, R:], row_p=orow, out_bf16=H_os),
-        _g(n_begin=2 * R, relu=True, bias=pk.b2cat, mul_p=hproj[:, R:], row_p=hrow, out_bf16=H_so),
-        _g(n_begin=3 * R, relu=True, bias=pk.b2cat, mul_p=Gt, row_p=img, out_bf16=H_g)]
-    M, N, K = sp.shape[0], pk.W2cat.shape[0], pk.W2cat.shape[1]
-    return dict(launch=lambda: _lib.gemm_bf16(sp, pk.W2cat, groups), M=M, N=N, K=K, flops=2.0 * M * N * K)
+        _g(n_begin=R, relu=True, bias=b2cat, mul_p=oproj[:, R:], row_p=orow, out_bf16=H_os),
+        _g(n_begin=2 * R, relu=True, bias=b2cat, mul_p=hproj[:, R:], row_p=hrow, out_bf16=H_so),
+        _g(n_begin=3 * R, relu=True, bias=b2cat, mul_p=Gt, row_p=img, out_bf16=H_g)]
+    M, N, K = sp.shape[0], W2cat.shape[0], W2cat.shape[1]
+    nbytes = sum(t.numel() * t.element_size() for t in (sp, W2cat, hproj, oproj, H_att, S_raw, H_os, H_so, H_g))
+    return dict(launch=lambda: _lib.gemm_bf16(sp, W2cat, groups), M=M, N=N, K=K, flops=2.0 * M * N * K, footprint=nbytes)
 
 
 # =============================================================================================

@@ -13,8 +13,10 @@ dev = torch.device("cuda:0")
 flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
 
 
-def timeit(fn, reps=10, do_flush=True):
-    fn(); torch.cuda.synchronize()
+def timeit(fn, reps=20, do_flush=True):
+    for _ in range(3):
+        fn()
+    torch.cuda.synchronize()
     tot = 0.0
     for _ in range(reps):
         if do_flush:
@@ -83,8 +85,11 @@ def anatomy():
 if "--anatomy" in sys.argv:
     anatomy()
     sys.exit(0)
-if "--fused-only" in sys.argv:
-    run(4096, 4096, 1024, "fused4")
+if "--fused-only" in sys.argv:       # A/B protocol: same pre-conditioning every time, plain GEMM of the same shape as control
+    run(4096, 4096, 4096, "plain")
+    for _ in range(3):
+        run(4096, 4096, 1024, "plain")
+        run(4096, 4096, 1024, "fused4")
     sys.exit(0)
 run(8192, 8192, 8192, "plain")
 run(4096, 4096, 4096, "plain")
