@@ -196,8 +196,50 @@ __global__ void __launch_bounds__(kGridThreads) transh_grid_kernel(
     }
     return;
   }
-  // rows mode: one warp per cell -- 4 x rel_tot x dim floats of pure shared-memory -> global copy per cell
-  for (int64_t c = warp; c < num_cells; c += nwarps) {
+  // rows mode, fast path: a CTA owns PAIRS of consecutive cells.  One cell's block of an output array is rel_tot*dim
+  // floats (23 400 B for 117 x 50: only 8-byte aligned), a pair's is 16-byte aligned whenever rel_tot*dim is even, so
+  // the pair is written as whole float4s -- 512 contiguous bytes per warp store -- each assembled from two float2
+  // shared-memory reads (dim even: a float2 never straddles a row, nR even: nor a cell).
+  int64_t c_done = 0;
+  if ((nR & 1) == 0 && (dim & 1) == 0 &&
+      (((uintptr_t)h_out | (uintptr_t)r_out | (uintptr_t)w_out | (uintptr_t)t_out) & 15u) == 0) {
+    const int64_t num_pairs = num_cells >> 1;
+    const int n4 = nR >> 1;                              // float4s per pair and per output array
+    const float* eh = sE + head_const * dim;
+    for (int64_t pr = blockIdx.x; pr < num_pairs; pr += gridDim.x) {
+      const int64_t c0 = 2 * pr;
+      int64_t ta = cell_tail ? __ldg(cell_tail + c0) : c0, tb = cell_tail ? __ldg(cell_tail + c0 + 1) : c0 + 1;
+      const int tl0 = (int)(ta >= ent_tot ? ent_tot - 1 : (ta < 0 ? 0 : ta));
+      const int tl1 = (int)(tb >= ent_tot ? ent_tot - 1 : (tb < 0 ? 0 : tb));
+      for (int q = threadIdx.x; q < 2 * rel_tot; q += kGridThreads)
+        __stcs(score + c0 * rel_tot + q, sS[(q < rel_tot ? tl0 * rel_tot : tl1 * rel_tot - rel_tot) + q]);
+      const float* et0 = sE + tl0 * dim; const float* et1 = sE + tl1 * dim;
+      const int64_t base = c0 * nR;
+      float4* ph = reinterpret_cast<float4*>(h_out + base); float4* pr4 = reinterpret_cast<float4*>(r_out + base);
+      float4* pw = reinterpret_cast<float4*>(w_out + base); float4* pt = reinterpret_cast<float4*>(t_out + base);
+      for (int k = threadIdx.x; k < n4; k += kGridThreads) {
+        float2 vh[2], vr[2], vw[2], vt[2];
+#pragma unroll
+        for (int half = 0; half < 2; ++half) {
+          int off = 4 * k + 2 * half;
+          const bool second = off >= nR;
+          if (second) off -= nR;
+          const int d = off % dim;
+          vh[half] = *reinterpret_cast<const float2*>(eh + d);
+          vt[half] = *reinterpret_cast<const float2*>((second ? et1 : et0) + d);
+          vr[half] = *reinterpret_cast<const float2*>(sR + off);
+          vw[half] = *reinterpret_cast<const float2*>(sW + off);
+        }
+        __stcs(ph + k, make_float4(vh[0].x, vh[0].y, vh[1].x, vh[1].y));
+        __stcs(pr4 + k, make_float4(vr[0].x, vr[0].y, vr[1].x, vr[1].y));
+        __stcs(pw + k, make_float4(vw[0].x, vw[0].y, vw[1].x, vw[1].y));
+        __stcs(pt + k, make_float4(vt[0].x, vt[0].y, vt[1].x, vt[1].y));
+      }
+    }
+    c_done = num_pairs * 2;                              // an odd last cell falls through to the per-warp path
+  }
+  // rows mode, general path: one warp per cell -- 4 x rel_tot x dim floats of pure shared-memory -> global copy per cell
+  for (int64_t c = c_done + warp; c < num_cells; c += nwarps) {
     int64_t t64 = cell_tail ? __ldg(cell_tail + c) : c;
     const int tl = (int)(t64 >= ent_tot ? ent_tot - 1 : (t64 < 0 ? 0 : t64));
     const float* srow = sS + tl * rel_tot;
@@ -230,8 +272,11 @@ static int launch_forward(const float* ent, const float* rel, const float* nrm, 
                           const TripleIndex& idx, int64_t T, int p_norm, int norm_flag, float* h_out, float* r_out,
                           float* w_out, float* t_out, float* score, cudaStream_t stream) {
   const size_t table_bytes = ((((size_t)ent_tot * dim + 3) & ~(size_t)3) + 2 * (((size_t)rel_tot * dim + 3) & ~(size_t)3) + 2 * (size_t)rel_tot) * sizeof(float);
-  const bool fits = table_bytes <= 100 * 1024;
-  const int64_t want = ceil_div64(T, kFwdWarps * 4 * 4);
+  // few triples and no row outputs (the [ent_tot, rel_tot] score table of the grid form): staging 60 KB of tables per CTA
+  // would be the whole run time -- read the rows through L1/L2 instead and spread one 4-triple step per warp
+  const bool small = T <= 32768 && h_out == nullptr;
+  const bool fits = table_bytes <= 100 * 1024 && !small;
+  const int64_t want = ceil_div64(T, kFwdWarps * 4 * (small ? 1 : 4));
   const int per_sm = fits ? (table_bytes > 72 * 1024 ? 2 : 3) : 8;
   int grid = (int)(want < (int64_t)num_sms() * per_sm ? want : (int64_t)num_sms() * per_sm);
   if (grid < 1) grid = 1;
@@ -324,7 +369,7 @@ extern "C" int skg_transh_forward_grid(const float* ent, const float* rel, const
   if (rc == SKG_OK) {
     // 2) broadcast over the cells
     const int per_sm = smem_bytes > 110 * 1024 ? 1 : (smem_bytes > 72 * 1024 ? 2 : 3);
-    const int64_t want = rows ? ceil_div64(num_cells, kGridWarps) : ceil_div64(num_cells, kGridThreads);
+    const int64_t want = rows ? ceil_div64(num_cells, 2) : ceil_div64(num_cells, kGridThreads);   // rows: a CTA per cell pair
     const int grid = (int)(want < (int64_t)num_sms() * per_sm ? want : (int64_t)num_sms() * per_sm);
     if (rows) {
       auto k = transh_grid_kernel<true>;

@@ -1,0 +1,23 @@
+import torch
+dev=torch.device("cuda:0")
+def t(fn, n=10):
+    fn(); fn(); torch.cuda.synchronize()
+    s=torch.cuda.Event(enable_timing=True); e=torch.cuda.Event(enable_timing=True)
+    s.record()
+    for _ in range(n): fn()
+    e.record(); torch.cuda.synchronize()
+    return s.elapsed_time(e)/n*1e-3
+for mb in (256, 1024, 4096):
+    buf=torch.empty(mb<<20, dtype=torch.uint8, device=dev)
+    sec=t(lambda: buf.zero_())
+    print("memset torch fill %5d MiB: %.1f GB/s" % (mb, buf.numel()/sec/1e9))
+    f=buf.view(torch.float32)
+    sec=t(lambda: f.fill_(1.5))
+    print("fill_ f32         %5d MiB: %.1f GB/s" % (mb, buf.numel()/sec/1e9))
+    import ctypes
+    rt=ctypes.CDLL("libcudart.so")
+    sec=t(lambda: rt.cudaMemsetAsync(ctypes.c_void_p(buf.data_ptr()), 0, ctypes.c_size_t(buf.numel()), ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)))
+    print("cudaMemsetAsync   %5d MiB: %.1f GB/s" % (mb, buf.numel()/sec/1e9))
+a=torch.empty(1<<30, dtype=torch.uint8, device=dev); b=torch.empty_like(a)
+sec=t(lambda: b.copy_(a)); print("copy 1GiB read+write: %.1f GB/s" % (2*a.numel()/sec/1e9))
+sec=t(lambda: a.sum(dtype=torch.int64) if False else a.view(torch.float32).sum()); print("read-only sum 1GiB: %.1f GB/s" % (a.numel()/sec/1e9))
