@@ -352,6 +352,7 @@ def measure_training(torch, dist, args, dev, rank, world, flush):
     ih.box_pair_head.transh_head.set_tables(*synthetic.make_transh_tables(42))
     ih = ih.to(dev).train()
     ih.box_pair_head.transh_head.transh.to(dev)
+    ih.box_pair_head.transh_head.negatives_on_device = True     # same distribution as head.py:939, device generator, batched
     n_img = args.train_images
     batch = synthetic.make_batch([(args.humans, args.boxes)] * n_img, seed=1042 + rank, with_targets=True)
     d = dict(f={"3": batch["features"]["3"].to(dev)}, bf=batch["box_features"].to(dev),
@@ -390,6 +391,7 @@ def measure_training(torch, dist, args, dev, rank, world, flush):
                         "(BASELINE configs[2])" % (n_img, args.humans, args.boxes),
             "value": pairs * world * args.train_steps / (t_ms * 1e-3), "unit": UNIT, "ms_per_step": t_ms / args.train_steps,
             "steps": args.train_steps, "n_gpus": world, "pairs_per_step_per_gpu": pairs,
+            "negatives": "TransH negatives drawn on the device (uniform without replacement per image, as head.py:939)",
             "step": "zero_grad + forward + backward (y, dx, dW of every dense layer on the tcgen05 GEMM) + %s + SGD update"
                     % ("bucketed NCCL gradient all-reduce (%d buckets)" % len(buckets.buckets) if world > 1 else "no all-reduce (1 GPU)"),
             "grad_bytes": sum(p.numel() * 4 for p in params),

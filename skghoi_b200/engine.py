@@ -624,6 +624,8 @@ def _transh_pos_neg(G, run, labels: Tensor, targets):
     th = G.transh_head
     tr = th.transh
     dev = seg.device
+    if getattr(th, "negatives_on_device", False):
+        return _transh_pos_neg_device(G, run, labels)
     lab_img = _split(labels, seg.pair_off[1:] - seg.pair_off[:-1])
     yk_img = _split(run["y_keep"], seg.pair_off[1:] - seg.pair_off[:-1])
     pos_s, neg_s, ents_h, ents_t, rels, rnorms = [], [], [], [], [], []
@@ -643,6 +645,51 @@ def _transh_pos_neg(G, run, labels: Tensor, targets):
         pos_s.append(score[:k]); neg_s.append(score[k:])
         ents_h.append(h_); ents_t.append(t_); rels.append(r); rnorms.append(w)
     return pos_s, neg_s, ents_h, ents_t, rels, rnorms
+
+
+def select_negatives_device(labels: Tensor, pair_img: Tensor, num_images: int):
+    """(pos_flat, neg_flat): flat indices into ``labels [P, num_cls]`` of the positives and, per image, of as many
+    zero-label entries drawn uniformly without replacement (random key per entry, one sort, rank inside the image)."""
+    Pn, nc = labels.shape
+    dev = labels.device
+    is_pos = labels != 0
+    n_pos_img = torch.zeros(num_images, dtype=torch.int64, device=dev).index_add_(0, pair_img, is_pos.sum(1))
+    key = torch.rand(Pn, nc, device=dev) + pair_img[:, None].to(torch.float32)
+    key = torch.where(is_pos, torch.full_like(key, float("inf")), key).view(-1)
+    order = torch.argsort(key)
+    finite = torch.isfinite(key[order])
+    img_sorted = torch.where(finite, pair_img.repeat_interleave(nc)[order], torch.full_like(order, num_images))
+    first = torch.searchsorted(img_sorted, torch.arange(num_images + 1, device=dev))   # first sorted slot of every image
+    rank = torch.arange(Pn * nc, device=dev) - first[img_sorted]
+    n_pos_ext = torch.cat([n_pos_img, n_pos_img.new_zeros(1)])
+    neg_flat = order[finite & (rank < n_pos_ext[img_sorted])]
+    pos_flat = torch.nonzero(is_pos.view(-1)).squeeze(1)                             # host sync (sizes)
+    return pos_flat, neg_flat
+
+
+def _transh_pos_neg_device(G, run, labels: Tensor):
+    """Batched form of the selection above for ``transH_head.negatives_on_device``: per image, as many negatives as
+    positives, drawn uniformly without replacement among that image's zero labels -- the same distribution as
+    ``randperm(#neg)[:#pos]`` (head.py:939) but from the DEVICE generator (random keys, one sort, rank < #pos) and for the
+    whole batch at once: one host sync, one TransH call.  Returned as one-element lists (the loss concatenates them)."""
+    seg: Segments = run["seg"]
+    th = G.transh_head
+    dev = seg.device
+    nc = G.num_cls
+    Pn = seg.total_pairs
+    if Pn == 0:
+        return [], [], [], [], [], []
+    pair_img = run["cell_img"].long()[run["pair2cell"].long()]                       # image of every valid pair
+    pos_flat, neg_flat = select_negatives_device(labels, pair_img, seg.B)
+    sel = torch.cat([pos_flat, neg_flat])
+    pair_idx = torch.div(sel, nc, rounding_mode="floor"); verb = sel - pair_idx * nc
+    tails = run["y_keep"][pair_idx]
+    heads = torch.full_like(tails, th.human_idx)
+    h_, r, w, t_, score = th.transh(heads, verb, tails)
+    k = pos_flat.numel()
+    kn = neg_flat.numel()
+    m = min(k, kn)                                   # an image with more positives than zero labels cannot occur (117 verbs)
+    return [score[:m]], [score[k:k + m]], [h_], [t_], [r], [w]
 
 
 def graph_head_forward(G, features, image_shapes, box_features, box_coords, box_labels, box_scores, targets=None,
@@ -695,15 +742,18 @@ def _shell_for(G):
 
 
 def interaction_head_from_pooled(ih, features, image_shapes, box_features, box_coords, box_labels, box_scores,
-                                 targets=None, meta=None) -> List[dict]:
-    """InteractionHead.forward from the pooled box features on (head.py:389-427)."""
+                                 targets=None, meta=None, run=None) -> List[dict]:
+    """InteractionHead.forward from the pooled box features on (head.py:389-427).  ``run`` (training pass): pair maps,
+    segment table and logits computed by the caller -- the native GEMM chain is then skipped and only the
+    post-processing / GT association / loss kernels run."""
     from . import ops
     from .kge import MarginLoss, NegativeSampling
     G = ih.box_pair_head
     if ih.training:
         assert targets is not None, "Targets should be passed during training"          # head.py:380-381
     meta, boxes_cat, labels_dev, scores_dev = _prep_inputs(G, features, box_features, box_coords, box_labels, box_scores, meta)
-    run = head_forward(ih, features["3"], image_shapes, box_features, boxes_cat, meta)
+    if run is None:
+        run = head_forward(ih, features["3"], image_shapes, box_features, boxes_cat, meta)
     seg: Segments = run["seg"]
     dev = seg.device
     Pn = seg.total_pairs

@@ -80,6 +80,9 @@ class transH_head(Module):
         self.num_object = num_object
         self.num_cls = num_cls
         self.resample = False
+        # False: negatives drawn like the reference, torch.randperm on the CPU generator per image (head.py:939, seed
+        # compatible); True: same distribution from the device generator for the whole batch at once (no per-image syncs)
+        self.negatives_on_device = False
         # built lazily (and outside the seeded construction order of the reference modules)
         self.__dict__["_transh"] = None
 

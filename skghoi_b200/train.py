@@ -170,24 +170,35 @@ def training_forward(ih, features, image_shapes, box_features: Tensor, box_coord
     from . import engine, ops
     assert targets is not None, "Targets should be passed during training"                 # head.py:380-381
     G = ih.box_pair_head
+    meta, boxes_cat, labels_dev, scores_dev = engine._prep_inputs(G, features, box_features, box_coords, box_labels,
+                                                                  box_scores, meta)
+    n, n_h = meta["n"], meta["n_h"]
+    if any(k > G.transh_head.num_object for k in n):
+        raise IndexError("index out of range in self")                                     # head.py:572
+    n_h_eff = [0 if (h == 0 or k <= 1) else h for h, k in zip(n_h, n)]
+    dev = box_features.device
+    # pair enumeration + spatial encoding + row maps: the same kernel as inference, no tape (boxes carry no gradient)
+    pe = engine.enumerate_pairs(None, n_h_eff, image_shapes, seg=engine.Segments(n_h_eff, n, image_shapes, dev),
+                                boxes_cat=boxes_cat)
+    seg = pe["seg"]
+    with torch.enable_grad():
+        logits = head_logits(ih, features["3"], box_features, pe)
+    # post-processing indices, priors, GT labels and the TransH loss from the native kernels, fed with the taped logits
+    lg = logits.detach()
+    run = dict(pe)
+    run.update(logits=lg if lg.is_contiguous() else lg.contiguous(),
+               post_i32=torch.empty(2 * max(seg.total_boxes, 1), dtype=torch.int32, device=dev),
+               post_i64=torch.empty(max(seg.total_humans, 1) + 2 * seg.B + 1, dtype=torch.int64, device=dev))
     was_training = ih.training
     ih.train()
     try:
-        # indices, priors, GT labels, result dicts from the native path (its kernels record no tape); its TransH loss
-        # is already differentiable w.r.t. the TransH tables (kge._TransHScore / _MarginLossFn)
-        with torch.enable_grad():
+        with torch.enable_grad():           # the TransH loss is differentiable w.r.t. the tables (kge autograd Functions)
             results = engine.interaction_head_from_pooled(ih, features, image_shapes, box_features.detach(), box_coords,
-                                                          box_labels, box_scores, targets=targets, meta=meta)
+                                                          box_labels, box_scores, targets=targets, meta=meta, run=run)
     finally:
         ih.train(was_training)
     with torch.enable_grad():
         native_losses = results.pop()
-        run = ih.__dict__["_skg_last_run"]
-        seg = run["seg"]
-        # copies: the maps live in the step workspace, which the next forward overwrites while the tape may still hold them
-        pe = {k: run[k].clone() for k in ("enc", "cell_hrow", "cell_orow", "cell_img", "pair2cell")}
-        pe["seg"] = seg
-        logits = head_logits(ih, features["3"], box_features, pe)
         nc = G.num_cls
         dev = logits.device
         gx = torch.cat([r["index"] + int(o) for r, o in zip(results, seg.pair_off[:-1])])

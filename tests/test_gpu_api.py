@@ -144,8 +144,14 @@ def test_training_pass_gradients_vs_oracle_autograd():
     assert abs(float(losses["transH_loss"].reshape(-1)[0]) - float(ref_loss["transH_loss"].reshape(-1)[0])) <= 1e-4
     (losses["hoi_loss"] + losses["interactiveness_loss"]).backward()
     # the native eval-style logits of the same step agree with the taped ones
-    run = ih.__dict__["_skg_last_run"]; tr = ih.__dict__["_skg_last_train"]
-    assert float((run["logits"][:, :118] - tr["logits"].detach()).abs().max()) <= 1e-2 * float(tr["logits"].abs().max())
+    # the taped logits agree with the fused inference path on the same inputs and weights
+    from skghoi_b200 import engine
+    tr = ih.__dict__["_skg_last_train"]
+    meta = engine._host_meta(batch["box_labels"], batch["box_scores"], 49)
+    with torch.no_grad():
+        native = engine.head_forward(ih, d["features"]["3"], d["image_shapes"], d["box_features"], torch.cat(d["box_coords"]),
+                                     meta)["logits"][:, :118].clone()
+    assert float((native - tr["logits"].detach()).abs().max()) <= 1e-2 * float(tr["logits"].abs().max())
     worst = (0.0, None)
     num = den = 0.0
     stats = []
