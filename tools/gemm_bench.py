@@ -49,6 +49,15 @@ def run(M, N, K, kind, bn=0):
                   g(n_begin=R, relu=True, bias=bias, mul_p=oproj[:, R:], row_p=orow, out_bf16=outs[2]),
                   g(n_begin=2 * R, relu=True, bias=bias, mul_p=hproj[:, R:], row_p=hrow, out_bf16=outs[3]),
                   g(n_begin=3 * R, relu=True, bias=bias, mul_p=gt, row_p=img, out_bf16=outs[4])]
+    elif kind in ("P_zero", "P_orow", "P_ident"):   # one group over all columns: Hadamard with ONE gathered table
+        ar = torch.arange(M, device=dev)
+        if kind == "P_zero":
+            tab = torch.randn(8, N, device=dev); rows = torch.zeros(M, dtype=torch.int32, device=dev)
+        elif kind == "P_orow":
+            tab = torch.randn(M // 16, N, device=dev); rows = ((ar // 512) * 32 + ar % 32).int()
+        else:
+            tab = torch.randn(M, N, device=dev); rows = ar.int()
+        groups = [_lib.epilogue_group(relu=True, bias=bias, mul_p=tab, row_p=rows, out_bf16=out16)]
     sec = timeit(lambda: _lib.gemm_bf16(A, B, groups, block_n=bn))
     tf = 2.0 * M * N * K / sec / 1e12
     print("%-7s M=%5d N=%5d K=%5d bn=%3d : %8.2f us  %7.1f TFLOP/s" % (kind, M, N, K, bn, sec * 1e6, tf))
@@ -84,6 +93,11 @@ def anatomy():
 
 if "--anatomy" in sys.argv:
     anatomy()
+    sys.exit(0)
+if "--epi" in sys.argv:
+    run(4096, 4096, 4096, "plain")
+    for kind in ("plain", "P_zero", "P_orow", "P_ident", "fused4", "plain"):
+        run(4096, 4096, 1024, kind)
     sys.exit(0)
 if "--fused-only" in sys.argv:       # A/B protocol: same pre-conditioning every time, plain GEMM of the same shape as control
     run(4096, 4096, 4096, "plain")
