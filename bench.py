@@ -321,6 +321,14 @@ def run_b200(args):
         cpu = {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
                "sample": "oracle/head_oracle.py (op-for-op fp32 restatement of the reference head), 20 steps of 1 image "
                          "(%d pairs) each, %.3f s/step" % (args.humans * (args.boxes - 1), sps)}
+    if rank == 0 and roof is not None:
+        tp = os.path.join(ROOT, "profiles", "ncu_traffic.json")
+        if os.path.isfile(tp):
+            tr_ = json.load(open(tp))
+            roof["traffic"] = tr_.get("roofline"); roof["traffic_source"] = tr_.get("source")
+            for k in extra_roofs:
+                if k in tr_ and isinstance(extra_roofs[k], dict):
+                    extra_roofs[k]["traffic"] = tr_[k]
     if rank == 0:
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
                 "warmup": max(args.warmup, 3), "ms_per_step": t_ms / args.steps, "higher_is_better": True,
