@@ -129,14 +129,18 @@ class ClockSampler:
         self.index = index; self.proc = None
 
     def start(self):
+        if self.index is None:
+            return
         try:
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
-                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                          "--format=csv,noheader,nounits", "-lms", "200"],
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
         except OSError:
             self.proc = None
 
     def stop(self):
+        if self.index is None:
+            return None
         if self.proc is None:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
         self.proc.terminate()
@@ -201,8 +205,12 @@ def run_b200(args):
     host = dict(f3=batch["features"]["3"].pin_memory(), bf=batch["box_features"].pin_memory(),
                 boxes=[b.pin_memory() for b in batch["box_coords"]], labels=[l.pin_memory() for l in batch["box_labels"]],
                 scores=[s.pin_memory() for s in batch["box_scores"]])
-    d = dict(f3=host["f3"].to(dev), bf=host["bf"].to(dev), boxes=[b.to(dev) for b in host["boxes"]],
-             labels=[l.to(dev) for l in host["labels"]], scores=[s.to(dev) for s in host["scores"]])
+    # the detection lists live in three packed device buffers; the module API gets per-image views of them
+    n_per_d = [int(b.shape[0]) for b in batch["box_coords"]]
+    d = dict(f3=host["f3"].to(dev), bf=host["bf"].to(dev),
+             boxes=list(torch.cat(batch["box_coords"]).to(dev).split(n_per_d)),
+             labels=list(torch.cat(batch["box_labels"]).to(dev).split(n_per_d)),
+             scores=list(torch.cat(batch["box_scores"]).to(dev).split(n_per_d)))
     meta = engine._host_meta(batch["box_labels"], batch["box_scores"], 49)   # host-side copy of the tiny label/score lists
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)          # > 126 MB L2
 
@@ -273,7 +281,9 @@ def run_b200(args):
         step_resident(); flush.zero_()
     torch.cuda.synchronize(dev)
     # ---- timed: device-resident inputs
-    sampler = ClockSampler(local)
+    # clocks / throttle reasons are sampled by rank 0 only (its own GPU): eight concurrent nvidia-smi pollers contend for
+    # the driver with the ranks' kernel launches and slow the host-bound step down
+    sampler = ClockSampler(local if rank == 0 else None)
     ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
     l0 = lib.skg_launch_count()
     barrier()

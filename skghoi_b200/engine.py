@@ -342,6 +342,7 @@ def _host_meta(box_labels: List[Tensor], box_scores: Optional[List[Tensor]], hum
 _INT64_BUFS = {"x", "y", "x_keep", "y_keep", "post_i64"}
 _INT32_BUFS = {"cell2pair", "cell_hrow", "cell_orow", "cell_img", "pair2cell", "nan_flag", "box2hum", "post_i32"}
 _workspaces = {}
+_ws_seg_owner = {}      # workspace data_ptr -> the Segments whose packed table currently sits in it
 
 
 def _workspace(dev, nbytes: int) -> Tensor:
@@ -394,14 +395,38 @@ def head_forward(ih, features3: Tensor, image_shapes, box_features: Tensor, boxe
     n, n_h = meta["n"], meta["n_h"]
     if any(k > G.transh_head.num_object for k in n):
         raise IndexError("index out of range in self")   # head.py:572: box index addresses the 80-row entity table
-    # images the reference skips (head.py:829-839) contribute no cells: treat them as n_h = 0
-    n_h_eff = [0 if (h == 0 or k <= 1) else h for h, k in zip(n_h, n)]
-    seg = Segments(n_h_eff, n, image_shapes)
     tr = G.transh_head.transh
     if tr.ent_embeddings.weight.device != dev:
         tr.to(dev)
     ent = tr.ent_embeddings.weight.detach()
     f3 = features3.contiguous()
+    flags = (_lib.HEAD_PRECISE_LOGITS if precise_logits else 0) | (_lib.HEAD_WANT_TAPS if want_taps else 0)
+    if profile:
+        flags |= _lib.HEAD_PROFILE
+    elif graph:
+        flags |= _lib.HEAD_GRAPH
+    import ctypes
+    # per-batch host preparation (segment table, batch descriptor, workspace plan) is cached INSIDE the caller's ``meta``
+    # dict: a caller that re-runs the same batch (same meta object) pays for it once
+    ck = (tuple(map(tuple, image_shapes)), flags, dev.index, int(f3.shape[2] * f3.shape[3]) if f3.dim() == 4 else 0)
+    cache = meta.get("_skg_fwd") if isinstance(meta, dict) else None
+    if cache is not None and cache["key"] == ck:
+        seg, b, plan = cache["seg"], cache["b"], cache["plan"]
+    else:
+        # images the reference skips (head.py:829-839) contribute no cells: treat them as n_h = 0
+        n_h_eff = [0 if (h == 0 or k <= 1) else h for h, k in zip(n_h, n)]
+        seg = Segments(n_h_eff, n, image_shapes)
+        b = _lib.HeadBatch()
+        b.num_images, b.total_boxes, b.total_humans = seg.B, seg.total_boxes, seg.total_humans
+        b.max_boxes_per_image = seg.max_n
+        b.seg_bytes = seg.nbytes
+        b.feat_hw = ck[3]
+        b.total_cells, b.total_pairs = seg.total_cells, seg.total_pairs
+        plan = _lib.HeadPlan()
+        _lib.call("skg_head_plan", ctypes.byref(pk.cw), ctypes.byref(b), flags, ctypes.byref(plan))
+        cache = dict(key=ck, seg=seg, b=b, plan=plan, run=None, ws_ptr=0)
+        if isinstance(meta, dict):
+            meta["_skg_fwd"] = cache
     bf = box_features.reshape(seg.total_boxes, -1)
     if not bf.is_contiguous():
         bf = bf.contiguous()
@@ -409,32 +434,25 @@ def head_forward(ih, features3: Tensor, image_shapes, box_features: Tensor, boxe
     w = pk.cw
     w.ent = ent.data_ptr()
     pk.fc_bias(ent, G.human_idx)
-    b = _lib.HeadBatch()
-    b.num_images, b.total_boxes, b.total_humans = seg.B, seg.total_boxes, seg.total_humans
-    b.max_boxes_per_image = seg.max_n
-    b.seg_bytes = seg.nbytes
-    b.feat_hw = int(f3.shape[2] * f3.shape[3]) if f3.dim() == 4 else 0
-    b.total_cells, b.total_pairs = seg.total_cells, seg.total_pairs
     b.features3, b.box_features, b.boxes = f3.data_ptr(), bf.data_ptr(), boxes_cat.data_ptr()
-    flags = (_lib.HEAD_PRECISE_LOGITS if precise_logits else 0) | (_lib.HEAD_WANT_TAPS if want_taps else 0)
-    if profile:
-        flags |= _lib.HEAD_PROFILE
-    elif graph:
-        flags |= _lib.HEAD_GRAPH
-    plan = _lib.HeadPlan()
-    import ctypes
-    _lib.call("skg_head_plan", ctypes.byref(w), ctypes.byref(b), flags, ctypes.byref(plan))
     with torch.cuda.device(dev):
         ws = _workspace(dev, int(plan.total_bytes))
-        so = int(plan.offset[_lib.head_buffer_names().index("seg")])
-        seg.upload(ws[so:so + seg.nbytes])          # fixed place in the workspace: stable pointers for the graph cache
-        b.box_off, b.n_h, b.hum_off = seg.d_box_off.data_ptr(), seg.d_n_h.data_ptr(), seg.d_hum_off.data_ptr()
-        b.cell_off, b.pair_off, b.hw = seg.d_cell_off.data_ptr(), seg.d_pair_off.data_ptr(), seg.d_hw.data_ptr()
+        wkey = ws.data_ptr()
+        if _ws_seg_owner.get(wkey) is not seg:       # the table of another batch (or nothing) sits in the workspace
+            so = int(plan.offset[_lib.head_buffer_names().index("seg")])
+            seg.upload(ws[so:so + seg.nbytes])      # fixed place in the workspace: stable pointers for the graph cache
+            _ws_seg_owner.clear(); _ws_seg_owner[wkey] = seg
+            b.box_off, b.n_h, b.hum_off = seg.d_box_off.data_ptr(), seg.d_n_h.data_ptr(), seg.d_hum_off.data_ptr()
+            b.cell_off, b.pair_off, b.hw = seg.d_cell_off.data_ptr(), seg.d_pair_off.data_ptr(), seg.d_hw.data_ptr()
         try:
             _lib.call("skg_head_forward", ctypes.byref(w), ctypes.byref(b), flags, _lib.ptr(ws), ws.numel(), _lib.stream_ptr(dev))
         except Exception:
-            _workspaces.clear()          # a failed step may leave the split-K scratch dirty: start from a fresh one
+            _workspaces.clear(); _ws_seg_owner.clear()   # a failed step may leave the split-K scratch dirty: start afresh
             raise
+    if cache["run"] is not None and cache["ws_ptr"] == wkey and not profile and not want_taps:
+        run = cache["run"]                           # same workspace, same plan: the named views are still valid
+        run["_keep"] = (f3, bf, boxes_cat, ent)
+        return run
     run = _Run(ws, plan, seg=seg, NH=seg.total_humans, NB=seg.total_boxes, _keep=(f3, bf, boxes_cat, ent))
     if profile:
         prof, i = [], 0
@@ -446,6 +464,8 @@ def head_forward(ih, features3: Tensor, image_shapes, box_features: Tensor, boxe
         run["enc32"]
     else:
         run["enc32"] = None
+        if not profile:
+            cache["run"], cache["ws_ptr"] = run, wkey
     return run
 
 
@@ -766,13 +786,19 @@ def interaction_head_from_pooled(ih, features, image_shapes, box_features, box_c
     tables.hum_off, tables.box_off, tables.pair_off = seg.d_hum_off.data_ptr(), seg.d_box_off.data_ptr(), seg.d_pair_off.data_ptr()
     tables.labels, tables.scores = labels_dev.data_ptr(), scores_dev.data_ptr()
     # entries per image (sizes the outputs): closed form on the host, no device round trip
-    lab_h = np.ascontiguousarray(meta["labels"], dtype=np.int64); sc_h = np.ascontiguousarray(meta["scores"], dtype=np.float32)
-    per_img = np.zeros(max(seg.B, 1), dtype=np.int64)
-    L = int(_lib.lib().skg_post_count_host(vt.lens32.ctypes.data, len(vt.lens32), lab_h.ctypes.data, sc_h.ctypes.data,
-                                           seg.box_off.ctypes.data, seg.n_h.ctypes.data, seg.B, per_img.ctypes.data))
-    if L < 0:
-        raise _lib.SkgError("skg_post_count_host: " + _lib.lib().skg_last_error().decode())
-    per_img = per_img[:seg.B]
+    pc = meta.get("_skg_post")
+    if pc is not None and pc[0] is seg:
+        _, L, psz, esz = pc
+    else:
+        lab_h = np.ascontiguousarray(meta["labels"], dtype=np.int64); sc_h = np.ascontiguousarray(meta["scores"], dtype=np.float32)
+        per_img = np.zeros(max(seg.B, 1), dtype=np.int64)
+        L = int(_lib.lib().skg_post_count_host(vt.lens32.ctypes.data, len(vt.lens32), lab_h.ctypes.data, sc_h.ctypes.data,
+                                               seg.box_off.ctypes.data, seg.n_h.ctypes.data, seg.B, per_img.ctypes.data))
+        if L < 0:
+            raise _lib.SkgError("skg_post_count_host: " + _lib.lib().skg_last_error().decode())
+        psz = [int(v) for v in (seg.pair_off[1:] - seg.pair_off[:-1])]
+        esz = [int(v) for v in per_img[:seg.B]]
+        meta["_skg_post"] = (seg, L, psz, esz)
     gt = _gt_labels(G, run, tables, boxes_cat, targets) if targets is not None else None
     # two allocations hold every output of the batch; the per-image results are views into them
     out_i = torch.empty(2 * L + Pn, dtype=torch.int64, device=dev)
@@ -785,8 +811,6 @@ def interaction_head_from_pooled(ih, features, image_shapes, box_features, box_c
                   _lib.ptr(run["post_i32"]), _lib.ptr(run["post_i64"]), _lib.ptr(index), _lib.ptr(pred), _lib.ptr(scores),
                   _lib.ptr(prior), _lib.ptr(weights), _lib.ptr(lab_e), _lib.ptr(unary), _lib.ptr(obj), _lib.ptr(bh_all),
                   _lib.ptr(bo_all), _lib.stream_ptr(dev))
-    psz = [int(v) for v in (seg.pair_off[1:] - seg.pair_off[:-1])]
-    esz = [int(v) for v in per_img]
     flat = dict(out_i=out_i, out_f=out_f, L=L, P=Pn, psz=psz, esz=esz, train=gt is not None)
     results = [dict(boxes_h=a, boxes_o=b_, index=c, prediction=d_, scores=e, object=f, prior=g, weights=h)
                for a, b_, c, d_, e, f, g, h in zip(bh_all.split(psz), bo_all.split(psz), index.split(esz), pred.split(esz),
