@@ -500,7 +500,7 @@ def measure_rooflines(torch, _lib, engine, ih, dev, flush, hbm_peak, tf_peak, pe
     # TransH: score-only grid mode (4 B / triple) and API-faithful mode (804 B written / triple)
     tr = ih.box_pair_head.transh_head.transh
     e, r, w = tr.ent_embeddings.weight.detach(), tr.rel_embeddings.weight.detach(), tr.norm_vector.weight.detach()
-    cells = 1 << 20
+    cells = 1 << 21
     tails = (torch.arange(cells, device=dev) % 32).to(torch.int64)
     score = torch.empty(cells * 117, dtype=torch.float32, device=dev)
 
@@ -516,7 +516,7 @@ def measure_rooflines(torch, _lib, engine, ih, dev, flush, hbm_peak, tf_peak, pe
                                       "us_per_launch": sec * 1e6, "triples_per_s": cells * 117 / sec,
                                       "us_per_launch_l2_flushed_single": sec_flush * 1e6}
     del score
-    cells2 = 8192
+    cells2 = 16384
     T = cells2 * 117
     outs = [torch.empty(T, 50, dtype=torch.float32, device=dev) for _ in range(4)]
     score = torch.empty(T, dtype=torch.float32, device=dev)

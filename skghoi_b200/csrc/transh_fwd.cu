@@ -143,11 +143,12 @@ __global__ void __launch_bounds__(kGridThreads) transh_grid_kernel(
     float* __restrict__ h_out, float* __restrict__ r_out, float* __restrict__ w_out, float* __restrict__ t_out,
     float* __restrict__ score) {
   extern __shared__ __align__(16) float smem[];
-  float* sS = smem;
+  float* sS = smem;             // score-only mode; rows mode reads the score table through L1 (__ldg) and keeps the
+                                // 37 KB out of shared memory: 63 KB per CTA -> three resident CTAs per SM instead of two
   const int nS = ent_tot * rel_tot, nE = ent_tot * dim, nR = rel_tot * dim;
   // rows mode: sS | sE | sR | sW ; score-only mode: sS | s_tail (the table pointers then collapse onto the end of sS)
-  float* sE = sS + ((nS + 3) & ~3); float* sR = sE + (ROWS ? ((nE + 3) & ~3) : 0); float* sW = sR + (ROWS ? ((nR + 3) & ~3) : 0);
-  stage_table(sS, S, nS);
+  float* sE = sS + (ROWS ? 0 : ((nS + 3) & ~3)); float* sR = sE + (ROWS ? ((nE + 3) & ~3) : 0); float* sW = sR + (ROWS ? ((nR + 3) & ~3) : 0);
+  if (!ROWS) stage_table(sS, S, nS);
   if (ROWS) { stage_table(sE, ent, nE); stage_table(sR, rel, nR); stage_table(sW, nrm, nR); }
   __syncthreads();
   const int lane = threadIdx.x & 31;
@@ -212,28 +213,42 @@ __global__ void __launch_bounds__(kGridThreads) transh_grid_kernel(
       const int tl0 = (int)(ta >= ent_tot ? ent_tot - 1 : (ta < 0 ? 0 : ta));
       const int tl1 = (int)(tb >= ent_tot ? ent_tot - 1 : (tb < 0 ? 0 : tb));
       for (int q = threadIdx.x; q < 2 * rel_tot; q += kGridThreads)
-        __stcs(score + c0 * rel_tot + q, sS[(q < rel_tot ? tl0 * rel_tot : tl1 * rel_tot - rel_tot) + q]);
+        __stcs(score + c0 * rel_tot + q, __ldg(S + (q < rel_tot ? tl0 * rel_tot : tl1 * rel_tot - rel_tot) + q));
       const float* et0 = sE + tl0 * dim; const float* et1 = sE + tl1 * dim;
       const int64_t base = c0 * nR;
       float4* ph = reinterpret_cast<float4*>(h_out + base); float4* pr4 = reinterpret_cast<float4*>(r_out + base);
       float4* pw = reinterpret_cast<float4*>(w_out + base); float4* pt = reinterpret_cast<float4*>(t_out + base);
+      const int dstart = (4 * (int)threadIdx.x) % dim;   // (4k) % dim, advanced incrementally; nR % dim == 0, so the
+      const int dstep = (4 * kGridThreads) % dim;        // wrap into the second cell leaves it unchanged
+      // one output array at a time: at any instant the CTA's stores sweep ONE contiguous 2*nR-float region
+      for (int k = threadIdx.x; k < n4; k += kGridThreads) {          // r_out, w_out: the tables themselves, twice
+        int o0 = 4 * k, o1 = 4 * k + 2;
+        if (o0 >= nR) o0 -= nR;
+        if (o1 >= nR) o1 -= nR;
+        const float2 r0 = *reinterpret_cast<const float2*>(sR + o0), r1 = *reinterpret_cast<const float2*>(sR + o1);
+        __stcs(pr4 + k, make_float4(r0.x, r0.y, r1.x, r1.y));
+      }
       for (int k = threadIdx.x; k < n4; k += kGridThreads) {
-        float2 vh[2], vr[2], vw[2], vt[2];
-#pragma unroll
-        for (int half = 0; half < 2; ++half) {
-          int off = 4 * k + 2 * half;
-          const bool second = off >= nR;
-          if (second) off -= nR;
-          const int d = off % dim;
-          vh[half] = *reinterpret_cast<const float2*>(eh + d);
-          vt[half] = *reinterpret_cast<const float2*>((second ? et1 : et0) + d);
-          vr[half] = *reinterpret_cast<const float2*>(sR + off);
-          vw[half] = *reinterpret_cast<const float2*>(sW + off);
-        }
-        __stcs(ph + k, make_float4(vh[0].x, vh[0].y, vh[1].x, vh[1].y));
-        __stcs(pr4 + k, make_float4(vr[0].x, vr[0].y, vr[1].x, vr[1].y));
-        __stcs(pw + k, make_float4(vw[0].x, vw[0].y, vw[1].x, vw[1].y));
-        __stcs(pt + k, make_float4(vt[0].x, vt[0].y, vt[1].x, vt[1].y));
+        int o0 = 4 * k, o1 = 4 * k + 2;
+        if (o0 >= nR) o0 -= nR;
+        if (o1 >= nR) o1 -= nR;
+        const float2 w0 = *reinterpret_cast<const float2*>(sW + o0), w1 = *reinterpret_cast<const float2*>(sW + o1);
+        __stcs(pw + k, make_float4(w0.x, w0.y, w1.x, w1.y));
+      }
+      int d0 = dstart;
+      for (int k = threadIdx.x; k < n4; k += kGridThreads) {          // h_out: the constant head row, 2*rel_tot times
+        int d1 = d0 + 2; if (d1 >= dim) d1 -= dim;
+        const float2 a0 = *reinterpret_cast<const float2*>(eh + d0), a1 = *reinterpret_cast<const float2*>(eh + d1);
+        __stcs(ph + k, make_float4(a0.x, a0.y, a1.x, a1.y));
+        d0 += dstep; if (d0 >= dim) d0 -= dim;
+      }
+      d0 = dstart;
+      for (int k = threadIdx.x; k < n4; k += kGridThreads) {          // t_out: tail row of cell 0, then of cell 1
+        int d1 = d0 + 2; if (d1 >= dim) d1 -= dim;
+        const float* e0 = (4 * k >= nR) ? et1 : et0; const float* e1 = (4 * k + 2 >= nR) ? et1 : et0;
+        const float2 a0 = *reinterpret_cast<const float2*>(e0 + d0), a1 = *reinterpret_cast<const float2*>(e1 + d1);
+        __stcs(pt + k, make_float4(a0.x, a0.y, a1.x, a1.y));
+        d0 += dstep; if (d0 >= dim) d0 -= dim;
       }
     }
     c_done = num_pairs * 2;                              // an odd last cell falls through to the per-warp path
@@ -242,9 +257,9 @@ __global__ void __launch_bounds__(kGridThreads) transh_grid_kernel(
   for (int64_t c = c_done + warp; c < num_cells; c += nwarps) {
     int64_t t64 = cell_tail ? __ldg(cell_tail + c) : c;
     const int tl = (int)(t64 >= ent_tot ? ent_tot - 1 : (t64 < 0 ? 0 : t64));
-    const float* srow = sS + tl * rel_tot;
+    const float* srow = S + tl * rel_tot;
     float* dst = score + c * rel_tot;
-    for (int r = lane; r < rel_tot; r += 32) __stcs(dst + r, srow[r]);
+    for (int r = lane; r < rel_tot; r += 32) __stcs(dst + r, __ldg(srow + r));
     const int64_t base = c * nR;
     const float* eh = sE + head_const * dim; const float* et = sE + tl * dim;
     if (vec2) {                                       // nR even, base even: 8-byte aligned float2 stores
@@ -338,7 +353,7 @@ extern "C" int skg_transh_forward_grid(const float* ent, const float* rel, const
   if (num_cells == 0) return SKG_OK;
   const bool rows = h_out != nullptr;
   const size_t nS = (size_t)ent_tot * rel_tot, nE = (size_t)ent_tot * dim, nR = (size_t)rel_tot * dim;
-  const size_t smem_bytes = (((nS + 3) & ~(size_t)3) + (rows ? ((nE + 3) & ~(size_t)3) + 2 * ((nR + 3) & ~(size_t)3) : (size_t)kGridThreads)) * sizeof(float);
+  const size_t smem_bytes = (rows ? ((nE + 3) & ~(size_t)3) + 2 * ((nR + 3) & ~(size_t)3) : ((nS + 3) & ~(size_t)3) + (size_t)kGridThreads) * sizeof(float);
   const bool implicit_tail_ok = cell_tail != nullptr || num_cells <= ent_tot;
   if (smem_bytes > 200 * 1024 || num_cells < 4 * (int64_t)ent_tot || !implicit_tail_ok) {
     // big tables or few cells: score every triple directly
