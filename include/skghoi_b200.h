@@ -343,6 +343,19 @@ int64_t skg_segments_pack(const int64_t* n, const int64_t* n_h, const double* hw
 int64_t skg_post_count_host(const int32_t* verb_len, int num_obj_cls, const int64_t* labels, const float* scores,
                             const int64_t* box_off, const int64_t* n_h, int num_images, int64_t* img_entries);
 
+/* InteractionHead.preprocess (head.py:92-151) for a whole batch, on the device: score >= box_score_thresh filter,
+ * class-wise NMS exactly as torchvision.ops.batched_nms computes it for small inputs (boxes shifted by
+ * label * (max active coordinate + 1), IoU = inter / (Sa + Sb - inter) > thresh, stable score order), survivors in
+ * descending score order with the human_idx detections first, at most max_human humans + max_object others.
+ * boxes [sum N, 4] fp32 xyxy (16-byte aligned), labels [sum N] int64, scores [sum N] fp32 are the images' detections
+ * concatenated (ground-truth boxes already prepended in training, head.py:105-116); det_off [B+1] int32 their prefix
+ * sum; max_dets_per_image sizes the shared-memory NMS.  out_index [B, max_human + max_object] int64: GLOBAL rows of the
+ * kept detections of image b in final order, padded with -1; out_counts [B, 2] int32 = (n, n_h). */
+int skg_preprocess_detections(const float* boxes, const int64_t* labels, const float* scores, const int32_t* det_off,
+                              int num_images, int max_dets_per_image, float box_score_thresh, float box_nms_thresh,
+                              int human_idx, int max_human, int max_object, int64_t* out_index, int32_t* out_counts,
+                              cudaStream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

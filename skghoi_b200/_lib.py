@@ -229,6 +229,8 @@ _SIGNATURES["skg_head_graph_stats"] = (None, [ctypes.POINTER(ctypes.c_longlong)]
 _SIGNATURES["skg_segments_pack"] = (c_int64, [P, P, P, I, P, L, P, P])
 _SIGNATURES["skg_post_count_host"] = (c_int64, [P, I, P, P, P, P, I, P])
 
+_SIGNATURES["skg_preprocess_detections"] = (I, [P, P, P, P, I, I, F, F, I, I, I, P, P, P])
+
 _buffer_names = None
 
 

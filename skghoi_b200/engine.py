@@ -924,12 +924,61 @@ def preprocess_detections(ih, detections: List[dict], targets, append_gt: Option
     return results
 
 
+def preprocess_detections_device(ih, detections: List[dict], targets, append_gt: Optional[bool] = None):
+    """InteractionHead.preprocess (head.py:92-151) for the whole batch in ONE kernel (csrc/preprocess.cu) and one
+    host round trip (the per-image counts), instead of four syncs per image.  Returns (results, meta): the list of
+    per-image dicts (views of three packed tensors, so the forward takes them without re-concatenation) and the host
+    meta ``forward_from_pooled`` wants."""
+    if append_gt is None:
+        append_gt = ih.training
+    boxes_l, labels_l, scores_l = [], [], []
+    for b_idx, det in enumerate(detections):
+        boxes, labels, scores = det["boxes"], det["labels"], det["scores"]
+        if append_gt:                                                                   # head.py:105-116
+            tgt = targets[b_idx]
+            ng = tgt["boxes_h"].shape[0]
+            boxes = torch.cat([tgt["boxes_h"], tgt["boxes_o"], boxes])
+            scores = torch.cat([torch.ones(2 * ng, device=scores.device), scores])
+            labels = torch.cat([ih.human_idx * torch.ones(ng, device=labels.device).long(), tgt["object"], labels])
+        boxes_l.append(boxes.reshape(-1, 4)); labels_l.append(labels.reshape(-1)); scores_l.append(scores.reshape(-1))
+    B = len(detections)
+    dev = boxes_l[0].device if B else torch.device("cuda")
+    _lib.require_cuda(*boxes_l)
+    counts_in = [int(b.shape[0]) for b in boxes_l]
+    boxes = torch.cat(boxes_l).to(torch.float32).contiguous() if B else torch.zeros(0, 4, device=dev)
+    labels = torch.cat(labels_l).to(torch.int64).contiguous() if B else torch.zeros(0, dtype=torch.int64, device=dev)
+    scores = torch.cat(scores_l).to(torch.float32).contiguous() if B else torch.zeros(0, device=dev)
+    det_off = torch.tensor(np.concatenate([[0], np.cumsum(counts_in)]).astype(np.int32)).to(dev, non_blocking=True)
+    max_keep = int(ih.max_human) + int(ih.max_object)
+    out_index = torch.empty(max(B, 1), max_keep, dtype=torch.int64, device=dev)
+    out_counts = torch.empty(max(B, 1), 2, dtype=torch.int32, device=dev)
+    with torch.cuda.device(dev):
+        _lib.call("skg_preprocess_detections", _lib.ptr(boxes), _lib.ptr(labels), _lib.ptr(scores), _lib.ptr(det_off), B,
+                  max(counts_in) if counts_in else 0, float(ih.box_score_thresh), float(ih.box_nms_thresh), int(ih.human_idx),
+                  int(ih.max_human), int(ih.max_object), _lib.ptr(out_index), _lib.ptr(out_counts), _lib.stream_ptr(dev))
+    sel = out_index[:B].reshape(-1)
+    sel = sel[sel >= 0]                                    # row-major: image order, humans first inside an image
+    kb, kl, ks = boxes[sel], labels[sel], scores[sel]
+    # one device->host copy: counts + the kept labels / scores (they size the launch and the outputs downstream)
+    packed = torch.cat([out_counts[:B].reshape(-1).to(torch.float64), kl.to(torch.float64), ks.to(torch.float64)]).cpu().numpy()
+    cnt = packed[:2 * B].astype(np.int64).reshape(B, 2)
+    n = [int(v) for v in cnt[:, 0]]; n_h = [int(v) for v in cnt[:, 1]]
+    tot = sum(n)
+    meta = dict(n=n, n_h=n_h, labels=packed[2 * B:2 * B + tot].astype(np.int64), scores=packed[2 * B + tot:].astype(np.float32))
+    results = [dict(boxes=b_, labels=l_, scores=s_) for b_, l_, s_ in zip(kb.split(n), kl.split(n), ks.split(n))]
+    return results, meta
+
+
 def interaction_head_forward(ih, features, detections, image_shapes, targets=None) -> List[dict]:
     """InteractionHead.forward (head.py:341-429): stock preprocess + RoIAlign, then the CUDA hot path."""
     if ih.training:
         assert targets is not None, "Targets should be passed during training"
-    detections = preprocess_detections(ih, detections, targets)
+    meta = None
+    if len(detections) and detections[0]["boxes"].is_cuda and getattr(ih, "device_preprocess", True):
+        detections, meta = preprocess_detections_device(ih, detections, targets)
+    else:
+        detections = preprocess_detections(ih, detections, targets)
     coords = [d["boxes"] for d in detections]; labels = [d["labels"] for d in detections]
     scores = [d["scores"] for d in detections]
-    box_features = ih.box_roi_pool(features, coords, image_shapes)                        # head.py:387
-    return interaction_head_from_pooled(ih, features, image_shapes, box_features, coords, labels, scores, targets)
+    box_features = ih.box_roi_pool(features, coords, image_shapes)                        # head.py:387 (stock torchvision)
+    return ih.forward_from_pooled(features, image_shapes, box_features, coords, labels, scores, targets, meta=meta)

@@ -200,8 +200,10 @@ class InteractionHead(Module):
         return super()._apply(fn, *args, **kwargs)
 
     def preprocess(self, detections: List[dict], targets: List[dict], append_gt: Optional[bool] = None):
-        from .engine import preprocess_detections
-        return preprocess_detections(self, detections, targets, append_gt)
+        from .engine import preprocess_detections, preprocess_detections_device
+        if len(detections) and detections[0]["boxes"].is_cuda and getattr(self, "device_preprocess", True):
+            return preprocess_detections_device(self, detections, targets, append_gt)[0]      # csrc/preprocess.cu
+        return preprocess_detections(self, detections, targets, append_gt)                    # stock torchvision ops
 
     def forward(self, features: OrderedDict, detections: List[dict], image_shapes: List[Tuple[int, int]],
                 targets: Optional[List[dict]] = None) -> List[dict]:

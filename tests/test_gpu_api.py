@@ -194,7 +194,8 @@ def test_interaction_head_full_forward_with_stock_preprocess():
     dets = [dict(boxes=b, labels=l, scores=s) for b, l, s in zip(d["box_coords"], d["box_labels"], d["box_scores"])]
     with torch.no_grad():
         got = ih(d["features"], dets, d["image_shapes"])
-        pre = ih.preprocess(dets, None)
+        from skghoi_b200 import engine
+        pre = engine.preprocess_detections(ih, dets, None)                     # the stock torchvision path
         coords = [p["boxes"] for p in pre]
         bf = ih.box_roi_pool(d["features"], coords, d["image_shapes"])
         want = ih.forward_from_pooled(d["features"], d["image_shapes"], bf, coords, [p["labels"] for p in pre],
@@ -204,3 +205,66 @@ def test_interaction_head_full_forward_with_stock_preprocess():
         for k in w:
             torch.testing.assert_close(g[k], w[k], rtol=1e-5, atol=1e-6)
         assert g["boxes_h"].shape[0] > 0
+
+
+def _crowded_detections(gen, n_img, n_det, human_frac=0.4):
+    """Many overlapping boxes per image, scores on both sides of the 0.2 threshold, exact score ties included."""
+    dets = []
+    for _ in range(n_img):
+        ctr = torch.rand(n_det, 2, generator=gen) * torch.tensor([900.0, 600.0]) + 100
+        ctr[n_det // 2:] = ctr[: n_det - n_det // 2] + torch.randn(n_det - n_det // 2, 2, generator=gen) * 12   # near-duplicates
+        wh = torch.rand(n_det, 2, generator=gen) * 150 + 40
+        boxes = torch.cat([ctr - wh / 2, ctr + wh / 2], 1)
+        labels = torch.randint(0, 80, (n_det,), generator=gen)
+        labels[torch.rand(n_det, generator=gen) < human_frac] = 49
+        scores = torch.rand(n_det, generator=gen)
+        scores[::7] = 0.5                                     # ties
+        dets.append(dict(boxes=boxes.to(DEV), labels=labels.to(DEV), scores=scores.to(DEV)))
+    return dets
+
+
+@pytest.mark.parametrize("train", [False, True])
+def test_device_preprocess_matches_stock_torchvision(train):
+    """csrc/preprocess.cu against InteractionHead.preprocess on stock torch / torchvision ops (head.py:92-151):
+    identical kept detections in identical order (bit-exact boxes / labels / scores), eval and train (GT prepended)."""
+    from skghoi_b200 import engine
+    gen = torch.Generator().manual_seed(3)
+    ih = _head(train)
+    dets = _crowded_detections(gen, 5, 120) + _crowded_detections(gen, 2, 7)
+    dets.append(dict(boxes=torch.zeros(0, 4, device=DEV), labels=torch.zeros(0, dtype=torch.int64, device=DEV),
+                     scores=torch.zeros(0, device=DEV)))                                    # an image without detections
+    low = _crowded_detections(gen, 1, 9)[0]; low["scores"] = low["scores"] * 0.1             # everything below the threshold
+    dets.append(low)
+    targets = None
+    if train:
+        targets = []
+        for d in dets:
+            k = 3
+            bh = torch.rand(k, 4, generator=gen).to(DEV) * 300; bh[:, 2:] += bh[:, :2] + 20
+            bo = torch.rand(k, 4, generator=gen).to(DEV) * 300; bo[:, 2:] += bo[:, :2] + 20
+            bh[1] = bh[0]                                                                      # duplicated GT human
+            targets.append(dict(boxes_h=bh, boxes_o=bo, object=torch.randint(0, 80, (k,), generator=gen).to(DEV),
+                                labels=torch.randint(0, 117, (k,), generator=gen).to(DEV)))
+    want = engine.preprocess_detections(ih, dets, targets)
+    got, meta = engine.preprocess_detections_device(ih, dets, targets)
+    assert len(got) == len(want)
+    def rows(r):
+        return [tuple(x) for x in torch.cat([r["scores"][:, None].double(), r["labels"][:, None].double(), r["boxes"].double()], 1).tolist()]
+    for b, (g, w) in enumerate(zip(got, want)):
+        assert meta["n"][b] == w["labels"].numel() and meta["n_h"][b] == int((w["labels"] == 49).sum())
+        assert torch.equal(g["scores"], w["scores"]), b                       # same score sequence, humans first
+        if torch.equal(g["labels"], w["labels"]):
+            assert torch.equal(g["boxes"], w["boxes"]), b
+            continue
+        # Equal scores (the prepended ground truth all scores 1.0): the reference orders them with a NON-stable
+        # torch.argsort(descending=True) (head.py:128), i.e. unspecified; the kernel keeps the original order.  The
+        # kept detections must still be the same set, and differ only inside groups of equal score.
+        assert train, b
+        assert sorted(rows(g)) == sorted(rows(w)), b
+        assert (g["labels"] == 49).sum() == (w["labels"] == 49).sum()
+        diff = torch.nonzero(g["labels"] != w["labels"]).squeeze(1)
+        assert bool((g["scores"][diff] == 1.0).all()), b
+    assert sum(meta["n"]) > 40 and any(k == 30 for k in meta["n"])            # the caps (15 + 15) were hit
+    # the module method takes the device path for CUDA inputs
+    via_method = ih.preprocess(dets, targets)
+    assert all(torch.equal(a["boxes"], b_["boxes"]) for a, b_ in zip(via_method, got))
