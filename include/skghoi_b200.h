@@ -356,6 +356,22 @@ int skg_preprocess_detections(const float* boxes, const int64_t* labels, const f
                               int human_idx, int max_human, int max_object, int64_t* out_index, int32_t* out_counts,
                               cudaStream_t stream);
 
+/* Negative sampler of the KG trainer (OpenKE sampling() / getBatch(), OpenKE/openke/base/Base.cpp:78-197, with the
+ * filtered corrupt_head / corrupt_tail of Corrupt.h:7-83 and the per-thread LCG of Random.h:18-28), bit-exact with the
+ * reference for any `work_threads`.  The index arrays are what importTrainFiles builds (Reader.h:52-160), on the device:
+ * head_hrt / tail_hrt [3, T] int64 = rows h | r | t of the de-duplicated training triples sorted by (h, r, t) resp.
+ * (t, r, h); lef_* / rig_* [E] the entity ranges in those orderings; left_mean / right_mean [R] fp32 for the "bern"
+ * head/tail coin (both NULL: fair coin, prob = 500/1000).  seeds_in [work_threads] = next_random[] before the call,
+ * seeds_out (distinct buffer) after it.  Outputs batch_h / batch_t / batch_r int64 and batch_y fp32 of length
+ * batch_size * (1 + neg_rate): positives first, then neg_rate blocks of negatives (batch_y = 1 / -1).
+ * mode 0: corrupt head or tail per the coin; -1: always the head; +1: always the tail.  negRelRate is not supported.
+ * Where the reference divides by zero -- (entity, relation) linked to EVERY entity -- the positive is kept. */
+int skg_kg_sample(const int64_t* head_hrt, const int64_t* tail_hrt, const int64_t* lef_head, const int64_t* rig_head,
+                  const int64_t* lef_tail, const int64_t* rig_tail, const float* left_mean, const float* right_mean,
+                  int64_t train_total, int64_t ent_total, const uint64_t* seeds_in, uint64_t* seeds_out, int work_threads,
+                  int64_t batch_size, int neg_rate, int mode, int64_t* batch_h, int64_t* batch_t, int64_t* batch_r,
+                  float* batch_y, cudaStream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

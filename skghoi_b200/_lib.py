@@ -231,6 +231,8 @@ _SIGNATURES["skg_post_count_host"] = (c_int64, [P, I, P, P, P, P, I, P])
 
 _SIGNATURES["skg_preprocess_detections"] = (I, [P, P, P, P, I, I, F, F, I, I, I, P, P, P])
 
+_SIGNATURES["skg_kg_sample"] = (I, [P, P, P, P, P, P, P, P, L, L, P, P, I, L, I, I, P, P, P, P, P])
+
 _buffer_names = None
 
 

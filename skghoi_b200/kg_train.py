@@ -1,0 +1,99 @@
+"""KG-embedding training loop on the device (BASELINE configs[3]): the upstream OpenKE pieces the head's
+TransH tables would be trained with -- the dict-of-batches ``forward(data)`` strategy
+(OpenKE/openke/module/strategy/NegativeSampling.py:13-32), the data loader contract around ``sampling``
+(OpenKE/openke/base/Base.cpp:161-197) and ``Trainer`` (OpenKE/openke/config/Trainer.py:43-99).  Sampling
+(``skg_kg_sample``), scoring and its gradient (``skg_transh_forward`` / ``_backward``) and the margin loss
+(``skg_margin_loss``) are CUDA kernels of this library; the optimiser is torch.optim, as in the reference."""
+from typing import Iterator, List, Optional, Sequence
+
+import torch
+from torch import nn
+
+from .kg_data import KGIndex, TrainDataSampler
+from .kge import MarginLoss, TransH
+
+
+class TrainDataLoader:
+    """``nbatches`` batches per epoch of ``batch_size = train_total // nbatches`` positives (or an explicit batch size),
+    ``neg_ent`` filtered corruptions each; iterating yields dicts ``{batch_h, batch_t, batch_r, batch_y, mode}`` on the
+    device (the reference's loader hands the same dict over host numpy buffers)."""
+
+    def __init__(self, index: KGIndex, nbatches: Optional[int] = None, batch_size: Optional[int] = None, neg_ent: int = 1,
+                 bern_flag: bool = False, threads: int = 8, seeds: Optional[Sequence[int]] = None):
+        if batch_size is None:
+            if not nbatches:
+                raise ValueError("give nbatches or batch_size")
+            batch_size = index.train_total // nbatches
+        if nbatches is None:
+            nbatches = max(index.train_total // batch_size, 1)
+        self.nbatches, self.batch_size, self.neg_ent = int(nbatches), int(batch_size), int(neg_ent)
+        self.sampler = TrainDataSampler(index, self.batch_size, self.neg_ent, bern_flag, threads, seeds)
+
+    def get_batch_size(self) -> int:
+        return self.batch_size
+
+    def __len__(self) -> int:
+        return self.nbatches
+
+    def __iter__(self) -> Iterator[dict]:
+        for _ in range(self.nbatches):
+            yield self.sampler.sample()
+
+
+class NegativeSamplingStrategy(nn.Module):
+    """OpenKE/openke/module/strategy/NegativeSampling.py:13-32: ``forward(data)`` scores the batch, splits it into the
+    positives [B, 1] and their negatives [B, neg], applies the loss and the optional L2 regulariser."""
+
+    def __init__(self, model: TransH, loss: nn.Module, batch_size: int = 256, regul_rate: float = 0.0):
+        super().__init__()
+        self.model, self.loss, self.batch_size, self.regul_rate = model, loss, int(batch_size), float(regul_rate)
+
+    def forward(self, data: dict) -> torch.Tensor:
+        h, t, r = data["batch_h"], data["batch_t"], data["batch_r"]
+        score = self.model._score(h, r, t, False)[4]
+        if self.model.margin_flag:
+            score = self.model.margin - score
+        B = self.batch_size
+        p_score = score[:B].view(-1, B).permute(1, 0)
+        n_score = score[B:].view(-1, B).permute(1, 0)
+        loss = self.loss(p_score, n_score)
+        if self.regul_rate != 0:
+            loss = loss + self.regul_rate * self.model.regularization(h, r, t)
+        return loss
+
+
+class Trainer:
+    """OpenKE/openke/config/Trainer.py:43-99: ``run()`` builds the optimiser named by ``opt_method`` and makes
+    ``train_times`` passes over the loader; returns the per-epoch summed losses."""
+
+    def __init__(self, model: nn.Module, data_loader, train_times: int = 1000, alpha: float = 0.5, opt_method: str = "sgd",
+                 weight_decay: float = 0.0, lr_decay: float = 0.0, optimizer=None):
+        self.model, self.data_loader, self.train_times = model, data_loader, int(train_times)
+        self.alpha, self.opt_method, self.weight_decay, self.lr_decay, self.optimizer = alpha, opt_method, weight_decay, lr_decay, optimizer
+
+    def train_one_step(self, data: dict) -> torch.Tensor:
+        self.optimizer.zero_grad(set_to_none=True)
+        loss = self.model(data)
+        loss.backward()
+        self.optimizer.step()
+        return loss.detach()
+
+    def run(self) -> List[float]:
+        if self.optimizer is None:
+            m = self.opt_method.lower()
+            p = self.model.parameters()
+            if m == "adagrad":
+                self.optimizer = torch.optim.Adagrad(p, lr=self.alpha, lr_decay=self.lr_decay, weight_decay=self.weight_decay)
+            elif m == "adadelta":
+                self.optimizer = torch.optim.Adadelta(p, lr=self.alpha, weight_decay=self.weight_decay)
+            elif m == "adam":
+                self.optimizer = torch.optim.Adam(p, lr=self.alpha, weight_decay=self.weight_decay)
+            else:
+                self.optimizer = torch.optim.SGD(p, lr=self.alpha, weight_decay=self.weight_decay)
+        history = []
+        for _ in range(self.train_times):
+            res = torch.zeros((), device=next(self.model.parameters()).device)
+            for data in self.data_loader:
+                res = res + self.train_one_step(data)          # one host read per epoch, not per step (Trainer.py:57 .item())
+            history.append(float(res))
+        return history
