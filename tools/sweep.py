@@ -86,3 +86,52 @@ for neg in (1, 25):
     ms = s.elapsed_time(e) / K
     T = pos.shape[0] * (1 + neg)
     print("| %d | %d | %d | %.3f | %.2f |   loss %.3f -> %.3f" % (pos.shape[0], neg, T, ms, T / ms / 1e3, float(l0), float(l1)))
+
+# ---- KG negative sampler: skg_kg_sample vs the reference's own Base.so on the host cores (same graph, same seeds)
+sys.path.insert(0, os.path.join(ROOT, "tests", "golden"))
+import make_kg_golden as MG                                  # noqa: E402
+from skghoi_b200.kg_data import KGIndex, TrainDataSampler    # noqa: E402
+from skghoi_b200.kg_train import NegativeSamplingStrategy, TrainDataLoader, Trainer   # noqa: E402
+h, t, r = MG.graph()
+idx = KGIndex(h, t, r, 80, 117, device=dev)
+print()
+print("| KG sampler | batch | neg | triples/call | us/call | M triples/s |")
+print("|---|---:|---:|---:|---:|---:|")
+for bs, neg in ((990, 25), (1 << 16, 25), (1 << 20, 8)):
+    smp = TrainDataSampler(idx, bs, neg, True, 8, MG.seeds_for(8))
+    for _ in range(3):
+        smp.sample()
+    torch.cuda.synchronize()
+    s = torch.cuda.Event(enable_timing=True); e = torch.cuda.Event(enable_timing=True)
+    K = 20
+    s.record()
+    for _ in range(K):
+        smp.sample()
+    e.record(); torch.cuda.synchronize()
+    us = s.elapsed_time(e) / K * 1e3
+    print("| skg_kg_sample (B200) | %d | %d | %d | %.1f | %.1f |" % (bs, neg, bs * (1 + neg), us, bs * (1 + neg) / us))
+try:
+    from oracle import kg_sampler_oracle as KO
+    cores = len(os.sched_getaffinity(0))
+    ref = KO.ReferenceSampler(h, t, r, 80, 117, cores, True)
+    ref.set_seeds(MG.seeds_for(cores))
+    for bs, neg in ((990, 25), (1 << 16, 25)):
+        ref.sample(bs, neg, 0)
+        t0 = time.perf_counter()
+        K = 10
+        for _ in range(K):
+            ref.sample(bs, neg, 0)
+        us = (time.perf_counter() - t0) / K * 1e6
+        print("| reference Base.so, %d host threads | %d | %d | %d | %.1f | %.1f |" % (cores, bs, neg, bs * (1 + neg), us, bs * (1 + neg) / us))
+except Exception as ex:                                      # noqa: BLE001
+    print("| reference Base.so unavailable: %s |" % ex)
+loader = TrainDataLoader(idx, nbatches=1, neg_ent=25, bern_flag=True, threads=8, seeds=MG.seeds_for(8))
+model = TransH(80, 117, dim=50, p_norm=1, norm_flag=True).to(dev)
+strat = NegativeSamplingStrategy(model, MarginLoss(margin=4.0), batch_size=loader.get_batch_size()).to(dev)
+tr = Trainer(strat, loader, train_times=20, alpha=0.5)
+tr.run(); torch.cuda.synchronize()
+t0 = time.perf_counter(); hist = tr.run(); torch.cuda.synchronize(); dt = time.perf_counter() - t0
+T = loader.get_batch_size() * 26
+print()
+print("KG training with the device sampler (Trainer.run, %d positives x 25 negatives per step): %.3f ms/step, %.1f M triples/s, loss %.3f -> %.3f"
+      % (loader.get_batch_size(), dt / 20 * 1e3, T * 20 / dt / 1e6, hist[0], hist[-1]))
