@@ -40,10 +40,10 @@ xk = torch.empty(Pn, dtype=torch.int64, device=dev); yk = torch.empty(Pn, dtype=
 nanf = torch.zeros(B, dtype=torch.int32, device=dev)
 tr = ih.box_pair_head.transh_head.transh
 e, r, w = tr.ent_embeddings.weight.detach(), tr.rel_embeddings.weight.detach(), tr.norm_vector.weight.detach()
-cells = 1 << 18
+cells = 1 << 21
 tails = (torch.arange(cells, device=dev) % 32).to(torch.int64)
 score = torch.empty(cells * 117, dtype=torch.float32, device=dev)
-cells2 = 8192
+cells2 = 16384
 outs = [torch.empty(cells2 * 117, 50, dtype=torch.float32, device=dev) for _ in range(4)]
 st = _lib.stream_ptr(dev)
 torch.cuda.synchronize()
