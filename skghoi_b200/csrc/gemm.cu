@@ -592,7 +592,9 @@ extern "C" int skg_gemm_bf16_splitk(const void* A, int64_t lda, const void* B, i
     for (int i = 0; i < num_groups; ++i) has_dot |= (groups[i].dot_out != nullptr);
     if (!has_dot) {
     if (block_n == 256 && mt * (N / 256) < num_sms() / 2) block_n = 128;
-    if (block_n == 128 && (N % 64 == 0 || N < 128) && mt * ceil_div(N, 128) < num_sms() / 2) block_n = 64;
+    // long-K launches with a split-K scratch (box_head fc6: K = 12544) fill the SMs through K splits instead
+    const bool split_k = scratch != nullptr && choose_splits(M, N, K, block_n, scratch_bytes) > 1;
+    if (block_n == 128 && !split_k && (N % 64 == 0 || N < 128) && mt * ceil_div(N, 128) < num_sms() / 2) block_n = 64;
     }
   }
   SKG_REQUIRE(block_n == 64 || block_n == 128 || block_n == 256, "block_n must be 64, 128 or 256");

@@ -76,9 +76,11 @@ def test_graph_replay_matches_plain_launches():
         outs = [engine.head_forward(ih, f3, batch["image_shapes"], bf, boxes_cat, meta, graph=True)["logits"].clone()
                 for _ in range(4)]
         for o in outs:
-            torch.testing.assert_close(o, plain, rtol=1e-5, atol=1e-5)     # split-K reduction order may differ in the last bit
+            # box_head fc6 reduces its K splits through fp32 red.global.add: the order differs from launch to launch, a
+            # last-bit change there can flip a bf16 rounding downstream -> logits move by a few 1e-4 (parity budget: 1e-2)
+            torch.testing.assert_close(o, plain, rtol=1e-3, atol=1e-3)
         bf.mul_(0.5)                                                        # same address, new contents
         replay = engine.head_forward(ih, f3, batch["image_shapes"], bf, boxes_cat, meta, graph=True)["logits"].clone()
         direct = engine.head_forward(ih, f3, batch["image_shapes"], bf, boxes_cat, meta, graph=False)["logits"].clone()
-    torch.testing.assert_close(replay, direct, rtol=1e-5, atol=1e-5)
+    torch.testing.assert_close(replay, direct, rtol=1e-3, atol=1e-3)
     assert float((replay - plain).abs().max()) > 1e-3
