@@ -78,8 +78,16 @@ def ptr(t):
     return ctypes.c_void_p(t.data_ptr())
 
 
+def raw_stream(device=None) -> int:
+    """cudaStream_t of torch's current stream on ``device`` as an integer (one C call, no Stream object)."""
+    idx = device.index if isinstance(device, torch.device) else device
+    if idx is None:
+        idx = torch.cuda.current_device()
+    return torch._C._cuda_getCurrentRawStream(idx)
+
+
 def stream_ptr(device=None):
-    return ctypes.c_void_p(torch.cuda.current_stream(device).cuda_stream)
+    return ctypes.c_void_p(raw_stream(device))
 
 
 def call(name, *args):

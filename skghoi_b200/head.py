@@ -223,12 +223,13 @@ class InteractionHead(Module):
         return interaction_head_from_pooled(self, features, image_shapes, box_features, box_coords, box_labels,
                                             box_scores, targets, meta=meta)
 
-    def host_meta(self, box_labels, box_scores):
+    def host_meta(self, box_labels, box_scores, n=None):
         """Host-side summary of a batch's detections (boxes / humans per image, labels, scores) that sizes the launch
         and the outputs.  Build it from HOST copies of the labels / scores (the reference reads its detections from a
-        host-side cache) and pass it as ``meta=`` to skip the device->host read ``forward`` otherwise needs."""
+        host-side cache) and pass it as ``meta=`` to skip the device->host read ``forward`` otherwise needs.  ``box_labels`` / ``box_scores`` are
+        per-image lists, or two PACKED tensors with the per-image counts in ``n``."""
         from .engine import _host_meta
-        return _host_meta(box_labels, box_scores, self.human_idx)
+        return _host_meta(box_labels, box_scores, self.human_idx, n=n)
 
     def results_to_host(self, results: List[dict], wait: bool = True):
         """Host copies of the dicts ``forward`` just returned (two pinned copies for the whole batch).  ``wait=False``
