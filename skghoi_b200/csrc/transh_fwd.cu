@@ -282,6 +282,86 @@ __global__ void __launch_bounds__(kGridThreads) transh_grid_kernel(
   }
 }
 
+// Rows mode through the bulk-copy engine.  Three of the four row outputs do not depend on the cell at all: r_out and
+// w_out repeat the whole relation / normal tables per cell, h_out repeats the constant head row.  A PAIR of cells is a
+// 16-byte aligned block of 2 * rel_tot * dim floats in every output array, so the CTA keeps one ready-made image of
+// that block per array in shared memory (3 x 46 800 B for 117 x 50) and one elected thread writes each pair with three
+// cp.async.bulk stores -- no load / store instructions at all for 3/4 of the bytes, the images are never rewritten, so
+// nothing ever waits on the copy engine.  The threads only assemble t_out (the pair's two tail rows) and the scores.
+__device__ __forceinline__ void bulk_store(float* gdst, const float* ssrc, uint32_t bytes) {
+  const uint32_t saddr = (uint32_t)__cvta_generic_to_shared(ssrc);
+  asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;\n" ::"l"(gdst), "r"(saddr), "r"(bytes) : "memory");
+}
+
+__global__ void __launch_bounds__(kGridThreads, 1) transh_grid_rows_bulk_kernel(
+    const float* __restrict__ S, const float* __restrict__ ent, const float* __restrict__ rel, const float* __restrict__ nrm,
+    int ent_tot, int rel_tot, int dim, int head_const, const int64_t* __restrict__ cell_tail, int64_t num_cells,
+    float* __restrict__ h_out, float* __restrict__ r_out, float* __restrict__ w_out, float* __restrict__ t_out,
+    float* __restrict__ score) {
+  extern __shared__ __align__(16) float smem[];
+  const int nE = ent_tot * dim, nR = rel_tot * dim;
+  float* sRR = smem;                       // [2 * nR] relation table, twice
+  float* sWW = sRR + 2 * nR;               // [2 * nR] normal-vector table, twice
+  float* sHH = sWW + 2 * nR;               // [2 * nR] head row, 2 * rel_tot times
+  float* sE = sHH + 2 * nR;                // [nE] entity table (tail rows)          (2 * nR floats = a multiple of 16 B)
+  for (int e = threadIdx.x; e < nR; e += kGridThreads) {
+    const float r = __ldg(rel + e), w = __ldg(nrm + e);
+    sRR[e] = r; sRR[e + nR] = r; sWW[e] = w; sWW[e + nR] = w;
+  }
+  for (int e = threadIdx.x; e < nE; e += kGridThreads) sE[e] = __ldg(ent + e);
+  {
+    int d = threadIdx.x % dim;
+    const int step = kGridThreads % dim;
+    for (int e = threadIdx.x; e < 2 * nR; e += kGridThreads) {
+      sHH[e] = __ldg(ent + head_const * dim + d);
+      d += step; if (d >= dim) d -= dim;
+    }
+  }
+  asm volatile("fence.proxy.async.shared::cta;\n" ::: "memory");   // generic-proxy writes -> visible to the bulk engine
+  __syncthreads();
+  const int64_t num_pairs = num_cells >> 1;
+  const int n4 = nR >> 1;                              // float4s per pair and per output array
+  const uint32_t pair_bytes = (uint32_t)(2 * nR) * 4u;
+  const int dstart = (4 * (int)threadIdx.x) % dim;
+  const int dstep = (4 * kGridThreads) % dim;
+  for (int64_t pr = blockIdx.x; pr < num_pairs; pr += gridDim.x) {
+    const int64_t c0 = 2 * pr;
+    const int64_t base = c0 * nR;
+    if (threadIdx.x == 0) {
+      bulk_store(r_out + base, sRR, pair_bytes);
+      bulk_store(w_out + base, sWW, pair_bytes);
+      bulk_store(h_out + base, sHH, pair_bytes);
+      asm volatile("cp.async.bulk.commit_group;\n" ::: "memory");
+    }
+    int64_t ta = cell_tail ? __ldg(cell_tail + c0) : c0, tb = cell_tail ? __ldg(cell_tail + c0 + 1) : c0 + 1;
+    const int tl0 = (int)(ta >= ent_tot ? ent_tot - 1 : (ta < 0 ? 0 : ta));
+    const int tl1 = (int)(tb >= ent_tot ? ent_tot - 1 : (tb < 0 ? 0 : tb));
+    for (int q = threadIdx.x; q < 2 * rel_tot; q += kGridThreads)
+      __stcs(score + c0 * rel_tot + q, __ldg(S + (q < rel_tot ? tl0 * rel_tot : tl1 * rel_tot - rel_tot) + q));
+    const float* et0 = sE + tl0 * dim; const float* et1 = sE + tl1 * dim;
+    float4* pt = reinterpret_cast<float4*>(t_out + base);
+    int d0 = dstart;
+    for (int k = threadIdx.x; k < n4; k += kGridThreads) {            // t_out: tail row of cell 0, then of cell 1
+      int d1 = d0 + 2; if (d1 >= dim) d1 -= dim;
+      const float* e0 = (4 * k >= nR) ? et1 : et0; const float* e1 = (4 * k + 2 >= nR) ? et1 : et0;
+      const float2 a0 = *reinterpret_cast<const float2*>(e0 + d0), a1 = *reinterpret_cast<const float2*>(e1 + d1);
+      __stcs(pt + k, make_float4(a0.x, a0.y, a1.x, a1.y));
+      d0 += dstep; if (d0 >= dim) d0 -= dim;
+    }
+  }
+  if ((num_cells & 1) && blockIdx.x == gridDim.x - 1) {                // odd last cell: plain stores
+    const int64_t c = num_cells - 1;
+    const int64_t t64 = cell_tail ? __ldg(cell_tail + c) : c;
+    const int tl = (int)(t64 >= ent_tot ? ent_tot - 1 : (t64 < 0 ? 0 : t64));
+    for (int q = threadIdx.x; q < rel_tot; q += kGridThreads) score[c * rel_tot + q] = __ldg(S + tl * rel_tot + q);
+    const int64_t base = c * nR;
+    for (int q = threadIdx.x; q < nR; q += kGridThreads) {
+      h_out[base + q] = sHH[q]; r_out[base + q] = sRR[q]; w_out[base + q] = sWW[q]; t_out[base + q] = sE[tl * dim + q % dim];
+    }
+  }
+  if (threadIdx.x == 0) asm volatile("cp.async.bulk.wait_group.read 0;\n" ::: "memory");   // images stay valid until read
+}
+
 template <int EPL>
 static int launch_forward(const float* ent, const float* rel, const float* nrm, int ent_tot, int rel_tot, int dim,
                           const TripleIndex& idx, int64_t T, int p_norm, int norm_flag, float* h_out, float* r_out,
@@ -386,7 +466,17 @@ extern "C" int skg_transh_forward_grid(const float* ent, const float* rel, const
     const int per_sm = smem_bytes > 110 * 1024 ? 1 : (smem_bytes > 72 * 1024 ? 2 : 3);
     const int64_t want = rows ? ceil_div64(num_cells, 2) : ceil_div64(num_cells, kGridThreads);   // rows: a CTA per cell pair
     const int grid = (int)(want < (int64_t)num_sms() * per_sm ? want : (int64_t)num_sms() * per_sm);
-    if (rows) {
+    const size_t bulk_bytes = ((size_t)6 * rel_tot * dim + (size_t)ent_tot * dim) * sizeof(float);
+    const bool bulk = rows && num_cells >= 2 && ((rel_tot * dim) & 1) == 0 && (dim & 1) == 0 && bulk_bytes <= 220 * 1024 &&
+                      (((uintptr_t)h_out | (uintptr_t)r_out | (uintptr_t)w_out | (uintptr_t)t_out) & 15u) == 0;
+    if (bulk) {
+      auto k = transh_grid_rows_bulk_kernel;
+      cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bulk_bytes);
+      const int64_t pairs = num_cells >> 1;
+      const int g = (int)(pairs < (int64_t)num_sms() ? pairs : (int64_t)num_sms());
+      k<<<g, kGridThreads, bulk_bytes, stream>>>(S, ent, rel, nrm, ent_tot, rel_tot, dim, (int)head_const, cell_tail, num_cells,
+                                                h_out, r_out, w_out, t_out, score);
+    } else if (rows) {
       auto k = transh_grid_kernel<true>;
       cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes);
       k<<<grid, kGridThreads, smem_bytes, stream>>>(S, ent, rel, nrm, ent_tot, rel_tot, dim, (int)head_const, cell_tail, num_cells,

@@ -161,13 +161,14 @@ def test_transh_generic_dims_vs_oracle(dim, ent_tot, rel_tot):
         assert torch.equal(got[0].cpu(), ref[0]) and torch.equal(got[3].cpu(), ref[3])
 
 
-def test_transh_head_grid_form():
-    """transH_head.forward (head.py:558-582): implicit (cell, verb) grid == explicit index vectors."""
+@pytest.mark.parametrize("n_h,n", [(3, 7), (1, 2), (1, 3), (16, 32), (15, 23)])
+def test_transh_head_grid_form(n_h, n):
+    """transH_head.forward (head.py:558-582): implicit (cell, verb) grid == explicit index vectors.  Odd and even cell
+    counts, fewer and more cell pairs than SMs (the rows go out through the bulk-copy kernel, pair by pair)."""
     from skghoi_b200.head import transH_head
     ent, rel, nrm = synthetic.make_transh_tables(42)
     th = transH_head(transh_dim=50, transh_p_norm=2, transh_norm_flag=True, human_idx=49, num_object=80, num_cls=117)
     th.set_tables(ent, rel, nrm, device=DEV)
-    n_h, n = 3, 7
     x, y = torch.meshgrid(torch.arange(n_h), torch.arange(n), indexing="ij")
     x, y = x.flatten(), y.flatten()
     got = th(x.to(DEV), y.to(DEV), n_h, n, None, None)
