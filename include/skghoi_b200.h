@@ -343,6 +343,20 @@ int64_t skg_segments_pack(const int64_t* n, const int64_t* n_h, const double* hw
 int64_t skg_post_count_host(const int32_t* verb_len, int num_obj_cls, const int64_t* labels, const float* scores,
                             const int64_t* box_off, const int64_t* n_h, int num_images, int64_t* img_entries);
 
+/* box_roi_pool of the interaction head (torchvision MultiScaleRoIAlign(['0','1','2','3'], 7, 2), built at models.py:158-162
+ * and called at head.py:387) for a whole batch: FPN level per box = clamp(floor(canonical_level + log2(sqrt(area) /
+ * canonical_scale) + 1e-6), k_min, k_max) - k_min (torchvision poolers.LevelMapper), then roi_align (aligned = False,
+ * sampling_ratio^2 bilinear samples per bin) on that level's map.
+ * feats / feat_h / feat_w / scales are HOST arrays of num_levels entries: device pointers of the [B, C, H_l, W_l] fp32
+ * maps, their sizes and spatial scales.  boxes [sum n, 4] fp32 xyxy in image coordinates (device, 16-byte aligned),
+ * box_off [B+1] int32 (device) the per-image prefix sum.  Outputs (either may be NULL): out_f32 [sum n, C, pooled,
+ * pooled] fp32, the reference layout; out_bf16 [sum n, ld_bf16] bf16, the same block rounded to bf16 in the K-major
+ * layout box_head's first GEMM reads (skips the fp32 tensor and the cast). */
+int skg_multiscale_roi_align(const float* const* feats, const int32_t* feat_h, const int32_t* feat_w, const float* scales,
+                             int num_levels, int channels, int num_images, const float* boxes, const int32_t* box_off,
+                             int64_t num_boxes, int pooled, int sampling_ratio, int k_min, int k_max, float canonical_scale,
+                             int canonical_level, float* out_f32, void* out_bf16, int64_t ld_bf16, cudaStream_t stream);
+
 /* InteractionHead.preprocess (head.py:92-151) for a whole batch, on the device: score >= box_score_thresh filter,
  * class-wise NMS exactly as torchvision.ops.batched_nms computes it for small inputs (boxes shifted by
  * label * (max active coordinate + 1), IoU = inter / (Sa + Sb - inter) > thresh, stable score order), survivors in

@@ -128,6 +128,7 @@ class PostTables(ctypes.Structure):
                                         "hum_base")]
 
 
+_SIGNATURES["skg_multiscale_roi_align"] = (I, [P, P, P, P, I, I, I, P, P, L, I, I, I, I, F, I, P, P, L, P])
 _SIGNATURES["skg_postprocess"] = (I, [P, I, I, ctypes.POINTER(PostTables), L, F, P, L, P, P, P, P, P, P, P, P, P])
 _SIGNATURES["skg_head_post"] = (I, [P, I, I, ctypes.POINTER(PostTables), P, I, I, I, L, F, P, L, P, P, P, P, P, P, P, P, P, P, P, P, P])
 _SIGNATURES["skg_prior_dense"] = (I, [ctypes.POINTER(PostTables), L, I, F, P, P])

@@ -182,6 +182,9 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   // red.global.add into a zeroed scratch tile; the last split to arrive runs the epilogue and re-zeroes it.
   const int num_items = num_tiles * splits;
 
+  // programmatic dependent launch: the next kernel of the chain may be scheduled right away (its prologue overlaps
+  // this kernel's tail); this kernel's own prologue below touches nothing a predecessor wrote
+  asm volatile("griddepcontrol.launch_dependents;\n" ::: "memory");
   if (warp == 0 && lane == 0) {
     asm volatile("prefetch.tensormap [%0];\n" ::"l"(&tmA) : "memory");
     asm volatile("prefetch.tensormap [%0];\n" ::"l"(&tmB) : "memory");
@@ -199,6 +202,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   __syncthreads();
   tcgen05_fence_after();
   const uint32_t tmem_base = *tmem_base_slot;
+  asm volatile("griddepcontrol.wait;\n" ::: "memory");   // every predecessor grid has completed, its writes are visible
 
   if (warp == 0) {
     // ===================== TMA producer =====================
@@ -541,7 +545,18 @@ static int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, int M, in
   }
   const int items = ceil_div(M, BM) * ceil_div(N, BN) * sk.splits;
   const int grid = items < num_sms() ? items : num_sms();
-  kern<<<grid, kGemmThreads, S::kTotal, stream>>>(tmA, tmB, M, N, K, epi, sk.splits, sk.ws, sk.cnt);
+  static const bool pdl = [] { const char* e = getenv("SKG_GEMM_PDL"); return !(e && e[0] == '0'); }();
+  if (pdl) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(grid); cfg.blockDim = dim3(kGemmThreads); cfg.dynamicSmemBytes = S::kTotal; cfg.stream = stream;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at; cfg.numAttrs = 1;
+    SKG_CUDA(cudaLaunchKernelEx(&cfg, kern, tmA, tmB, M, N, K, epi, sk.splits, sk.ws, sk.cnt));
+  } else {
+    kern<<<grid, kGemmThreads, S::kTotal, stream>>>(tmA, tmB, M, N, K, epi, sk.splits, sk.ws, sk.cnt);
+  }
   return check_launch("gemm_bf16_kernel");
 }
 
