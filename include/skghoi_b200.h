@@ -301,6 +301,9 @@ typedef struct skg_head_batch {
   const float* boxes;         /* [boxes, 4] */
   const int32_t* box_off; const int32_t* n_h; const int32_t* hum_off;   /* segment table, as skg_pairs_spatial_encode */
   const int64_t* cell_off; const int64_t* pair_off; const float* hw;
+  const void* box_features_bf16;  /* optional [boxes, K0] bf16 rows (K0 = pool_k rounded up to 8, zero padded): the pooled
+                                     features already in the first GEMM's operand layout, e.g. written by
+                                     skg_multiscale_roi_align; when set, box_features is ignored and may be NULL */
 } skg_head_batch;
 
 #define SKG_HEAD_NUM_BUFFERS 64

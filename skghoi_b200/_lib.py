@@ -213,7 +213,7 @@ class HeadBatch(ctypes.Structure):
     _fields_ = [(k, ctypes.c_int32) for k in ("num_images", "total_boxes", "total_humans", "max_boxes_per_image", "feat_hw")] + \
                [("total_cells", c_int64), ("total_pairs", c_int64), ("seg_bytes", c_int64)] + \
                [(k, c_void_p) for k in ("features3", "box_features", "boxes", "box_off", "n_h", "hum_off", "cell_off",
-                                        "pair_off", "hw")]
+                                        "pair_off", "hw", "box_features_bf16")]
 
 
 HEAD_NUM_BUFFERS = 64

@@ -268,7 +268,7 @@ static int enqueue_forward(const skg_head_weights* wp, const skg_head_batch* bp,
   const int NB = b.total_boxes, NH = b.total_humans, B = b.num_images, R = w.R, E = w.E;
   if (C == 0 || B == 0) return SKG_OK;
   SKG_REQUIRE(C < (int64_t)1 << 31, "too many grid cells in one batch");
-  SKG_REQUIRE(b.features3 && b.box_features && b.boxes && b.box_off && b.n_h && b.hum_off && b.cell_off && b.pair_off && b.hw,
+  SKG_REQUIRE(b.features3 && (b.box_features || b.box_features_bf16) && b.boxes && b.box_off && b.n_h && b.hum_off && b.cell_off && b.pair_off && b.hw,
               "null batch pointer");
   SKG_REQUIRE(b.max_boxes_per_image <= w.ent_tot, "index out of range in self: a box index addresses the %d-row entity table (head.py:572)",
               w.ent_tot);
@@ -296,10 +296,14 @@ static int enqueue_forward(const skg_head_weights* wp, const skg_head_batch* bp,
   // ---- sa: box head (head.py:635-641, 812); its second layer writes straight into the fc input rows
   SKG_TRY(skg_node_prep(w.ent, w.ent_dim, w.ent_tot, b.box_off, b.n_h, b.hum_off, B, NB, H(B_OIN), w.fc_k, E, I32(B_BOX2HUM), sa));
   MARK("node_prep", sa);
-  SKG_TRY(skg_cast_pad_bf16(b.box_features, w.pool_k, nullptr, 0, NB, w.pool_k, H(B_XB), w.K0, w.K0, sa));
-  MARK("cast box_features", sa);
+  const void* xb = b.box_features_bf16;            // pooled features already in operand layout (native RoIAlign)
+  if (!xb) {
+    SKG_TRY(skg_cast_pad_bf16(b.box_features, w.pool_k, nullptr, 0, NB, w.pool_k, H(B_XB), w.K0, w.K0, sa));
+    MARK("cast box_features", sa);
+    xb = H(B_XB);
+  }
   g = group0(); g.flags = SKG_EPI_RELU; g.bias = w.bb1; g.out_bf16 = H(B_X1); g.ld_ob = E;
-  SKG_TRY(skg_gemm_bf16_splitk(H(B_XB), w.K0, w.Wb1, w.K0, NB, E, w.K0, &g, 1, 0, H(B_SPLITK1), sk_bytes, sa));
+  SKG_TRY(skg_gemm_bf16_splitk(xb, w.K0, w.Wb1, w.K0, NB, E, w.K0, &g, 1, 0, H(B_SPLITK1), sk_bytes, sa));
   MARK("gemm box_head.1", sa);
   g = group0(); g.flags = SKG_EPI_RELU; g.bias = w.bb2; g.out_bf16 = H(B_OIN); g.ld_ob = w.fc_k;
   SKG_TRY(skg_gemm_bf16(H(B_X1), E, w.Wb2, E, NB, E, E, &g, 1, 0, sa));

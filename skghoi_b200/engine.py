@@ -469,7 +469,13 @@ def head_forward(ih, features3: Tensor, image_shapes, box_features: Tensor, boxe
     w = pk.cw
     w.ent = ent.data_ptr()
     pk.fc_bias(ent, G.human_idx)
-    b.features3, b.box_features, b.boxes = f3.data_ptr(), bf.data_ptr(), boxes_cat.data_ptr()
+    b.features3, b.boxes = f3.data_ptr(), boxes_cat.data_ptr()
+    if bf.dtype == torch.bfloat16:                   # operand rows written by the native RoIAlign (roi.py)
+        if bf.shape[1] != int(pk.cw.K0) or bf.data_ptr() % 16:
+            raise ValueError("bf16 box features must be 16-byte aligned [boxes, %d] rows" % int(pk.cw.K0))
+        b.box_features, b.box_features_bf16 = None, bf.data_ptr()
+    else:
+        b.box_features, b.box_features_bf16 = bf.data_ptr(), None
     with torch.cuda.device(dev):
         ws = _workspace(dev, int(plan.total_bytes))
         wkey = ws.data_ptr()
@@ -1026,5 +1032,39 @@ def interaction_head_forward(ih, features, detections, image_shapes, targets=Non
         detections = preprocess_detections(ih, detections, targets)
     coords = [d["boxes"] for d in detections]; labels = [d["labels"] for d in detections]
     scores = [d["scores"] for d in detections]
-    box_features = ih.box_roi_pool(features, coords, image_shapes)                        # head.py:387 (stock torchvision)
+    pool = _native_pooler(ih) if features["3"].is_cuda and getattr(ih, "native_roi_align", True) else None
+    if pool is None:
+        box_features = ih.box_roi_pool(features, coords, image_shapes)                    # head.py:387 (stock torchvision)
+    elif ih.training and torch.is_grad_enabled():
+        box_features = pool(features, coords, image_shapes)                               # fp32 [sum n, C, 7, 7] for the tape
+    else:
+        # inference: the pooled block goes straight into box_head's bf16 GEMM operand; the
+        # [sum n, 256, 7, 7] fp32 tensor and its cast never reach HBM
+        K0 = int(packed_head(ih).cw.K0)
+        box_features = torch.empty(sum(int(c.shape[0]) for c in coords), K0, dtype=torch.bfloat16, device=features["3"].device)
+        if K0 != pool.channels_times_bins(features):
+            box_features.zero_()
+        pool.pool(features, coords, image_shapes, want_f32=False, bf16_out=box_features)
     return ih.forward_from_pooled(features, image_shapes, box_features, coords, labels, scores, targets, meta=meta)
+
+
+def _native_pooler(ih):
+    """The native counterpart of ``ih.box_roi_pool``: itself when it already is one, a mirror of a torchvision
+    ``MultiScaleRoIAlign`` (same level names, output size, sampling ratio, canonical scale / level), else None."""
+    from . import roi
+    p = ih.box_roi_pool
+    if isinstance(p, roi.MultiScaleRoIAlign):
+        return p
+    cached = ih.__dict__.get("_skg_native_pool")
+    if cached is not None and cached[0] is p:
+        return cached[1]
+    native = None
+    try:
+        from torchvision.ops import MultiScaleRoIAlign as TV
+        if isinstance(p, TV) and p.sampling_ratio > 0 and p.output_size[0] == p.output_size[1]:
+            native = roi.MultiScaleRoIAlign(list(p.featmap_names), tuple(p.output_size), int(p.sampling_ratio),
+                                            canonical_scale=p.canonical_scale, canonical_level=p.canonical_level)
+    except ImportError:
+        pass
+    ih.__dict__["_skg_native_pool"] = (p, native)
+    return native

@@ -85,5 +85,8 @@ class MultiScaleRoIAlign(torch.nn.Module):
                       _lib.stream_ptr(dev))
         return out
 
+    def channels_times_bins(self, x: Dict[str, Tensor]) -> int:
+        return int(self._levels(x)[0].shape[1]) * self.output_size[0] * self.output_size[1]
+
     def forward(self, x: Dict[str, Tensor], boxes: List[Tensor], image_shapes: List[Tuple[int, int]]) -> Tensor:
         return self.pool(x, boxes, image_shapes)

@@ -185,8 +185,10 @@ def test_training_pass_gradients_vs_oracle_autograd():
 
 
 def test_interaction_head_full_forward_with_stock_preprocess():
-    """InteractionHead.forward (head.py:341-429): stock torchvision NMS / RoIAlign, then the CUDA path -- must equal
-    forward_from_pooled on the same preprocessed detections."""
+    """InteractionHead.forward (head.py:341-429) -- device preprocess, native RoIAlign written straight into box_head's
+    bf16 operand, CUDA path -- against stock torchvision NMS + RoIAlign feeding forward_from_pooled on the same
+    detections.  Integer outputs are identical; scores agree to the bf16 budget (a last-bit difference in a pooled
+    value, or the split-K summation order of box_head's first layer, can flip a bf16 rounding downstream)."""
     shapes = [(5, 12), (3, 9)]
     batch = synthetic.make_batch(shapes, seed=9, levels=("0", "1", "2", "3"))
     d = _to_dev(batch)
@@ -203,8 +205,17 @@ def test_interaction_head_full_forward_with_stock_preprocess():
     assert len(got) == len(want) == 2
     for g, w in zip(got, want):
         for k in w:
-            torch.testing.assert_close(g[k], w[k], rtol=1e-5, atol=1e-6)
+            if w[k].dtype == torch.int64 or k in ("boxes_h", "boxes_o", "prior"):
+                assert torch.equal(g[k], w[k]), k
+            else:
+                torch.testing.assert_close(g[k], w[k], rtol=1e-2, atol=1e-4)
         assert g["boxes_h"].shape[0] > 0
+    # the stock pooler, when asked for, gives the same results
+    ih.native_roi_align = False
+    with torch.no_grad():
+        stock = ih(d["features"], dets, d["image_shapes"])
+    for g, w in zip(stock, want):
+        torch.testing.assert_close(g["scores"], w["scores"], rtol=1e-2, atol=1e-4)
 
 
 def _crowded_detections(gen, n_img, n_det, human_frac=0.4):
