@@ -191,12 +191,21 @@ __global__ void __launch_bounds__(128) aggregate_kernel(const float* __restrict_
   const __nv_bfloat16* H = is_h ? H_os : H_so;
   for (int c = threadIdx.x * 8; c < width; c += 128 * 8) {
     float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-    for (int t = 0; t < cnt; ++t) {
-      const float w = sw[t] * inv;
-      const uint4 u = __ldg(reinterpret_cast<const uint4*>(H + (base + t * step) * ld_h + c));
-      const float2 a = unpack2(u.x), b2 = unpack2(u.y), c2 = unpack2(u.z), d = unpack2(u.w);
-      acc[0] = fmaf(w, a.x, acc[0]); acc[1] = fmaf(w, a.y, acc[1]); acc[2] = fmaf(w, b2.x, acc[2]); acc[3] = fmaf(w, b2.y, acc[3]);
-      acc[4] = fmaf(w, c2.x, acc[4]); acc[5] = fmaf(w, c2.y, acc[5]); acc[6] = fmaf(w, d.x, acc[6]); acc[7] = fmaf(w, d.y, acc[7]);
+    // eight message rows in flight per thread (the rows of an object's column are n * ld_h apart: every load is its own
+    // L2 round trip), accumulated in the original order
+    for (int t0 = 0; t0 < cnt; t0 += 8) {
+      uint4 u[8];
+#pragma unroll
+      for (int k = 0; k < 8; ++k)
+        u[k] = (t0 + k < cnt) ? __ldg(reinterpret_cast<const uint4*>(H + (base + (t0 + k) * step) * ld_h + c)) : make_uint4(0, 0, 0, 0);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        if (t0 + k >= cnt) break;
+        const float w = sw[t0 + k] * inv;
+        const float2 a = unpack2(u[k].x), b2 = unpack2(u[k].y), c2 = unpack2(u[k].z), d = unpack2(u[k].w);
+        acc[0] = fmaf(w, a.x, acc[0]); acc[1] = fmaf(w, a.y, acc[1]); acc[2] = fmaf(w, b2.x, acc[2]); acc[3] = fmaf(w, b2.y, acc[3]);
+        acc[4] = fmaf(w, c2.x, acc[4]); acc[5] = fmaf(w, c2.y, acc[5]); acc[6] = fmaf(w, d.x, acc[6]); acc[7] = fmaf(w, d.y, acc[7]);
+      }
     }
     *reinterpret_cast<uint4*>((is_h ? Z_h : Z_o) + (int64_t)local * width + c) =
         make_uint4(pack2(acc[0], acc[1]), pack2(acc[2], acc[3]), pack2(acc[4], acc[5]), pack2(acc[6], acc[7]));
@@ -225,6 +234,63 @@ __global__ void layernorm_kernel(const float* __restrict__ x, int64_t rows, int6
     const float y = (xr[c] - mean) * rstd * __ldg(w + c) + __ldg(b + c);
     if (out_f32) out_f32[row * width + c] = y;
     if (out_bf16) out_bf16[row * width + c] = __float2bfloat16(y);
+  }
+}
+
+// LayerNorm, one 256-thread CTA per row, the row held in registers (VPT float4s per thread): one pass over global
+// memory instead of three, every load in flight at once.  Same two-pass mean / variance formula as above.
+template <int VPT>
+__global__ void __launch_bounds__(256) layernorm_row_kernel(const float* __restrict__ x, int64_t rows_a, int width,
+                                                            const float* __restrict__ w_a, const float* __restrict__ b_a,
+                                                            const float* __restrict__ w_b, const float* __restrict__ b_b,
+                                                            float eps, float* __restrict__ out_f32,
+                                                            __nv_bfloat16* __restrict__ out_bf16) {
+  __shared__ float red[8];
+  const int64_t row = blockIdx.x;
+  const int n4 = width >> 2;
+  const float4* xr = reinterpret_cast<const float4*>(x + row * width);
+  float4 v[VPT];
+  float s = 0.f;
+#pragma unroll
+  for (int j = 0; j < VPT; ++j) {
+    const int q = threadIdx.x + 256 * j;
+    v[j] = q < n4 ? __ldg(xr + q) : make_float4(0.f, 0.f, 0.f, 0.f);
+    s += (v[j].x + v[j].y) + (v[j].z + v[j].w);
+  }
+  s = warp_sum(s);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = s;
+  __syncthreads();
+  float tot = 0.f;
+#pragma unroll
+  for (int k = 0; k < 8; ++k) tot += red[k];
+  const float mean = tot / (float)width;
+  __syncthreads();
+  float sq = 0.f;
+#pragma unroll
+  for (int j = 0; j < VPT; ++j) {
+    if (threadIdx.x + 256 * j < n4) {
+      const float a = v[j].x - mean, b = v[j].y - mean, c = v[j].z - mean, d = v[j].w - mean;
+      sq += (a * a + b * b) + (c * c + d * d);
+    }
+  }
+  sq = warp_sum(sq);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = sq;
+  __syncthreads();
+  tot = 0.f;
+#pragma unroll
+  for (int k = 0; k < 8; ++k) tot += red[k];
+  const float rstd = rsqrtf(tot / (float)width + eps);
+  const float4* w = reinterpret_cast<const float4*>(row < rows_a ? w_a : w_b);
+  const float4* b = reinterpret_cast<const float4*>(row < rows_a ? b_a : b_b);
+#pragma unroll
+  for (int j = 0; j < VPT; ++j) {
+    const int q = threadIdx.x + 256 * j;
+    if (q >= n4) continue;
+    const float4 g = __ldg(w + q), o = __ldg(b + q);
+    const float4 y = make_float4((v[j].x - mean) * rstd * g.x + o.x, (v[j].y - mean) * rstd * g.y + o.y,
+                                 (v[j].z - mean) * rstd * g.z + o.z, (v[j].w - mean) * rstd * g.w + o.w);
+    if (out_f32) reinterpret_cast<float4*>(out_f32 + row * width)[q] = y;
+    if (out_bf16) reinterpret_cast<uint2*>(out_bf16 + row * width)[q] = make_uint2(pack2(y.x, y.y), pack2(y.z, y.w));
   }
 }
 
@@ -336,8 +402,17 @@ extern "C" int skg_layernorm(const float* x, int64_t rows, int64_t rows_a, int w
                              cudaStream_t stream) {
   if (rows == 0) return SKG_OK;
   SKG_REQUIRE(x && w_a && b_a && (rows_a >= rows || (w_b && b_b)) && (out_f32 || out_bf16), "bad layernorm arguments");
-  layernorm_kernel<<<(int)ceil_div64(rows * 32, 256), 256, 0, stream>>>(x, rows, rows_a, width, w_a, b_a, w_b ? w_b : w_a,
-                                                                       b_b ? b_b : b_a, eps, out_f32, (__nv_bfloat16*)out_bf16);
+  const float* wb = w_b ? w_b : w_a; const float* bb = b_b ? b_b : b_a;
+  const uintptr_t al = (uintptr_t)x | (uintptr_t)w_a | (uintptr_t)b_a | (uintptr_t)wb | (uintptr_t)bb | (uintptr_t)out_f32;
+  if (width % 4 == 0 && width <= 4096 && (al & 15u) == 0 && ((uintptr_t)out_bf16 & 7u) == 0 && rows <= 0x7fffffff) {
+    if (width <= 1024)
+      layernorm_row_kernel<1><<<(int)rows, 256, 0, stream>>>(x, rows_a, width, w_a, b_a, wb, bb, eps, out_f32, (__nv_bfloat16*)out_bf16);
+    else
+      layernorm_row_kernel<4><<<(int)rows, 256, 0, stream>>>(x, rows_a, width, w_a, b_a, wb, bb, eps, out_f32, (__nv_bfloat16*)out_bf16);
+    return check_launch("layernorm_row_kernel");
+  }
+  layernorm_kernel<<<(int)ceil_div64(rows * 32, 256), 256, 0, stream>>>(x, rows, rows_a, width, w_a, b_a, wb, bb, eps, out_f32,
+                                                                       (__nv_bfloat16*)out_bf16);
   return check_launch("layernorm_kernel");
 }
 
