@@ -35,7 +35,9 @@ __global__ void postprocess_kernel(const float* __restrict__ logits, int ld_logi
                                    int64_t total_entries, int64_t* __restrict__ out_index, int64_t* __restrict__ out_pred,
                                    float* __restrict__ out_scores, float* __restrict__ out_prior /*[2, total]*/,
                                    float* __restrict__ out_weights /*[P]*/, float* __restrict__ out_labels /*[total]*/,
-                                   float* __restrict__ out_unary /*[P]*/, int64_t* __restrict__ out_object /*[P]*/) {
+                                   float* __restrict__ out_unary /*[P]*/, int64_t* __restrict__ out_object /*[P]*/,
+                                   const float4* __restrict__ boxes /*or null*/, float4* __restrict__ boxes_h,
+                                   float4* __restrict__ boxes_o) {
   const int lane = threadIdx.x & 31;
   const int64_t p = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
   if (p >= pairs) return;
@@ -50,6 +52,9 @@ __global__ void postprocess_kernel(const float* __restrict__ logits, int ld_logi
   if (lane == 0) {
     out_weights[p] = w;
     if (out_object) out_object[p] = lab_o;
+  }
+  if (boxes && lane < 2) {           // boxes_h / boxes_o of the pair (head.py:975-976: coords[x_keep], coords[y_keep])
+    if (lane == 0) boxes_h[p] = __ldg(boxes + boff + i); else boxes_o[p] = __ldg(boxes + orow);
   }
   if (gt_labels && out_unary) {     // unary_labels = clamp(sum_k labels[p, k], max=1)   (head.py:330)
     float s = 0.f;
@@ -128,13 +133,11 @@ __global__ void associate_gt_kernel(const float4* __restrict__ boxes, PostTables
 //   row_tot[i]    = (score_i > 0) ? sum_j cnt_j - cnt_i : 0      entries emitted by human row i (head.py:315 nonzero)
 //   img_entries[b] = sum_i row_tot[i]
 // One CTA per image; the boxes of one image are scanned by warp 0 in chunks of 32.
-__global__ void post_counts_kernel(const int32_t* __restrict__ verb_off, const int64_t* __restrict__ labels,
-                                   const float* __restrict__ scores, const int32_t* __restrict__ box_off,
-                                   const int32_t* __restrict__ hum_off, int32_t* __restrict__ box_cnt,
-                                   int32_t* __restrict__ box_prefix, int64_t* __restrict__ hum_base,
-                                   int64_t* __restrict__ img_entries) {
-  if (threadIdx.x >= 32) return;
-  const int b = blockIdx.x, lane = threadIdx.x;
+__device__ __forceinline__ void post_counts_image(int b, int lane, const int32_t* __restrict__ verb_off,
+                                                  const int64_t* __restrict__ labels, const float* __restrict__ scores,
+                                                  const int32_t* __restrict__ box_off, const int32_t* __restrict__ hum_off,
+                                                  int32_t* __restrict__ box_cnt, int32_t* __restrict__ box_prefix,
+                                                  int64_t* __restrict__ hum_base, int64_t* __restrict__ img_entries) {
   const int lo = __ldg(box_off + b), n = __ldg(box_off + b + 1) - lo;
   const int h0 = __ldg(hum_off + b), nh = __ldg(hum_off + b + 1) - h0;
   int run = 0;
@@ -162,6 +165,40 @@ __global__ void post_counts_kernel(const int32_t* __restrict__ verb_off, const i
     rrun += __shfl_sync(0xffffffffu, inc, 31);
   }
   if (lane == 0) img_entries[b] = rrun;
+}
+
+__global__ void post_counts_kernel(const int32_t* __restrict__ verb_off, const int64_t* __restrict__ labels,
+                                   const float* __restrict__ scores, const int32_t* __restrict__ box_off,
+                                   const int32_t* __restrict__ hum_off, int32_t* __restrict__ box_cnt,
+                                   int32_t* __restrict__ box_prefix, int64_t* __restrict__ hum_base,
+                                   int64_t* __restrict__ img_entries) {
+  if (threadIdx.x >= 32) return;
+  post_counts_image(blockIdx.x, threadIdx.x, verb_off, labels, scores, box_off, hum_off, box_cnt, box_prefix, hum_base, img_entries);
+}
+
+// The whole offset table in ONE single-CTA launch: a warp per image (round robin), then the image bases.
+constexpr int kPostOffThreads = 512;
+__global__ void __launch_bounds__(kPostOffThreads) post_offsets_kernel(
+    const int32_t* __restrict__ verb_off, const int64_t* __restrict__ labels, const float* __restrict__ scores,
+    const int32_t* __restrict__ box_off, const int32_t* __restrict__ hum_off, int B, int32_t* __restrict__ box_cnt,
+    int32_t* __restrict__ box_prefix, int64_t* __restrict__ hum_base, int64_t* __restrict__ img_entries,
+    int64_t* __restrict__ img_base) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  for (int b = warp; b < B; b += kPostOffThreads / 32)
+    post_counts_image(b, lane, verb_off, labels, scores, box_off, hum_off, box_cnt, box_prefix, hum_base, img_entries);
+  __syncthreads();                                   // global writes of this CTA are visible to it after the barrier
+  if (threadIdx.x == 0) {
+    long long run = 0;
+    for (int b = 0; b < B; ++b) { img_base[b] = run; run += img_entries[b]; }
+    img_base[B] = run;
+  }
+  __syncthreads();
+  const int total_h = __ldg(hum_off + B);
+  for (int h = threadIdx.x; h < total_h; h += kPostOffThreads) {
+    int lo = 0, hi = B;
+    while (hi - lo > 1) { const int mid = (lo + hi) >> 1; if (__ldg(hum_off + mid) <= h) lo = mid; else hi = mid; }
+    hum_base[h] += img_base[lo];
+  }
 }
 
 __global__ void post_bases_kernel(const int32_t* __restrict__ hum_off, int B, const int64_t* __restrict__ img_entries,
@@ -208,10 +245,11 @@ static int fill_tables(PostTables& t, const skg_post_tables* h) {
   return SKG_OK;
 }
 
-extern "C" int skg_postprocess(const float* logits, int ld_logits, int num_cls, const skg_post_tables* tables, int64_t pairs,
-                               float prior_power, const float* gt_labels, int64_t total_entries, int64_t* out_index,
-                               int64_t* out_pred, float* out_scores, float* out_prior, float* out_weights,
-                               float* out_labels, float* out_unary, int64_t* out_object, cudaStream_t stream) {
+static int postprocess_launch(const float* logits, int ld_logits, int num_cls, const skg_post_tables* tables, int64_t pairs,
+                              float prior_power, const float* gt_labels, int64_t total_entries, int64_t* out_index,
+                              int64_t* out_pred, float* out_scores, float* out_prior, float* out_weights,
+                              float* out_labels, float* out_unary, int64_t* out_object, const float* boxes, float* boxes_h,
+                              float* boxes_o, cudaStream_t stream) {
   if (pairs == 0) return SKG_OK;
   PostTables t;
   int rc = fill_tables(t, tables);
@@ -223,8 +261,18 @@ extern "C" int skg_postprocess(const float* logits, int ld_logits, int num_cls, 
   postprocess_kernel<<<(int)ceil_div64(pairs * 32, 256), 256, 0, stream>>>(logits, ld_logits, num_cls, t, pairs, prior_power,
                                                                           gt_labels, total_entries, out_index, out_pred,
                                                                           out_scores, out_prior, out_weights, out_labels,
-                                                                          out_unary, out_object);
+                                                                          out_unary, out_object, (const float4*)boxes,
+                                                                          (float4*)boxes_h, (float4*)boxes_o);
   return check_launch("postprocess_kernel");
+}
+
+extern "C" int skg_postprocess(const float* logits, int ld_logits, int num_cls, const skg_post_tables* tables, int64_t pairs,
+                               float prior_power, const float* gt_labels, int64_t total_entries, int64_t* out_index,
+                               int64_t* out_pred, float* out_scores, float* out_prior, float* out_weights,
+                               float* out_labels, float* out_unary, int64_t* out_object, cudaStream_t stream) {
+  return postprocess_launch(logits, ld_logits, num_cls, tables, pairs, prior_power, gt_labels, total_entries, out_index, out_pred,
+                            out_scores, out_prior, out_weights, out_labels, out_unary, out_object, nullptr, nullptr, nullptr,
+                            stream);
 }
 
 extern "C" int skg_prior_dense(const skg_post_tables* tables, int64_t pairs, int num_cls, float prior_power, float* prior,
@@ -261,6 +309,11 @@ extern "C" int skg_post_offsets(const int32_t* verb_off, const int64_t* labels, 
   if (num_images == 0) return SKG_OK;
   SKG_REQUIRE(verb_off && labels && scores && box_off && hum_off && box_cnt && box_prefix && hum_base && img_entries && img_base,
               "null pointer argument");
+  if (num_images <= 4 * (kPostOffThreads / 32)) {     // a batch of images: one single-CTA launch does both steps
+    post_offsets_kernel<<<1, kPostOffThreads, 0, stream>>>(verb_off, labels, scores, box_off, hum_off, num_images, box_cnt,
+                                                         box_prefix, hum_base, img_entries, img_base);
+    return check_launch("post_offsets_kernel");
+  }
   post_counts_kernel<<<num_images, 32, 0, stream>>>(verb_off, labels, scores, box_off, hum_off, box_cnt, box_prefix, hum_base,
                                                     img_entries);
   int rc = check_launch("post_counts_kernel");
@@ -300,9 +353,11 @@ extern "C" int skg_head_post(const float* logits, int ld_logits, int num_cls, co
                             img_entries, img_base, stream);
   if (rc) return rc;
   t.box_cnt = box_cnt; t.box_prefix = box_prefix; t.hum_base = hum_base;
-  rc = skg_postprocess(logits, ld_logits, num_cls, &t, pairs, prior_power, gt_labels, total_entries, out_index, out_pred,
-                       out_scores, out_prior, out_weights, out_labels, out_unary, out_object, stream);
-  if (rc) return rc;
-  if (boxes_h && boxes_o) rc = skg_gather_pair_boxes(boxes, &t, pairs, boxes_h, boxes_o, stream);
-  return rc;
+  const bool with_boxes = boxes && boxes_h && boxes_o;
+  if (with_boxes)
+    SKG_REQUIRE((((uintptr_t)boxes | (uintptr_t)boxes_h | (uintptr_t)boxes_o) & 15u) == 0, "boxes / boxes_h / boxes_o must be 16-byte aligned");
+  // the pair boxes ride along in the per-pair warp of the post-processing kernel (one launch less on the critical path)
+  return postprocess_launch(logits, ld_logits, num_cls, &t, pairs, prior_power, gt_labels, total_entries, out_index, out_pred,
+                            out_scores, out_prior, out_weights, out_labels, out_unary, out_object, with_boxes ? boxes : nullptr,
+                            boxes_h, boxes_o, stream);
 }
