@@ -299,38 +299,28 @@ def run_b200(args):
         step_resident(); flush.zero_()
     torch.cuda.synchronize(dev)
     # a step is ~0.3 ms: W of them end before clocks, allocator pools and the graph cache have settled, so keep stepping
-    # (untimed) for a fixed 0.3 s on top of the W warm-up steps
+    # (untimed) for a fixed 0.5 s on top of the W warm-up steps
+    # the clock sampler starts here: nvidia-smi's start-up (NVML initialisation takes driver locks) then falls into the
+    # spin-up instead of the timed region; its samples cover spin-up + timed steps, all under load
+    sampler = ClockSampler(local if rank == 0 else None)
+    sampler.start()
     t_spin = time.perf_counter()
-    while time.perf_counter() - t_spin < 0.3:
+    while time.perf_counter() - t_spin < 0.5:
         for _ in range(20):
             step_resident(); flush.zero_()
         torch.cuda.synchronize(dev)
     # ---- timed: device-resident inputs
     # clocks / throttle reasons are sampled by rank 0 only (its own GPU): eight concurrent nvidia-smi pollers contend for
     # the driver with the ranks' kernel launches and slow the host-bound step down
-    sampler = ClockSampler(local if rank == 0 else None)
     ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
     l0 = lib.skg_launch_count()
     barrier()
-    sampler.start()
     for s, e in ev:
         s.record(); step_resident(); e.record()
         flush.zero_()
     barrier()
     launches = lib.skg_launch_count() - l0
     t_ms = sum(s.elapsed_time(e) for s, e in ev)
-    # pinned host -> device copy bandwidth of this box (explains the e2e floor: h2d_bytes_per_step / this)
-    big = torch.empty(64 << 20, dtype=torch.uint8).pin_memory(); dbig = torch.empty_like(big, device=dev)
-    dbig.copy_(big, non_blocking=True); torch.cuda.synchronize(dev)
-    h2d_gbs = 0.0
-    for _ in range(3):                                   # best of three event-timed bursts of five copies
-        c0, c1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        c0.record()
-        for _ in range(5):
-            dbig.copy_(big, non_blocking=True)
-        c1.record(); torch.cuda.synchronize(dev)
-        h2d_gbs = max(h2d_gbs, 5 * big.numel() / (c0.elapsed_time(c1) * 1e-3) / 1e9)
-    del big, dbig
     # ---- timed: end to end from pinned host buffers (pipelined loop, host wall clock over all K steps)
     run_e2e(max(args.warmup, 3) + 20)
     barrier()
@@ -339,13 +329,29 @@ def run_b200(args):
         pr = cProfile.Profile(); pr.enable(); run_e2e(200); torch.cuda.synchronize(dev); pr.disable()
         pstats.Stats(pr, stream=sys.stderr).sort_stats("tottime").print_stats(40)
         print("graph stats (replays, captures, plain):", _lib.graph_stats(), file=sys.stderr)
-        sampler.start(); sampler.stop()
+        sampler.stop()
         return
+    if os.environ.get("SKG_E2E_REPEAT"):
+        for _ in range(int(os.environ["SKG_E2E_REPEAT"])):
+            t0 = time.perf_counter(); run_e2e(args.steps); torch.cuda.synchronize(dev)
+            print("e2e repeat: %.3f ms/step" % ((time.perf_counter() - t0) / args.steps * 1e3), file=sys.stderr)
     t0 = time.perf_counter()
     run_e2e(args.steps)
     torch.cuda.synchronize(dev)
     e2e_s = time.perf_counter() - t0
     barrier()
+    # the H2D of one step ALONE (the e2e floor): this step's own pinned buffers into one of the device sets, nothing else
+    # running, best of five event-timed bursts of five steps' worth of copies
+    h2d_gbs = 0.0
+    for _ in range(5):
+        c0, c1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        c0.record()
+        for _ in range(5):
+            sets[0]["small"].copy_(host["small"], non_blocking=True)
+            sets[0]["f3"].copy_(host["f3"], non_blocking=True)
+            sets[0]["bf"].copy_(host["bf"], non_blocking=True)
+        c1.record(); torch.cuda.synchronize(dev)
+        h2d_gbs = max(h2d_gbs, 5 * h2d_bytes / (c0.elapsed_time(c1) * 1e-3) / 1e9)
     clocks = sampler.stop()
     tt = torch.tensor([t_ms, e2e_s * 1e3], dtype=torch.float64, device=dev)
     if world > 1:

@@ -4,6 +4,7 @@ There is NO fallback: if the shared library is missing or a call fails, an excep
 PyTorch is used only to own device memory and streams; tensors cross the boundary as raw
 ``data_ptr()`` addresses plus explicit sizes.
 """
+import contextlib
 import ctypes
 import os
 from ctypes import c_char_p, c_float, c_int, c_int64, c_void_p
@@ -84,6 +85,14 @@ def raw_stream(device=None) -> int:
     if idx is None:
         idx = torch.cuda.current_device()
     return torch._C._cuda_getCurrentRawStream(idx)
+
+
+_NULL_CTX = contextlib.nullcontext()
+
+
+def on_device(device):
+    """``torch.cuda.device(device)`` only when ``device`` is not already current (the context manager costs ~10 us)."""
+    return _NULL_CTX if torch.cuda.current_device() == device.index else torch.cuda.device(device)
 
 
 def stream_ptr(device=None):

@@ -476,7 +476,7 @@ def head_forward(ih, features3: Tensor, image_shapes, box_features: Tensor, boxe
         b.box_features, b.box_features_bf16 = None, bf.data_ptr()
     else:
         b.box_features, b.box_features_bf16 = bf.data_ptr(), None
-    with torch.cuda.device(dev):
+    with _lib.on_device(dev):
         ws = _workspace(dev, int(plan.total_bytes))
         wkey = ws.data_ptr()
         if _ws_seg_owner.get(wkey) is not seg:       # the table of another batch (or nothing) sits in the workspace
@@ -822,12 +822,18 @@ def interaction_head_from_pooled(ih, features, image_shapes, box_features, box_c
     Pn = seg.total_pairs
     nc = G.num_cls
     vt = _verb_table(G, dev)
-    tables = _lib.PostTables()
-    tables.verb_off, tables.verb_idx = vt.d_off.data_ptr(), vt.d_idx.data_ptr()
-    tables.pair2cell, tables.cell_hrow = run["pair2cell"].data_ptr(), run["cell_hrow"].data_ptr()
-    tables.cell_orow, tables.cell_img = run["cell_orow"].data_ptr(), run["cell_img"].data_ptr()
-    tables.hum_off, tables.box_off, tables.pair_off = seg.d_hum_off.data_ptr(), seg.d_box_off.data_ptr(), seg.d_pair_off.data_ptr()
-    tables.labels, tables.scores = labels_dev.data_ptr(), scores_dev.data_ptr()
+    tkey = (labels_dev.data_ptr(), scores_dev.data_ptr(), run["pair2cell"].data_ptr(), seg.d_hum_off.data_ptr())
+    tc = run.get("_post_tables")
+    if tc is not None and tc[0] == tkey:
+        tables = tc[1]                               # same run views, same label / score buffers: the descriptor stands
+    else:
+        tables = _lib.PostTables()
+        tables.verb_off, tables.verb_idx = vt.d_off.data_ptr(), vt.d_idx.data_ptr()
+        tables.pair2cell, tables.cell_hrow = run["pair2cell"].data_ptr(), run["cell_hrow"].data_ptr()
+        tables.cell_orow, tables.cell_img = run["cell_orow"].data_ptr(), run["cell_img"].data_ptr()
+        tables.hum_off, tables.box_off, tables.pair_off = seg.d_hum_off.data_ptr(), seg.d_box_off.data_ptr(), seg.d_pair_off.data_ptr()
+        tables.labels, tables.scores = labels_dev.data_ptr(), scores_dev.data_ptr()
+        dict.__setitem__(run, "_post_tables", (tkey, tables))
     # entries per image (sizes the outputs): closed form on the host, no device round trip
     pc = meta.get("_skg_post")
     if pc is None or pc[0] is not seg:
@@ -856,7 +862,7 @@ def interaction_head_from_pooled(ih, features, image_shapes, box_features, box_c
     out_f = torch.empty(_flat_f_size(L, Pn, gt is not None), dtype=torch.float32, device=dev)
     index, pred, obj = out_i[:L], out_i[L:2 * L], out_i[2 * L:]
     bh_all, bo_all, scores, prior, weights, lab_e, unary = _flat_f_views(out_f, L, Pn, gt is not None)
-    with torch.cuda.device(dev):
+    with _lib.on_device(dev):
         _lib.call("skg_head_post", _lib.ptr(run["logits"]), run["logits"].stride(0), nc, ctypes_byref(tables), _lib.ptr(boxes_cat),
                   seg.B, seg.total_boxes, seg.total_humans, Pn, 1.0 if G.training else 2.8, _lib.ptr(gt), L,
                   _lib.ptr(run["post_i32"]), _lib.ptr(run["post_i64"]), _lib.ptr(index), _lib.ptr(pred), _lib.ptr(scores),
