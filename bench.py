@@ -422,10 +422,10 @@ def measure_training(torch, dist, args, dev, rank, world, flush):
     meta = engine._host_meta(batch["box_labels"], batch["box_scores"], 49)
     params = [p for p in ih.parameters() if p.requires_grad]
     opt = torch.optim.SGD(params, lr=1e-4, momentum=0.9)
-    buckets = shard.GradBuckets(params)
+    buckets = shard.GradBuckets(params).attach()      # gradients live in the flat buckets: no per-parameter pack / unpack
 
     def step():
-        opt.zero_grad(set_to_none=True)
+        buckets.zero_grad()
         res = ih.forward_from_pooled(d["f"], batch["image_shapes"], d["bf"], d["boxes"], d["labels"], d["scores"],
                                      d["targets"], meta=meta)
         ls = res[-1]

@@ -115,13 +115,48 @@ class GradBuckets:
             o += k
         return flat
 
+    # -- attached mode: the gradients LIVE in the flat buckets -----------------------------------------------------
+    def attach(self) -> "GradBuckets":
+        """Makes every parameter's ``.grad`` a view into its bucket's flat buffer (autograd accumulates into an existing
+        ``.grad`` in place), so an averaging step is one all-reduce + one scale per BUCKET -- no per-parameter pack / unpack
+        (~400 small launches for the head).  Use ``zero_grad()`` of this object instead of the optimiser's
+        ``zero_grad(set_to_none=True)``, which would drop the views (``start`` then falls back to packing)."""
+        self._views = []
+        for b, ps in enumerate(self.buckets):
+            n = sum(p.numel() for p in ps)
+            flat = self._flat[b] = torch.zeros(n, dtype=ps[0].dtype, device=ps[0].device)
+            o = 0
+            for p in ps:
+                k = p.numel()
+                v = flat[o:o + k].view_as(p)
+                if p.grad is not None:
+                    v.copy_(p.grad)
+                p.grad = v
+                self._views.append((p, v.data_ptr()))
+                o += k
+        return self
+
+    def zero_grad(self) -> None:
+        if not self._attached():
+            for p in self.params:
+                p.grad = None
+            return
+        for flat in self._flat:
+            flat.zero_()
+
+    def _attached(self) -> bool:
+        views = getattr(self, "_views", None)
+        return bool(views) and all(p.grad is not None and p.grad.data_ptr() == ptr for p, ptr in views)
+
     def start(self) -> None:
-        """Packs every bucket and launches its all-reduce (async)."""
+        """Launches every bucket's all-reduce (async); packs the buckets first unless the gradients already live there."""
         self._work = []
+        self._direct = False
         if self.world == 1:
             return
+        self._direct = self._attached()
         for b in range(len(self.buckets)):
-            flat = self._pack(b)
+            flat = self._flat[b] if self._direct else self._pack(b)
             self._work.append(dist.all_reduce(flat, group=self.group, async_op=True))
 
     def finish(self) -> None:
@@ -129,6 +164,12 @@ class GradBuckets:
         if self.world == 1:
             return
         inv = 1.0 / self.world
+        if self._direct:
+            for b, w in enumerate(self._work):
+                w.wait()
+                self._flat[b].mul_(inv)
+            self._work = []
+            return
         for b, w in enumerate(self._work):
             w.wait()
             flat = self._flat[b]

@@ -43,6 +43,14 @@ def _worker(rank, world, port, out):
         gb.allreduce()
         res["grads"] = [p.grad.clone() for p in net.parameters()]
         res["local"] = local
+        # 3b. attached mode: gradients live in the flat buckets; zero_grad + backward + all-reduce without packing
+        gb2 = shard.GradBuckets(net.parameters(), bucket_bytes=64).attach()
+        gb2.zero_grad()
+        net[2](net[1](net[0](x))).sum().backward()
+        assert gb2._attached()
+        gb2.allreduce()
+        assert gb2._direct
+        res["grads_attached"] = [p.grad.clone() for p in net.parameters()]
         # 4. timing: max over ranks
         res["tmax"] = shard.max_over_ranks([1.0 + rank, 5.0 - rank])
         out[rank] = res
@@ -72,6 +80,8 @@ def test_world2_gloo_host_logic():
         torch.testing.assert_close(g0, g1, rtol=0, atol=0)
         want = torch.zeros_like(g0) if a is None else (a + b) / 2
         torch.testing.assert_close(g0, want, rtol=1e-6, atol=1e-7)
+    for g0, ga in zip(r0["grads"], r0["grads_attached"]):          # attached mode gives the same rank mean
+        torch.testing.assert_close(ga, g0, rtol=1e-6, atol=1e-7)
     assert r0["tmax"] == r1["tmax"] == [2.0, 5.0]
 
 
