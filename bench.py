@@ -422,7 +422,9 @@ def measure_training(torch, dist, args, dev, rank, world, flush):
     meta = engine._host_meta(batch["box_labels"], batch["box_scores"], 49)
     params = [p for p in ih.parameters() if p.requires_grad]
     opt = torch.optim.SGD(params, lr=1e-4, momentum=0.9)
-    buckets = shard.GradBuckets(params).attach()      # gradients live in the flat buckets: no per-parameter pack / unpack
+    buckets = shard.GradBuckets(params)
+    if world > 1:
+        buckets.attach()      # gradients live in the flat buckets: no per-parameter pack / unpack around the all-reduce
 
     def step():
         buckets.zero_grad()
