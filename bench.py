@@ -366,6 +366,9 @@ def run_b200(args):
     train = None
     if not args.no_train:
         train = measure_training(torch, dist, args, dev, rank, world, flush)
+    kg = None
+    if rank == 0 and not args.no_train:
+        kg = measure_kg(torch, dev)
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         v, cores, sps = cpu_head_throughput(args, steps=20, warmup=1)
@@ -395,9 +398,53 @@ def run_b200(args):
         line.update(extra_roofs)
         if train is not None:
             line["training"] = train
+        if kg is not None:
+            line["kg_training"] = kg
         print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
+
+
+def measure_kg(torch, dev):
+    """BASELINE configs[3]: TransH embedding training on the HOI label graph (80 objects, 117 verbs) with negative sampling
+    -- the device sampler (skg_kg_sample, bit-exact with OpenKE's C++ sampler) inside Trainer.run, OpenKE defaults
+    (nbatches = 1, 25 negatives per positive, bern, dim 50, margin 4, SGD) -- and the sampler alone on a large batch."""
+    from skghoi_b200 import synthetic
+    from skghoi_b200.kg_data import KGIndex, TrainDataSampler
+    from skghoi_b200.kg_train import NegativeSamplingStrategy, TrainDataLoader, Trainer
+    from skghoi_b200.kge import MarginLoss, TransH
+    otv = synthetic.hico_object_to_verb()
+    h, t, r = [], [], []
+    for o in range(80):
+        for v in otv[o]:
+            h.append(49); r.append(int(v)); t.append(o)
+    idx = KGIndex(h, t, r, 80, 117, device=dev)
+    seeds = [12345 + 977 * i for i in range(8)]
+    loader = TrainDataLoader(idx, nbatches=1, neg_ent=25, bern_flag=True, threads=8, seeds=seeds)
+    model = TransH(80, 117, dim=50, p_norm=1, norm_flag=True).to(dev)
+    strat = NegativeSamplingStrategy(model, MarginLoss(margin=4.0), batch_size=loader.get_batch_size()).to(dev)
+    steps = 50
+    tr = Trainer(strat, loader, train_times=steps, alpha=0.5)
+    tr.run(); torch.cuda.synchronize(dev)                                   # warm-up epoch block
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(); hist = tr.run(); e1.record(); torch.cuda.synchronize(dev)
+    ms = e0.elapsed_time(e1) / steps
+    trip = loader.get_batch_size() * 26
+    bs = 1 << 16
+    smp = TrainDataSampler(idx, bs, 25, True, 8, seeds)
+    for _ in range(3):
+        smp.sample()
+    e0.record()
+    for _ in range(20):
+        smp.sample()
+    e1.record(); torch.cuda.synchronize(dev)
+    us = e0.elapsed_time(e1) / 20 * 1e3
+    return {"workload": "TransH KG embedding training on the HOI label graph (80 objects, 117 verbs, %d triples), %d positives x 25 "
+                        "negatives per step (BASELINE configs[3])" % (idx.train_total, loader.get_batch_size()),
+            "value": trip / (ms * 1e-3), "unit": "triples/s", "ms_per_step": ms, "steps": steps,
+            "step": "device negative sampling (skg_kg_sample) + TransH forward + margin loss + backward + SGD",
+            "loss_first_last": [float(hist[0]), float(hist[-1])],
+            "sampler_alone": {"batch": bs, "neg_rate": 25, "us_per_call": us, "triples_per_s": bs * 26 / (us * 1e-6)}}
 
 
 def measure_training(torch, dist, args, dev, rank, world, flush):
