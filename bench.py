@@ -18,6 +18,8 @@ JSON keys beyond the base contract:
              timed alone with CUDA events; spatial / transh hold the two bandwidth kernels;
   cpu_baseline  the CPU restatement of the reference head (oracle/head_oracle.py, kind "port")
              timed on this box's host cores on a bounded sample (rank 0, N = 1 only).
+  training   supplementary: one interaction-head training step (BASELINE configs[2]), data-parallel when N > 1;
+  kg_training  supplementary: TransH KG training on the HOI label graph with the device negative sampler (configs[3]).
 `--impl reference` times that CPU head alone (the reference is eager PyTorch; its own checkout is
 not on the GPU box, so the pinned op-for-op port stands in).
 """
