@@ -243,8 +243,20 @@ class MarginLoss(Loss):
             else:
                 raise RuntimeError("p_score %s does not broadcast against n_score %s"
                                    % (tuple(p_score.shape), tuple(n_score.shape)))
-        adv_t = float(self.adv_temperature) if self.adv_flag else 0.0
-        return _MarginLossFn.apply(p, n_score, float(self.margin), adv_t, self.adv_flag)
+        adv_t = self._scalar("adv_temperature") if self.adv_flag else 0.0
+        return _MarginLossFn.apply(p, n_score, self._scalar("margin"), adv_t, self.adv_flag)
+
+    def _scalar(self, name: str) -> float:
+        """Host value of a one-element hyper-parameter tensor.  Reading it off the device is a synchronisation per loss
+        call (and not allowed inside a CUDA-graph capture): read once, re-read only when the tensor was replaced or
+        written in place (load_state_dict, .to(...))."""
+        t = getattr(self, name)
+        key = (t.data_ptr(), t._version)
+        cache = self.__dict__.setdefault("_scalar_cache", {})
+        hit = cache.get(name)
+        if hit is None or hit[0] != key:
+            hit = cache[name] = (key, float(t))
+        return hit[1]
 
     def predict(self, p_score, n_score):
         return self.forward(p_score, n_score).cpu().data.numpy()

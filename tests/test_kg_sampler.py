@@ -159,3 +159,37 @@ def test_kg_training_loop_first_loss_vs_oracle_and_descent():
     assert abs(float(got) - float(want)) <= 1e-4 * max(1.0, abs(float(want))), (float(got), float(want))
     hist = Trainer(strat, loader, train_times=30, alpha=0.5, opt_method="sgd").run()
     assert hist[-1] < 0.7 * hist[0], hist[::6]
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("nb", [1, 4])
+def test_kg_trainer_graph_replay_equals_eager_loop(nb):
+    """Trainer(graph=True) replays whole epochs (device sampler + forward + loss + backward + SGD) as one CUDA graph:
+    same batches (the seed ping-pong returns to its start inside a graph), same losses, same final embeddings and
+    sampler seeds as the eager loop -- odd and even batches per epoch, with an eager remainder."""
+    from skghoi_b200.kg_data import KGIndex
+    from skghoi_b200.kg_train import NegativeSamplingStrategy, TrainDataLoader, Trainer
+    from skghoi_b200.kge import MarginLoss, TransH
+    h, t, r = MG.graph()
+    idx = KGIndex(h, t, r, 80, 117, device="cuda:0")
+
+    def run(graph):
+        loader = TrainDataLoader(idx, nbatches=nb, neg_ent=5, bern_flag=True, threads=4, seeds=MG.seeds_for(4))
+        torch.manual_seed(0)
+        model = TransH(80, 117, dim=50, p_norm=1, norm_flag=True).to("cuda:0")
+        strat = NegativeSamplingStrategy(model, MarginLoss(margin=4.0), batch_size=loader.get_batch_size()).to("cuda:0")
+        hist = Trainer(strat, loader, train_times=11, alpha=0.5, opt_method="sgd", graph=graph).run()
+        return hist, model.ent_embeddings.weight.detach().cpu().clone(), loader.sampler.seeds()
+
+    eager, graphed = run(False), run(True)
+    assert len(graphed[0]) == len(eager[0]) == 11
+    assert graphed[2] == eager[2]                         # identical sampler state: the very same batches were drawn
+    # one step per epoch: graph and eager agree to the last bits.  Four steps per epoch (44 updates): the TransH backward
+    # accumulates with fp32 atomics whose order varies, the L1 score's sign gradients amplify that, and two EAGER runs
+    # already differ by ~1e-2 in the losses and ~2e-2 in the embeddings (tools/kg_graph_vs_eager.py) -- same spread here
+    if nb == 1:
+        torch.testing.assert_close(torch.tensor(graphed[0]), torch.tensor(eager[0]), rtol=0, atol=1e-4)
+        torch.testing.assert_close(graphed[1], eager[1], rtol=0, atol=1e-4)
+    else:
+        torch.testing.assert_close(torch.tensor(graphed[0]), torch.tensor(eager[0]), rtol=5e-2, atol=1e-2)
+        torch.testing.assert_close(graphed[1], eager[1], rtol=0, atol=1e-1)
