@@ -72,21 +72,35 @@ def workload_config(args, extra=None):
 # ------------------------------------------------------------------------------------------------
 # CPU reference arm / cpu_baseline  (the only place outside tests/ and smoke() that executes oracle/)
 # ------------------------------------------------------------------------------------------------
-def cpu_head_throughput(args, steps, warmup):
-    """Times the reference head's CPU restatement (reference-faithful per-row entity loop) on the
-    host cores; one step = ONE image of the workload (bounded sample).  Returns (pairs/s, cores, s/step)."""
+def _oracle_inputs(args, images, device=None):
     import torch
-    from oracle import head_oracle as O
     from skghoi_b200 import synthetic
     from skghoi_b200.head import build_interaction_head
-    cores = len(os.sched_getaffinity(0))
-    torch.set_num_threads(cores)
     otv = synthetic.hico_object_to_verb()
     ih = build_interaction_head(otv, seed=42)
     P = {k: v.detach().clone() for k, v in ih.state_dict().items()}
     tables = synthetic.make_transh_tables(42)
-    batch = synthetic.make_batch([(args.humans, args.boxes)], seed=42)
-    pairs = args.humans * (args.boxes - 1)
+    batch = synthetic.make_batch([(args.humans, args.boxes)] * images, seed=42)
+    if device is not None:
+        P = {k: v.to(device) for k, v in P.items()}
+        tables = tuple(t.to(device) for t in tables)
+        batch = dict(batch, features={k: v.to(device) for k, v in batch["features"].items()},
+                     box_features=batch["box_features"].to(device), box_coords=[b.to(device) for b in batch["box_coords"]],
+                     box_labels=[l.to(device) for l in batch["box_labels"]], box_scores=[x.to(device) for x in batch["box_scores"]])
+    return P, tables, batch, otv
+
+
+def cpu_head_throughput(args, steps, warmup, images=1, threads=None, budget_s=None):
+    """Times the reference head's CPU restatement (reference-faithful per-row entity loop, head.py:877-883) on the host
+    cores; one step = ``images`` images of the workload.  ``budget_s`` caps the timed steps so that the run ends in time
+    (the first timed step sizes the rest).  Returns (pairs/s, threads, s/step, timed steps)."""
+    import torch
+    from oracle import head_oracle as O
+    cores = len(os.sched_getaffinity(0))
+    threads = cores if threads is None else threads
+    torch.set_num_threads(threads)
+    P, tables, batch, otv = _oracle_inputs(args, images)
+    pairs = images * args.humans * (args.boxes - 1)
 
     def step():
         with torch.no_grad():
@@ -96,21 +110,30 @@ def cpu_head_throughput(args, steps, warmup):
     for _ in range(warmup):
         step()
     t0 = time.perf_counter()
-    for _ in range(steps):
-        step()
+    done = 0
+    while done < steps:
+        step(); done += 1
+        if budget_s is not None and done < steps:
+            per = (time.perf_counter() - t0) / done
+            if per * (done + 1) > budget_s:
+                break
     dt = time.perf_counter() - t0
-    return pairs * steps / dt, cores, dt / steps
+    torch.set_num_threads(cores)
+    return pairs * done / dt, threads, dt / done, done
 
 
 def run_reference(args):
+    """`--impl reference`: the reference head's own CPU implementation (pinned op-for-op port; the reference checkout is
+    not on the GPU box and needs mmcv / mmdet / pocket) on the SAME batch as the b200 arm -- all `--images` images per step,
+    all host threads, the requested warm-up and step counts (steps are cut only if the run would pass ~4 minutes)."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    steps = max(1, min(args.steps, 40)); warmup = max(1, min(args.warmup, 2))
-    v, cores, sps = cpu_head_throughput(args, steps, warmup)
-    sample = "1 image (%d humans x %d boxes = %d pairs) per step, %d timed steps, fp32 torch CPU, %d threads" % (
-        args.humans, args.boxes, args.humans * (args.boxes - 1), steps, cores)
-    line = {"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": steps,
+    steps = max(1, args.steps); warmup = max(0, args.warmup)
+    v, cores, sps, done = cpu_head_throughput(args, steps, warmup, images=args.images, budget_s=200.0)
+    sample = "%d images (%d humans x %d boxes, %d pairs) per step, %d timed steps after %d warm-up, fp32 torch CPU, %d threads" % (
+        args.images, args.humans, args.boxes, args.images * args.humans * (args.boxes - 1), done, warmup, cores)
+    line = {"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": done,
             "warmup": warmup, "ms_per_step": sps * 1e3, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": workload_config(args, {"sample": sample}),
@@ -118,6 +141,41 @@ def run_reference(args):
             "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
     print(json.dumps(line))
+
+
+def gpu_eager_baseline(args, dev):
+    """SURVEY 8(d) / BASELINE.md 2(i): the reference head as stock eager PyTorch on the SAME B200 -- the op-for-op port
+    (oracle/head_oracle.py, 16 branch Linears per MBF, 117*N2 materialised TransH triples, per-image Python loop with
+    its device->host syncs) with its tensors on cuda:0.  fp32 (TF32 off, the PyTorch default for matmul) and TF32 on;
+    the per-row entity pick as the reference's Python loop (head.py:877-883) and as the equivalent strided slice."""
+    import torch
+    from oracle import head_oracle as O
+    P, tables, batch, otv = _oracle_inputs(args, args.images, device=dev)
+    pairs = args.images * args.humans * (args.boxes - 1)
+    out = {"workload": "same batch as `value` (%d images x (%d, %d)), reference head as eager PyTorch on cuda:0 (oracle port), "
+                       "device-resident inputs, wall clock with synchronize" % (args.images, args.humans, args.boxes),
+           "unit": UNIT}
+    old = (torch.backends.cuda.matmul.allow_tf32, torch.backends.cudnn.allow_tf32)
+    try:
+        for name, tf32, pick, steps in (("fp32_slice", False, "slice", 5), ("tf32_slice", True, "slice", 5),
+                                        ("fp32_loop", False, "loop", 2)):
+            torch.backends.cuda.matmul.allow_tf32 = tf32; torch.backends.cudnn.allow_tf32 = tf32
+
+            def step():
+                with torch.no_grad():
+                    O.interaction_head_forward(P, tables, batch["features"]["3"], batch["image_shapes"], batch["box_features"],
+                                               batch["box_coords"], batch["box_labels"], batch["box_scores"], otv, row_pick=pick)
+            step(); torch.cuda.synchronize(dev)
+            t0 = time.perf_counter()
+            for _ in range(steps):
+                step()
+            torch.cuda.synchronize(dev)
+            dt = (time.perf_counter() - t0) / steps
+            out[name] = {"value": pairs / dt, "ms_per_step": dt * 1e3, "steps": steps,
+                         "row_pick": "python loop over 117*N2 rows (head.py:877-883)" if pick == "loop" else "[::117] slice (same values)"}
+    finally:
+        torch.backends.cuda.matmul.allow_tf32, torch.backends.cudnn.allow_tf32 = old
+    return out
 
 
 # ------------------------------------------------------------------------------------------------
@@ -369,14 +427,18 @@ def run_b200(args):
     if not args.no_train:
         train = measure_training(torch, dist, args, dev, rank, world, flush)
     kg = None
-    if rank == 0 and not args.no_train:
-        kg = measure_kg(torch, dev)
+    if not args.no_train:
+        kg = measure_kg(torch, dist, dev, rank, world)
     cpu = None
+    gpu_eager = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        v, cores, sps = cpu_head_throughput(args, steps=20, warmup=1)
+        gpu_eager = gpu_eager_baseline(args, dev)
+        v, cores, sps, done = cpu_head_throughput(args, steps=10, warmup=1, images=args.images, budget_s=15.0)
+        v1, _, sps1, done1 = cpu_head_throughput(args, steps=3, warmup=1, images=1, threads=1, budget_s=8.0)
         cpu = {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
-               "sample": "oracle/head_oracle.py (op-for-op fp32 restatement of the reference head), 20 steps of 1 image "
-                         "(%d pairs) each, %.3f s/step" % (args.humans * (args.boxes - 1), sps)}
+               "sample": "oracle/head_oracle.py (op-for-op fp32 restatement of the reference head), %d steps of the whole "
+                         "%d-image batch (%d pairs) each, %.3f s/step" % (done, args.images, args.images * args.humans * (args.boxes - 1), sps),
+               "single_thread": {"value": v1, "cores": 1, "sample": "%d steps of 1 image, %.3f s/step" % (done1, sps1)}}
     if rank == 0 and roof is not None:
         tp = os.path.join(ROOT, "profiles", "ncu_traffic.json")
         if os.path.isfile(tp):
@@ -402,16 +464,20 @@ def run_b200(args):
             line["training"] = train
         if kg is not None:
             line["kg_training"] = kg
+        if gpu_eager is not None:
+            line["gpu_eager_baseline"] = gpu_eager
         print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
 
 
-def measure_kg(torch, dev):
+def measure_kg(torch, dist, dev, rank, world):
     """BASELINE configs[3]: TransH embedding training on the HOI label graph (80 objects, 117 verbs) with negative sampling
     -- the device sampler (skg_kg_sample, bit-exact with OpenKE's C++ sampler) inside Trainer.run, OpenKE defaults
-    (nbatches = 1, 25 negatives per positive, bern, dim 50, margin 4, SGD) -- and the sampler alone on a large batch."""
-    from skghoi_b200 import synthetic
+    (nbatches = 1, 25 negatives per positive, bern, dim 50, margin 4, SGD) -- and the sampler alone on a large batch.
+    N > 1: the triple batch is sharded over the ranks (same global batch on every rank, each scores its slice, ONE
+    62.8 KB all-reduce of the table gradients per step): "strong" scaling of a fixed global batch."""
+    from skghoi_b200 import shard, synthetic
     from skghoi_b200.kg_data import KGIndex, TrainDataSampler
     from skghoi_b200.kg_train import NegativeSamplingStrategy, TrainDataLoader, Trainer
     from skghoi_b200.kge import MarginLoss, TransH
@@ -423,19 +489,36 @@ def measure_kg(torch, dev):
     idx = KGIndex(h, t, r, 80, 117, device=dev)
     seeds = [12345 + 977 * i for i in range(8)]
     loader = TrainDataLoader(idx, nbatches=1, neg_ent=25, bern_flag=True, threads=8, seeds=seeds)
+    torch.manual_seed(7)                                                    # identical initial tables on every rank
     model = TransH(80, 117, dim=50, p_norm=1, norm_flag=True).to(dev)
     strat = NegativeSamplingStrategy(model, MarginLoss(margin=4.0), batch_size=loader.get_batch_size()).to(dev)
     steps = 50
-    tr = Trainer(strat, loader, train_times=steps, alpha=0.5)
+    tr = Trainer(strat, loader, train_times=steps, alpha=0.5, distributed=world > 1)
     tr.run(); torch.cuda.synchronize(dev)                                   # warm-up epoch block
+    if world > 1:
+        dist.barrier()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record(); hist = tr.run(); e1.record(); torch.cuda.synchronize(dev)
-    ms = e0.elapsed_time(e1) / steps
+    ms = shard.max_over_ranks([e0.elapsed_time(e1) / steps], device=dev)[0]
+    trip = loader.get_batch_size() * 26
+    # algorithmic bytes per triple of one step: sampler writes 3 int64 + 1 fp32 (28 B), the scorer reads the 3 indices (24 B)
+    # and writes the score (4 B), its backward re-reads them (24 B) and scatters 4 table-row gradients of 50 fp32 (800 B)
+    bytes_per_triple = 28 + 28 + 24 + 800
+    out = {"workload": "TransH KG embedding training on the HOI label graph (80 objects, 117 verbs, %d triples), %d positives x 25 "
+                       "negatives per step (BASELINE configs[3])" % (idx.train_total, loader.get_batch_size()),
+           "value": trip / (ms * 1e-3), "unit": "triples/s", "ms_per_step": ms, "steps": steps, "n_gpus": world,
+           "scaling": "strong (fixed global batch, triple batch sharded over ranks, tables replicated)" if world > 1 else "single GPU",
+           "step": "device negative sampling (skg_kg_sample) + TransH forward + margin loss + backward + %sSGD"
+                   % ("one all-reduce of the table gradients (62.8 KB) + " if world > 1 else ""),
+           "loss_first_last": [float(hist[0]), float(hist[-1])],
+           "roofline": {"bound": "hbm (nominal: the step is launch-latency bound, ~25 launches for < 20 MB of traffic)",
+                        "bytes_per_triple": bytes_per_triple, "achieved": trip * bytes_per_triple / (ms * 1e-3) / 1e9, "unit": "GB/s"}}
+    if world > 1:
+        return out if rank == 0 else None
     # the same loop with whole epochs replayed as one CUDA graph (Trainer(graph=True)): capture cost included
-    trg = Trainer(strat, loader, train_times=500, alpha=0.5, optimizer=tr.optimizer, graph=True)
+    trg = Trainer(strat, loader, train_times=500, alpha=0.5, optimizer=tr.optimizer, graph=True, distributed=False)
     torch.cuda.synchronize(dev); t0 = time.perf_counter(); hist_g = trg.run(); torch.cuda.synchronize(dev)
     ms_g = (time.perf_counter() - t0) / 500 * 1e3
-    trip = loader.get_batch_size() * 26
     bs = 1 << 16
     smp = TrainDataSampler(idx, bs, 25, True, 8, seeds)
     for _ in range(3):
@@ -445,14 +528,10 @@ def measure_kg(torch, dev):
         smp.sample()
     e1.record(); torch.cuda.synchronize(dev)
     us = e0.elapsed_time(e1) / 20 * 1e3
-    return {"workload": "TransH KG embedding training on the HOI label graph (80 objects, 117 verbs, %d triples), %d positives x 25 "
-                        "negatives per step (BASELINE configs[3])" % (idx.train_total, loader.get_batch_size()),
-            "value": trip / (ms * 1e-3), "unit": "triples/s", "ms_per_step": ms, "steps": steps,
-            "step": "device negative sampling (skg_kg_sample) + TransH forward + margin loss + backward + SGD",
-            "loss_first_last": [float(hist[0]), float(hist[-1])],
-            "graph_replay": {"ms_per_step": ms_g, "value": trip / (ms_g * 1e-3), "steps": 500, "loss_last": float(hist_g[-1]),
-                             "note": "Trainer(graph=True): two steps per CUDA graph, wall clock incl. warm-up steps and capture"},
-            "sampler_alone": {"batch": bs, "neg_rate": 25, "us_per_call": us, "triples_per_s": bs * 26 / (us * 1e-6)}}
+    out["graph_replay"] = {"ms_per_step": ms_g, "value": trip / (ms_g * 1e-3), "steps": 500, "loss_last": float(hist_g[-1]),
+                           "note": "Trainer(graph=True): two steps per CUDA graph, wall clock incl. warm-up steps and capture"}
+    out["sampler_alone"] = {"batch": bs, "neg_rate": 25, "us_per_call": us, "triples_per_s": bs * 26 / (us * 1e-6)}
+    return out
 
 
 def measure_training(torch, dist, args, dev, rank, world, flush):

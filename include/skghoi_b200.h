@@ -173,6 +173,11 @@ int skg_node_prep(const float* ent, int ent_dim, int ent_tot, const int32_t* box
                   const int32_t* hum_off, int num_images, int total_boxes, void* o_in, int ld, int enc_dim,
                   int32_t* box2hum, cudaStream_t stream);
 
+/* bias_out[r] = bias_in[r] + sum_k W_ent[r, k] * ent[entity, k]  (r < rows): the constant contribution of the human side's
+ * entity columns of fc_head (head.py:571, 877-884: head_stack == E[human_idx] for every row). */
+int skg_fc_bias_fold(const float* bias_in, const float* W_ent, const float* ent, int ent_dim, int entity, int rows,
+                     float* bias_out, cudaStream_t stream);
+
 /* avg_pool(features['3']).flatten(1) (head.py:811): planes = B*C, hw = H*W. */
 int skg_global_pool(const float* features, int64_t planes, int hw, void* out_bf16, float* out_f32,
                     cudaStream_t stream);
@@ -290,6 +295,10 @@ typedef struct skg_head_weights {
   const void* Wpred; const float* bpred;      /* [n_logit_pad, 2R] predictor rows then the suppressor row (models.py:176-177) */
   const void* Wpred_hh; const void* Wpred_lo; /* split-bf16 predictor operands ([hi | hi] and lo), NULL -> single bf16 pass */
   const float* ent;                           /* TransH entity table [ent_tot, ent_dim] (head.py:574-578) */
+  const float* Wfh_ent;                       /* fc_head.0.weight[:, E:] fp32 [R, ent_dim]: when set, every forward re-folds
+                                                 bfc[:R] = bfh[:R] + Wfh_ent @ ent[human_idx] ON THE DEVICE (bfc is then
+                                                 written by the library), so the constant human-side entity term follows the
+                                                 table's current contents -- also under CUDA-graph replay */
 } skg_head_weights;
 
 typedef struct skg_head_batch {

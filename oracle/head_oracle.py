@@ -10,7 +10,8 @@ pinned against outputs of the UNMODIFIED reference executed in the build contain
 (``oracle/ref_harness.py`` -> ``tests/golden/make_golden.py`` -> ``tests/golden/*.pt``), and
 ``tests/test_oracle_vs_golden.py`` re-checks it against those fixtures on every run.
 
-Everything is plain fp32 ``torch`` on the CPU, written op-for-op in the order the reference executes
+Everything is plain fp32 ``torch`` (on the CPU in the tests; tensor constructors follow the inputs' device so that
+bench.py's ``gpu_eager_baseline`` leg can time the very same eager code on ``cuda:0``), written op-for-op in the order the reference executes
 (16 separate branch Linears per MBF, 117*N2 materialised TransH triples, the per-row entity pick),
 so that timing it is an honest stand-in for the reference's own CPU head.  Each function cites the
 reference file:line it restates (paths relative to the reference root; ``head.py`` abbreviates
@@ -144,7 +145,7 @@ def transh_forward(ent: Tensor, rel: Tensor, nrm: Tensor, head: Tensor, relation
 def margin_loss(p_score: Tensor, n_score: Tensor, margin: float = 6.0,
                 adv_temperature: Optional[float] = None) -> Tensor:
     """MarginLoss.py:28-36."""
-    m = torch.tensor([margin], dtype=p_score.dtype)
+    m = torch.tensor([margin], dtype=p_score.dtype, device=p_score.device)
     if adv_temperature is not None:
         wgt = F.softmax(-n_score * adv_temperature, dim=-1).detach()
         return (wgt * torch.max(p_score - n_score, -m)).sum(dim=-1).mean() + m
@@ -199,7 +200,7 @@ def message_mbf_forward(P: Dict[str, Tensor], prefix: str, node_type: str, appea
 def associate_with_ground_truth(boxes_h: Tensor, boxes_o: Tensor, target: dict, num_cls: int,
                                 fg_iou_thresh: float = 0.5) -> Tensor:
     """head.py:703-719."""
-    labels = torch.zeros(boxes_h.shape[0], num_cls)
+    labels = torch.zeros(boxes_h.shape[0], num_cls, device=boxes_h.device)
     x, y = torch.nonzero(torch.min(box_iou_matrix(boxes_h, target["boxes_h"]),
                                    box_iou_matrix(boxes_o, target["boxes_o"])) >= fg_iou_thresh).unbind(1)
     labels[x, target["labels"][y]] = 1
@@ -209,7 +210,7 @@ def associate_with_ground_truth(boxes_h: Tensor, boxes_o: Tensor, target: dict, 
 def compute_prior_scores(x: Tensor, y: Tensor, scores: Tensor, object_class: Tensor,
                          object_to_verb: List[list], num_cls: int, training: bool) -> Tensor:
     """head.py:721-767."""
-    prior_h = torch.zeros(len(x), num_cls)
+    prior_h = torch.zeros(len(x), num_cls, device=scores.device)
     prior_o = torch.zeros_like(prior_h)
     p = 1.0 if training else 2.8
     s_h = scores[x].pow(p); s_o = scores[y].pow(p)
@@ -253,16 +254,18 @@ def graph_head_forward(P: Dict[str, Tensor], tables: Tuple[Tensor, Tensor, Tenso
         n = len(coords)
         n_h = int(torch.sum(labels == human_idx))
         if n_h == 0 or n <= 1:                                                # head.py:829-839
-            out["feat"].append(torch.zeros(0, 2048)); out["boxes_h"].append(torch.zeros(0, 4))
-            out["boxes_o"].append(torch.zeros(0, 4)); out["obj"].append(torch.zeros(0, dtype=torch.int64))
-            out["prior"].append(torch.zeros(2, 0, num_cls)); out["labels"].append(torch.zeros(0, num_cls))
+            dv = bf.device
+            out["feat"].append(torch.zeros(0, 2048, device=dv)); out["boxes_h"].append(torch.zeros(0, 4, device=dv))
+            out["boxes_o"].append(torch.zeros(0, 4, device=dv)); out["obj"].append(torch.zeros(0, dtype=torch.int64, device=dv))
+            out["prior"].append(torch.zeros(2, 0, num_cls, device=dv)); out["labels"].append(torch.zeros(0, num_cls, device=dv))
             counter += n
             continue
         if not torch.all(labels[:n_h] == human_idx):
             raise ValueError("Human detections are not permuted to the top")  # head.py:840-841
         node_enc = bf[counter: counter + n]
         h_node_enc = node_enc[:n_h]
-        x, y = torch.meshgrid(torch.arange(n_h), torch.arange(n), indexing="ij")   # head.py:847-850
+        dv = coords.device
+        x, y = torch.meshgrid(torch.arange(n_h, device=dv), torch.arange(n, device=dv), indexing="ij")   # head.py:847-850
         x_keep, y_keep = torch.nonzero(x != y).unbind(1)                      # head.py:852
         if len(x_keep) == 0:
             raise ValueError("There are no valid human-object pairs")
@@ -272,8 +275,8 @@ def graph_head_forward(P: Dict[str, Tensor], tables: Tuple[Tensor, Tensor, Tenso
             sp46 = torch.nan_to_num(sp46)
         # transH_head.forward head.py:570-580
         N2 = len(x)
-        relations = torch.arange(num_cls).repeat(N2)
-        heads = torch.full((N2 * num_cls,), human_idx, dtype=torch.int64)
+        relations = torch.arange(num_cls, device=dv).repeat(N2)
+        heads = torch.full((N2 * num_cls,), human_idx, dtype=torch.int64, device=dv)
         tails = y.repeat_interleave(num_cls)
         th, tr, tw, tt, tscore = transh_forward(ent, rel, nrm, heads, relations, tails, 2, True)
         if row_pick == "loop":                                                # head.py:875-883
@@ -290,7 +293,7 @@ def graph_head_forward(P: Dict[str, Tensor], tables: Tuple[Tensor, Tensor, Tenso
         for l in (0, 2, 4):                                                   # head.py:662-669, 888
             sp = F.relu(_linear(P, f"{pf}.spatial_head.{l}", sp))
         sp_r = sp.reshape(n_h, n, -1)
-        adj = torch.ones(n_h, n)
+        adj = torch.ones(n_h, n, device=dv)
         for _ in range(num_iter):                                             # head.py:892-925
             app = torch.cat([g_h, g_o], 1)
             weights = mbf_forward(P, f"{pf}.attention_head", app, sp)

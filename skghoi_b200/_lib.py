@@ -32,6 +32,7 @@ _SIGNATURES = {
     "skg_spatial_fc1": (I, [P, P, P, L, I, I, P, P]),
     "skg_node_inputs": (I, [P, I, P, I, I, I, P, P, I, I, I, P, P, I, P]),
     "skg_global_pool": (I, [P, L, I, P, P, P]),
+    "skg_fc_bias_fold": (I, [P, P, P, I, I, I, P, P]),
     "skg_node_prep": (I, [P, I, I, P, P, P, I, I, P, I, I, P, P]),
     "skg_message_aggregate": (I, [P, I, F, P, P, L, P, P, P, I, I, I, I, I, P, P, P, P]),
     "skg_layernorm": (I, [P, L, L, I, P, P, P, P, F, P, P, P]),
@@ -214,7 +215,7 @@ class HeadWeights(ctypes.Structure):
         ("w_adj", c_void_p), ("b_adj", c_float),
         ("ln_h_w", c_void_p), ("ln_h_b", c_void_p), ("ln_o_w", c_void_p), ("ln_o_b", c_void_p), ("ln_eps", c_float),
         ("Wpred", c_void_p), ("bpred", c_void_p), ("Wpred_hh", c_void_p), ("Wpred_lo", c_void_p),
-        ("ent", c_void_p)]
+        ("ent", c_void_p), ("Wfh_ent", c_void_p)]
 
 
 class HeadBatch(ctypes.Structure):

@@ -296,6 +296,10 @@ static int enqueue_forward(const skg_head_weights* wp, const skg_head_batch* bp,
   // ---- sa: box head (head.py:635-641, 812); its second layer writes straight into the fc input rows
   SKG_TRY(skg_node_prep(w.ent, w.ent_dim, w.ent_tot, b.box_off, b.n_h, b.hum_off, B, NB, H(B_OIN), w.fc_k, E, I32(B_BOX2HUM), sa));
   MARK("node_prep", sa);
+  if (w.Wfh_ent) {   // constant human-side entity term of fc_head, re-folded from the table's CURRENT contents
+    SKG_TRY(skg_fc_bias_fold(w.bfh, w.Wfh_ent, w.ent, w.ent_dim, w.human_idx, R, const_cast<float*>(w.bfc), sa));
+    MARK("fc_bias_fold", sa);
+  }
   const void* xb = b.box_features_bf16;            // pooled features already in operand layout (native RoIAlign)
   if (!xb) {
     SKG_TRY(skg_cast_pad_bf16(b.box_features, w.pool_k, nullptr, 0, NB, w.pool_k, H(B_XB), w.K0, w.K0, sa));

@@ -117,6 +117,18 @@ __global__ void node_prep_kernel(const float* __restrict__ ent, int ent_dim, int
   if (threadIdx.x == 0 && box2hum) box2hum[row] = idx < __ldg(n_h + lo) ? __ldg(hum_off + lo) + idx : -1;
 }
 
+// bias_out[r] = bias_in[r] + W_ent[r, :] . ent[entity, :]   (one warp per row)
+__global__ void fc_bias_fold_kernel(const float* __restrict__ bias_in, const float* __restrict__ W_ent, const float* __restrict__ ent,
+                                    int ent_dim, int entity, int rows, float* __restrict__ bias_out) {
+  const int lane = threadIdx.x & 31;
+  const int row = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  if (row >= rows) return;
+  float s = 0.f;
+  for (int k = lane; k < ent_dim; k += 32) s = fmaf(__ldg(W_ent + (int64_t)row * ent_dim + k), __ldg(ent + (int64_t)entity * ent_dim + k), s);
+  s = warp_sum(s);
+  if (lane == 0) bias_out[row] = __ldg(bias_in + row) + s;
+}
+
 // global_features = avg_pool(features['3']).flatten(1) (head.py:811): one warp per (image, channel)
 __global__ void global_pool_kernel(const float* __restrict__ f, int64_t planes, int hw, __nv_bfloat16* __restrict__ out_bf16,
                                    float* __restrict__ out_f32) {
@@ -372,6 +384,14 @@ extern "C" int skg_node_prep(const float* ent, int ent_dim, int ent_tot, const i
   node_prep_kernel<<<total_boxes, 64, 0, stream>>>(ent, ent_dim, ent_tot, box_off, n_h, hum_off, num_images,
                                                    (__nv_bfloat16*)o_in, ld, enc_dim, box2hum);
   return check_launch("node_prep_kernel");
+}
+
+extern "C" int skg_fc_bias_fold(const float* bias_in, const float* W_ent, const float* ent, int ent_dim, int entity, int rows,
+                                float* bias_out, cudaStream_t stream) {
+  if (rows == 0) return SKG_OK;
+  SKG_REQUIRE(bias_in && W_ent && ent && bias_out && ent_dim > 0 && entity >= 0, "bad fc_bias_fold arguments");
+  fc_bias_fold_kernel<<<ceil_div(rows * 32, 256), 256, 0, stream>>>(bias_in, W_ent, ent, ent_dim, entity, rows, bias_out);
+  return check_launch("fc_bias_fold_kernel");
 }
 
 extern "C" int skg_global_pool(const float* features, int64_t planes, int hw, void* out_bf16, float* out_f32,

@@ -143,14 +143,24 @@ def _version_sum(params) -> int:
 
 
 class PackedMBF:
-    """Concatenated-branch bf16 operands of one MultiBranchFusion / MessageMBF (head.py:446-474)."""
+    """Concatenated-branch bf16 operands of one MultiBranchFusion / MessageMBF (head.py:446-474).  The representation
+    width is padded to a multiple of the narrowest GEMM N tile (128) with zero rows / columns, so any cardinality x
+    sub-width product is accepted (the reference only asks that the width divide by the cardinality, head.py:455-458)."""
 
     def __init__(self, mbf):
-        W1, b1, W2, b2, W3, b3 = mbf.packed()
+        W1, b1, W2, b2, W3, b3 = (t.detach().float() for t in mbf.packed())
+        R = W3.shape[0]
+        Rp = (R + 127) // 128 * 128
+        if Rp != R:
+            z = lambda rows, cols: torch.zeros(rows, cols, dtype=torch.float32, device=W1.device)   # noqa: E731
+            W1 = torch.cat([W1, z(Rp - R, W1.shape[1])]); W2 = torch.cat([W2, z(Rp - R, W2.shape[1])])
+            W3p = z(Rp, Rp); W3p[:R, :R] = W3; W3 = W3p
+            pad = torch.zeros(Rp - R, dtype=torch.float32, device=W1.device)
+            b1, b2, b3 = torch.cat([b1, pad]), torch.cat([b2, pad]), torch.cat([b3, pad])
         self.W1, self.b1 = _bf16(W1, pad_k=8), _f32(b1)
         self.W2, self.b2 = _bf16(W2, pad_k=8), _f32(b2)
         self.W3, self.b3 = _bf16(W3), _f32(b3)
-        self.R = W3.shape[0]
+        self.R, self.Rp = R, Rp
         self.key = _versions(mbf)
 
 
@@ -181,19 +191,17 @@ def _mbf_apply(mbf, appearance: Tensor, spatial: Tensor, row_p: Optional[Tensor]
     _lib.require_cuda(appearance, spatial)
     pk = _packed_mbf(mbf)
     dev = spatial.device
-    R = pk.R
-    if R % 128 or pk.W2.shape[1] % 8:
-        raise _lib.SkgError("representation_size must be a multiple of 128 for the tensor-core path")
+    R, Rp = pk.R, pk.Rp
     a16 = _to_bf16_operand(appearance)
     s16 = _to_bf16_operand(spatial)
-    a1 = torch.empty(a16.shape[0], R, dtype=torch.float32, device=dev)
+    a1 = torch.empty(a16.shape[0], Rp, dtype=torch.float32, device=dev)
     _lib.gemm_bf16(a16, pk.W1, [_lib.epilogue_group(bias=pk.b1, out_f32=a1)], K=pk.W1.shape[1])
-    H = torch.empty(rows, R, dtype=torch.bfloat16, device=dev)
+    H = torch.empty(rows, Rp, dtype=torch.bfloat16, device=dev)
     _lib.gemm_bf16(s16, pk.W2, [_lib.epilogue_group(relu=True, bias=pk.b2, mul_p=a1, row_p=row_p, out_bf16=H)],
                    K=pk.W2.shape[1])
-    out = torch.empty(rows, R, dtype=torch.float32, device=dev)
+    out = torch.empty(rows, Rp, dtype=torch.float32, device=dev)
     _lib.gemm_bf16(H, pk.W3, [_lib.epilogue_group(relu=mbf._outer_relu, bias=pk.b3, out_f32=out)])
-    return out
+    return out if Rp == R else out[:, :R].contiguous()
 
 
 def mbf_forward(mbf, appearance: Tensor, spatial: Tensor) -> Tensor:
@@ -247,13 +255,13 @@ class PackedHead:
         self.Wft, self.bft = _bf16(G.fc_tail[0].weight, pad_k=64), _f32(G.fc_tail[0].bias)
         self.fc_k = self.Wfh.shape[1]
         # fused fc_head | fc_tail over all boxes: the human side's entity columns multiply the CONSTANT row E[human_idx]
-        # (head.py:571, 877-882), so they are zeroed here and folded into the bias by ``fc_bias`` below
+        # (head.py:571, 877-882), so they are zeroed here and folded into bfc[:R] on the DEVICE by every forward
+        # (skg_fc_bias_fold inside skg_head_forward: no host-side change detection, also right under graph replay)
         Wfh_node = G.fc_head[0].weight.detach().float().clone()
         self.Wfh_ent = Wfh_node[:, E:].clone().contiguous()          # [R, transh_dim] fp32
         Wfh_node[:, E:] = 0
         self.Wfc = _bf16(torch.cat([Wfh_node, G.fc_tail[0].weight.detach().float()], 0), pad_k=64)
         self.bfc = torch.cat([self.bfh, self.bft]).contiguous()
-        self.ent_key = None
         att = G.attention_head.packed(); os_ = G.obj_to_sub.packed(); so = G.sub_to_obj.packed()
         gg = G.attention_head_g.packed()
         z = torch.zeros(R, device=dev)
@@ -283,13 +291,6 @@ class PackedHead:
         self.Wpred_lo = _bf16(lo.float(), pad_rows=128)                                 # [128, 2R]   against hi
         self.cw = self._c_struct(G)
 
-    def fc_bias(self, ent: Tensor, human_idx: int) -> None:
-        """bfc[:R] = fc_head bias + W_head[:, E:] @ E[human_idx]; refreshed only when the TransH entity table changes."""
-        key = (ent.data_ptr(), ent._version)
-        if key != self.ent_key:
-            self.bfc[:self.R] = self.bfh[:self.R] + self.Wfh_ent @ ent[human_idx].float()
-            self.ent_key = key
-
     def _c_struct(self, G):
         """skg_head_weights: raw device pointers of the packed operands (this object keeps them alive)."""
         w = _lib.HeadWeights()
@@ -299,7 +300,7 @@ class PackedHead:
         w.human_idx, w.ent_tot, w.ent_dim = G.human_idx, G.transh_head.num_object, G.transh_head.transh_dim
         w.sp_in = G.spatial_head[0].weight.shape[1]
         for name in ("Wb1", "bb1", "Wb2", "bb2", "Wsp0", "bsp0", "Wsp1", "bsp1", "Wsp2", "bsp2", "Wfh", "bfh", "Wft", "bft",
-                     "Wfc", "bfc",
+                     "Wfc", "bfc", "Wfh_ent",
                      "W_hproj", "b_hproj", "W_oproj", "b_oproj", "Wg1", "bg1", "W2cat", "b2cat", "W3att", "b3att",
                      "W3os", "b3os", "W3so", "b3so", "W3g", "b3g", "w_adj", "Wpred", "bpred", "Wpred_hh", "Wpred_lo"):
             setattr(w, name, getattr(self, name).data_ptr())
@@ -419,6 +420,7 @@ def head_forward(ih, features3: Tensor, image_shapes, box_features: Tensor, boxe
     tr = G.transh_head.transh
     if tr.ent_embeddings.weight.device != dev:
         tr.to(dev)
+    G.transh_head.maybe_resample()
     ent = tr.ent_embeddings.weight.detach()
     f3 = features3.contiguous()
     flags = (_lib.HEAD_PRECISE_LOGITS if precise_logits else 0) | (_lib.HEAD_WANT_TAPS if want_taps else 0)
@@ -468,7 +470,6 @@ def head_forward(ih, features3: Tensor, image_shapes, box_features: Tensor, boxe
     _lib.require_cuda(f3, bf, boxes_cat)
     w = pk.cw
     w.ent = ent.data_ptr()
-    pk.fc_bias(ent, G.human_idx)
     b.features3, b.boxes = f3.data_ptr(), boxes_cat.data_ptr()
     if bf.dtype == torch.bfloat16:                   # operand rows written by the native RoIAlign (roi.py)
         if bf.shape[1] != int(pk.cw.K0) or bf.data_ptr() % 16:

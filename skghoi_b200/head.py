@@ -67,7 +67,8 @@ class transH_head(Module):
     """Reference head.py:533-582.  The reference builds a NEW randomly initialised TransH on every
     call (head.py:574-578), so its tables are never trained or checkpointed; here the tables live
     in ``self.transh`` (not part of the reference state_dict -- saved under the extra key prefix
-    ``transh``) and can be re-drawn per call with ``resample=True`` for reference-like behaviour."""
+    ``transh``) and are re-drawn once per batch with ``resample=True`` for reference-like behaviour (honoured by this
+    module's ``forward``, by ``engine.head_forward`` and by the training pass)."""
 
     def __init__(self, transh_dim: int = 200, transh_p_norm: int = 2, transh_norm_flag: bool = True,
                  human_idx: int = 49, num_object: int = 80, num_cls: int = 117) -> None:
@@ -103,6 +104,17 @@ class transH_head(Module):
         if device is not None:
             m.to(device)
 
+    def maybe_resample(self) -> None:
+        """``resample=True``: re-draws the three tables like the reference, which constructs a fresh Xavier-initialised
+        TransH on every call (head.py:574-578).  In place on the parameters (no ``.data`` detour: the version counters
+        move, and every forward re-reads the table on the device anyway).  Called by ``forward`` and by the engine /
+        training paths once per batch."""
+        if self.resample:
+            m = self.transh
+            with torch.no_grad():
+                for emb in (m.ent_embeddings, m.rel_embeddings, m.norm_vector):
+                    nn.init.xavier_uniform_(emb.weight)
+
     def forward(self, ind_x, ind_y, n_h: int, n: int, x_keep, y_keep, labels: Optional[Tensor] = None):
         """head.py:558-582: 117 triples per grid cell, head = human_idx, tail = box index ``ind_y``."""
         m = self.transh
@@ -110,9 +122,7 @@ class transH_head(Module):
         _lib.require_cuda(ind_y)
         if m.ent_embeddings.weight.device != dev:
             m.to(dev)
-        if self.resample:
-            for emb in (m.ent_embeddings, m.rel_embeddings, m.norm_vector):
-                nn.init.xavier_uniform_(emb.weight.data)
+        self.maybe_resample()
         cells = len(ind_x)
         T = cells * self.num_cls
         e, r, w = m.ent_embeddings.weight, m.rel_embeddings.weight, m.norm_vector.weight
