@@ -556,9 +556,8 @@ def measure_training(torch, dist, args, dev, rank, world, flush):
     meta = engine._host_meta(batch["box_labels"], batch["box_scores"], 49)
     params = [p for p in ih.parameters() if p.requires_grad]
     opt = torch.optim.SGD(params, lr=1e-4, momentum=0.9)
-    buckets = shard.GradBuckets(params)
-    if world > 1:
-        buckets.attach()      # gradients live in the flat buckets: no per-parameter pack / unpack around the all-reduce
+    buckets = shard.GradBuckets(params).attach()      # gradients live in flat buckets: stable .grad addresses for the native
+    #                                                   backward's unpack table, one all-reduce + one scale per bucket when N > 1
 
     def step():
         buckets.zero_grad()
@@ -587,7 +586,7 @@ def measure_training(torch, dist, args, dev, rank, world, flush):
             "value": pairs * world * args.train_steps / (t_ms * 1e-3), "unit": UNIT, "ms_per_step": t_ms / args.train_steps,
             "steps": args.train_steps, "n_gpus": world, "pairs_per_step_per_gpu": pairs,
             "negatives": "TransH negatives drawn on the device (uniform without replacement per image, as head.py:939)",
-            "step": "zero_grad + forward + backward (y, dx, dW of every dense layer on the tcgen05 GEMM) + %s + SGD update"
+            "step": "zero_grad + skg_head_forward(TRAIN) + post / losses + skg_head_backward (every dX / dW on the tcgen05 GEMM, trainops kernels) + gradient unpack + %s + SGD update"
                     % ("bucketed NCCL gradient all-reduce (%d buckets)" % len(buckets.buckets) if world > 1 else "no all-reduce (1 GPU)"),
             "grad_bytes": sum(p.numel() * 4 for p in params),
             "final_losses": {k: float(v.detach().reshape(-1)[0]) for k, v in ls.items()}}

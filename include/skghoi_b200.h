@@ -115,6 +115,7 @@ int skg_focal_loss(const float* x, const float* y, int64_t n, float alpha, float
  *     v += residual[row_r[r]][lc]                         (optional)
  *     dot_out[out_row[r]][4*tile + h] = sum_lc v * dot_w[lc]  (optional fused row-dot; four partials per N tile,
  *                                                          one per column quarter h, summed by the consumer)
+ *     v = mask_bf16[r][lc] > 0 ? v : 0                     (optional: the ReLU mask of a backward (dX) GEMM)
  *     out_bf16 / out_f32 [out_row[r]][lc] = v             (optional; out_row NULL = r, < 0 = skip row)
  * row_* NULL means the identity map.  bias, dot_w and the gathered tables are read in 32-column
  * chunks, so they (and out_bf16 / raw_bf16 rows) must be padded to a multiple of 32 columns;
@@ -133,6 +134,8 @@ typedef struct skg_epilogue_group {
   void* raw_bf16; int32_t ld_raw;
   const int32_t* out_row;
   void* lo_bf16; int32_t ld_lo;   /* optional: bf16(v - float(bf16(v))), the rounding residual of out_bf16 */
+  const void* mask_bf16; int32_t ld_mask;   /* optional ReLU-backward gate, applied last before the stores:
+                                               v = mask_bf16[r][lc] > 0 ? v : 0  (r = GEMM row, before out_row) */
 } skg_epilogue_group;
 
 /* groups is a HOST array of num_groups descriptors (copied into the launch).  block_n = 128, 256
@@ -216,6 +219,8 @@ typedef struct skg_post_tables {
   const int32_t* box_prefix;  /* [boxes]  exclusive within-image prefix of box_cnt (postprocess only) */
   const int32_t* box_cnt;     /* [boxes]  number of valid verbs of the box's class (postprocess only) */
   const int64_t* hum_base;    /* [humans] batch-global output offset of each human row (postprocess only) */
+  const int32_t* logit_row;   /* [P] row of pair p inside `logits` (NULL = p).  The training layout (SKG_HEAD_TRAIN) keeps the
+                                 logits in cell rows: logit_row = pair2cell */
 } skg_post_tables;
 
 /* InteractionHead.postprocess (head.py:291-337) for the whole batch: logits [P, ld] holds num_cls verb
@@ -259,6 +264,89 @@ int skg_associate_gt(const float* boxes, const skg_post_tables* tables, int64_t 
                      const int32_t* gt_off, const float* gt_boxes_h, const float* gt_boxes_o,
                      const int64_t* gt_verb, float fg_iou_thresh, float* labels, cudaStream_t stream);
 
+
+/* ---- backward-pass kernels of the training step (csrc/trainops.cu; BASELINE configs[2]) -----------------------------
+ * The reference trains the head with autograd (utils.py:213-229: forward, loss.backward(), optimizer step); these are the
+ * backward counterparts of the fused forward kernels above, so that the whole step runs on this library. */
+
+/* out[c, r] = in[row_map ? row_map[r] : r, c] for r < rows, c < cols (bf16; rows with a negative map entry read as zero):
+ * the M-major copies the weight-gradient GEMMs dW = G^T X consume.  colsum (optional, fp32 [cols], caller-zeroed)
+ * += column sums of `in` -- the bias gradient of the layer comes for free with the transposition of G. */
+int skg_transpose_bf16(const void* in, int64_t ld_in, int64_t rows, int cols, const int32_t* row_map, void* out,
+                       int64_t ld_out, float* colsum, cudaStream_t stream);
+
+/* d(g_hoi * hoi_loss + g_int * interactiveness_loss) / d logits (compute_interaction_classification_loss head.py:153-177,
+ * compute_interactiveness_loss head.py:180-205 through postprocess head.py:308-316, binary_focal_loss ops.py:159-211):
+ * logits [*, ld_logits] fp32 (num_cls verb logits + the suppressor logit; the row of pair p is logit_row[p], or p when
+ * NULL), gt_labels [P, num_cls], n_p[2] the two normalisers, g_hoi / g_int device scalars (NULL = 1).  dlogits
+ * [*, ld_d] bf16 must be ZERO on entry; entries of valid (pair, verb) combinations and the suppressor column are written. */
+int skg_head_loss_backward(const float* logits, int ld_logits, int num_cls, const skg_post_tables* tables,
+                           const int32_t* logit_row, int64_t pairs, float prior_power, const float* gt_labels,
+                           const float* n_p, const float* g_hoi, const float* g_int, void* dlogits_bf16, int ld_d,
+                           cudaStream_t stream);
+
+/* Backward of the branch products fc_1(app) * fc_2(sp) of the four MBFs (MultiBranchFusion head.py:469-474, MessageMBF
+ * head.py:509-527), all five products of a cell in one pass.  S [cells, 4R] raw fc_2 outputs (attention_head | obj_to_sub |
+ * sub_to_obj | attention_head_g); dP_* [cells, R] gradients of the pre-activations (att = attention weights pass,
+ * fin = final attention pass on the refined nodes); hproj [NH, 2R] = (U_h | V_so), oproj [NB, 2R] = (U_o | V_os), U2h,
+ * U2o, GT the appearance-side tables.  Writes dS [cells, 4R] (bf16) and the per-node sums dhproj, dU2h (stored) and
+ * doproj, dU2o, dGT (ACCUMULATED with fp32 atomics: caller zeroes them). */
+typedef struct skg_hadamard_bwd {
+  const void* S; int64_t ld_s;
+  const void* dP_att; const void* dP_fin; const void* dP_os; const void* dP_so; const void* dP_g; int64_t ld_dp;
+  const float* hproj; const float* oproj; const float* U2h; const float* U2o; const float* GT;
+  void* dS; int64_t ld_ds;
+  float* dhproj; float* doproj; float* dU2h; float* dU2o; float* dGT;
+  const int32_t* box_off; const int32_t* hum_off; const int64_t* cell_off;
+  int32_t num_images, R;
+} skg_hadamard_bwd;
+/* phase 1 (needs dP_fin, dP_g): dS[:, 3R:4R], dU2h, dU2o, dGT.  phase 2 (needs all five): dS[:, 0:3R], dhproj, doproj. */
+int skg_hadamard_backward(const skg_hadamard_bwd* args, int total_humans, int phase, cudaStream_t stream);
+
+/* Backward of skg_message_aggregate (head.py:907-921): given dZ_h [NH, width] / dZ_o [NB, width] (bf16) writes the gated
+ * gradients of the message pre-activations dP_os / dP_so [cells, ld_dp] (bf16) and the two halves of the adjacency
+ * gradient, dadj_h / dadj_o [cells] (softmax over an image's boxes resp. humans); adjacency [cells] as the forward stored it. */
+int skg_message_aggregate_backward(const float* adjacency, const void* dZ_h, const void* dZ_o, const void* H_os,
+                                   const void* H_so, int64_t ld_h, const int32_t* box_off, const int32_t* hum_off,
+                                   const int64_t* cell_off, int num_images, int total_boxes, int total_humans,
+                                   int max_per_image, int width, void* dP_os, void* dP_so, int64_t ld_dp, float* dadj_h,
+                                   float* dadj_o, cudaStream_t stream);
+
+/* Backward of the adjacency Linear(R -> 1) on wts = relu(fc_3(...)) kept in bf16 (head.py:896-897): dwts [cells, ld_dw]
+ * (bf16, ReLU gated); dw_adj [width] and db_adj [1] are ACCUMULATED. */
+int skg_adjacency_backward(const float* dadj_h, const float* dadj_o, const void* wts, int64_t ld_w, const float* w_adj,
+                           int64_t cells, int width, void* dwts, int64_t ld_dw, float* dw_adj, float* db_adj,
+                           cudaStream_t stream);
+
+/* Backward of skg_layernorm on x = base + relu(msg) (head.py:909-914, 921-925): dx [rows, width] fp32 (the gradient that
+ * also flows down the residual path), dmsg_bf16 = dx gated by (x - base > 0); dw_* / db_* [width] are ACCUMULATED.
+ * Rows [0, rows_a) use (base_a, w_a), the rest (base_b [rows - rows_a, width], w_b). */
+int skg_layernorm_backward(const float* x, const float* dy, const float* base_a, const float* base_b, int64_t rows,
+                           int64_t rows_a, int width, const float* w_a, const float* w_b, float eps, float* dx,
+                           void* dmsg_bf16, float* dw_a, float* db_a, float* dw_b, float* db_b, cudaStream_t stream);
+
+/* Weight / bias gradient of skg_spatial_fc1 (head.py:663): dW [out, in] and db [out] are ACCUMULATED. */
+int skg_spatial_fc1_backward(const float* enc, const void* g_bf16, int64_t cells, int in_features, int out_features,
+                             float* dW, float* db, cudaStream_t stream);
+
+/* hum2box[box2hum[k]] = k: inverse of the box -> human-row map of skg_node_prep (human rows are the first n_h boxes). */
+int skg_hum2box(const int32_t* box2hum, int total_boxes, int32_t* hum2box, cudaStream_t stream);
+
+/* Descriptor-driven block copy: weight packing (the reference's per-branch fp32 parameters, state_dict layout of SURVEY
+ * 8(a), -> the concatenated bf16 operands of skg_head_weights, plus their transposes for the dX GEMMs) and gradient
+ * unpacking (packed fp32 gradients -> the per-branch .grad tensors) as ONE launch each.  descs / tiles live in DEVICE
+ * memory; tiles holds (descriptor index, first row, first column) triples of 32 x 32 tiles. */
+#define SKG_BLOCK_SRC_BF16 1
+#define SKG_BLOCK_DST_BF16 2
+#define SKG_BLOCK_ACCUMULATE 4   /* fp32 dst += (atomic) instead of = */
+#define SKG_BLOCK_SCALE 8        /* multiply by `scale` */
+typedef struct skg_block_desc {
+  const void* src; void* dst; void* dst_t;      /* dst_t (optional): bf16 [cols, ld_dst_t] transposed copy */
+  int32_t rows, cols;
+  int64_t ld_src, ld_dst, ld_dst_t;
+  int32_t flags; float scale;
+} skg_block_desc;
+int skg_block_copy(const skg_block_desc* descs_dev, const int32_t* tiles_dev, int num_tiles, cudaStream_t stream);
 
 /* ---- the whole pair path in one call (csrc/forward.cu) ------------------------------------------
  * GraphHead.forward + predictor / suppressor for a batch (head.py:769-993, 408-411): pair
@@ -315,7 +403,7 @@ typedef struct skg_head_batch {
                                      skg_multiscale_roi_align; when set, box_features is ignored and may be NULL */
 } skg_head_batch;
 
-#define SKG_HEAD_NUM_BUFFERS 64
+#define SKG_HEAD_NUM_BUFFERS 96
 typedef struct skg_head_plan_t {
   int64_t total_bytes;
   int32_t num_buffers;
@@ -333,6 +421,10 @@ int skg_head_plan(const skg_head_weights* weights, const skg_head_batch* batch, 
 #define SKG_HEAD_WANT_TAPS 2        /* also keep fp32 copies of the refined node encodings */
 #define SKG_HEAD_GRAPH 8            /* replay the step as a CUDA graph when the same (weights, batch incl. input pointers,
                                        workspace) key repeats; any change falls back to plain launches */
+#define SKG_HEAD_TRAIN 16           /* training forward (skg_head_backward follows): keeps the raw fc_2 outputs of all four MBFs
+                                       and the attention weights, the pair features and logits stay in CELL rows (buffers
+                                       "feat" [cells, 2R], "logits" [cells, n_logit]; the diagonal cells i == j are masked by
+                                       the loss), single-pass predictor */
 #define SKG_HEAD_PROFILE 4          /* record an event after every launch and SYNCHRONISE at the end (diagnostics only) */
 /* launch i of the last profiled skg_head_forward on this thread: label, stream (0 caller's, 1 side), microseconds since
  * the previous event on that stream; returns -1 past the end */
@@ -341,6 +433,47 @@ int skg_head_profile_get(int i, const char** name, int* stream_id, float* us);
 void skg_head_graph_stats(long long* replays, long long* captures, long long* plain);
 int skg_head_forward(const skg_head_weights* weights, const skg_head_batch* batch, int flags, void* workspace,
                      int64_t workspace_bytes, cudaStream_t stream);
+
+/* ---- backward of the whole pair path (csrc/backward.cu): the training step of BASELINE configs[2] ------------------------
+ * Reference: loss.backward() through GraphHead.forward / the predictor and the two focal losses (utils.py:213-229,
+ * head.py:153-205, 769-993).  Call order per step: skg_head_forward(flags | SKG_HEAD_TRAIN) -> skg_head_post on the cell-row
+ * logits (logit rows = pair2cell) -> skg_head_backward with the SAME weights / batch / workspace.  Every dX and dW
+ * product is a launch of skg_gemm_bf16 (dX: the transposed weight copies of skg_head_weights_t as B operand, the ReLU gate
+ * of the layer's input fused into the epilogue; dW = G^T X on M-major copies made by skg_transpose_bf16, whose column sums
+ * are the bias gradients), the element-wise and per-node reductions are the kernels of csrc/trainops.cu.
+ * `grads` mirrors the packed operand layout of skg_head_weights in fp32; the caller ZEROES it before the call (bias and
+ * per-node gradients are accumulated with atomics, weight gradients are stored).  skg_block_copy maps it back onto the
+ * reference's per-branch parameter layout. */
+typedef struct skg_head_weights_t {     /* transposed bf16 copies: B operands of the dX GEMMs (K-major = N of the forward) */
+  const void* Wb2T;      /* [E, E] */
+  const void* Wsp1T;     /* [128, 256] */
+  const void* Wsp2T;     /* [256, R] */
+  const void* WfcT;      /* [fc_k, 2R] */
+  const void* W_hprojT;  /* [R, 2R] */
+  const void* W_oprojT;  /* [R, 2R] */
+  const void* W2catT;    /* [R, 4R] */
+  const void* W3attT; const void* W3osT; const void* W3soT; const void* W3gT;   /* [R, R] */
+  const void* WpredT;    /* [2R, n_logit_pad] */
+} skg_head_weights_t;
+
+typedef struct skg_head_grads {         /* fp32, shapes of the packed operands in skg_head_weights */
+  float* Wb1; float* bb1; float* Wb2; float* bb2; float* Wsp0; float* bsp0; float* Wsp1; float* bsp1; float* Wsp2; float* bsp2;
+  float* Wfc; float* bfc; float* W_hproj; float* b_hproj; float* W_oproj; float* b_oproj; float* Wg1; float* bg1;
+  float* W2cat; float* b2cat; float* W3att; float* b3att; float* W3os; float* b3os; float* W3so; float* b3so; float* W3g; float* b3g;
+  float* w_adj; float* b_adj; float* ln_h_w; float* ln_h_b; float* ln_o_w; float* ln_o_b; float* Wpred; float* bpred;
+} skg_head_grads;
+
+typedef struct skg_head_loss_args {
+  const skg_post_tables* tables;   /* HOST struct of DEVICE pointers, as skg_head_post */
+  const float* gt_labels;          /* [P, num_cls] from skg_associate_gt */
+  const float* n_p;                /* [2] normalisers of hoi_loss / interactiveness_loss (rank-averaged when distributed) */
+  const float* g_hoi; const float* g_int;   /* upstream gradients of the two losses (device scalars, NULL = 1) */
+  float prior_power;               /* 1.0 in training (head.py:742) */
+} skg_head_loss_args;
+
+int skg_head_backward(const skg_head_weights* weights, const skg_head_weights_t* weights_t, const skg_head_batch* batch,
+                      const skg_head_loss_args* loss, const skg_head_grads* grads, int flags, void* workspace,
+                      int64_t workspace_bytes, cudaStream_t stream);
 
 /* Host-side packing of the per-batch segment table every batched kernel consumes (all HOST pointers): n / n_h [B]
  * boxes and humans per image, hw [B,2] = (h, w) as doubles.  `out` receives

@@ -128,6 +128,7 @@ class EpilogueGroup(ctypes.Structure):
         ("raw_bf16", c_void_p), ("ld_raw", ctypes.c_int32),
         ("out_row", c_void_p),
         ("lo_bf16", c_void_p), ("ld_lo", ctypes.c_int32),
+        ("mask_bf16", c_void_p), ("ld_mask", ctypes.c_int32),
     ]
 
 
@@ -135,7 +136,7 @@ class PostTables(ctypes.Structure):
     """Mirror of ``skg_post_tables``."""
     _fields_ = [(k, c_void_p) for k in ("verb_off", "verb_idx", "pair2cell", "cell_hrow", "cell_orow", "cell_img",
                                         "hum_off", "box_off", "pair_off", "labels", "scores", "box_prefix", "box_cnt",
-                                        "hum_base")]
+                                        "hum_base", "logit_row")]
 
 
 _SIGNATURES["skg_multiscale_roi_align"] = (I, [P, P, P, P, I, I, I, P, P, L, I, I, I, I, F, I, P, P, L, P])
@@ -152,7 +153,7 @@ _SIGNATURES["skg_gemm_bf16"] = (I, [P, L, P, L, I, I, I, ctypes.POINTER(Epilogue
 
 def epilogue_group(n_begin=0, relu=False, bias=None, mul_p=None, row_p=None, mul_q=None, row_q=None,
                    residual=None, row_r=None, dot_w=None, dot_out=None, out_bf16=None, out_f32=None,
-                   raw_bf16=None, out_row=None, lo_bf16=None):
+                   raw_bf16=None, out_row=None, lo_bf16=None, mask_bf16=None):
     """Builds one epilogue group from tensors (leading dimensions are taken from ``stride(0)``)."""
     def a(t):
         return t.data_ptr() if t is not None else None
@@ -171,6 +172,7 @@ def epilogue_group(n_begin=0, relu=False, bias=None, mul_p=None, row_p=None, mul
     g.raw_bf16, g.ld_raw = a(raw_bf16), ld(raw_bf16)
     g.out_row = a(out_row)
     g.lo_bf16, g.ld_lo = a(lo_bf16), ld(lo_bf16)
+    g.mask_bf16, g.ld_mask = a(mask_bf16), ld(mask_bf16)
     return g
 
 
@@ -226,7 +228,7 @@ class HeadBatch(ctypes.Structure):
                                         "pair_off", "hw", "box_features_bf16")]
 
 
-HEAD_NUM_BUFFERS = 64
+HEAD_NUM_BUFFERS = 96
 
 
 class HeadPlan(ctypes.Structure):
@@ -240,6 +242,7 @@ HEAD_PRECISE_LOGITS = 1
 HEAD_WANT_TAPS = 2
 HEAD_PROFILE = 4
 HEAD_GRAPH = 8
+HEAD_TRAIN = 16
 _SIGNATURES["skg_head_profile_get"] = (I, [I, ctypes.POINTER(c_char_p), ctypes.POINTER(I), ctypes.POINTER(c_float)])
 _SIGNATURES["skg_head_buffer_name"] = (c_char_p, [I])
 _SIGNATURES["skg_head_plan"] = (I, [ctypes.POINTER(HeadWeights), ctypes.POINTER(HeadBatch), I, ctypes.POINTER(HeadPlan)])
@@ -251,6 +254,18 @@ _SIGNATURES["skg_post_count_host"] = (c_int64, [P, I, P, P, P, P, I, P])
 _SIGNATURES["skg_preprocess_detections"] = (I, [P, P, P, P, I, I, F, F, I, I, I, P, P, P])
 
 _SIGNATURES["skg_kg_sample"] = (I, [P, P, P, P, P, P, P, P, L, L, P, P, I, L, I, I, P, P, P, P, P])
+
+# ---- training step (csrc/trainops.cu, csrc/backward.cu); struct pointers travel as void* (ctypes.byref) -------------
+_SIGNATURES["skg_block_copy"] = (I, [P, P, I, P])
+_SIGNATURES["skg_head_backward"] = (I, [P, P, P, P, P, I, P, L, P])
+_SIGNATURES["skg_transpose_bf16"] = (I, [P, L, L, I, P, P, L, P, P])
+_SIGNATURES["skg_hum2box"] = (I, [P, I, P, P])
+_SIGNATURES["skg_head_loss_backward"] = (I, [P, I, I, P, P, L, F, P, P, P, P, P, I, P])
+_SIGNATURES["skg_hadamard_backward"] = (I, [P, I, I, P])
+_SIGNATURES["skg_message_aggregate_backward"] = (I, [P, P, P, P, P, L, P, P, P, I, I, I, I, I, P, P, L, P, P, P])
+_SIGNATURES["skg_adjacency_backward"] = (I, [P, P, P, L, P, L, I, P, L, P, P, P])
+_SIGNATURES["skg_layernorm_backward"] = (I, [P, P, P, P, L, L, I, P, P, F, P, P, P, P, P, P, P])
+_SIGNATURES["skg_spatial_fc1_backward"] = (I, [P, P, L, I, I, P, P, P])
 
 _buffer_names = None
 

@@ -13,67 +13,10 @@
 // so the few-CTA node-row GEMMs overlap the wide cell-row ones instead of leaving 140 SMs idle.
 #include "common.cuh"
 #include "skghoi_b200.h"
+#include "head_plan.cuh"
 #include <string.h>
 
 namespace skg {
-
-enum Buf : int {
-  B_SPLITK0 = 0, B_SPLITK1, B_SEG, B_ENC, B_X, B_Y, B_XKEEP, B_YKEEP, B_CELL2PAIR, B_CELL_HROW, B_CELL_OROW, B_CELL_IMG, B_PAIR2CELL, B_NANFLAG,
-  B_S1, B_S2, B_SP, B_XB, B_X1, B_BOX2HUM, B_OIN, B_HN32, B_HN16, B_ON32, B_ON16, B_HPROJ, B_OPROJ, B_GFEAT, B_G32,
-  B_GT, B_HATT, B_SRAW, B_HOS, B_HSO, B_HG, B_DOTPART, B_Z, B_ADJ, B_PRE, B_ENC16, B_ENC32, B_U2H, B_U2O, B_H2, B_FEAT,
-  B_TMP, B_LOGITS, B_POST32, B_POST64, B_COUNT
-};
-static_assert(B_COUNT <= SKG_HEAD_NUM_BUFFERS, "raise SKG_HEAD_NUM_BUFFERS");
-
-static const char* kBufNames[B_COUNT] = {
-  "splitk_main", "splitk_side", "seg", "enc", "x", "y", "x_keep", "y_keep", "cell2pair", "cell_hrow", "cell_orow", "cell_img", "pair2cell", "nan_flag",
-  "s1", "s2", "sp", "xb", "x1", "box2hum", "o_in", "hN32", "hN16", "oN32", "oN16", "hproj", "oproj", "gfeat", "g32",
-  "Gt", "H_att", "S_raw", "H_os", "H_so", "H_g", "dot_part", "Z", "adjacency", "pre", "enc16", "enc32", "U2h", "U2o", "H2", "feat",
-  "tmp", "logits", "post_i32", "post_i64"};
-
-static inline int64_t align_up(int64_t v, int64_t a) { return (v + a - 1) / a * a; }
-
-static int make_plan(const skg_head_weights& w, const skg_head_batch& b, int flags, skg_head_plan_t* p) {
-  SKG_REQUIRE(w.R > 0 && w.R % 256 == 0, "representation_size must be a multiple of 256 for the tensor-core path, got %d", w.R);
-  SKG_REQUIRE(w.E > 0 && w.E % 128 == 0, "node_encoding_size must be a multiple of 128, got %d", w.E);
-  SKG_REQUIRE(w.K0 % 8 == 0 && w.fc_k % 8 == 0 && w.Kg % 8 == 0 && w.K0 >= w.pool_k && w.Kg >= w.Cg, "padded K sizes must be multiples of 8");
-  SKG_REQUIRE(w.fc_k >= w.E + w.ent_dim, "fc_k must cover node encoding + TransH dim");
-  SKG_REQUIRE(w.sp_in == 46, "spatial_head input must be 46 (2 x 23 ratio features, head.py:663)");
-  SKG_REQUIRE(w.n_logit == w.num_cls + 1 && w.n_logit_pad >= w.n_logit && w.n_logit_pad % 128 == 0, "bad logit sizes");
-  SKG_REQUIRE(b.num_images >= 0 && b.total_boxes >= 0 && b.total_humans >= 0 && b.total_cells >= 0 && b.total_pairs >= 0, "negative sizes");
-  const int64_t C = b.total_cells, P = b.total_pairs, NB = b.total_boxes, NH = b.total_humans, B = b.num_images;
-  const int R = w.R;
-  const bool precise = (flags & SKG_HEAD_PRECISE_LOGITS) != 0;
-  memset(p, 0, sizeof(*p));
-  p->num_buffers = B_COUNT;
-  auto set = [&](int i, int64_t rows, int64_t cols, int es) { p->rows[i] = rows; p->cols[i] = cols; p->elem_size[i] = es; };
-  // split-K scratch of the two streams: FIRST in the layout so their position does not depend on the batch shape;
-  // must be zero before the first call on a workspace and are left zero by every call (skg_gemm_bf16_splitk)
-  const int64_t sk_elems = skg_gemm_splitk_scratch_bytes(0, 0) / 4;
-  set(B_SPLITK0, 1, sk_elems, 4); set(B_SPLITK1, 1, sk_elems, 4);
-  set(B_SEG, 1, b.seg_bytes > 0 ? b.seg_bytes : 0, 1);
-  set(B_ENC, C, 46, 4); set(B_X, C, 1, 8); set(B_Y, C, 1, 8); set(B_XKEEP, P, 1, 8); set(B_YKEEP, P, 1, 8);
-  set(B_CELL2PAIR, C, 1, 4); set(B_CELL_HROW, C, 1, 4); set(B_CELL_OROW, C, 1, 4); set(B_CELL_IMG, C, 1, 4);
-  set(B_PAIR2CELL, P, 1, 4); set(B_NANFLAG, B > 0 ? B : 1, 1, 4);
-  set(B_S1, C, 128, 2); set(B_S2, C, 256, 2); set(B_SP, C, R, 2);
-  set(B_XB, NB, w.K0, 2); set(B_X1, NB, w.E, 2); set(B_BOX2HUM, NB, 1, 4); set(B_OIN, NB, w.fc_k, 2);
-  set(B_HN32, NH, R, 4); set(B_HN16, NH, R, 2); set(B_ON32, NB, R, 4); set(B_ON16, NB, R, 2);
-  set(B_HPROJ, NH, 2 * R, 4); set(B_OPROJ, NB, 2 * R, 4);
-  set(B_GFEAT, B, w.Kg, 2); set(B_G32, B, w.Cg, 4); set(B_GT, B, R, 4);
-  set(B_HATT, C, R, 2); set(B_SRAW, C, R, 2); set(B_HOS, C, R, 2); set(B_HSO, C, R, 2); set(B_HG, C, R, 2);
-  set(B_DOTPART, C, 4 * (R / 256), 4); set(B_Z, NH + NB, R, 2); set(B_ADJ, C, 1, 4); set(B_PRE, NH + NB, R, 4);
-  set(B_ENC16, NH + NB, R, 2); set(B_ENC32, (flags & SKG_HEAD_WANT_TAPS) ? NH + NB : 0, R, 4);
-  set(B_U2H, NH, R, 4); set(B_U2O, NB, R, 4); set(B_H2, C, R, 2);
-  set(B_FEAT, P, precise ? 4 * R : 2 * R, 2); set(B_TMP, precise ? P : 0, w.n_logit_pad, 4); set(B_LOGITS, P, w.n_logit, 4);
-  set(B_POST32, 2 * NB, 1, 4); set(B_POST64, NH + 2 * B + 1, 1, 8);   // scratch of skg_head_post
-  int64_t off = 0;
-  for (int i = 0; i < B_COUNT; ++i) {
-    p->offset[i] = off;
-    off = align_up(off + p->rows[i] * p->cols[i] * p->elem_size[i], 256);
-  }
-  p->total_bytes = off > 0 ? off : 256;
-  return SKG_OK;
-}
 
 // library-owned side streams + an event pool for fork / join (per host thread and device)
 struct SideStream {
@@ -132,18 +75,6 @@ static void prof_mark(const char* name, int sid, cudaStream_t s) {
   p.name[p.n] = name; p.sid[p.n] = sid; p.n++;
 }
 #define MARK(name, s) prof_mark(name, (s) == st ? 0 : (s) == sa ? 1 : (s) == sb ? 2 : 3, (s))
-
-static skg_epilogue_group group0() {
-  skg_epilogue_group g;
-  memset(&g, 0, sizeof(g));
-  return g;
-}
-
-#define SKG_TRY(call)        \
-  do {                       \
-    int rc__ = (call);       \
-    if (rc__) return rc__;   \
-  } while (0)
 
 }  // namespace skg
 
@@ -272,7 +203,8 @@ static int enqueue_forward(const skg_head_weights* wp, const skg_head_batch* bp,
               "null batch pointer");
   SKG_REQUIRE(b.max_boxes_per_image <= w.ent_tot, "index out of range in self: a box index addresses the %d-row entity table (head.py:572)",
               w.ent_tot);
-  const bool precise = (flags & SKG_HEAD_PRECISE_LOGITS) != 0 && w.Wpred_hh && w.Wpred_lo;
+  const bool train = (flags & SKG_HEAD_TRAIN) != 0;
+  const bool precise = !train && (flags & SKG_HEAD_PRECISE_LOGITS) != 0 && w.Wpred_hh && w.Wpred_lo;
   SKG_REQUIRE(precise || w.Wpred, "missing predictor weights");
   uint8_t* base = reinterpret_cast<uint8_t*>(workspace);
   auto F = [&](int i) { return reinterpret_cast<float*>(base + plan.offset[i]); };
@@ -366,7 +298,10 @@ static int enqueue_forward(const skg_head_weights* wp, const skg_head_batch* bp,
     for (int i = 0; i < 4; ++i) { gq[i] = group0(); gq[i].n_begin = i * R; gq[i].flags = SKG_EPI_RELU; gq[i].bias = w.b2cat; gq[i].ld_ob = R; }
     gq[0].mul_p = F(B_HPROJ); gq[0].row_p = I32(B_CELL_HROW); gq[0].ld_p = 2 * R;
     gq[0].mul_q = F(B_OPROJ); gq[0].row_q = I32(B_CELL_OROW); gq[0].ld_q = 2 * R;
-    gq[0].out_bf16 = H(B_HATT); gq[0].raw_bf16 = H(B_SRAW); gq[0].ld_raw = R;
+    const int ld_raw = (int)plan.cols[B_SRAW];     // R, or 4R in training: the raw fc_2 outputs of all four MBFs are kept
+    gq[0].out_bf16 = H(B_HATT); gq[0].raw_bf16 = H(B_SRAW); gq[0].ld_raw = ld_raw;
+    if (train)
+      for (int i = 1; i < 4; ++i) { gq[i].raw_bf16 = reinterpret_cast<__nv_bfloat16*>(H(B_SRAW)) + i * R; gq[i].ld_raw = ld_raw; }
     gq[1].mul_p = F(B_OPROJ) + R; gq[1].row_p = I32(B_CELL_OROW); gq[1].ld_p = 2 * R; gq[1].out_bf16 = H(B_HOS);
     gq[2].mul_p = F(B_HPROJ) + R; gq[2].row_p = I32(B_CELL_HROW); gq[2].ld_p = 2 * R; gq[2].out_bf16 = H(B_HSO);
     gq[3].mul_p = F(B_GT); gq[3].row_p = I32(B_CELL_IMG); gq[3].ld_p = R; gq[3].out_bf16 = H(B_HG);
@@ -378,13 +313,14 @@ static int enqueue_forward(const skg_head_weights* wp, const skg_head_batch* bp,
   SKG_TRY(stream_dep(side, st, sb));
   MARK("start", sb);
   g = group0(); g.flags = SKG_EPI_RELU; g.bias = w.b3g; g.out_bf16 = reinterpret_cast<__nv_bfloat16*>(H(B_FEAT)) + R; g.ld_ob = feat_ld;
-  g.out_row = I32(B_CELL2PAIR);
+  g.out_row = train ? nullptr : I32(B_CELL2PAIR);
   if (precise) { g.lo_bf16 = reinterpret_cast<__nv_bfloat16*>(H(B_FEAT)) + 3 * R; g.ld_lo = feat_ld; }
   SKG_TRY(skg_gemm_bf16(H(B_HG), R, w.W3g, R, (int)C, R, R, &g, 1, 0, sb));
   MARK("gemm attention_head_g.fc_3", sb);
   // ---- attention weights -> adjacency (head.py:896-897); the two iterations of head.py:892 are identical
   const int nt = 4 * (R / 256);
   g = group0(); g.flags = SKG_EPI_RELU; g.bias = w.b3att; g.dot_w = w.w_adj; g.dot_out = F(B_DOTPART); g.ld_dot = nt;
+  if (train) { g.out_bf16 = H(B_WTS); g.ld_ob = R; }      // the backward needs the ReLU mask and the values (dw_adj)
   SKG_TRY(skg_gemm_bf16(H(B_HATT), R, w.W3att, R, (int)C, R, R, &g, 1, 256, st));
   MARK("gemm attention_head.fc_3 + adjacency dot", st);
   // ---- messages (head.py:907-925)
@@ -413,26 +349,27 @@ static int enqueue_forward(const skg_head_weights* wp, const skg_head_batch* bp,
   SKG_TRY(skg_gemm_bf16(HR(B_ENC16, NH), R, w.W_oproj, R, NB, R, R, &g, 1, 0, st));
   MARK("gemm U2o", st);
   SKG_TRY(stream_dep(side, sc, st));
-  SKG_TRY(skg_hadamard_cells(H(B_SRAW), R, F(B_U2H), R, F(B_U2O), R, I32(B_CELL_HROW), I32(B_CELL_OROW), C, R, H(B_H2), R, st));
+  SKG_TRY(skg_hadamard_cells(H(B_SRAW), plan.cols[B_SRAW], F(B_U2H), R, F(B_U2O), R, I32(B_CELL_HROW), I32(B_CELL_OROW), C, R, H(B_H2), R, st));
   MARK("hadamard_cells", st);
-  g = group0(); g.flags = SKG_EPI_RELU; g.bias = w.b3att; g.out_bf16 = H(B_FEAT); g.ld_ob = feat_ld; g.out_row = I32(B_CELL2PAIR);
+  g = group0(); g.flags = SKG_EPI_RELU; g.bias = w.b3att; g.out_bf16 = H(B_FEAT); g.ld_ob = feat_ld; g.out_row = train ? nullptr : I32(B_CELL2PAIR);
   if (precise) { g.lo_bf16 = reinterpret_cast<__nv_bfloat16*>(H(B_FEAT)) + 2 * R; g.ld_lo = feat_ld; }
   SKG_TRY(skg_gemm_bf16(H(B_H2), R, w.W3att, R, (int)C, R, R, &g, 1, 0, st));
   MARK("gemm attention_head.fc_3 (pairs)", st);
   SKG_TRY(stream_dep(side, sb, st));
   // ================= predictor + suppressor (head.py:410-411) as one N = num_cls + 1 GEMM
-  if (P > 0) {
+  const int64_t LR = train ? C : P;      // logit rows: pair-compacted, or cell rows in training
+  if (LR > 0) {
     g = group0();
     if (precise) {   // split bf16: logits = [hi | lo] x [W_hi | W_hi]^T + hi x W_lo^T   (3 bf16 passes ~ fp32 product)
       g.bias = w.bpred; g.out_f32 = F(B_TMP); g.ld_of = w.n_logit_pad;
-      SKG_TRY(skg_gemm_bf16(H(B_FEAT), feat_ld, w.Wpred_hh, 4 * R, (int)P, w.n_logit, 4 * R, &g, 1, 0, st));
+      SKG_TRY(skg_gemm_bf16(H(B_FEAT), feat_ld, w.Wpred_hh, 4 * R, (int)LR, w.n_logit, 4 * R, &g, 1, 0, st));
       MARK("gemm predictor [hi|lo]x[Whi|Whi]", st);
       g = group0(); g.residual = F(B_TMP); g.ld_r = w.n_logit_pad; g.out_f32 = F(B_LOGITS); g.ld_of = w.n_logit;
-      SKG_TRY(skg_gemm_bf16(H(B_FEAT), feat_ld, w.Wpred_lo, 2 * R, (int)P, w.n_logit, 2 * R, &g, 1, 0, st));
+      SKG_TRY(skg_gemm_bf16(H(B_FEAT), feat_ld, w.Wpred_lo, 2 * R, (int)LR, w.n_logit, 2 * R, &g, 1, 0, st));
       MARK("gemm predictor hi x Wlo", st);
     } else {
       g.bias = w.bpred; g.out_f32 = F(B_LOGITS); g.ld_of = w.n_logit;
-      SKG_TRY(skg_gemm_bf16(H(B_FEAT), feat_ld, w.Wpred, 2 * R, (int)P, w.n_logit, 2 * R, &g, 1, 0, st));
+      SKG_TRY(skg_gemm_bf16(H(B_FEAT), feat_ld, w.Wpred, 2 * R, (int)LR, w.n_logit, 2 * R, &g, 1, 0, st));
       MARK("gemm predictor", st);
     }
   }

@@ -27,7 +27,7 @@ constexpr int kEpiWarps = 8;       // kEpiParts per TMEM lane quadrant
 constexpr int kEpiParts = kEpiWarps / 4;   // column parts of a tile, one epilogue warp each per quadrant
 constexpr int kGemmThreads = 32 * (4 + kEpiWarps);  // warps: 0 TMA, 1 MMA, 2 TMEM alloc, 3 idle, 4..19 epilogue
 // epilogue features (compile-time mask FEAT of gemm_bf16_kernel; bias / ReLU / out_row are always available)
-enum : uint32_t { F_P = 1, F_Q = 2, F_RAW = 4, F_RES = 8, F_DOT = 16, F_OB = 32, F_OF = 64, F_LO = 128, F_ALL = 255 };
+enum : uint32_t { F_P = 1, F_Q = 2, F_RAW = 4, F_RES = 8, F_DOT = 16, F_OB = 32, F_OF = 64, F_LO = 128, F_MASK = 256, F_ALL = 511 };
 constexpr int kEpiWarp0 = 4;
 constexpr int kMaxGroups = 4;
 
@@ -289,6 +289,8 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       __nv_bfloat16* g_raw = (FEAT & F_RAW) ? reinterpret_cast<__nv_bfloat16*>(G.raw_bf16) : nullptr;
       __nv_bfloat16* g_lo = (FEAT & F_LO) ? reinterpret_cast<__nv_bfloat16*>(G.lo_bf16) : nullptr;
       float* g_of = (FEAT & F_OF) ? G.out_f32 : nullptr;
+      const __nv_bfloat16* __restrict__ g_mask = (FEAT & F_MASK) ? reinterpret_cast<const __nv_bfloat16*>(G.mask_bf16) : nullptr;
+      const int ld_mask = G.ld_mask;
       const int ld_p = G.ld_p, ld_q = G.ld_q, ld_r = G.ld_r, ld_ob = G.ld_ob, ld_raw = G.ld_raw, ld_lo = G.ld_lo, ld_of = G.ld_of;
       // per-row maps: loaded by the lane that owns the row, then handed to the lanes that process it
       int rp_i[4], rq_i[4], rr_i[4], ro_i[4];
@@ -327,7 +329,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         // the accumulator.  They are software-pipelined one block ahead in registers: with one warp per scheduler
         // quadrant-part there is no other work to hide an L2 round trip behind, and shared memory is full of pipeline
         // stages, so the L1 that would otherwise catch these re-reads is down to a few KB.
-        struct Tabs { float4 b4, w4, tp[4], tq[4], tr[4]; };
+        struct Tabs { float4 b4, w4, tp[4], tq[4], tr[4]; uint2 tm[4]; };
         auto load_tabs = [&](int blk, Tabs& T) {
           const int c0 = part * (BN / kEpiParts) + blk * 16;
           const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -347,6 +349,13 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           if ((FEAT & F_RES) && g_res) {
 #pragma unroll
             for (int it = 0; it < 4; ++it) T.tr[it] = __ldg(reinterpret_cast<const float4*>(g_res + (int64_t)rr_i[it] * ld_r + lc));
+          }
+          if ((FEAT & F_MASK) && g_mask) {   // ReLU-backward gate rows: indexed by the GEMM row (rows beyond M read row 0)
+#pragma unroll
+            for (int it = 0; it < 4; ++it) {
+              const int grow = m0 + quad * 32 + it * 8 + sub;
+              T.tm[it] = __ldg(reinterpret_cast<const uint2*>(g_mask + (int64_t)(grow < M ? grow : 0) * ld_mask + lc));
+            }
           }
         };
         auto process = [&](int blk, const Tabs& T) {
@@ -404,6 +413,13 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             if (relu) { v.x = fmaxf(v.x, 0.f); v.y = fmaxf(v.y, 0.f); v.z = fmaxf(v.z, 0.f); v.w = fmaxf(v.w, 0.f); }
             if ((FEAT & F_RES) && g_res) { v.x += T.tr[it].x; v.y += T.tr[it].y; v.z += T.tr[it].z; v.w += T.tr[it].w; }
             if (FEAT & F_DOT) dot[it] += v.x * w4.x + v.y * w4.y + v.z * w4.z + v.w * w4.w;
+            if ((FEAT & F_MASK) && g_mask) {            // bf16 > 0  <=>  sign bit clear and magnitude bits set
+              const uint2 mk = T.tm[it];
+              if ((mk.x & 0x8000u) || !(mk.x & 0x7fffu)) v.x = 0.f;
+              if ((mk.x & 0x80000000u) || !(mk.x & 0x7fff0000u)) v.y = 0.f;
+              if ((mk.y & 0x8000u) || !(mk.y & 0x7fffu)) v.z = 0.f;
+              if ((mk.y & 0x80000000u) || !(mk.y & 0x7fff0000u)) v.w = 0.f;
+            }
             if (store_ok) {
               if ((FEAT & F_OB) && g_ob)
                 *reinterpret_cast<uint2*>(g_ob + (int64_t)ro * ld_ob + lc) = make_uint2(pack_bf16(v.x, v.y), pack_bf16(v.z, v.w));
@@ -626,6 +642,7 @@ extern "C" int skg_gemm_bf16_splitk(const void* A, int64_t lda, const void* B, i
     SKG_REQUIRE(!g.mul_p || g.ld_p % 4 == 0, "group %d: ld_p must be a multiple of 4", i);
     SKG_REQUIRE(!g.mul_q || g.ld_q % 4 == 0, "group %d: ld_q must be a multiple of 4", i);
     SKG_REQUIRE(!g.residual || g.ld_r % 4 == 0, "group %d: ld_r must be a multiple of 4", i);
+    SKG_REQUIRE(!g.mask_bf16 || g.ld_mask % 4 == 0, "group %d: ld_mask must be a multiple of 4", i);
     epi.g[i] = g;
   }
   // bias / tables are read in 32-column chunks up to the padded width: callers pad them to block_n multiples
@@ -648,7 +665,8 @@ extern "C" int skg_gemm_bf16_splitk(const void* A, int64_t lda, const void* B, i
   for (int i = 0; i < num_groups; ++i) {
     const skg_epilogue_group& g = groups[i];
     need |= (g.mul_p ? F_P : 0) | (g.mul_q ? F_Q : 0) | (g.raw_bf16 ? F_RAW : 0) | (g.residual ? F_RES : 0) |
-            ((g.dot_w || g.dot_out) ? F_DOT : 0) | (g.out_bf16 ? F_OB : 0) | (g.out_f32 ? F_OF : 0) | (g.lo_bf16 ? F_LO : 0);
+            ((g.dot_w || g.dot_out) ? F_DOT : 0) | (g.out_bf16 ? F_OB : 0) | (g.out_f32 ? F_OF : 0) | (g.lo_bf16 ? F_LO : 0) |
+            (g.mask_bf16 ? F_MASK : 0);
   }
 #define SKG_GEMM_CASE64(F)                                                                        \
   if (block_n == 64 && (need & ~(uint32_t)(F)) == 0) {                                            \
@@ -659,6 +677,8 @@ extern "C" int skg_gemm_bf16_splitk(const void* A, int64_t lda, const void* B, i
   SKG_GEMM_CASE64(F_OF)
   SKG_GEMM_CASE64(F_OB | F_OF)
   SKG_GEMM_CASE64(F_RES | F_OF)
+  SKG_GEMM_CASE64(F_MASK | F_OB)
+  SKG_GEMM_CASE64(F_RES | F_MASK | F_OB)
   SKG_GEMM_CASE64(F_ALL)
 #undef SKG_GEMM_CASE64
 #define SKG_GEMM_CASE(F, SKV)                                                                 \
@@ -678,6 +698,9 @@ extern "C" int skg_gemm_bf16_splitk(const void* A, int64_t lda, const void* B, i
   SKG_GEMM_CASE(F_DOT, false)                  // attention weights -> adjacency row-dot
   SKG_GEMM_CASE(F_RES | F_OF, true)                // message fc_3 + residual, split-bf16 predictor second pass
   SKG_GEMM_CASE(F_OB | F_LO, false)                // final pair features with rounding residual
+  SKG_GEMM_CASE(F_MASK | F_OB, false)              // training: dX = (G W) gated by the ReLU mask of the layer's input
+  SKG_GEMM_CASE(F_RES | F_MASK | F_OB, false)      // training: dX + the residual path's gradient, gated
+  SKG_GEMM_CASE(F_DOT | F_OB, false)               // training forward: adjacency row-dot that also keeps the weights
   SKG_GEMM_CASE(F_ALL, true)
 #undef SKG_GEMM_CASE
   set_error("no epilogue variant");

@@ -24,6 +24,7 @@ struct PostTables {
   const int32_t* box_prefix; // [boxes]  exclusive prefix (within image) of the per-box verb counts
   const int32_t* box_cnt;    // [boxes]  number of valid verbs of the box's class
   const int64_t* hum_base;   // [humans] output offset of the first entry of human row i (batch-global)
+  const int32_t* logit_row;  // [P] row of pair p in the logits (NULL = p): the training layout keeps logits in cell rows
 };
 
 __device__ __forceinline__ float sigmoidf_ref(float x) { return 1.f / (1.f + expf(-x)); }
@@ -47,7 +48,8 @@ __global__ void postprocess_kernel(const float* __restrict__ logits, int ld_logi
   const int i = hr - __ldg(t.hum_off + b), j = orow - boff;
   const float s_h = __ldg(t.scores + boff + i), s_o = __ldg(t.scores + orow);
   const float ph = powf(s_h, pw), po = powf(s_o, pw);
-  const float w = sigmoidf_ref(__ldg(logits + p * ld_logits + num_cls));
+  const float* __restrict__ lrow = logits + (t.logit_row ? (int64_t)__ldg(t.logit_row + p) : p) * ld_logits;
+  const float w = sigmoidf_ref(__ldg(lrow + num_cls));
   const int64_t lab_o = __ldg(t.labels + orow);
   if (lane == 0) {
     out_weights[p] = w;
@@ -69,7 +71,7 @@ __global__ void postprocess_kernel(const float* __restrict__ logits, int ld_logi
   const int64_t pair_in_img = p - __ldg(t.pair_off + b);
   for (int k = lane; k < cnt; k += 32) {
     const int v = __ldg(t.verb_idx + vo + k);
-    const float s = sigmoidf_ref(__ldg(logits + p * ld_logits + v));
+    const float s = sigmoidf_ref(__ldg(lrow + v));
     const int64_t e = base + k;
     out_index[e] = pair_in_img;
     out_pred[e] = v;
@@ -122,7 +124,9 @@ __global__ void associate_gt_kernel(const float4* __restrict__ boxes, PostTables
   const float4 bh = __ldg(boxes + boff + (hr - __ldg(t.hum_off + b))), bo = __ldg(boxes + orow);
   for (int g = __ldg(gt_off + b); g < __ldg(gt_off + b + 1); ++g) {
     const float m = fminf(box_iou1(bh, __ldg(gt_h + g)), box_iou1(bo, __ldg(gt_o + g)));
-    if (m >= thresh) labels[p * num_cls + __ldg(gt_verb + g)] = 1.f;
+    int64_t v = __ldg(gt_verb + g);
+    if (v < 0) v += num_cls;                                                      // tensor indexing wraps negative ids
+    if (m >= thresh && v >= 0 && v < num_cls) labels[p * num_cls + v] = 1.f;   // range-checked on the host too (_gt_labels)
   }
 }
 
@@ -241,7 +245,7 @@ static int fill_tables(PostTables& t, const skg_post_tables* h) {
   t.verb_off = h->verb_off; t.verb_idx = h->verb_idx; t.pair2cell = h->pair2cell; t.cell_hrow = h->cell_hrow;
   t.cell_orow = h->cell_orow; t.cell_img = h->cell_img; t.hum_off = h->hum_off; t.box_off = h->box_off;
   t.pair_off = h->pair_off; t.labels = h->labels; t.scores = h->scores; t.box_prefix = h->box_prefix;
-  t.box_cnt = h->box_cnt; t.hum_base = h->hum_base;
+  t.box_cnt = h->box_cnt; t.hum_base = h->hum_base; t.logit_row = h->logit_row;
   return SKG_OK;
 }
 

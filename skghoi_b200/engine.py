@@ -367,9 +367,11 @@ _GEOMETRY_CACHE_MAX = 64
 _ws_seg_owner = {}      # workspace data_ptr -> the Segments whose packed table currently sits in it
 
 
-def _workspace(dev, nbytes: int) -> Tensor:
-    """One growing scratch buffer per (device, stream): every intermediate of the step lives in it."""
-    key = (dev.index, _lib.raw_stream(dev))
+def _workspace(dev, nbytes: int, kind: str = "eval") -> Tensor:
+    """One growing scratch buffer per (device, stream, kind): every intermediate of the step lives in it.  The training
+    step has its own (``kind='train'``): its forward buffers must survive until ``loss.backward()``, whatever inference
+    calls happen in between."""
+    key = (dev.index, _lib.raw_stream(dev), kind)
     ws = _workspaces.get(key)
     if ws is None or ws.numel() < nbytes:
         ws = torch.zeros(int(nbytes * 1.25) + 256, dtype=torch.uint8, device=dev)   # split-K scratch must start zeroed
@@ -405,13 +407,17 @@ class _Run(dict):
 
 
 def head_forward(ih, features3: Tensor, image_shapes, box_features: Tensor, boxes_cat: Tensor, meta: dict,
-                 want_taps: bool = False, precise_logits: bool = True, profile: bool = False, graph: bool = True) -> dict:
+                 want_taps: bool = False, precise_logits: bool = True, profile: bool = False, graph: bool = True,
+                 train: bool = False, pk=None) -> dict:
     """Runs the whole pair path for a batch through ONE C-ABI call (skg_head_forward, csrc/forward.cu).
     Inputs: features['3'] [B,256,h,w] fp32, pooled box features [sum n, 256, 7, 7] fp32, concatenated boxes
     [sum n, 4] fp32 (all CUDA), host ``meta``.  Returns named views into the step's workspace: logits [P,118]
     fp32 (117 verb logits + suppressor logit), feat (bf16 [P, 2R] hi part, + lo part when precise_logits),
-    pair indices, encodings, row maps and every intermediate."""
-    pk = packed_head(ih)
+    pair indices, encodings, row maps and every intermediate.  ``train=True`` (skghoi_b200.train): the SKG_HEAD_TRAIN
+    layout -- logits / feat in CELL rows, raw fc_2 outputs and attention weights kept for skg_head_backward -- on the
+    training step's own workspace, with the operands of ``pk`` (train.TrainState.pk, re-packed once per optimiser step)."""
+    if pk is None:
+        pk = packed_head(ih)
     G = ih.box_pair_head
     dev = pk.device
     n, n_h = meta["n"], meta["n_h"]
@@ -424,6 +430,9 @@ def head_forward(ih, features3: Tensor, image_shapes, box_features: Tensor, boxe
     ent = tr.ent_embeddings.weight.detach()
     f3 = features3.contiguous()
     flags = (_lib.HEAD_PRECISE_LOGITS if precise_logits else 0) | (_lib.HEAD_WANT_TAPS if want_taps else 0)
+    if train:
+        flags = (flags & ~_lib.HEAD_PRECISE_LOGITS) | _lib.HEAD_TRAIN
+        graph = False
     if profile:
         flags |= _lib.HEAD_PROFILE
     elif graph:
@@ -478,7 +487,7 @@ def head_forward(ih, features3: Tensor, image_shapes, box_features: Tensor, boxe
     else:
         b.box_features, b.box_features_bf16 = bf.data_ptr(), None
     with _lib.on_device(dev):
-        ws = _workspace(dev, int(plan.total_bytes))
+        ws = _workspace(dev, int(plan.total_bytes), "train" if train else "eval")
         wkey = ws.data_ptr()
         if _ws_seg_owner.get(wkey) is not seg:       # the table of another batch (or nothing) sits in the workspace
             so = int(plan.offset[_lib.head_buffer_names().index("seg")])
@@ -494,8 +503,12 @@ def head_forward(ih, features3: Tensor, image_shapes, box_features: Tensor, boxe
     if cache["run"] is not None and cache["ws_ptr"] == wkey and not profile and not want_taps:
         run = cache["run"]                           # same workspace, same plan: the named views are still valid
         run["_keep"] = (f3, bf, boxes_cat, ent)
+        if train:
+            run["_batch"] = type(b).from_buffer_copy(b)
         return run
     run = _Run(ws, plan, seg=seg, NH=seg.total_humans, NB=seg.total_boxes, _keep=(f3, bf, boxes_cat, ent))
+    if train:                                        # what skg_head_backward is called with (train._StepRecord)
+        run["_train"] = True; run["_flags"] = flags; run["_batch"] = type(b).from_buffer_copy(b)
     if profile:
         prof, i = [], 0
         nm, sid, us = _lib.c_char_p(), _lib.c_int(), _lib.c_float()
@@ -623,7 +636,13 @@ def _gt_labels(G, run: dict, tables, boxes_cat: Tensor, targets: List[dict]) -> 
     if sum(counts):
         gh = torch.cat([t["boxes_h"] for t in targets]).to(dev, torch.float32).contiguous()
         go = torch.cat([t["boxes_o"] for t in targets]).to(dev, torch.float32).contiguous()
+        gv_host = [t["labels"] for t in targets if not t["labels"].is_cuda]
         gv = torch.cat([t["labels"] for t in targets]).to(dev, torch.int64).contiguous()
+        # the reference indexes labels[x, target['labels'][y]] (head.py:717) and raises IndexError for a verb outside
+        # [0, num_cls); checked on whichever copy is cheapest (host tensors: no device round trip)
+        chk = torch.cat(gv_host) if len(gv_host) == len(targets) else gv
+        if chk.numel() and (int(chk.max()) >= G.num_cls or int(chk.min()) < -G.num_cls):
+            raise IndexError("target verb id out of range for %d classes" % G.num_cls)
     else:
         gh = go = torch.zeros(1, 4, device=dev); gv = torch.zeros(1, dtype=torch.int64, device=dev)
     labels = torch.empty(Pn, G.num_cls, dtype=torch.float32, device=dev)
@@ -834,6 +853,8 @@ def interaction_head_from_pooled(ih, features, image_shapes, box_features, box_c
         tables.cell_orow, tables.cell_img = run["cell_orow"].data_ptr(), run["cell_img"].data_ptr()
         tables.hum_off, tables.box_off, tables.pair_off = seg.d_hum_off.data_ptr(), seg.d_box_off.data_ptr(), seg.d_pair_off.data_ptr()
         tables.labels, tables.scores = labels_dev.data_ptr(), scores_dev.data_ptr()
+        if run.get("_train"):
+            tables.logit_row = run["pair2cell"].data_ptr()         # training layout: logits live in cell rows
         dict.__setitem__(run, "_post_tables", (tkey, tables))
     # entries per image (sizes the outputs): closed form on the host, no device round trip
     pc = meta.get("_skg_post")
@@ -888,8 +909,11 @@ def interaction_head_from_pooled(ih, features, image_shapes, box_features, box_c
         hoi = ops.binary_focal_loss(scores, lab_e, reduction="sum", gamma=0.2) / n_p[0]
         inter = ops.binary_focal_loss(weights, unary, reduction="sum", gamma=2.0) / n_p[1]
         pos, neg, eh, et, rl, rn = _transh_pos_neg(G, run, gt, targets)
-        ns = NegativeSampling(loss=MarginLoss(margin=1), batch_size=256).to(dev)
-        transh = ns(pos, neg, eh, rl, rn, et) / n_p[1]
+        ns = ih.__dict__.get("_skg_ns")                      # built once per head (head.py:229-231 builds it per call)
+        if ns is None or ns[0] != dev:
+            ns = ih.__dict__["_skg_ns"] = (dev, NegativeSampling(loss=MarginLoss(margin=1), batch_size=256).to(dev))
+        transh = ns[1](pos, neg, eh, rl, rn, et) / n_p[1]
+        ih.__dict__["_skg_last_post"] = dict(tables=tables, gt=gt, n_p=n_p, keep=(labels_dev, scores_dev, boxes_cat))
         results.append(dict(hoi_loss=hoi, interactiveness_loss=inter, transH_loss=transh))
     return results
 

@@ -239,6 +239,12 @@ class MarginLoss(Loss):
         p = p_score.reshape(-1)
         if p.numel() != n_score.shape[0] or n_score.dim() != 2:
             if p_score.shape == n_score.shape:        # element-wise case
+                if self.adv_flag and n_score.shape[1] > 1:
+                    # per-element positives against [rows, cols] negatives under the self-adversarial weighting: the softmax
+                    # runs over each ROW's columns (MarginLoss.py:29-30), which the [rows] x [rows, cols] kernel layout cannot
+                    # express -- rare shape, plain tensor expression
+                    m = self.margin.to(p_score.device)
+                    return (self.get_weights(n_score) * torch.max(p_score - n_score, -m)).sum(dim=-1).mean() + m
                 p = p_score.reshape(-1); n_score = n_score.reshape(-1, 1)
             else:
                 raise RuntimeError("p_score %s does not broadcast against n_score %s"

@@ -1,194 +1,369 @@
-"""Differentiable (training) pass of the interaction head: BASELINE configs[2], SURVEY 8(b) "fwd/bwd", 8(e).
+"""Training pass of the interaction head on the native kernels: BASELINE configs[2], SURVEY 8(b) "fwd/bwd", 8(e).
 
-Every dense contraction of the head -- forward, input gradient and weight gradient -- runs on the hand-written
-tcgen05 GEMM (``skg_gemm_bf16``, csrc/gemm.cu) through ``LinearFn``; pair enumeration + spatial encoding, GT
-association, priors, post-processing indices, the focal losses and the TransH scores / margin loss are the same
-CUDA kernels the inference path uses.  The element-wise glue between the GEMMs (Hadamard products, ReLU masks,
-segment softmax, LayerNorm) is expressed with ATen ops so that autograd provides its backward: PyTorch is the
-plumbing here (device memory + autograd tape), the contractions are ours.  The forward uses the same algebraic
-restructuring as the inference engine: 16-branch MBFs concatenated, ``attention_head.fc_1``
-split per node, one fused ``fc_2`` GEMM for the four MBFs, ``fc_3`` of the messages applied after the weighted sum,
-the two identical message-passing iterations computed once (SURVEY defect 5: only the last one reaches the loss).
+The reference trains the head with autograd (utils.py:213-229: forward, ``loss.backward()``, optimiser step; losses
+head.py:153-235).  Here one training step is three C-ABI calls around the loss bookkeeping:
 
-Reference: GraphHead.forward head.py:769-993, InteractionHead.forward head.py:389-427, losses head.py:153-235.
+    skg_head_forward(SKG_HEAD_TRAIN)   the inference chain, keeping what the backward needs (csrc/forward.cu)
+    skg_head_post + loss kernels        result dicts, GT association, focal losses, TransH margin loss (unchanged)
+    skg_head_backward                   every dX / dW / db of the chain (csrc/backward.cu, csrc/trainops.cu)
+
+and two descriptor-driven block-copy launches (``skg_block_copy``): packing the reference's per-branch fp32 parameters
+into the concatenated bf16 operands (+ the transposed copies the dX GEMMs read) once per optimiser step, and unpacking
+the packed fp32 gradients into the per-branch ``.grad`` tensors.  PyTorch is the plumbing: it owns the parameters, the
+``.grad`` buffers and the optimiser, and a one-node autograd Function makes ``loss.backward()`` run the native backward
+(the gradients are ACCUMULATED into ``p.grad`` like autograd does; ``transH_loss`` keeps its own tape through the TransH
+tables).  Gradients of the head's parameters w.r.t. ``hoi_loss`` and ``interactiveness_loss``; the TransH entity rows
+that enter fc_head / fc_tail are constants of the step (the reference re-draws the tables on every call, head.py:574-578).
 """
+import ctypes
+import weakref
 from typing import List, Optional
 
+import numpy as np
 import torch
-import torch.nn.functional as F
 from torch import Tensor
 
 from . import _lib
 
-
-def _ceil(x: int, m: int) -> int:
-    return (x + m - 1) // m * m
+_SRC_BF16, _DST_BF16, _ACC, _SCALE = 1, 2, 4, 8
 
 
-def _operand(t: Tensor) -> Tensor:
-    """[rows, K] -> bf16, K contiguous, row pitch a multiple of 8 elements (TMA: 16-byte pitch), 16-byte aligned."""
-    rows, k = t.shape
-    kp = _ceil(k, 8)
-    if kp == k:
-        return t.to(torch.bfloat16).contiguous()
-    out = torch.zeros(rows, kp, dtype=torch.bfloat16, device=t.device)
-    out[:, :k] = t
-    return out
+class BlockDesc(ctypes.Structure):
+    """Mirror of ``skg_block_desc``."""
+    _fields_ = [("src", ctypes.c_void_p), ("dst", ctypes.c_void_p), ("dst_t", ctypes.c_void_p),
+                ("rows", ctypes.c_int32), ("cols", ctypes.c_int32),
+                ("ld_src", ctypes.c_int64), ("ld_dst", ctypes.c_int64), ("ld_dst_t", ctypes.c_int64),
+                ("flags", ctypes.c_int32), ("scale", ctypes.c_float)]
 
 
-def _operand_t(t: Tensor) -> Tensor:
-    """[rows, K] -> its transpose [K, rows] as a bf16 operand (rows become the contraction dimension)."""
-    rows, k = t.shape
-    rp = _ceil(rows, 8)
-    if rp == rows:
-        return t.to(torch.bfloat16).t().contiguous()
-    out = torch.zeros(k, rp, dtype=torch.bfloat16, device=t.device)
-    out[:, :rows] = t.t()
-    return out
+class HeadWeightsT(ctypes.Structure):
+    """Mirror of ``skg_head_weights_t``."""
+    _fields_ = [(k, ctypes.c_void_p) for k in ("Wb2T", "Wsp1T", "Wsp2T", "WfcT", "W_hprojT", "W_oprojT", "W2catT", "W3attT",
+                                               "W3osT", "W3soT", "W3gT", "WpredT")]
 
 
-def gemm_nt(A: Tensor, B: Tensor, K: int, bias: Optional[Tensor] = None, relu: bool = False) -> Tensor:
-    """fp32 [M, N] = A[M, :K] @ B[N, :K]^T (+ bias) (ReLU) on skg_gemm_bf16; A, B bf16 operands from ``_operand``."""
-    M, N = A.shape[0], B.shape[0]
-    np_ = _ceil(N, 8)
-    out = torch.empty(M, np_, dtype=torch.float32, device=A.device)
-    if M == 0:
-        return out[:, :N]
-    bp = None
-    if bias is not None:
-        bp = torch.zeros(_ceil(N, 256), dtype=torch.float32, device=A.device)
-        bp[:N] = bias
-    g = _lib.epilogue_group(relu=relu, bias=bp, out_f32=out)
-    _lib.gemm_bf16(A, B, [g], M=M, N=N, K=K)
-    return out if np_ == N else out[:, :N]
+_GRAD_FIELDS = ("Wb1", "bb1", "Wb2", "bb2", "Wsp0", "bsp0", "Wsp1", "bsp1", "Wsp2", "bsp2", "Wfc", "bfc", "W_hproj", "b_hproj",
+                "W_oproj", "b_oproj", "Wg1", "bg1", "W2cat", "b2cat", "W3att", "b3att", "W3os", "b3os", "W3so", "b3so", "W3g",
+                "b3g", "w_adj", "b_adj", "ln_h_w", "ln_h_b", "ln_o_w", "ln_o_b", "Wpred", "bpred")
 
 
-class LinearFn(torch.autograd.Function):
-    """y = x W^T + b (optionally ReLU) with all three GEMMs (y, dx, dW) on the tcgen05 kernel; bf16 operands,
-    fp32 accumulation, fp32 results; the bias gradient is a column sum."""
+class HeadGrads(ctypes.Structure):
+    """Mirror of ``skg_head_grads``."""
+    _fields_ = [(k, ctypes.c_void_p) for k in _GRAD_FIELDS]
+
+
+class HeadLossArgs(ctypes.Structure):
+    """Mirror of ``skg_head_loss_args``."""
+    _fields_ = [("tables", ctypes.POINTER(_lib.PostTables)), ("gt_labels", ctypes.c_void_p), ("n_p", ctypes.c_void_p),
+                ("g_hoi", ctypes.c_void_p), ("g_int", ctypes.c_void_p), ("prior_power", ctypes.c_float)]
+
+
+class _HadamardBwd(ctypes.Structure):
+    """Mirror of ``skg_hadamard_bwd`` (only the tests call the kernel on its own)."""
+    _fields_ = [("S", ctypes.c_void_p), ("ld_s", ctypes.c_int64),
+                ("dP_att", ctypes.c_void_p), ("dP_fin", ctypes.c_void_p), ("dP_os", ctypes.c_void_p), ("dP_so", ctypes.c_void_p),
+                ("dP_g", ctypes.c_void_p), ("ld_dp", ctypes.c_int64),
+                ("hproj", ctypes.c_void_p), ("oproj", ctypes.c_void_p), ("U2h", ctypes.c_void_p), ("U2o", ctypes.c_void_p),
+                ("GT", ctypes.c_void_p), ("dS", ctypes.c_void_p), ("ld_ds", ctypes.c_int64),
+                ("dhproj", ctypes.c_void_p), ("doproj", ctypes.c_void_p), ("dU2h", ctypes.c_void_p), ("dU2o", ctypes.c_void_p),
+                ("dGT", ctypes.c_void_p), ("box_off", ctypes.c_void_p), ("hum_off", ctypes.c_void_p), ("cell_off", ctypes.c_void_p),
+                ("num_images", ctypes.c_int32), ("R", ctypes.c_int32)]
+
+
+class _BlockTable:
+    """A list of 2-D block copies executed as ONE ``skg_block_copy`` launch (descriptor + tile tables live on the device)."""
+
+    def __init__(self, device):
+        self.device = device
+        self.descs: List[BlockDesc] = []
+        self.keep = []
+        self.d_descs = self.d_tiles = None
+        self.num_tiles = 0
+
+    def add(self, src: Tensor, dst: Optional[Tensor], dst_t: Optional[Tensor] = None, flags: int = 0, scale: float = 1.0):
+        """src [rows, cols] -> dst [rows, cols] (+ dst_t [cols, rows]); 2-D views with unit inner stride."""
+        assert src.dim() == 2 and src.stride(1) == 1 and (dst is None or (dst.shape == src.shape and dst.stride(1) == 1))
+        d = BlockDesc()
+        d.src, d.dst = src.data_ptr(), (dst.data_ptr() if dst is not None else None)
+        d.rows, d.cols = int(src.shape[0]), int(src.shape[1])
+        d.ld_src, d.ld_dst = int(src.stride(0)), (int(dst.stride(0)) if dst is not None else 0)
+        if dst_t is not None:
+            assert tuple(dst_t.shape) == (src.shape[1], src.shape[0]) and dst_t.stride(1) == 1 and dst_t.dtype == torch.bfloat16
+            d.dst_t, d.ld_dst_t = dst_t.data_ptr(), int(dst_t.stride(0))
+        f = flags
+        if src.dtype == torch.bfloat16:
+            f |= _SRC_BF16
+        if dst is not None and dst.dtype == torch.bfloat16:
+            f |= _DST_BF16
+        if scale != 1.0:
+            f |= _SCALE
+        d.flags, d.scale = f, float(scale)
+        self.descs.append(d)
+        self.keep.append((src, dst, dst_t))
+
+    def finalize(self):
+        n = len(self.descs)
+        arr = (BlockDesc * n)(*self.descs)
+        raw = np.frombuffer(arr, dtype=np.uint8).copy()
+        self.d_descs = torch.from_numpy(raw).to(self.device)
+        tiles = []
+        for i, d in enumerate(self.descs):
+            rr = np.arange(0, d.rows, 32, dtype=np.int32); cc = np.arange(0, d.cols, 32, dtype=np.int32)
+            g = np.stack(np.meshgrid(rr, cc, indexing="ij"), -1).reshape(-1, 2)
+            tiles.append(np.concatenate([np.full((len(g), 1), i, np.int32), g], 1))
+        t = np.concatenate(tiles).astype(np.int32)
+        self.num_tiles = int(t.shape[0])
+        self.d_tiles = torch.from_numpy(np.ascontiguousarray(t)).to(self.device)
+        return self
+
+    def run(self):
+        with _lib.on_device(self.device):
+            _lib.call("skg_block_copy", _lib.ptr(self.d_descs), _lib.ptr(self.d_tiles), self.num_tiles, _lib.stream_ptr(self.device))
+
+
+def _v(t: Tensor) -> Tensor:
+    """1-D tensor as a [1, n] row block."""
+    return t.reshape(1, -1)
+
+
+class TrainState:
+    """Everything the native training step keeps per head: the packed bf16 operands (shared layout with the inference
+    engine), their transposed copies, the packed fp32 gradient buffer and the two block-copy tables.
+
+    ``refresh()`` re-packs after an optimiser step (one launch, detected through the parameters' version counters;
+    ``force=True`` after writes the counters cannot see).  ``grads_into_params()`` adds the packed gradients of the last
+    backward into the per-branch ``p.grad`` tensors (allocated as views of one flat buffer when missing)."""
+
+    def __init__(self, ih):
+        from . import engine
+        self.ih = weakref.ref(ih)
+        self.pk = engine.PackedHead(ih)                 # initial pack through the reference-layout tensors
+        pk, G = self.pk, ih.box_pair_head
+        dev = pk.device
+        self.device = dev
+        R, E = pk.R, pk.E
+        bf = lambda *shape: torch.zeros(*shape, dtype=torch.bfloat16, device=dev)   # noqa: E731
+        self.T = dict(Wb2T=bf(E, E), Wsp1T=bf(128, 256), Wsp2T=bf(256, R), WfcT=bf(pk.fc_k, 2 * R), W_hprojT=bf(R, 2 * R),
+                      W_oprojT=bf(R, 2 * R), W2catT=bf(R, 4 * R), W3attT=bf(R, R), W3osT=bf(R, R), W3soT=bf(R, R), W3gT=bf(R, R),
+                      WpredT=bf(2 * R, pk.Wpred.shape[0]))
+        self.wt = HeadWeightsT()
+        for k, t in self.T.items():
+            setattr(self.wt, k, t.data_ptr())
+        # packed fp32 gradients: one flat buffer, regions in the layout of the packed operands
+        shapes = dict(Wb1=pk.Wb1.shape, bb1=(E,), Wb2=pk.Wb2.shape, bb2=(E,), Wsp0=pk.Wsp0.shape, bsp0=(128,), Wsp1=pk.Wsp1.shape,
+                      bsp1=(256,), Wsp2=pk.Wsp2.shape, bsp2=(R,), Wfc=pk.Wfc.shape, bfc=(2 * R,), W_hproj=pk.W_hproj.shape,
+                      b_hproj=(2 * R,), W_oproj=pk.W_oproj.shape, b_oproj=(2 * R,), Wg1=pk.Wg1.shape, bg1=(R,), W2cat=pk.W2cat.shape,
+                      b2cat=(4 * R,), W3att=(R, R), b3att=(R,), W3os=(R, R), b3os=(R,), W3so=(R, R), b3so=(R,), W3g=(R, R), b3g=(R,),
+                      w_adj=(R,), b_adj=(4,), ln_h_w=(R,), ln_h_b=(R,), ln_o_w=(R,), ln_o_b=(R,), Wpred=pk.Wpred.shape,
+                      bpred=(pk.Wpred.shape[0],))
+        total = sum((int(np.prod(s)) + 63) // 64 * 64 for s in shapes.values()) + 256
+        self.gflat = torch.zeros(total, dtype=torch.float32, device=dev)
+        self.g = {}
+        self.cg = HeadGrads()
+        o = 0
+        for k in _GRAD_FIELDS:
+            n = int(np.prod(shapes[k]))
+            self.g[k] = self.gflat[o:o + n].view(*shapes[k])
+            setattr(self.cg, k, self.g[k].data_ptr())
+            o += (n + 63) // 64 * 64
+        self._build_pack_table(ih)
+        self._unpack = None
+        self._grad_key = None
+        self.params = list(ih.parameters())
+        self.vsum = engine._version_sum(self.params)
+        self.pack.run()                                 # fills the transposed copies (and re-derives the operands)
+        self.anchor = torch.zeros(1, device=dev, requires_grad=True)
+
+    # ---- parameter -> operand map (the inverse, operand gradient -> parameter gradient, is built from the same list) ----
+    def _blocks(self, ih):
+        """Yields (parameter view [rows, cols], operand name, row offset, col offset, transposed-operand name or None,
+        kind) with kind 'w' (bf16 operand), 'f' (fp32 operand / bias), 'bsum' (fp32, summed over the branches)."""
+        G = ih.box_pair_head
+        pk = self.pk
+        R, E = pk.R, pk.E
+        out = []
+        w = lambda p, name, r0=0, c0=0, tname=None: out.append((p, name, r0, c0, tname, "w"))      # noqa: E731
+        f = lambda p, name, c0=0, kind="f": out.append((_v(p), name, 0, c0, None, kind))            # noqa: E731
+        w(G.box_head[1].weight, "Wb1"); f(G.box_head[1].bias, "bb1")
+        w(G.box_head[3].weight, "Wb2", tname="Wb2T"); f(G.box_head[3].bias, "bb2")
+        out.append((G.spatial_head[0].weight, "Wsp0", 0, 0, None, "f")); f(G.spatial_head[0].bias, "bsp0")
+        w(G.spatial_head[2].weight, "Wsp1", tname="Wsp1T"); f(G.spatial_head[2].bias, "bsp1")
+        w(G.spatial_head[4].weight, "Wsp2", tname="Wsp2T"); f(G.spatial_head[4].bias, "bsp2")
+        fh, ft = G.fc_head[0], G.fc_tail[0]
+        w(fh.weight[:, :E], "Wfc", 0, 0, "WfcT")
+        out.append((fh.weight[:, E:], "Wfh_ent", 0, 0, None, "f"))
+        f(fh.bias, "bfh")
+        w(ft.weight, "Wfc", R, 0, "WfcT"); f(ft.bias, "bfc", R)
+        sub = R // G.attention_head.cardinality
+        for c in range(G.attention_head.cardinality):
+            a1 = G.attention_head.fc_1[c]
+            w(a1.weight[:, :E], "W_hproj", c * sub, 0, "W_hprojT"); w(a1.weight[:, E:], "W_oproj", c * sub, 0, "W_oprojT")
+            f(a1.bias, "b_oproj", c * sub)
+            w(G.sub_to_obj.fc_1[c].weight, "W_hproj", R + c * sub, 0, "W_hprojT"); f(G.sub_to_obj.fc_1[c].bias, "b_hproj", R + c * sub)
+            w(G.obj_to_sub.fc_1[c].weight, "W_oproj", R + c * sub, 0, "W_oprojT"); f(G.obj_to_sub.fc_1[c].bias, "b_oproj", R + c * sub)
+            w(G.attention_head_g.fc_1[c].weight, "Wg1", c * sub, 0); f(G.attention_head_g.fc_1[c].bias, "bg1", c * sub)
+            for gi, m in enumerate((G.attention_head, G.obj_to_sub, G.sub_to_obj, G.attention_head_g)):
+                w(m.fc_2[c].weight, "W2cat", gi * R + c * sub, 0, "W2catT"); f(m.fc_2[c].bias, "b2cat", gi * R + c * sub)
+            for m, nm in ((G.attention_head, "att"), (G.obj_to_sub, "os"), (G.sub_to_obj, "so"), (G.attention_head_g, "g")):
+                w(m.fc_3[c].weight, "W3" + nm, 0, c * sub, "W3" + nm + "T"); f(m.fc_3[c].bias, "b3" + nm, 0, "bsum")
+        f(G.adjacency.weight.reshape(-1), "w_adj"); f(G.adjacency.bias, "b_adj")
+        f(G.norm_h.weight, "ln_h_w"); f(G.norm_h.bias, "ln_h_b"); f(G.norm_o.weight, "ln_o_w"); f(G.norm_o.bias, "ln_o_b")
+        nc = pk.num_cls
+        w(ih.box_pair_predictor.weight, "Wpred", 0, 0, "WpredT"); f(ih.box_pair_predictor.bias, "bpred", 0)
+        w(ih.box_pair_suppressor.weight, "Wpred", nc, 0, "WpredT"); f(ih.box_pair_suppressor.bias, "bpred", nc)
+        return out
+
+    def _operand(self, name: str) -> Optional[Tensor]:
+        pk = self.pk
+        if name in ("ln_h_w", "ln_h_b", "ln_o_w", "ln_o_b"):
+            return pk.ln[("ln_h_w", "ln_h_b", "ln_o_w", "ln_o_b").index(name)]
+        if name == "b_adj":
+            return None                                  # a host float of the descriptor: softmax is shift invariant
+        t = getattr(pk, name)
+        return t if t.dim() > 1 else _v(t)
+
+    def _build_pack_table(self, ih):
+        tab = _BlockTable(self.device)
+        self._bsum = []
+        for p, name, r0, c0, tname, kind in self._blocks(ih):
+            dst_full = self._operand(name)
+            if dst_full is None:
+                continue
+            src = p.detach()
+            rows, cols = src.shape
+            dst = dst_full[r0:r0 + rows, c0:c0 + cols]
+            if dst.data_ptr() == src.data_ptr():
+                continue                                 # the operand aliases the parameter (fp32 biases, LayerNorm affine)
+            dst_t = self.T[tname][c0:c0 + cols, r0:r0 + rows] if tname else None
+            if kind == "bsum":
+                if not any(d is dst_full for d in self._bsum):
+                    self._bsum.append(dst_full)
+                tab.add(src, dst, None, flags=_ACC)
+            else:
+                tab.add(src, dst, dst_t)
+        self.pack = tab.finalize()
+
+    def refresh(self, force: bool = False) -> None:
+        from . import engine
+        vs = engine._version_sum(self.params)
+        if not force and vs == self.vsum:
+            return
+        for t in self._bsum:
+            t.zero_()
+        self.pack.run()
+        self.vsum = vs
+
+    # ---- gradients --------------------------------------------------------------------------------------------------
+    def _ensure_unpack(self):
+        params = self.params
+        missing = [p for p in params if p.requires_grad and p.grad is None]
+        if missing:
+            flat = torch.zeros(sum(p.numel() for p in missing), dtype=torch.float32, device=self.device)
+            o = 0
+            for p in missing:
+                p.grad = flat[o:o + p.numel()].view_as(p)
+                o += p.numel()
+        key = tuple(p.grad.data_ptr() if p.grad is not None else 0 for p in params)
+        if self._unpack is not None and key == self._grad_key:
+            return
+        ih = self.ih()
+        tab = _BlockTable(self.device)
+        for p, name, r0, c0, tname, kind in self._blocks(ih):
+            base = p._base if p._base is not None else p
+            if not getattr(base, "requires_grad", False) or base.grad is None:
+                continue
+            if name in ("Wfh_ent", "bfh"):               # fc_head bias / entity columns: both come from dbfc[:R]
+                if name == "bfh":
+                    tab.add(self.g["bfc"].reshape(1, -1)[:, :p.shape[1]], base.grad.reshape(1, -1), None, flags=_ACC)
+                continue
+            gsrc = self.g[name] if self.g[name].dim() > 1 else _v(self.g[name])
+            rows, cols = p.shape
+            src = gsrc[r0:r0 + rows, c0:c0 + cols]
+            # the parameter view p (a slice / reshape of the parameter) maps onto the same slice of its .grad
+            gview = base.grad.as_strided(p.shape, p.stride(), base.grad.storage_offset() + p.storage_offset() - base.storage_offset())
+            tab.add(src, gview, None, flags=_ACC)
+        self._unpack = tab.finalize()
+        self._grad_key = key
+
+    def grads_into_params(self) -> None:
+        """p.grad += packed gradients of the last skg_head_backward (one block-copy launch + the rank-1 entity block)."""
+        self._ensure_unpack()
+        self._unpack.run()
+        ih = self.ih()
+        G = ih.box_pair_head
+        fh = G.fc_head[0].weight
+        if fh.requires_grad and fh.grad is not None:
+            ent = G.transh_head.transh.ent_embeddings.weight.detach()
+            # d fc_head.weight[:, E:] = sum_rows g_row (x) E[human_idx] = dbias (x) E[human_idx]   (head_stack rows are constant)
+            fh.grad[:, self.pk.E:].addmm_(self.g["bfc"][:self.pk.R].unsqueeze(1), ent[G.human_idx].float().unsqueeze(0))
+
+
+def train_state(ih) -> TrainState:
+    ts = ih.__dict__.get("_skg_train")
+    if ts is None or ts.device != next(ih.parameters()).device or ts.params[0].data_ptr() != next(ih.parameters()).data_ptr():
+        ts = TrainState(ih)
+        ih.__dict__["_skg_train"] = ts
+    else:
+        ts.refresh()
+    return ts
+
+
+class _StepRecord:
+    """What ``loss.backward()`` needs from the forward of the same step."""
+
+    def __init__(self, ts, run, b, flags, ws, tables, gt, n_p, keep):
+        self.ts, self.run, self.b, self.flags, self.ws, self.tables, self.gt, self.n_p, self.keep = ts, run, b, flags, ws, tables, gt, n_p, keep
+        self.done = False
+
+    def backward(self, g_hoi: Optional[Tensor], g_int: Optional[Tensor]) -> None:
+        ts = self.ts
+        dev = ts.device
+        zero = None
+        if g_hoi is None or g_int is None:
+            zero = torch.zeros(1, dtype=torch.float32, device=dev)
+        gh = (g_hoi if g_hoi is not None else zero).reshape(-1).float().contiguous()
+        gi = (g_int if g_int is not None else zero).reshape(-1).float().contiguous()
+        la = HeadLossArgs()
+        la.tables = ctypes.pointer(self.tables)
+        la.gt_labels, la.n_p, la.g_hoi, la.g_int, la.prior_power = self.gt.data_ptr(), self.n_p.data_ptr(), gh.data_ptr(), gi.data_ptr(), 1.0
+        with _lib.on_device(dev):
+            ts.gflat.zero_()
+            _lib.call("skg_head_backward", ctypes.byref(ts.pk.cw), ctypes.byref(ts.wt), ctypes.byref(self.b), ctypes.byref(la),
+                      ctypes.byref(ts.cg), self.flags, _lib.ptr(self.ws), self.ws.numel(), _lib.stream_ptr(dev))
+        ts.grads_into_params()
+        self.done = True
+
+
+class _HeadLossFn(torch.autograd.Function):
+    """One autograd node for the whole head: forward hands out the two loss values the kernels computed, backward runs
+    skg_head_backward and ADDS the parameter gradients into ``p.grad`` (so the node itself has no differentiable inputs
+    besides a dummy anchor)."""
 
     @staticmethod
-    def forward(ctx, x: Tensor, W: Tensor, b: Optional[Tensor], relu: bool):
-        _lib.require_cuda(x, W)
-        K = x.shape[1]
-        y = gemm_nt(_operand(x), _operand(W), K, b, relu)
-        ctx.save_for_backward(x, W, y if relu else None)
-        ctx.has_bias = b is not None
-        ctx.relu = relu
-        return y
+    def forward(ctx, anchor, hoi, inter, rec):
+        ctx.rec = rec
+        return hoi.clone(), inter.clone()
 
     @staticmethod
-    def backward(ctx, g: Tensor):
-        x, W, y = ctx.saved_tensors
-        if ctx.relu:
-            g = g * (y > 0)
-        M, K = x.shape
-        N = W.shape[0]
-        gx = gW = gb = None
-        if ctx.needs_input_grad[0]:
-            gx = gemm_nt(_operand(g), _operand_t(W), N)                 # [M, K] = g[M, N] @ W[N, K]
-            gx = gx if gx.is_contiguous() else gx.contiguous()
-        if ctx.needs_input_grad[1]:
-            gW = gemm_nt(_operand_t(g), _operand_t(x), M)               # [N, K] = g^T[N, M] @ x[M, K]
-            gW = gW if gW.is_contiguous() else gW.contiguous()
-        if ctx.has_bias and ctx.needs_input_grad[2]:
-            gb = g.sum(0)
-        return gx, gW, gb, None
-
-
-def linear(x: Tensor, W: Tensor, b: Optional[Tensor] = None, relu: bool = False) -> Tensor:
-    return LinearFn.apply(x, W, b, relu)
-
-
-def segment_softmax(v: Tensor, seg: Tensor, num_segments: int) -> Tensor:
-    """softmax of ``v`` inside each segment id (head.py:903, 914: adjacency rows / columns of one image)."""
-    m = torch.full((num_segments,), float("-inf"), dtype=v.dtype, device=v.device).scatter_reduce(0, seg, v.detach(), "amax")
-    e = torch.exp(v - m[seg])
-    s = torch.zeros(num_segments, dtype=v.dtype, device=v.device).index_add(0, seg, e)
-    return e / s[seg]
-
-
-def head_logits(ih, features3: Tensor, box_features: Tensor, pe: dict) -> Tensor:
-    """Differentiable logits [pairs, num_cls + 1] (predictor | suppressor) from the pooled box features.
-    ``pe`` = engine.enumerate_pairs(...) of the batch (encodings + row maps, no gradient)."""
-    G = ih.box_pair_head
-    seg = pe["seg"]
-    dev = box_features.device
-    R = G.representation_size
-    hrow, orow, img = pe["cell_hrow"].long(), pe["cell_orow"].long(), pe["cell_img"].long()
-    p2c = pe["pair2cell"].long()
-    NH, NB = seg.total_humans, seg.total_boxes
-    # node rows: box_head on every box, entity rows appended (head.py:812, 875-885)
-    node = linear(linear(box_features.flatten(1), G.box_head[1].weight, G.box_head[1].bias, True),
-                  G.box_head[3].weight, G.box_head[3].bias, True)
-    ent = G.transh_head.transh.ent_embeddings.weight.detach()
-    box_local = torch.cat([torch.arange(int(k)) for k in seg.n]).to(dev)                   # box index inside its image
-    human_rows = torch.cat([torch.arange(int(o), int(o) + int(k)) for o, k in zip(seg.box_off[:-1], seg.n_h)]).to(dev)
-    hN = linear(torch.cat([node[human_rows], ent[G.human_idx].expand(NH, -1)], 1), G.fc_head[0].weight, G.fc_head[0].bias, True)
-    oN = linear(torch.cat([node, ent[box_local]], 1), G.fc_tail[0].weight, G.fc_tail[0].bias, True)
-    # spatial head (head.py:662-669); the 46 -> 128 layer stays fp32 (inputs span [-23, 1e3]) like the inference kernel
-    sh = G.spatial_head
-    sp = F.relu(F.linear(pe["enc"], sh[0].weight, sh[0].bias))
-    sp = linear(linear(sp, sh[2].weight, sh[2].bias, True), sh[4].weight, sh[4].bias, True)
-    a_W1, a_b1, a_W2, a_b2, a_W3, a_b3 = G.attention_head.packed()
-    o_W1, o_b1, o_W2, o_b2, o_W3, o_b3 = G.obj_to_sub.packed()
-    s_W1, s_b1, s_W2, s_b2, s_W3, s_b3 = G.sub_to_obj.packed()
-    g_W1, g_b1, g_W2, g_b2, g_W3, g_b3 = G.attention_head_g.packed()
-    # one fc_2 GEMM for the four MBFs that read the spatial features
-    S = linear(sp, torch.cat([a_W2, o_W2, s_W2, g_W2]), torch.cat([a_b2, o_b2, s_b2, g_b2]))
-    S_att, S_os, S_so, S_g = S.split(R, dim=1)
-    W1h, W1o = a_W1[:, :R], a_W1[:, R:]
-
-    def att_tables(h, o):                                                                  # fc_1 of cat(h[x], o[y]) per node
-        return linear(h, W1h), linear(o, W1o, a_b1)
-    Uh, Uo = att_tables(hN, oN)
-    wts = linear(F.relu(S_att * (Uh[hrow] + Uo[orow])), a_W3, a_b3, True)                  # head.py:896
-    adj = F.linear(wts, G.adjacency.weight, G.adjacency.bias).squeeze(1)                   # head.py:897
-    # messages (head.py:900-925): fc_3 commutes with the softmax-weighted sum (weights sum to 1)
-    H_os = F.relu(S_os * linear(oN, o_W1, o_b1)[orow])
-    H_so = F.relu(S_so * linear(hN, s_W1, s_b1)[hrow])
-    Zh = torch.zeros(NH, R, device=dev).index_add(0, hrow, segment_softmax(adj, hrow, NH)[:, None] * H_os)
-    Zo = torch.zeros(NB, R, device=dev).index_add(0, orow, segment_softmax(adj, orow, NB)[:, None] * H_so)
-    h_enc = F.layer_norm(hN + linear(Zh, o_W3, o_b3, True), (R,), G.norm_h.weight, G.norm_h.bias, G.norm_h.eps)
-    o_enc = F.layer_norm(oN + linear(Zo, s_W3, s_b3, True), (R,), G.norm_o.weight, G.norm_o.bias, G.norm_o.eps)
-    # final fusion on the valid pairs (head.py:966-973)
-    Uh2, Uo2 = att_tables(h_enc, o_enc)
-    f1 = linear(F.relu(S_att[p2c] * (Uh2[hrow[p2c]] + Uo2[orow[p2c]])), a_W3, a_b3, True)
-    glob = features3.mean(dim=(2, 3))
-    f2 = linear(F.relu(S_g[p2c] * linear(glob, g_W1, g_b1)[img[p2c]]), g_W3, g_b3, True)
-    feat = torch.cat([f1, f2], 1)
-    Wl = torch.cat([ih.box_pair_predictor.weight, ih.box_pair_suppressor.weight])
-    bl = torch.cat([ih.box_pair_predictor.bias, ih.box_pair_suppressor.bias])
-    return linear(feat, Wl, bl)                                                            # head.py:410-411
+    def backward(ctx, g_hoi, g_int):
+        ctx.rec.backward(g_hoi, g_int)
+        return None, None, None, None
 
 
 def training_forward(ih, features, image_shapes, box_features: Tensor, box_coords: List[Tensor], box_labels, box_scores,
                      targets, meta=None) -> List[dict]:
     """InteractionHead.forward in training mode from the pooled box features on (head.py:389-427): the per-image
     result dicts plus the loss dict, with ``hoi_loss`` / ``interactiveness_loss`` differentiable w.r.t. every head
-    parameter and ``transH_loss`` w.r.t. the TransH tables."""
-    from . import engine, ops
+    parameter (native backward) and ``transH_loss`` w.r.t. the TransH tables."""
+    from . import engine
     assert targets is not None, "Targets should be passed during training"                 # head.py:380-381
     G = ih.box_pair_head
     meta, boxes_cat, labels_dev, scores_dev = engine._prep_inputs(G, features, box_features, box_coords, box_labels,
                                                                   box_scores, meta)
-    n, n_h = meta["n"], meta["n_h"]
-    if any(k > G.transh_head.num_object for k in n):
-        raise IndexError("index out of range in self")                                     # head.py:572
-    n_h_eff = [0 if (h == 0 or k <= 1) else h for h, k in zip(n_h, n)]
-    dev = box_features.device
-    # pair enumeration + spatial encoding + row maps: the same kernel as inference, no tape (boxes carry no gradient)
-    pe = engine.enumerate_pairs(None, n_h_eff, image_shapes, seg=engine.Segments(n_h_eff, n, image_shapes, dev),
-                                boxes_cat=boxes_cat)
-    seg = pe["seg"]
-    with torch.enable_grad():
-        logits = head_logits(ih, features["3"], box_features, pe)
-    # post-processing indices, priors, GT labels and the TransH loss from the native kernels, fed with the taped logits
-    lg = logits.detach()
-    run = dict(pe)
-    run.update(logits=lg if lg.is_contiguous() else lg.contiguous(),
-               post_i32=torch.empty(2 * max(seg.total_boxes, 1), dtype=torch.int32, device=dev),
-               post_i64=torch.empty(max(seg.total_humans, 1) + 2 * seg.B + 1, dtype=torch.int64, device=dev))
+    ts = train_state(ih)
+    with torch.no_grad():
+        run = engine.head_forward(ih, features["3"], image_shapes, box_features.detach(), boxes_cat, meta, precise_logits=False,
+                                  graph=False, train=True, pk=ts.pk)
     was_training = ih.training
     ih.train()
     try:
@@ -197,22 +372,11 @@ def training_forward(ih, features, image_shapes, box_features: Tensor, box_coord
                                                           box_labels, box_scores, targets=targets, meta=meta, run=run)
     finally:
         ih.train(was_training)
-    with torch.enable_grad():
-        native_losses = results.pop()
-        nc = G.num_cls
-        dev = logits.device
-        gx = torch.cat([r["index"] + int(o) for r, o in zip(results, seg.pair_off[:-1])])
-        gy = torch.cat([r["prediction"] for r in results])
-        prior = torch.cat([r["prior"] for r in results], 1)
-        lab = torch.cat([r["labels"] for r in results]); unary = torch.cat([r["unary_labels"] for r in results])
-        weights = torch.sigmoid(logits[:, nc])
-        scores = torch.sigmoid(logits[:, :nc])[gx, gy] * prior.prod(0) * weights[gx].detach()   # head.py:316
-        n_p = torch.stack([(lab != 0).sum(), (unary != 0).sum()]).float()
-        if ih.distributed:
-            from .shard import average_normalisers
-            n_p = average_normalisers(n_p)
-        hoi = ops.binary_focal_loss(scores, lab, reduction="sum", gamma=0.2) / n_p[0]      # head.py:153-177
-        inter = ops.binary_focal_loss(weights, unary, reduction="sum", gamma=2.0) / n_p[1]  # head.py:180-205
-    ih.__dict__["_skg_last_train"] = dict(logits=logits, scores=scores, weights=weights)
-    results.append(dict(hoi_loss=hoi, interactiveness_loss=inter, transH_loss=native_losses["transH_loss"]))
+    losses = results.pop()
+    post = ih.__dict__["_skg_last_post"]
+    rec = _StepRecord(ts, run, run["_batch"], run["_flags"], run._ws, post["tables"], post["gt"], post["n_p"],
+                      keep=(boxes_cat, labels_dev, scores_dev, run.get("_keep")))
+    hoi, inter = _HeadLossFn.apply(ts.anchor, losses["hoi_loss"].detach(), losses["interactiveness_loss"].detach(), rec)
+    ih.__dict__["_skg_last_train"] = dict(logits=run["logits"], run=run, rec=rec)
+    results.append(dict(hoi_loss=hoi, interactiveness_loss=inter, transH_loss=losses["transH_loss"]))
     return results

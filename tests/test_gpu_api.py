@@ -116,11 +116,15 @@ def test_graph_head_tuple_vs_oracle():
     assert labels == [] and pos == [] and neg == []
 
 
-def test_training_pass_gradients_vs_oracle_autograd():
-    """hoi_loss + interactiveness_loss differentiated w.r.t. every head parameter: all three GEMMs of every dense
-    layer (y, dx, dW) on the tcgen05 kernel with bf16 operands, against fp32 autograd through the CPU oracle."""
-    gold = load_golden("head_small2_train")
-    batch = _batch(gold)
+def _grad_parity(shapes=None, gold_name=None, seed=77, tol_total=3e-2, tol_tensor=2.5e-1):
+    """hoi_loss + interactiveness_loss differentiated w.r.t. every head parameter by the NATIVE backward (skg_head_backward:
+    every dX / dW on the tcgen05 GEMM with bf16 operands, trainops.cu kernels in between, block-copy unpack into the
+    per-branch .grad tensors) against fp32 autograd through the CPU oracle."""
+    if gold_name is not None:
+        gold = load_golden(gold_name)
+        batch = _batch(gold)
+    else:
+        batch = synthetic.make_batch(shapes, seed=seed, with_targets=True)
     d = _to_dev(batch)
     ih = _head(True)
     otv = synthetic.hico_object_to_verb()
@@ -141,17 +145,17 @@ def test_training_pass_gradients_vs_oracle_autograd():
     for k in ("hoi_loss", "interactiveness_loss"):
         a, b = float(losses[k].detach()), float(ref_loss[k].detach())
         assert abs(a - b) <= 1e-2 * abs(b), (k, a, b)
-    assert abs(float(losses["transH_loss"].reshape(-1)[0]) - float(ref_loss["transH_loss"].reshape(-1)[0])) <= 1e-4
+    assert abs(float(losses["transH_loss"].detach().reshape(-1)[0]) - float(ref_loss["transH_loss"].detach().reshape(-1)[0])) <= 1e-4
     (losses["hoi_loss"] + losses["interactiveness_loss"]).backward()
-    # the native eval-style logits of the same step agree with the taped ones
-    # the taped logits agree with the fused inference path on the same inputs and weights
+    # the training-layout logits (cell rows) agree with the fused inference path on the same inputs and weights
     from skghoi_b200 import engine
     tr = ih.__dict__["_skg_last_train"]
+    train_logits = tr["logits"][tr["run"]["pair2cell"].long()].clone()
     meta = engine._host_meta(batch["box_labels"], batch["box_scores"], 49)
     with torch.no_grad():
         native = engine.head_forward(ih, d["features"]["3"], d["image_shapes"], d["box_features"], torch.cat(d["box_coords"]),
                                      meta)["logits"][:, :118].clone()
-    assert float((native - tr["logits"].detach()).abs().max()) <= 1e-2 * float(tr["logits"].abs().max())
+    assert float((native - train_logits).abs().max()) <= 1e-2 * float(train_logits.abs().max())
     worst = (0.0, None)
     num = den = 0.0
     stats = []
@@ -169,19 +173,66 @@ def test_training_pass_gradients_vs_oracle_autograd():
     total = (num / den) ** 0.5
     stats.sort(reverse=True)
     print("training gradients: total rel L2 %.3e, worst tensor %.3e (%s)" % (total, worst[0], worst[1]))
-    for rel, name, ref_n in stats[:12]:
+    for rel, name, ref_n in stats[:16]:
         print("   %.3e  |g_ref| %.3e  %s" % (rel, ref_n, name))
     import statistics
     print("   median per-tensor rel L2 %.3e" % statistics.median(s[0] for s in stats))
-    # bf16 operands (activations, weights AND the back-propagated gradient) in a ~10-GEMM-deep chain
-    assert total <= GRAD_TOL_TOTAL, total
+    assert total <= tol_total, total
     for rel, name, ref_n in stats:
-        assert rel <= GRAD_TOL_TENSOR or ref_n < 1e-6, (name, rel, ref_n)
+        assert rel <= tol_tensor or ref_n < 1e-6, (name, rel, ref_n)
+    return ih, losses
+
+
+def test_training_pass_gradients_vs_oracle_autograd():
+    """The tiny train golden (26 pairs): single 64-row branch tensors with |g| ~ 1e-3 carry 5-15 % bf16 noise, the full
+    gradient vector agrees to ~1.5 %."""
+    ih, losses = _grad_parity(gold_name="head_small2_train", tol_total=GRAD_TOL_TOTAL, tol_tensor=GRAD_TOL_TENSOR)
     # the TransH tables train through the margin loss only
     tab = ih.box_pair_head.transh_head.transh
     tab.zero_grad()
     losses["transH_loss"].sum().backward()
     assert tab.ent_embeddings.weight.grad is not None and float(tab.ent_embeddings.weight.grad.abs().sum()) > 0
+
+
+def test_training_pass_gradients_c2_sized_batch():
+    """gradient parity at <= 5e-2 per parameter tensor on a C2-sized batch (8 images x (16, 32), 3968
+    pairs) -- the per-tensor noise of the 26-pair fixture averages out."""
+    _grad_parity(shapes=[(16, 32)] * 8, seed=77, tol_total=2e-2, tol_tensor=5e-2)
+
+
+def test_training_step_accumulates_and_follows_optimizer_updates():
+    """p.grad is ACCUMULATED like autograd does (two backwards = twice the gradient), and the packed operands are
+    refreshed after an optimiser step (the second step sees the updated weights: its loss moves)."""
+    batch = synthetic.make_batch([(4, 9), (3, 7)], seed=5, with_targets=True)
+    d = _to_dev(batch)
+    ih = _head(True)
+    ih.box_pair_head.transh_head.negatives_on_device = True
+    params = [p for p in ih.parameters() if p.requires_grad]
+    opt = torch.optim.SGD(params, lr=1e-2)
+
+    def step(backward_twice=False):
+        res = ih.forward_from_pooled(d["features"], d["image_shapes"], d["box_features"], d["box_coords"], d["box_labels"],
+                                     d["box_scores"], d["targets"])
+        ls = res[-1]
+        tot = ls["hoi_loss"] + ls["interactiveness_loss"]
+        tot.backward(retain_graph=backward_twice)
+        if backward_twice:
+            tot.backward()
+        return float(tot.detach())
+    opt.zero_grad(set_to_none=False)
+    l0 = step()
+    g1 = [p.grad.detach().clone() for p in params]
+    opt.zero_grad(set_to_none=False)
+    step(backward_twice=True)
+    for a, b in zip(g1, params):
+        torch.testing.assert_close(b.grad, 2 * a, rtol=2e-2, atol=1e-6 + 2e-2 * float(a.abs().max()))
+    opt.zero_grad(set_to_none=False)
+    l1 = step()
+    opt.step()
+    opt.zero_grad(set_to_none=False)
+    l2 = step()
+    assert abs(l1 - l0) <= 1e-3 * abs(l0)            # same weights, same batch
+    assert l2 < l1                                   # one SGD step on this batch lowers its loss
 
 
 def test_interaction_head_full_forward_with_stock_preprocess():

@@ -6,7 +6,7 @@ MultiBranchFusion / MessageMBF module forwards (head.py:469-474, 509-530) -- all
 import pytest
 import torch
 
-from helpers import build_head, head_params, synthetic, logits_close
+from helpers import build_head, head_params, synthetic, logits_close, assert_logits_parity
 from oracle import head_oracle as O
 
 pytestmark = pytest.mark.gpu
@@ -51,8 +51,8 @@ def _oracle(case):
 @pytest.mark.parametrize("precise", [True, False])
 @pytest.mark.parametrize("case", list(CASES))
 def test_full_head_logits_vs_oracle(case, precise):
-    """Pair indices bit-exact, spatial encodings 1e-5, logits within 1e-2 relative in BOTH operational forms of SURVEY
-    8(d) (max-norm and per element) -- for the split-bf16 predictor and for the plain single-pass one."""
+    """Pair indices bit-exact, spatial encodings 1e-5, logits within 1e-2 relative (helpers.assert_logits_parity: max-norm,
+    relative L2 and the per-element band of SURVEY 8(d)) -- for the split-bf16 predictor and the plain single-pass one."""
     from skghoi_b200 import engine
     batch, res, lp_ref, ls_ref, taps = _oracle(case)
     ih = _gpu_head()
@@ -68,13 +68,8 @@ def test_full_head_logits_vs_oracle(case, precise):
     lg = out["logits"].cpu()
     lp, ls = lg[:, :117], lg[:, 117:]
     assert lp.shape == lp_ref.shape and ls.shape == ls_ref.shape
-    ok_p, st_p = logits_close(lp, lp_ref)
-    ok_s, st_s = logits_close(ls, ls_ref)
-    rel_p = float((lp - lp_ref).norm() / lp_ref.norm())
-    print(case, "precise" if precise else "plain", "logits_p", st_p, "rel_l2 %.3e" % rel_p, "logits_s", st_s)
-    assert st_p["max_abs"] <= 1e-2 * st_p["ref_max"] and rel_p <= 1e-2, st_p
-    assert st_s["max_abs"] <= 1e-2 * st_s["ref_max"], st_s
-    assert ok_p and ok_s, (st_p, st_s)                  # per-element form: |d| <= 1e-2 |ref| + 1e-2 rms(ref)
+    assert_logits_parity(lp, lp_ref, "%s %s logits_p" % (case, "precise" if precise else "plain"))
+    assert_logits_parity(ls, ls_ref, "%s %s logits_s" % (case, "precise" if precise else "plain"))
 
 
 @pytest.mark.parametrize("case", ["c2_8x16x32", "c5_2x40x80", "ragged"])
@@ -140,9 +135,8 @@ def test_vcoco_parameterisation_vs_oracle():
     lg = run["logits"].cpu()
     assert lg.shape[1] == nc + 1
     assert torch.equal(run["y_keep"].cpu(), torch.cat(taps["y_keep"]))
-    ok_p, st_p = logits_close(lg[:, :nc], lp_ref)
-    ok_s, st_s = logits_close(lg[:, nc:], ls_ref)
-    assert ok_p and ok_s, (st_p, st_s)
+    assert_logits_parity(lg[:, :nc], lp_ref, "vcoco logits_p")
+    assert_logits_parity(lg[:, nc:], ls_ref, "vcoco logits_s")
     for g, r in zip(got, res):
         assert torch.equal(g["index"].cpu(), r["index"]) and torch.equal(g["prediction"].cpu(), r["prediction"])
         assert torch.equal(g["object"].cpu(), r["object"])
