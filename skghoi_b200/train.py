@@ -170,8 +170,8 @@ class TrainState:
         self._unpack = None
         self._grad_key = None
         self.params = list(ih.parameters())
-        self.vsum = engine._version_sum(self.params)
-        self.pack.run()                                 # fills the transposed copies (and re-derives the operands)
+        self.vsum = -1
+        self.refresh(force=True)                        # fills the transposed copies (and re-derives the operands)
         self.anchor = torch.zeros(1, device=dev, requires_grad=True)
 
     # ---- parameter -> operand map (the inverse, operand gradient -> parameter gradient, is built from the same list) ----
@@ -216,7 +216,7 @@ class TrainState:
     def _operand(self, name: str) -> Optional[Tensor]:
         pk = self.pk
         if name in ("ln_h_w", "ln_h_b", "ln_o_w", "ln_o_b"):
-            return pk.ln[("ln_h_w", "ln_h_b", "ln_o_w", "ln_o_b").index(name)]
+            return _v(pk.ln[("ln_h_w", "ln_h_b", "ln_o_w", "ln_o_b").index(name)])
         if name == "b_adj":
             return None                                  # a host float of the descriptor: softmax is shift invariant
         t = getattr(pk, name)
