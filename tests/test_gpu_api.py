@@ -230,8 +230,12 @@ def test_training_step_accumulates_and_follows_optimizer_updates():
     g1 = [p.grad.detach().clone() for p in params]
     opt.zero_grad(set_to_none=False)
     step(backward_twice=True)
+    # two runs of the same step differ by the split-K summation order of box_head's first layer (fp32 red.global.add), which
+    # can flip a bf16 rounding or a ReLU gate downstream: compare per tensor in relative L2, elements with a loose bound
     for a, b in zip(g1, params):
-        torch.testing.assert_close(b.grad, 2 * a, rtol=2e-2, atol=1e-6 + 5e-2 * float(a.abs().max()))
+        den = float((2 * a).norm()) + 1e-12
+        assert float((b.grad - 2 * a).norm()) <= 2e-2 * den + 1e-7, (float((b.grad - 2 * a).norm()), den)
+        torch.testing.assert_close(b.grad, 2 * a, rtol=5e-2, atol=1e-6 + 2e-1 * float(a.abs().max()))
     opt.zero_grad(set_to_none=False)
     l1 = step()
     opt.step()
