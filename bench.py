@@ -50,6 +50,7 @@ def parse_args():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-rooflines", action="store_true")
     ap.add_argument("--no-train", action="store_true", help="skip the supplementary training-step line (configs[2])")
+    ap.add_argument("--no-varying", action="store_true", help="skip the varying-geometry leg (fresh batch geometry every step)")
     ap.add_argument("--train-images", type=int, default=16, help="images per training step per GPU (configs[2]: 16)")
     ap.add_argument("--train-steps", type=int, default=10)
     ap.add_argument("--profile-e2e", action="store_true", help="cProfile of the (untimed) e2e loop to stderr, then exit")
@@ -63,6 +64,8 @@ def workload_config(args, extra=None):
            "cells_per_step_per_gpu": args.images * args.humans * args.boxes,
            "pairs_per_step_per_gpu": args.images * args.humans * (args.boxes - 1),
            "boundary": "InteractionHead.forward_from_pooled (head.py:389-427; RoIAlign/NMS stay stock torchvision)",
+           "repeat": "value / e2e replay ONE batch (same geometry, same buffers: every host cache and the CUDA graph hit); "
+                     "varying_geometry times a stream of never-seen batches",
            "parallelism": "dp%d (images sharded, no data-path collective)" % args.gpus}
     if extra:
         cfg.update(extra)
@@ -423,6 +426,9 @@ def run_b200(args):
     roof = None; extra_roofs = {}
     if rank == 0 and not args.no_rooflines:
         roof, extra_roofs = measure_rooflines(torch, _lib, engine, ih, dev, flush, hbm_peak, tf_peak, peak_src)
+    varying = None
+    if not args.no_varying:
+        varying = measure_varying_geometry(torch, dist, args, ih, dev, rank, world)
     train = None
     if not args.no_train:
         train = measure_training(torch, dist, args, dev, rank, world, flush)
@@ -460,6 +466,8 @@ def run_b200(args):
                         "timing": "host wall clock over all K steps; per step: H2D of its inputs from pinned memory (copy stream, one step ahead), forward through InteractionHead.forward_from_pooled, 256 MiB L2 flush write, D2H of its results to pinned memory, read on the host one step later (event wait)"},
                 "gpu_launches": int(launches), "clocks": clocks, "roofline": roof, "cpu_baseline": cpu}
         line.update(extra_roofs)
+        if varying is not None:
+            line["varying_geometry"] = varying
         if train is not None:
             line["training"] = train
         if kg is not None:
@@ -469,6 +477,94 @@ def run_b200(args):
         print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
+
+
+def measure_varying_geometry(torch, dist, args, ih, dev, rank, world):
+    """VERDICT r1 item 3 / ADVICE: the headline replays ONE batch, real detection streams change (n_h, n) per image every
+    batch (head.py:136-139, 826-841).  Here every step is a batch the process has never seen: per image n_h ~ U[1, 15],
+    n ~ U[n_h + 1, 30] (what InteractionHead.preprocess emits with max_human = max_object = 15), its own detections and
+    its own input buffers (distinct device addresses).  `stream` = one pass over `fresh` never-seen batches after a
+    warm-up on OTHER batches (capacity-bucket graphs, SKG_HEAD_CAPACITY); `cycle_capacity` / `cycle_exact` = a 16-batch
+    cycle replayed with bucket graphs / with one exact-geometry graph per batch (the old best case: no padding)."""
+    from skghoi_b200 import _lib, engine, synthetic
+    n_img = args.images
+    warm_n, fresh_n = 64, 128
+    g = torch.Generator().manual_seed(9000 + rank)
+
+    def draw():
+        shapes = []
+        for _ in range(n_img):
+            nh = int(torch.randint(1, 16, (1,), generator=g))
+            shapes.append((nh, int(torch.randint(nh + 1, 31, (1,), generator=g))))
+        return shapes
+    img_shapes = [(800, 1216)] * n_img
+    gd = torch.Generator(device=dev).manual_seed(77 + rank)
+    batches = []
+    for i in range(warm_n + fresh_n):
+        shapes = draw()
+        boxes, labels, scores = synthetic.make_detections(shapes, img_shapes, g)
+        tot = sum(n for _, n in shapes)
+        batches.append(dict(shapes=shapes, pairs=sum(h * (n - 1) for h, n in shapes), cells=sum(h * n for h, n in shapes),
+                            f3={"3": torch.randn(n_img, 256, 25, 38, device=dev, generator=gd)},
+                            bf=torch.randn(tot, 256, 7, 7, device=dev, generator=gd),
+                            boxes=[b.to(dev) for b in boxes], labels=[l.to(dev) for l in labels], scores=[x.to(dev) for x in scores],
+                            meta=engine._host_meta(labels, scores, 49)))
+
+    def step(bt):
+        bt["meta"].pop("_skg_fwd", None); bt["meta"].pop("_skg_post", None)     # no per-batch host cache carried over
+        with torch.no_grad():
+            return engine.interaction_head_from_pooled(ih, bt["f3"], img_shapes, bt["bf"], bt["boxes"], bt["labels"], bt["scores"],
+                                                       meta=bt["meta"])
+
+    def timed(seq, reps=1):
+        torch.cuda.synchronize(dev)
+        if world > 1:
+            dist.barrier()
+        g0 = _lib.graph_stats()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        t0 = time.perf_counter()
+        e0.record()
+        for _ in range(reps):
+            for bt in seq:
+                step(bt)
+        e1.record()
+        host_ms = (time.perf_counter() - t0) * 1e3
+        torch.cuda.synchronize(dev)
+        g1 = _lib.graph_stats()
+        ms = e0.elapsed_time(e1)
+        from skghoi_b200 import shard
+        ms = shard.max_over_ranks([ms], device=dev)[0] if world > 1 else ms
+        steps = reps * len(seq)
+        pairs = reps * sum(bt["pairs"] for bt in seq)
+        return {"value": pairs * world / (ms * 1e-3), "unit": UNIT, "ms_per_step": ms / steps, "steps": steps,
+                "pairs_per_step_mean": pairs / steps, "host_enqueue_ms_per_step": host_ms / steps,
+                "graph": {"replays": g1[0] - g0[0], "captures": g1[1] - g0[1], "plain": g1[2] - g0[2]}}
+    engine.CAPACITY_BUCKETS = True
+    engine._geometry_cache.clear()
+    for _ in range(2):
+        for bt in batches[:warm_n]:
+            step(bt)
+    stream = timed(batches[warm_n:])
+    cyc = batches[warm_n:warm_n + 16]
+    timed(cyc, 2)
+    cycle_cap = timed(cyc, 8)
+    engine.CAPACITY_BUCKETS = False
+    engine._geometry_cache.clear()
+    timed(cyc, 3)
+    cycle_exact = timed(cyc, 8)
+    engine.CAPACITY_BUCKETS = True
+    engine._geometry_cache.clear()
+    cells = [bt["cells"] for bt in batches[warm_n:]]
+    out = {"workload": "%d images/step, per image n_h ~ U[1,15], n ~ U[n_h+1,30]; every timed step is a batch geometry, detections "
+                       "and input buffers (%d distinct sets, %.1f GB: larger than L2) the process has never seen"
+                       % (n_img, fresh_n, sum(bt["bf"].numel() * 4 + bt["f3"]["3"].numel() * 4 for bt in batches[warm_n:]) / 1e9),
+           "cells_per_step": {"min": min(cells), "mean": sum(cells) / len(cells), "max": max(cells)},
+           "stream": stream, "cycle_capacity": cycle_cap, "cycle_exact": cycle_exact,
+           "stream_vs_exact": stream["ms_per_step"] and (cycle_exact["value"] and stream["value"] / cycle_exact["value"]),
+           "note": "stream / cycle_capacity: graphs keyed on a capacity bucket (cells to a 128-row tile, node rows to 128; true "
+                   "counts and input addresses read from the segment table on the device); cycle_exact: one graph per exact "
+                   "geometry on a 16-batch cycle (no padding, the headline's best case at this batch size)"}
+    return out if rank == 0 else None
 
 
 def measure_kg(torch, dist, dev, rank, world):

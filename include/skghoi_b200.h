@@ -426,6 +426,18 @@ int skg_head_plan(const skg_head_weights* weights, const skg_head_batch* batch, 
                                        "feat" [cells, 2R], "logits" [cells, n_logit]; the diagonal cells i == j are masked by
                                        the loss), single-pass predictor */
 #define SKG_HEAD_PROFILE 4          /* record an event after every launch and SYNCHRONISE at the end (diagnostics only) */
+#define SKG_HEAD_CAPACITY 32        /* the sizes in skg_head_batch are CAPACITIES (skg_head_capacity): every launch is sized by
+                                       them, the true counts (box_off[B], hum_off[B], cell_off[B]) and the addresses of
+                                       features3 / box_features / boxes are read on the device from the packed segment table
+                                       (skg_segments_pack layout incl. its address block) that the caller uploads into
+                                       workspace buffer "seg" before every step.  Rows beyond the true counts are padding
+                                       (zero encodings, cell2pair = -1, never read back).  With SKG_HEAD_GRAPH one captured
+                                       graph then serves EVERY batch that fits the capacity bucket, whatever its per-image
+                                       detection counts and input addresses (real detection streams change them every
+                                       batch, head.py:826-841).  Inference only */
+/* capacity bucket of a batch: cells rounded up to a GEMM row tile (128 up to 2048 cells, then <= 6.25 % slack), node rows to
+ * 128, pairs = cells; the input addresses of `cap` are cleared (they travel in the segment table) */
+int skg_head_capacity(const skg_head_weights* weights, const skg_head_batch* exact, skg_head_batch* cap);
 /* launch i of the last profiled skg_head_forward on this thread: label, stream (0 caller's, 1 side), microseconds since
  * the previous event on that stream; returns -1 past the end */
 int skg_head_profile_get(int i, const char** name, int* stream_id, float* us);
@@ -433,6 +445,56 @@ int skg_head_profile_get(int i, const char** name, int* stream_id, float* us);
 void skg_head_graph_stats(long long* replays, long long* captures, long long* plain);
 int skg_head_forward(const skg_head_weights* weights, const skg_head_batch* batch, int flags, void* workspace,
                      int64_t workspace_bytes, cudaStream_t stream);
+
+/* ---- per-head serving session (csrc/session.cu) ----------------------------------------------------------------------------
+ * The opaque handle of SURVEY 8(b): it owns a copy of the packed-weight descriptor (the bf16 operands stay owned by the
+ * caller and must outlive it), the verb table, a pinned staging ring for the per-step segment table and the workspace plans
+ * of the capacity buckets it has seen.  One inference step of InteractionHead.forward from the pooled box features on
+ * (head.py:389-427) is
+ *     skg_session_prepare   host only: humans-first check (head.py:840-841), segment table, capacity bucket, result sizes
+ *     (the caller sizes the workspace and the two flat outputs from `sizes`)
+ *     skg_session_run       1 H2D copy (segment table + input addresses), the bucket's CUDA graph, 2 post-processing launches
+ * whatever the batch geometry and the input addresses are.  One session per host thread and stream. */
+typedef struct skg_session skg_session;
+typedef struct skg_session_config {
+  skg_head_weights weights;
+  const int32_t* verb_len;        /* HOST   [num_obj_cls] valid verbs per object class (object_class_to_target_class) */
+  const int32_t* verb_off_dev;    /* DEVICE [num_obj_cls + 1] CSR of the same table */
+  const int32_t* verb_idx_dev;    /* DEVICE [nnz] */
+  int32_t num_obj_cls;
+  int32_t max_images;             /* largest batch a step may carry */
+  int32_t flags;                  /* SKG_HEAD_PRECISE_LOGITS or 0 */
+  float prior_power;              /* 2.8 in inference (head.py:742) */
+} skg_session_config;
+typedef struct skg_step_sizes {
+  int64_t boxes, humans, cells, pairs, entries;   /* true counts of the step; entries = sum over images of nonzero(prior[0]) */
+  int64_t cap_boxes, cap_humans, cap_cells;       /* its capacity bucket */
+  int64_t workspace_bytes;                        /* the bucket's workspace (256-byte aligned base, zero-filled on first use) */
+  int64_t out_i64, out_f32;                       /* elements of the two flat outputs of skg_session_run */
+} skg_step_sizes;
+typedef struct skg_step_io {
+  const float* features3;          /* [B, Cg, feat_hw] */
+  const float* box_features;       /* [boxes, pool_k] fp32, or NULL with box_features_bf16 */
+  const void* box_features_bf16;   /* [cap_boxes, K0] bf16 operand rows (skg_multiscale_roi_align), or NULL */
+  const float* boxes;              /* [boxes, 4] */
+  const int64_t* labels;           /* [boxes] */
+  const float* scores;             /* [boxes] */
+  const float* ent;                /* TransH entity table [ent_tot, ent_dim] */
+  int64_t* out_i64;                /* [index entries | prediction entries | object pairs] */
+  float* out_f32;                  /* [boxes_h 4*pairs | boxes_o 4*pairs | scores entries | prior 2*entries | weights pairs] */
+} skg_step_io;
+int skg_session_create(const skg_session_config* config, skg_session** session);
+void skg_session_destroy(skg_session* session);
+/* all HOST pointers: n [B] boxes per image, labels / scores [sum n] (humans first in every image), hw [B, 2] image sizes as
+ * doubles; pairs_per_image / entries_per_image [B] may be NULL.  Errors: "index out of range in self" when an image has more
+ * boxes than the entity table has rows (head.py:572), "Human detections are not permuted to the top" (head.py:840-841) */
+int skg_session_prepare(skg_session* session, int num_images, const int64_t* n, const int64_t* labels, const float* scores,
+                        const double* hw, int feat_hw, skg_step_sizes* sizes, int64_t* pairs_per_image, int64_t* entries_per_image);
+int skg_session_run(skg_session* session, const skg_step_io* io, void* workspace, int64_t workspace_bytes, cudaStream_t stream);
+/* workspace plans of the prepared step: of its capacity bucket (offsets) and of its exact sizes (row counts) */
+int skg_session_plans(const skg_session* session, skg_head_plan_t* capacity_plan, skg_head_plan_t* exact_plan);
+/* tensor-map descriptor cache of this thread (csrc/gemm.cu): lookups served from the cache, cuTensorMapEncodeTiled calls */
+void skg_tensor_map_cache_stats(long long* hits, long long* encodes);
 
 /* ---- backward of the whole pair path (csrc/backward.cu): the training step of BASELINE configs[2] ------------------------
  * Reference: loss.backward() through GraphHead.forward / the predictor and the two focal losses (utils.py:213-229,
@@ -478,7 +540,9 @@ int skg_head_backward(const skg_head_weights* weights, const skg_head_weights_t*
 /* Host-side packing of the per-batch segment table every batched kernel consumes (all HOST pointers): n / n_h [B]
  * boxes and humans per image, hw [B,2] = (h, w) as doubles.  `out` receives
  *   cell_off i64[B+1] | pair_off i64[B+1] | box_off i32[B+1] | n_h i32[B] | hum_off i32[B+1] | hw f32[3B] (h, w, h*w)
- * (n_h forced to 0 for images the reference skips, head.py:829-839); offsets[6] = byte offsets of the six arrays,
+ *   | pad to 16 | addr u64[4]  (device addresses of features3, fp32 box_features, boxes, 0: zeroed here, filled in by the
+ *   caller for SKG_HEAD_CAPACITY)
+ * (n_h forced to 0 for images the reference skips, head.py:829-839); offsets[7] = byte offsets of the seven arrays,
  * totals[5] = boxes, humans, cells, pairs, max boxes per image.  Returns the bytes used (multiple of 16) or -1. */
 int64_t skg_segments_pack(const int64_t* n, const int64_t* n_h, const double* hw, int num_images, void* out,
                           int64_t out_bytes, int64_t* offsets, int64_t* totals);

@@ -243,6 +243,34 @@ HEAD_WANT_TAPS = 2
 HEAD_PROFILE = 4
 HEAD_GRAPH = 8
 HEAD_TRAIN = 16
+HEAD_CAPACITY = 32
+_SIGNATURES["skg_head_capacity"] = (I, [ctypes.POINTER(HeadWeights), ctypes.POINTER(HeadBatch), ctypes.POINTER(HeadBatch)])
+
+
+class SessionConfig(ctypes.Structure):
+    """Mirror of ``skg_session_config``."""
+    _fields_ = [("weights", HeadWeights), ("verb_len", c_void_p), ("verb_off_dev", c_void_p), ("verb_idx_dev", c_void_p),
+                ("num_obj_cls", ctypes.c_int32), ("max_images", ctypes.c_int32), ("flags", ctypes.c_int32), ("prior_power", c_float)]
+
+
+class StepSizes(ctypes.Structure):
+    """Mirror of ``skg_step_sizes``."""
+    _fields_ = [(k, c_int64) for k in ("boxes", "humans", "cells", "pairs", "entries", "cap_boxes", "cap_humans", "cap_cells",
+                                       "workspace_bytes", "out_i64", "out_f32")]
+
+
+class StepIO(ctypes.Structure):
+    """Mirror of ``skg_step_io``."""
+    _fields_ = [(k, c_void_p) for k in ("features3", "box_features", "box_features_bf16", "boxes", "labels", "scores", "ent",
+                                        "out_i64", "out_f32")]
+
+
+_SIGNATURES["skg_session_create"] = (I, [ctypes.POINTER(SessionConfig), ctypes.POINTER(c_void_p)])
+_SIGNATURES["skg_session_destroy"] = (None, [c_void_p])
+_SIGNATURES["skg_session_prepare"] = (I, [c_void_p, I, P, P, P, P, I, ctypes.POINTER(StepSizes), P, P])
+_SIGNATURES["skg_session_run"] = (I, [c_void_p, ctypes.POINTER(StepIO), P, L, P])
+_SIGNATURES["skg_session_plans"] = (I, [c_void_p, ctypes.POINTER(HeadPlan), ctypes.POINTER(HeadPlan)])
+_SIGNATURES["skg_tensor_map_cache_stats"] = (None, [ctypes.POINTER(ctypes.c_longlong)] * 2)
 _SIGNATURES["skg_head_profile_get"] = (I, [I, ctypes.POINTER(c_char_p), ctypes.POINTER(I), ctypes.POINTER(c_float)])
 _SIGNATURES["skg_head_buffer_name"] = (c_char_p, [I])
 _SIGNATURES["skg_head_plan"] = (I, [ctypes.POINTER(HeadWeights), ctypes.POINTER(HeadBatch), I, ctypes.POINTER(HeadPlan)])

@@ -51,4 +51,14 @@ __device__ __forceinline__ float warp_max(float v) {
 // number of SMs of the current device (cached)
 int num_sms();
 
+// ---- capacity mode (SKG_HEAD_CAPACITY): launches that read input addresses / true row counts from the segment table ----
+int cast_pad_bf16_indirect(const unsigned long long* src_slot, int64_t ld_src, const int32_t* rows_dev, int64_t rows_cap, int cols,
+                           void* dst, int64_t ld_dst, int cols_pad, cudaStream_t stream);
+int global_pool_indirect(const unsigned long long* f_slot, int64_t planes, int hw, void* out_bf16, float* out_f32, cudaStream_t stream);
+int pairs_spatial_encode_impl(const float* boxes, const unsigned long long* boxes_slot, const int32_t* box_off, const int32_t* n_h,
+                              const int64_t* cell_off, const int64_t* pair_off, const int32_t* hum_off, const float* hw,
+                              int num_images, int64_t total_cells, int num_features, float eps, int nan_guard, float* enc,
+                              int64_t* x, int64_t* y, int64_t* x_keep, int64_t* y_keep, int32_t* cell2pair, int32_t* cell_hrow,
+                              int32_t* cell_orow, int32_t* cell_img, int32_t* pair2cell, int32_t* nan_flag, cudaStream_t stream);
+
 }  // namespace skg

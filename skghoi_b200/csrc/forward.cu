@@ -102,7 +102,7 @@ struct GraphEntry {
   long long launches = 0;
   unsigned long long stamp = 0;
 };
-static thread_local GraphEntry g_graphs[8];
+static thread_local GraphEntry g_graphs[64];
 static thread_local unsigned long long g_graph_clock = 0;
 static thread_local long long g_graph_stats[3] = {0, 0, 0};   // replays, captures, plain launches
 
@@ -186,6 +186,29 @@ extern "C" int skg_head_forward(const skg_head_weights* wp, const skg_head_batch
   return SKG_OK;
 }
 
+// byte offset of the input-address block inside the packed segment table (skg_segments_pack layout)
+static inline int64_t seg_ptr_offset(int64_t B) {
+  const int64_t o_hw = 8 * (B + 1) * 2 + 4 * (B + 1) + 4 * B + 4 * (B + 1);
+  return (o_hw + 12 * B + 15) / 16 * 16;
+}
+
+extern "C" int skg_head_capacity(const skg_head_weights* wp, const skg_head_batch* exact, skg_head_batch* cap) {
+  SKG_REQUIRE(wp && exact && cap, "null pointer argument");
+  *cap = *exact;
+  auto up = [](int64_t v, int64_t g) { return v <= 0 ? g : (v + g - 1) / g * g; };
+  // cells: one GEMM M tile (128 rows) up to 2048, then <= 6.25 % slack; node rows: one M tile
+  const int64_t C = exact->total_cells;
+  int64_t g = 128;
+  while (g * 16 < C) g *= 2;
+  cap->total_cells = up(C, g);
+  cap->total_pairs = cap->total_cells;
+  cap->total_boxes = (int32_t)up(exact->total_boxes, 128);
+  cap->total_humans = (int32_t)up(exact->total_humans, 128);
+  cap->max_boxes_per_image = wp->ent_tot;
+  cap->features3 = nullptr; cap->box_features = nullptr; cap->boxes = nullptr;   // read from the segment table's address block
+  return SKG_OK;
+}
+
 static int enqueue_forward(const skg_head_weights* wp, const skg_head_batch* bp, int flags, void* workspace,
                            int64_t workspace_bytes, cudaStream_t st) {
   const skg_head_weights& w = *wp;
@@ -199,14 +222,24 @@ static int enqueue_forward(const skg_head_weights* wp, const skg_head_batch* bp,
   const int NB = b.total_boxes, NH = b.total_humans, B = b.num_images, R = w.R, E = w.E;
   if (C == 0 || B == 0) return SKG_OK;
   SKG_REQUIRE(C < (int64_t)1 << 31, "too many grid cells in one batch");
-  SKG_REQUIRE(b.features3 && (b.box_features || b.box_features_bf16) && b.boxes && b.box_off && b.n_h && b.hum_off && b.cell_off && b.pair_off && b.hw,
-              "null batch pointer");
+  const bool cap = (flags & SKG_HEAD_CAPACITY) != 0;
+  SKG_REQUIRE(b.box_off && b.n_h && b.hum_off && b.cell_off && b.pair_off && b.hw, "null batch pointer");
+  SKG_REQUIRE(cap || (b.features3 && (b.box_features || b.box_features_bf16) && b.boxes), "null batch pointer");
+  SKG_REQUIRE(!cap || !(flags & (SKG_HEAD_TRAIN | SKG_HEAD_WANT_TAPS)), "SKG_HEAD_CAPACITY is an inference mode (no TRAIN / WANT_TAPS)");
+  SKG_REQUIRE(!cap || b.seg_bytes >= seg_ptr_offset(B) + 32, "SKG_HEAD_CAPACITY needs the packed segment table inside the workspace");
   SKG_REQUIRE(b.max_boxes_per_image <= w.ent_tot, "index out of range in self: a box index addresses the %d-row entity table (head.py:572)",
               w.ent_tot);
   const bool train = (flags & SKG_HEAD_TRAIN) != 0;
   const bool precise = !train && (flags & SKG_HEAD_PRECISE_LOGITS) != 0 && w.Wpred_hh && w.Wpred_lo;
   SKG_REQUIRE(precise || w.Wpred, "missing predictor weights");
   uint8_t* base = reinterpret_cast<uint8_t*>(workspace);
+  // capacity mode: the batch sizes above are CAPACITIES; the true counts (box_off[B], cell_off[B], ...) and the three input
+  // addresses live in the segment table the caller uploaded into buffer "seg" for THIS step
+  const unsigned long long* slots = cap ? reinterpret_cast<const unsigned long long*>(base + plan.offset[B_SEG] + seg_ptr_offset(B)) : nullptr;
+  if (cap) {
+    SKG_REQUIRE(reinterpret_cast<const uint8_t*>(b.cell_off) == base + plan.offset[B_SEG],
+                "SKG_HEAD_CAPACITY: the segment table must sit in workspace buffer \"seg\"");
+  }
   auto F = [&](int i) { return reinterpret_cast<float*>(base + plan.offset[i]); };
   auto H = [&](int i) { return reinterpret_cast<void*>(base + plan.offset[i]); };
   auto I32 = [&](int i) { return reinterpret_cast<int32_t*>(base + plan.offset[i]); };
@@ -234,7 +267,8 @@ static int enqueue_forward(const skg_head_weights* wp, const skg_head_batch* bp,
   }
   const void* xb = b.box_features_bf16;            // pooled features already in operand layout (native RoIAlign)
   if (!xb) {
-    SKG_TRY(skg_cast_pad_bf16(b.box_features, w.pool_k, nullptr, 0, NB, w.pool_k, H(B_XB), w.K0, w.K0, sa));
+    if (cap) SKG_TRY(cast_pad_bf16_indirect(slots + 1, w.pool_k, b.box_off + B, NB, w.pool_k, H(B_XB), w.K0, w.K0, sa));
+    else SKG_TRY(skg_cast_pad_bf16(b.box_features, w.pool_k, nullptr, 0, NB, w.pool_k, H(B_XB), w.K0, w.K0, sa));
     MARK("cast box_features", sa);
     xb = H(B_XB);
   }
@@ -266,9 +300,11 @@ static int enqueue_forward(const skg_head_weights* wp, const skg_head_batch* bp,
   MARK("gemm oproj", sa);
   // ---- sb: global feature term of attention_head_g (head.py:811, 971)
   if (w.Kg == w.Cg) {
-    SKG_TRY(skg_global_pool(b.features3, (int64_t)B * w.Cg, b.feat_hw, H(B_GFEAT), nullptr, sb));
+    if (cap) SKG_TRY(global_pool_indirect(slots, (int64_t)B * w.Cg, b.feat_hw, H(B_GFEAT), nullptr, sb));
+    else SKG_TRY(skg_global_pool(b.features3, (int64_t)B * w.Cg, b.feat_hw, H(B_GFEAT), nullptr, sb));
   } else {
-    SKG_TRY(skg_global_pool(b.features3, (int64_t)B * w.Cg, b.feat_hw, nullptr, F(B_G32), sb));
+    if (cap) SKG_TRY(global_pool_indirect(slots, (int64_t)B * w.Cg, b.feat_hw, nullptr, F(B_G32), sb));
+    else SKG_TRY(skg_global_pool(b.features3, (int64_t)B * w.Cg, b.feat_hw, nullptr, F(B_G32), sb));
     SKG_TRY(skg_cast_pad_bf16(F(B_G32), w.Cg, nullptr, 0, B, w.Cg, H(B_GFEAT), w.Kg, w.Kg, sb));
   }
   MARK("global_pool", sb);
@@ -277,9 +313,9 @@ static int enqueue_forward(const skg_head_weights* wp, const skg_head_batch* bp,
   MARK("gemm attention_head_g.fc_1", sb);
 
   // ================= main: pairs + spatial head (head.py:847-868, 662-669, 888)
-  SKG_TRY(skg_pairs_spatial_encode(b.boxes, b.box_off, b.n_h, b.cell_off, b.pair_off, b.hum_off, b.hw, B, C, 23, 1e-10f, 1,
-                                   F(B_ENC), I64(B_X), I64(B_Y), I64(B_XKEEP), I64(B_YKEEP), I32(B_CELL2PAIR), I32(B_CELL_HROW),
-                                   I32(B_CELL_OROW), I32(B_CELL_IMG), I32(B_PAIR2CELL), I32(B_NANFLAG), st));
+  SKG_TRY(pairs_spatial_encode_impl(cap ? nullptr : b.boxes, cap ? slots + 2 : nullptr, b.box_off, b.n_h, b.cell_off, b.pair_off, b.hum_off,
+                                    b.hw, B, C, 23, 1e-10f, 1, F(B_ENC), I64(B_X), I64(B_Y), I64(B_XKEEP), I64(B_YKEEP), I32(B_CELL2PAIR),
+                                    I32(B_CELL_HROW), I32(B_CELL_OROW), I32(B_CELL_IMG), I32(B_PAIR2CELL), I32(B_NANFLAG), st));
   MARK("pairs_spatial_encode", st);
   SKG_TRY(skg_spatial_fc1(F(B_ENC), w.Wsp0, w.bsp0, C, 46, 128, H(B_S1), st));
   MARK("spatial_fc1", st);
@@ -426,15 +462,17 @@ extern "C" int64_t skg_post_count_host(const int32_t* verb_len, int num_obj_cls,
 
 // Host-side packing of the per-batch segment table (engine.Segments): one buffer, one H2D copy.
 //   layout: cell_off i64[B+1] | pair_off i64[B+1] | box_off i32[B+1] | n_h i32[B] | hum_off i32[B+1] | hw f32[3B] | pad to 16
-// n_h_eff[b] = 0 for images the reference skips (n_h == 0 or n <= 1, head.py:829-839).  offsets[6] receive the byte offsets
-// of the six arrays, totals[5] = boxes, humans, cells, pairs, max boxes per image.  Returns the bytes used or -1.
+//           | ptrs u64[4] = addresses of features3, box_features (fp32), boxes, 0 -- filled by the caller for SKG_HEAD_CAPACITY
+// n_h_eff[b] = 0 for images the reference skips (n_h == 0 or n <= 1, head.py:829-839).  offsets[7] receive the byte offsets
+// of the seven arrays, totals[5] = boxes, humans, cells, pairs, max boxes per image.  Returns the bytes used or -1.
 extern "C" int64_t skg_segments_pack(const int64_t* n, const int64_t* n_h, const double* hw, int num_images, void* out,
                                      int64_t out_bytes, int64_t* offsets, int64_t* totals) {
   const int64_t B = num_images;
   if (B < 0 || !out || !offsets || !totals || (B > 0 && (!n || !n_h || !hw))) { set_error("null pointer argument"); return -1; }
   const int64_t o_cell = 0, o_pair = o_cell + 8 * (B + 1), o_box = o_pair + 8 * (B + 1), o_nh = o_box + 4 * (B + 1),
                 o_hum = o_nh + 4 * B, o_hw = o_hum + 4 * (B + 1);
-  const int64_t used = (o_hw + 12 * B + 15) / 16 * 16;
+  const int64_t o_ptr = (o_hw + 12 * B + 15) / 16 * 16;   // input-address block of the capacity mode (4 x u64, zero here)
+  const int64_t used = o_ptr + 32;
   if (out_bytes < used) { set_error("segment buffer too small: %lld < %lld", (long long)out_bytes, (long long)used); return -1; }
   uint8_t* base = reinterpret_cast<uint8_t*>(out);
   int64_t* cell_off = reinterpret_cast<int64_t*>(base + o_cell);
@@ -457,6 +495,7 @@ extern "C" int64_t skg_segments_pack(const int64_t* n, const int64_t* n_h, const
   cell_off[B] = cells; pair_off[B] = pairs; box_off[B] = (int32_t)boxes; hum_off[B] = (int32_t)humans;
   for (int64_t i = o_hw + 12 * B; i < used; ++i) base[i] = 0;
   offsets[0] = o_cell; offsets[1] = o_pair; offsets[2] = o_box; offsets[3] = o_nh; offsets[4] = o_hum; offsets[5] = o_hw;
+  offsets[6] = o_ptr;
   totals[0] = boxes; totals[1] = humans; totals[2] = cells; totals[3] = pairs; totals[4] = max_n;
   return used;
 }

@@ -528,8 +528,35 @@ static PFN_encodeTiled get_encode_fn() {
   return fn;
 }
 
-// 2-D bf16 row-major [rows, cols] (cols contiguous, row pitch ld elements), box = [box_rows, 64 cols], 128B swizzle
+// Descriptor cache: a tensor map is a pure function of (address, rows, cols, pitch, box rows), and a serving / training loop
+// launches the same few dozen operand shapes at the same workspace addresses step after step -- cuTensorMapEncodeTiled (two
+// driver calls per GEMM launch, ~60 per step on the plain-launch path) is paid once per distinct operand.
+struct TmapKey {
+  const void* ptr; int64_t rows, cols, ld; int box_rows;
+  bool operator==(const TmapKey& o) const { return ptr == o.ptr && rows == o.rows && cols == o.cols && ld == o.ld && box_rows == o.box_rows; }
+};
+struct TmapSlot { TmapKey key; CUtensorMap map; bool used; };
+constexpr int kTmapSlots = 1024;   // direct-mapped
+static thread_local TmapSlot* g_tmaps = nullptr;
+static thread_local long long g_tmap_stats[2] = {0, 0};   // hits, encodes
+
+static int make_tmap_uncached(CUtensorMap* map, const void* ptr, int64_t rows, int64_t cols, int64_t ld, int box_rows);
+
 static int make_tmap(CUtensorMap* map, const void* ptr, int64_t rows, int64_t cols, int64_t ld, int box_rows) {
+  if (!g_tmaps) g_tmaps = new TmapSlot[kTmapSlots]();
+  const TmapKey key{ptr, rows, cols, ld, box_rows};
+  uint64_t h = reinterpret_cast<uintptr_t>(ptr) >> 4;
+  h = (h ^ (uint64_t)rows * 0x9E3779B97F4A7C15ull ^ (uint64_t)cols * 0xC2B2AE3D27D4EB4Full ^ (uint64_t)ld * 0x165667B19E3779F9ull ^ (uint64_t)box_rows) * 0xD6E8FEB86659FD93ull;
+  TmapSlot& slot = g_tmaps[(h >> 32) % kTmapSlots];
+  if (slot.used && slot.key == key) { *map = slot.map; g_tmap_stats[0]++; return SKG_OK; }
+  const int rc = make_tmap_uncached(map, ptr, rows, cols, ld, box_rows);
+  if (rc) return rc;
+  slot.key = key; slot.map = *map; slot.used = true; g_tmap_stats[1]++;
+  return SKG_OK;
+}
+
+// 2-D bf16 row-major [rows, cols] (cols contiguous, row pitch ld elements), box = [box_rows, 64 cols], 128B swizzle
+static int make_tmap_uncached(CUtensorMap* map, const void* ptr, int64_t rows, int64_t cols, int64_t ld, int box_rows) {
   PFN_encodeTiled enc = get_encode_fn();
   if (!enc) { set_error("cuTensorMapEncodeTiled entry point not available"); return SKG_ERR_CUDA; }
   cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
@@ -579,6 +606,11 @@ static int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, int M, in
 }  // namespace skg
 
 using namespace skg;
+
+extern "C" void skg_tensor_map_cache_stats(long long* hits, long long* encodes) {
+  if (hits) *hits = g_tmap_stats[0];
+  if (encodes) *encodes = g_tmap_stats[1];
+}
 
 constexpr int kSplitKCounters = 1024;   // ints at the head of the split-K scratch
 

@@ -18,17 +18,24 @@ __device__ __forceinline__ float2 unpack2(uint32_t u) {
 }
 
 // dst[r, c] = bf16(relu?(src[r, c] + bias[c])) for c < cols, 0 for cols <= c < cols_pad
+// Capacity mode (SKG_HEAD_CAPACITY): `src_slot` holds the source ADDRESS and `rows_dev` the true row count in device
+// memory (the step's segment table), rows in [*rows_dev, rows) are written as zeros -- the launch itself depends on the
+// capacity only, so a captured graph serves every batch of the bucket.
 __global__ void cast_pad_bf16_kernel(const float* __restrict__ src, int64_t ld_src, const float* __restrict__ bias,
                                      int relu, int64_t rows, int cols, __nv_bfloat16* __restrict__ dst, int64_t ld_dst,
-                                     int cols_pad) {
+                                     int cols_pad, const unsigned long long* __restrict__ src_slot,
+                                     const int32_t* __restrict__ rows_dev) {
   const int64_t quads_per_row = cols_pad >> 2;   // cols_pad % 4 == 0
   const int64_t total = rows * quads_per_row;
+  if (src_slot) src = reinterpret_cast<const float*>(__ldg(src_slot));
+  const int64_t rows_true = rows_dev ? (int64_t)__ldg(rows_dev) : rows;
   for (int64_t q = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; q < total; q += (int64_t)gridDim.x * blockDim.x) {
     const int64_t r = q / quads_per_row;
     const int c = (int)(q - r * quads_per_row) << 2;
+    if (r >= rows_true) { *reinterpret_cast<uint2*>(dst + r * ld_dst + c) = make_uint2(0u, 0u); continue; }
     float v[4];
     const float* s = src + r * ld_src + c;
-    if (c + 4 <= cols && ((ld_src & 3) == 0)) {
+    if (c + 4 <= cols && ((ld_src & 3) == 0) && ((reinterpret_cast<uintptr_t>(src) & 15u) == 0)) {
       const float4 f = __ldg(reinterpret_cast<const float4*>(s));
       v[0] = f.x; v[1] = f.y; v[2] = f.z; v[3] = f.w;
     } else {
@@ -108,6 +115,11 @@ __global__ void node_prep_kernel(const float* __restrict__ ent, int ent_dim, int
                                  const int32_t* __restrict__ n_h, const int32_t* __restrict__ hum_off, int B,
                                  __nv_bfloat16* __restrict__ o_in, int ld, int enc_dim, int32_t* __restrict__ box2hum) {
   const int row = blockIdx.x;
+  if (row >= __ldg(box_off + B)) {                    // capacity padding: no box behind this row
+    for (int c = enc_dim + threadIdx.x; c < ld; c += blockDim.x) o_in[(int64_t)row * ld + c] = __float2bfloat16(0.f);
+    if (threadIdx.x == 0 && box2hum) box2hum[row] = -1;
+    return;
+  }
   int lo = 0, hi = B;
   while (hi - lo > 1) { const int mid = (lo + hi) >> 1; if (__ldg(box_off + mid) <= row) lo = mid; else hi = mid; }
   const int idx = row - __ldg(box_off + lo);
@@ -131,10 +143,11 @@ __global__ void fc_bias_fold_kernel(const float* __restrict__ bias_in, const flo
 
 // global_features = avg_pool(features['3']).flatten(1) (head.py:811): one warp per (image, channel)
 __global__ void global_pool_kernel(const float* __restrict__ f, int64_t planes, int hw, __nv_bfloat16* __restrict__ out_bf16,
-                                   float* __restrict__ out_f32) {
+                                   float* __restrict__ out_f32, const unsigned long long* __restrict__ f_slot) {
   const int lane = threadIdx.x & 31;
   const int64_t warp = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
   if (warp >= planes) return;
+  if (f_slot) f = reinterpret_cast<const float*>(__ldg(f_slot));   // capacity mode: the address lives in the segment table
   const float* p = f + warp * hw;
   float s = 0.f;
   for (int i = lane; i < hw; i += 32) s += __ldg(p + i);
@@ -165,6 +178,7 @@ __global__ void __launch_bounds__(128) aggregate_kernel(const float* __restrict_
   const bool is_h = row < total_humans;
   const int local = is_h ? row : row - total_humans;
   const int32_t* off = is_h ? hum_off : box_off;
+  if (local >= __ldg(off + B)) return;             // capacity padding (SKG_HEAD_CAPACITY): no node behind this row
   int lo = 0, hi = B;
   while (hi - lo > 1) { const int mid = (lo + hi) >> 1; if (__ldg(off + mid) <= local) lo = mid; else hi = mid; }
   const int b = lo;
@@ -347,9 +361,27 @@ extern "C" int skg_cast_pad_bf16(const float* src, int64_t ld_src, const float* 
   SKG_REQUIRE(src && dst && cols > 0 && cols_pad >= cols && cols_pad % 4 == 0 && ld_dst >= cols_pad && ld_dst % 4 == 0,
               "bad cast_pad arguments");
   cast_pad_bf16_kernel<<<grid_for(rows * (cols_pad / 4), 256), 256, 0, stream>>>(src, ld_src, bias, relu, rows, cols,
-                                                                              (__nv_bfloat16*)dst, ld_dst, cols_pad);
+                                                                              (__nv_bfloat16*)dst, ld_dst, cols_pad, nullptr, nullptr);
   return check_launch("cast_pad_bf16_kernel");
 }
+
+namespace skg {
+int cast_pad_bf16_indirect(const unsigned long long* src_slot, int64_t ld_src, const int32_t* rows_dev, int64_t rows_cap, int cols,
+                           void* dst, int64_t ld_dst, int cols_pad, cudaStream_t stream) {
+  if (rows_cap == 0) return SKG_OK;
+  SKG_REQUIRE(src_slot && rows_dev && dst && cols > 0 && cols_pad >= cols && cols_pad % 4 == 0 && ld_dst >= cols_pad && ld_dst % 4 == 0,
+              "bad cast_pad arguments");
+  cast_pad_bf16_kernel<<<grid_for(rows_cap * (cols_pad / 4), 256), 256, 0, stream>>>(nullptr, ld_src, nullptr, 0, rows_cap, cols,
+                                                                                  (__nv_bfloat16*)dst, ld_dst, cols_pad, src_slot, rows_dev);
+  return check_launch("cast_pad_bf16_kernel");
+}
+int global_pool_indirect(const unsigned long long* f_slot, int64_t planes, int hw, void* out_bf16, float* out_f32, cudaStream_t stream) {
+  if (planes == 0) return SKG_OK;
+  SKG_REQUIRE(f_slot && hw > 0 && (out_bf16 || out_f32), "bad global_pool arguments");
+  global_pool_kernel<<<(int)ceil_div64(planes * 32, 256), 256, 0, stream>>>(nullptr, planes, hw, (__nv_bfloat16*)out_bf16, out_f32, f_slot);
+  return check_launch("global_pool_kernel");
+}
+}  // namespace skg
 
 extern "C" int skg_spatial_fc1(const float* enc, const float* weight, const float* bias, int64_t cells, int in_features,
                                int out_features, void* out_bf16, cudaStream_t stream) {
@@ -398,7 +430,7 @@ extern "C" int skg_global_pool(const float* features, int64_t planes, int hw, vo
                                cudaStream_t stream) {
   if (planes == 0) return SKG_OK;
   SKG_REQUIRE(features && hw > 0 && (out_bf16 || out_f32), "bad global_pool arguments");
-  global_pool_kernel<<<(int)ceil_div64(planes * 32, 256), 256, 0, stream>>>(features, planes, hw, (__nv_bfloat16*)out_bf16, out_f32);
+  global_pool_kernel<<<(int)ceil_div64(planes * 32, 256), 256, 0, stream>>>(features, planes, hw, (__nv_bfloat16*)out_bf16, out_f32, nullptr);
   return check_launch("global_pool_kernel");
 }
 

@@ -138,9 +138,14 @@ struct PairOutputs {
   int32_t* nan_flag;   // [B] set to 1 when the image's encoding holds a NaN (may be null)
 };
 
+// Capacity mode (boxes_slot != nullptr, SKG_HEAD_CAPACITY): `total_cells` is the CAPACITY the launch was sized for, the
+// true cell count is cell_off[B] of the segment table and the box array's address is read from `boxes_slot`, both in device
+// memory -- nothing of the launch depends on the batch, so a captured graph serves every batch of the bucket.  Padding
+// cells get zero encodings and neutral row maps (cell2pair = -1, node rows 0).
 template <int F>
 __global__ void __launch_bounds__(kTileCells, 8) pairs_spatial_kernel(const float4* __restrict__ boxes, SegTable seg,
-                                                                      int64_t total_cells, float eps, PairOutputs o) {
+                                                                      int64_t total_cells, float eps, PairOutputs o,
+                                                                      const unsigned long long* __restrict__ boxes_slot) {
   // One 128-cell tile per CTA iteration, staged in shared memory in the exact output layout (23.5 KB) and drained by one
   // bulk asynchronous copy; 8 CTAs per SM (188 KB of shared memory, <= 64 registers) keep 32 warps of MUFU / store
   // work in flight, so the drain of one CTA's tile overlaps the arithmetic of the seven others.
@@ -148,6 +153,12 @@ __global__ void __launch_bounds__(kTileCells, 8) pairs_spatial_kernel(const floa
   __shared__ __align__(128) float tile[kTileCells * W];
   const int tid = threadIdx.x;
   const int64_t num_tiles = (total_cells + kTileCells - 1) / kTileCells;
+  int64_t true_cells = total_cells;
+  if (boxes_slot) {
+    boxes = reinterpret_cast<const float4*>(__ldg(boxes_slot));
+    const int64_t tc = __ldg(seg.cell_off + seg.B);
+    true_cells = tc < total_cells ? tc : total_cells;
+  }
   // each CTA owns a CONTIGUOUS run of tiles, so a thread's image index only ever moves forward
   const int64_t t_begin = (int64_t)blockIdx.x * num_tiles / gridDim.x;
   const int64_t t_end = (int64_t)(blockIdx.x + 1) * num_tiles / gridDim.x;
@@ -159,7 +170,15 @@ __global__ void __launch_bounds__(kTileCells, 8) pairs_spatial_kernel(const floa
     int boff = 0, n = 1, i = 0, j = 0;
     float4 b1 = make_float4(0.f, 0.f, 0.f, 0.f), b2 = b1;
     float h = 1.f, w = 1.f, hw = 1.f;
-    const bool live = r < total_cells;
+    const bool live = r < true_cells;
+    if (!live && r < total_cells) {                  // capacity padding
+      if (o.x) o.x[r] = 0;
+      if (o.y) o.y[r] = 0;
+      if (o.cell_hrow) o.cell_hrow[r] = 0;
+      if (o.cell_orow) o.cell_orow[r] = 0;
+      if (o.cell_img) o.cell_img[r] = 0;
+      if (o.cell2pair) o.cell2pair[r] = -1;
+    }
     if (live) {
       b = (b < 0) ? find_segment(seg.cell_off, seg.B, r) : advance_segment(seg.cell_off, seg.B, b, r);
       boff = __ldg(seg.box_off + b);
@@ -189,6 +208,9 @@ __global__ void __launch_bounds__(kTileCells, 8) pairs_spatial_kernel(const floa
     if (live) {
       const bool has_nan = encode_pair<F>(b1, b2, h, w, hw, eps, &tile[tid * W]);
       if (has_nan && o.nan_flag) atomicOr(o.nan_flag + b, 1);
+    } else if (r < total_cells) {
+#pragma unroll
+      for (int k = 0; k < W; ++k) tile[tid * W + k] = 0.f;
     }
     // make the generic-proxy smem writes visible to the async (TMA) proxy, then drain the tile
     asm volatile("fence.proxy.async.shared::cta;\n" ::: "memory");
@@ -267,11 +289,23 @@ extern "C" int skg_pairs_spatial_encode(const float* boxes, const int32_t* box_o
                                         int64_t* x_keep, int64_t* y_keep, int32_t* cell2pair, int32_t* cell_hrow,
                                         int32_t* cell_orow, int32_t* cell_img, int32_t* pair2cell, int32_t* nan_flag,
                                         cudaStream_t stream) {
+  return skg::pairs_spatial_encode_impl(boxes, nullptr, box_off, n_h, cell_off, pair_off, hum_off, hw, num_images, total_cells,
+                                        num_features, eps, nan_guard, enc, x, y, x_keep, y_keep, cell2pair, cell_hrow, cell_orow,
+                                        cell_img, pair2cell, nan_flag, stream);
+}
+
+int skg::pairs_spatial_encode_impl(const float* boxes, const unsigned long long* boxes_slot, const int32_t* box_off, const int32_t* n_h,
+                                   const int64_t* cell_off, const int64_t* pair_off, const int32_t* hum_off,
+                                   const float* hw, int num_images, int64_t total_cells, int num_features,
+                                   float eps, int nan_guard, float* enc, int64_t* x, int64_t* y,
+                                   int64_t* x_keep, int64_t* y_keep, int32_t* cell2pair, int32_t* cell_hrow,
+                                   int32_t* cell_orow, int32_t* cell_img, int32_t* pair2cell, int32_t* nan_flag,
+                                   cudaStream_t stream) {
   SKG_REQUIRE(num_features == 18 || num_features == 23, "num_features must be 18 or 23, got %d", num_features);
   SKG_REQUIRE(num_images >= 0 && total_cells >= 0, "negative sizes");
   SKG_REQUIRE(!nan_guard || nan_flag, "nan_guard needs a nan_flag buffer");
   if (total_cells == 0 || num_images == 0) return SKG_OK;
-  SKG_REQUIRE(boxes && box_off && n_h && cell_off && pair_off && hum_off && hw && enc, "null pointer argument");
+  SKG_REQUIRE((boxes || boxes_slot) && box_off && n_h && cell_off && pair_off && hum_off && hw && enc, "null pointer argument");
   SKG_REQUIRE((reinterpret_cast<uintptr_t>(boxes) & 15u) == 0, "boxes must be 16-byte aligned");
   SegTable seg{box_off, n_h, cell_off, pair_off, hum_off, hw, num_images};
   PairOutputs o{enc, x, y, x_keep, y_keep, cell2pair, cell_hrow, cell_orow, cell_img, pair2cell, nan_flag};
@@ -280,9 +314,9 @@ extern "C" int skg_pairs_spatial_encode(const float* boxes, const int32_t* box_o
   // 8 resident 128-thread CTAs per SM (23.5 KB smem each); grid is a multiple of the SM count
   const int grid = (int)(tiles < (int64_t)num_sms() * 8 ? tiles : (int64_t)num_sms() * 8);
   if (num_features == 23)
-    pairs_spatial_kernel<23><<<grid, kTileCells, 0, stream>>>((const float4*)boxes, seg, total_cells, eps, o);
+    pairs_spatial_kernel<23><<<grid, kTileCells, 0, stream>>>((const float4*)boxes, seg, total_cells, eps, o, boxes_slot);
   else
-    pairs_spatial_kernel<18><<<grid, kTileCells, 0, stream>>>((const float4*)boxes, seg, total_cells, eps, o);
+    pairs_spatial_kernel<18><<<grid, kTileCells, 0, stream>>>((const float4*)boxes, seg, total_cells, eps, o, boxes_slot);
   int rc = check_launch("pairs_spatial_kernel");
   if (rc) return rc;
   if (nan_guard) {

@@ -28,12 +28,12 @@ class Segments:
         assert len(n_h) == B and len(image_shapes) == B
         nn_ = np.ascontiguousarray(n, dtype=np.int64); nh = np.ascontiguousarray(n_h, dtype=np.int64)
         hw = np.ascontiguousarray(image_shapes, dtype=np.float64).reshape(B, 2)
-        nbytes = (40 * B + 24 + 15) // 16 * 16
+        nbytes = (40 * B + 24 + 15) // 16 * 16 + 32       # + the input-address block of the capacity mode
         # pinned: the H2D copy is then truly asynchronous (a pageable source makes torch synchronise the stream);
         # torch's caching host allocator keeps the block alive until the copy has executed
         self.host = torch.empty(nbytes, dtype=torch.uint8, pin_memory=torch.cuda.is_available())
         raw = self.host.numpy()
-        offs = np.empty(6, dtype=np.int64); tot = np.empty(5, dtype=np.int64)
+        offs = np.empty(7, dtype=np.int64); tot = np.empty(5, dtype=np.int64)
         used = _lib.lib().skg_segments_pack(nn_.ctypes.data, nh.ctypes.data, hw.ctypes.data, B, raw.ctypes.data, nbytes,
                                             offs.ctypes.data, tot.ctypes.data)
         if used < 0:
@@ -49,9 +49,15 @@ class Segments:
         self.hum_off = np.frombuffer(raw, np.int32, B + 1, o[4]).astype(np.int64)
         self.total_boxes, self.total_humans, self.total_cells, self.total_pairs, self.max_n = (int(t) for t in tot)
         self.nbytes = int(used)
+        self._ptrs = np.frombuffer(raw, np.uint64, 4, o[6])      # features3, box_features (fp32), boxes, 0 (SKG_HEAD_CAPACITY)
         self.dev = None
         if device is not None:
             self.upload(torch.empty(self.nbytes, dtype=torch.uint8, device=device))
+
+    def set_input_addresses(self, features3: int, box_features: int, boxes: int) -> None:
+        """Fills the address block of the HOST copy (capacity mode: the kernels read their inputs through it); takes
+        effect with the next ``upload``."""
+        self._ptrs[0], self._ptrs[1], self._ptrs[2] = features3, box_features, boxes
 
     def upload(self, dst: Tensor) -> None:
         """Copies the packed table into ``dst`` (uint8 CUDA tensor of ``nbytes``) on the current stream."""
@@ -361,7 +367,23 @@ def _host_meta(box_labels, box_scores, human_idx: int, meta=None, n=None):
 
 _INT64_BUFS = {"x", "y", "x_keep", "y_keep", "post_i64"}
 _INT32_BUFS = {"cell2pair", "cell_hrow", "cell_orow", "cell_img", "pair2cell", "nan_flag", "box2hum", "post_i32"}
+_STACKED_BUFS = {"Z", "pre", "enc16", "enc32"}        # [humans | boxes] row blocks: the box block starts at the capacity boundary
 _workspaces = {}
+CAPACITY_BUCKETS = True     # graph replays keyed on a capacity bucket instead of the exact batch geometry (SKG_HEAD_CAPACITY)
+_cap_plans = {}
+
+
+def _cap_plan(pk, b, flags):
+    key = (id(pk), int(b.num_images), int(b.total_boxes), int(b.total_humans), int(b.total_cells), int(b.seg_bytes), flags)
+    plan = _cap_plans.get(key)
+    if plan is None:
+        import ctypes
+        plan = _lib.HeadPlan()
+        _lib.call("skg_head_plan", ctypes.byref(pk.cw), ctypes.byref(b), flags, ctypes.byref(plan))
+        if len(_cap_plans) > 256:
+            _cap_plans.clear()
+        _cap_plans[key] = plan
+    return plan
 _geometry_cache = collections.OrderedDict()   # (n, n_h, image shapes, flags, device) -> host prep of that batch geometry
 _GEOMETRY_CACHE_MAX = 64
 _ws_seg_owner = {}      # workspace data_ptr -> the Segments whose packed table currently sits in it
@@ -379,19 +401,32 @@ def _workspace(dev, nbytes: int, kind: str = "eval") -> Tensor:
     return ws
 
 
+_buf_index = None
+
+
+def _buffer_index():
+    global _buf_index
+    if _buf_index is None:
+        _buf_index = {n: i for i, n in enumerate(_lib.head_buffer_names())}
+    return _buf_index
+
+
 class _Run(dict):
     """Result of ``head_forward``: named views into the step's workspace, created on first access.
     The views alias scratch memory that the next step on the same stream overwrites."""
 
-    def __init__(self, ws: Tensor, plan, **kw):
+    def __init__(self, ws: Tensor, plan, rows_plan=None, **kw):
         super().__init__(**kw)
         self._ws, self._plan = ws, plan
-        self._index = {n: i for i, n in enumerate(_lib.head_buffer_names())}
+        self._rows = rows_plan if rows_plan is not None else plan    # capacity mode: the batch's true row counts
+        self._index = _buffer_index()
 
     def __missing__(self, name):
         i = self._index[name]                      # KeyError for unknown names
         p = self._plan
-        rows, cols, es, off = int(p.rows[i]), int(p.cols[i]), int(p.elem_size[i]), int(p.offset[i])
+        if self._rows is not p and name in _STACKED_BUFS:
+            raise KeyError("%s stacks human and box rows at the capacity boundary: not exposed in capacity mode" % name)
+        rows, cols, es, off = int(self._rows.rows[i]), int(p.cols[i]), int(p.elem_size[i]), int(p.offset[i])
         dt = torch.int64 if name in _INT64_BUFS else torch.int32 if name in _INT32_BUFS else \
             torch.bfloat16 if es == 2 else torch.uint8 if es == 1 else torch.float32
         t = self._ws[off:off + rows * cols * es].view(dt)
@@ -404,6 +439,173 @@ class _Run(dict):
             return self[name]
         except KeyError:
             return default
+
+
+class HeadSession:
+    """``skg_session`` (csrc/session.cu): the per-head serving handle -- packed-weight descriptor, verb table, pinned staging
+    ring, bucket plans -- behind which one inference step is two C calls whatever the batch geometry."""
+
+    def __init__(self, ih, pk: "PackedHead", precise: bool, max_images: int):
+        import ctypes
+        G = ih.box_pair_head
+        self.pk, self.device, self.precise, self.max_images = pk, pk.device, precise, max_images
+        self.vt = _verb_table(G, pk.device)
+        cfg = _lib.SessionConfig()
+        ctypes.memmove(ctypes.byref(cfg.weights), ctypes.byref(pk.cw), ctypes.sizeof(_lib.HeadWeights))
+        cfg.verb_len, cfg.verb_off_dev, cfg.verb_idx_dev = self.vt.lens32.ctypes.data, self.vt.d_off.data_ptr(), self.vt.d_idx.data_ptr()
+        cfg.num_obj_cls, cfg.max_images = len(self.vt.lens32), max_images
+        cfg.flags = _lib.HEAD_PRECISE_LOGITS if precise else 0
+        cfg.prior_power = 2.8                                    # inference (head.py:742)
+        self.handle = ctypes.c_void_p()
+        with _lib.on_device(pk.device):
+            _lib.call("skg_session_create", ctypes.byref(cfg), ctypes.byref(self.handle))
+        self.sizes = _lib.StepSizes()
+        self.io = _lib.StepIO()
+        self._destroy = _lib.lib().skg_session_destroy
+
+    def __del__(self):
+        h = getattr(self, "handle", None)
+        if h is not None and h.value:
+            self._destroy(h)
+            self.handle = None
+
+
+def _session(ih, pk, precise: bool, B: int) -> HeadSession:
+    key = "_skg_session_p" if precise else "_skg_session"
+    ss = ih.__dict__.get(key)
+    if ss is None or ss.pk is not pk or ss.max_images < B:
+        ss = HeadSession(ih, pk, precise, max(64, 2 * B))
+        ih.__dict__[key] = ss
+    return ss
+
+
+class _SessionRun(_Run):
+    """Named workspace views of a session step (tests / diagnostics); the plans are fetched on first access."""
+
+    def __init__(self, sess: HeadSession, ws: Tensor, **kw):
+        dict.__init__(self, **kw)
+        self._ws, self._sess, self._plan, self._rows = ws, sess, None, None
+        self._index = _buffer_index()
+
+    def __missing__(self, name):
+        if self._plan is None:
+            import ctypes
+            cap, ex = _lib.HeadPlan(), _lib.HeadPlan()
+            _lib.call("skg_session_plans", self._sess.handle, ctypes.byref(cap), ctypes.byref(ex))
+            self._plan, self._rows = cap, ex
+        return _Run.__missing__(self, name)
+
+
+class LazyResults(list):
+    """The per-image result dicts of a step (views into its two flat output buffers), built on first access: a serving
+    loop that ships the flat buffers to the host (``results_to_host``) never pays for 8 tensor views per image."""
+
+    def __init__(self, flat: dict):
+        super().__init__()
+        self._flat, self._built = flat, False
+
+    def _build(self):
+        if not self._built:
+            self._built = True
+            f = self._flat
+            list.extend(self, _split_flat(f, f["out_i"], f["out_f"]))
+
+    def __len__(self):
+        return len(self._flat["psz"])
+
+    def __getitem__(self, i):
+        self._build()
+        return list.__getitem__(self, i)
+
+    def __iter__(self):
+        self._build()
+        return list.__iter__(self)
+
+    def __repr__(self):
+        self._build()
+        return list.__repr__(self)
+
+
+def _split_flat(flat, out_i, out_f):
+    L, Pn, psz, esz = flat["L"], flat["P"], flat["psz"], flat["esz"]
+    index, pred, obj = out_i[:L], out_i[L:2 * L], out_i[2 * L:]
+    bh, bo, scores, prior, weights, lab_e, unary = _flat_f_views(out_f, L, Pn, flat["train"])
+    sp = torch.split_with_sizes
+    out = [dict(boxes_h=a, boxes_o=b_, index=c, prediction=d_, scores=e, object=f, prior=g, weights=h)
+           for a, b_, c, d_, e, f, g, h in zip(sp(bh, psz), sp(bo, psz), sp(index, esz), sp(pred, esz), sp(scores, esz),
+                                               sp(obj, psz), sp(prior, esz, 1), sp(weights, psz))]
+    if flat["train"]:
+        for r, l_b, u_b in zip(out, sp(lab_e, esz), sp(unary, psz)):
+            r["labels"] = l_b; r["unary_labels"] = u_b
+    return out
+
+
+SESSION_PATH = True       # eval steps through skg_session_* (two C calls per step); False = the per-kernel Python orchestration
+
+
+def _session_forward(ih, pk, features3: Tensor, image_shapes, box_features: Tensor, boxes_cat: Tensor, labels_dev: Tensor,
+                     scores_dev: Tensor, meta: dict, precise: bool = True):
+    """One inference step of ``InteractionHead.forward`` from the pooled features on through ``skg_session_prepare`` /
+    ``skg_session_run``."""
+    import ctypes
+    G = ih.box_pair_head
+    dev = pk.device
+    n = meta["n"]
+    B = len(n)
+    sess = _session(ih, pk, precise, B)
+    hc = meta.get("_skg_sess")
+    if hc is None:
+        hc = (np.ascontiguousarray(n, dtype=np.int64), np.ascontiguousarray(image_shapes, dtype=np.float64).reshape(B, 2),
+              np.ascontiguousarray(meta["labels"], dtype=np.int64), np.ascontiguousarray(meta["scores"], dtype=np.float32),
+              np.empty(max(B, 1), dtype=np.int64), np.empty(max(B, 1), dtype=np.int64))
+        hc = hc + tuple(a.ctypes.data for a in hc)
+        meta["_skg_sess"] = hc
+    n_arr, hw_arr, lab_h, sc_h, pairs_img, ent_img, p_n, p_hw, p_lab, p_sc, p_pairs, p_ent = hc
+    tr = G.transh_head.transh
+    if tr.ent_embeddings.weight.device != dev:
+        tr.to(dev)
+    G.transh_head.maybe_resample()
+    ent = tr.ent_embeddings.weight.detach()
+    f3 = features3 if features3.is_contiguous() else features3.contiguous()
+    bf = box_features.reshape(int(n_arr.sum()), -1) if box_features.dim() != 2 else box_features
+    if not bf.is_contiguous():
+        bf = bf.contiguous()
+    _lib.require_cuda(f3, bf, boxes_cat)
+    sizes, io = sess.sizes, sess.io
+    l = _lib.lib()
+    rc = l.skg_session_prepare(sess.handle, B, p_n, p_lab, p_sc, p_hw, int(f3.shape[2] * f3.shape[3]) if f3.dim() == 4 else 0,
+                               ctypes.byref(sizes), p_pairs, p_ent)
+    if rc:
+        msg = l.skg_last_error().decode(errors="replace")
+        if msg.startswith("index out of range in self"):
+            raise IndexError(msg)                                # head.py:572
+        if msg.startswith("Human detections"):
+            raise ValueError(msg)                                # head.py:840-841
+        raise _lib.SkgError("skg_session_prepare failed (%d): %s" % (rc, msg))
+    L, Pn = int(sizes.entries), int(sizes.pairs)
+    io.features3, io.boxes, io.labels, io.scores, io.ent = f3.data_ptr(), boxes_cat.data_ptr(), labels_dev.data_ptr(), scores_dev.data_ptr(), ent.data_ptr()
+    if bf.dtype == torch.bfloat16:
+        if bf.shape[1] != int(pk.cw.K0) or bf.data_ptr() % 16:
+            raise ValueError("bf16 box features must be 16-byte aligned [boxes, %d] rows" % int(pk.cw.K0))
+        if bf.untyped_storage().nbytes() - bf.storage_offset() * 2 < int(sizes.cap_boxes) * int(pk.cw.K0) * 2:
+            raise ValueError("capacity mode: the bf16 operand buffer must hold %d rows" % int(sizes.cap_boxes))
+        io.box_features, io.box_features_bf16 = None, bf.data_ptr()
+    else:
+        io.box_features, io.box_features_bf16 = bf.data_ptr(), None
+    with _lib.on_device(dev):
+        ws = _workspace(dev, int(sizes.workspace_bytes), "eval")
+        out_i = torch.empty(int(sizes.out_i64), dtype=torch.int64, device=dev)
+        out_f = torch.empty(int(sizes.out_f32), dtype=torch.float32, device=dev)
+        io.out_i64, io.out_f32 = out_i.data_ptr(), out_f.data_ptr()
+        rc = l.skg_session_run(sess.handle, ctypes.byref(io), ws.data_ptr(), ws.numel(), _lib.raw_stream(dev))
+        if rc:
+            _workspaces.clear(); _ws_seg_owner.clear()
+            raise _lib.SkgError("skg_session_run failed (%d): %s" % (rc, l.skg_last_error().decode(errors="replace")))
+    _ws_seg_owner.clear()                                        # the segment table in the workspace is the session's now
+    flat = dict(out_i=out_i, out_f=out_f, L=L, P=Pn, psz=pairs_img[:B].tolist(), esz=ent_img[:B].tolist(), train=False)
+    ih.__dict__["_skg_last_flat"] = flat
+    ih.__dict__["_skg_last_run"] = _SessionRun(sess, ws, NH=int(sizes.humans), NB=int(sizes.boxes), _keep=(f3, bf, boxes_cat, ent, labels_dev, scores_dev))
+    return LazyResults(flat)
 
 
 def head_forward(ih, features3: Tensor, image_shapes, box_features: Tensor, boxes_cat: Tensor, meta: dict,
@@ -437,10 +639,19 @@ def head_forward(ih, features3: Tensor, image_shapes, box_features: Tensor, boxe
         flags |= _lib.HEAD_PROFILE
     elif graph:
         flags |= _lib.HEAD_GRAPH
+        if CAPACITY_BUCKETS and not want_taps:
+            # launches sized by a capacity bucket, true counts + input addresses read from the segment table on the device:
+            # ONE captured graph per bucket serves every batch geometry and every set of input buffers
+            flags |= _lib.HEAD_CAPACITY
+    cap_mode = bool(flags & _lib.HEAD_CAPACITY)
     import ctypes
     # per-batch host preparation (segment table, batch descriptor, workspace plan) is cached INSIDE the caller's ``meta``
     # dict: a caller that re-runs the same batch (same meta object) pays for it once
-    ck = (tuple(map(tuple, image_shapes)), flags, dev.index, int(f3.shape[2] * f3.shape[3]) if f3.dim() == 4 else 0)
+    bf = box_features.reshape(sum(n), -1)
+    if not bf.is_contiguous():
+        bf = bf.contiguous()
+    addr = (f3.data_ptr(), 0 if bf.dtype == torch.bfloat16 else bf.data_ptr(), boxes_cat.data_ptr()) if cap_mode else None
+    ck = (tuple(map(tuple, image_shapes)), flags, dev.index, int(f3.shape[2] * f3.shape[3]) if f3.dim() == 4 else 0, addr)
     cache = meta.get("_skg_fwd") if isinstance(meta, dict) else None
     if cache is None or cache["key"] != ck or cache["ih"]() is not ih:
         # ... and per batch GEOMETRY (boxes / humans per image, image sizes) across meta objects: a stream of batches that
@@ -455,6 +666,7 @@ def head_forward(ih, features3: Tensor, image_shapes, box_features: Tensor, boxe
             cache = None
     if cache is not None:
         seg, b, plan = cache["seg"], cache["b"], cache["plan"]
+        rows_plan = cache["rows_plan"]
     else:
         # images the reference skips (head.py:829-839) contribute no cells: treat them as n_h = 0
         n_h_eff = [0 if (h == 0 or k <= 1) else h for h, k in zip(n_h, n)]
@@ -467,24 +679,31 @@ def head_forward(ih, features3: Tensor, image_shapes, box_features: Tensor, boxe
         b.total_cells, b.total_pairs = seg.total_cells, seg.total_pairs
         plan = _lib.HeadPlan()
         _lib.call("skg_head_plan", ctypes.byref(pk.cw), ctypes.byref(b), flags, ctypes.byref(plan))
-        cache = dict(key=ck, seg=seg, b=b, plan=plan, run=None, ws_ptr=0, ih=weakref.ref(ih))
+        rows_plan = plan
+        if cap_mode:
+            seg.set_input_addresses(*addr)
+            b_cap = _lib.HeadBatch()
+            _lib.call("skg_head_capacity", ctypes.byref(pk.cw), ctypes.byref(b), ctypes.byref(b_cap))
+            b = b_cap
+            plan = _cap_plan(pk, b, flags)               # offsets of the bucket; ``rows_plan`` keeps the batch's true row counts
+        cache = dict(key=ck, seg=seg, b=b, plan=plan, rows_plan=rows_plan, run=None, ws_ptr=0, ih=weakref.ref(ih))
         _geometry_cache[(tuple(n), tuple(n_h), ck)] = cache
         while len(_geometry_cache) > _GEOMETRY_CACHE_MAX:
             _geometry_cache.popitem(last=False)
         if isinstance(meta, dict):
             meta["_skg_fwd"] = cache
-    bf = box_features.reshape(seg.total_boxes, -1)
-    if not bf.is_contiguous():
-        bf = bf.contiguous()
     _lib.require_cuda(f3, bf, boxes_cat)
     w = pk.cw
     w.ent = ent.data_ptr()
-    b.features3, b.boxes = f3.data_ptr(), boxes_cat.data_ptr()
+    if not cap_mode:
+        b.features3, b.boxes = f3.data_ptr(), boxes_cat.data_ptr()
     if bf.dtype == torch.bfloat16:                   # operand rows written by the native RoIAlign (roi.py)
         if bf.shape[1] != int(pk.cw.K0) or bf.data_ptr() % 16:
             raise ValueError("bf16 box features must be 16-byte aligned [boxes, %d] rows" % int(pk.cw.K0))
+        if cap_mode and bf.untyped_storage().nbytes() - bf.storage_offset() * 2 < int(b.total_boxes) * int(pk.cw.K0) * 2:
+            raise ValueError("capacity mode: the bf16 operand buffer must hold %d rows (roi.operand_buffer)" % int(b.total_boxes))
         b.box_features, b.box_features_bf16 = None, bf.data_ptr()
-    else:
+    elif not cap_mode:
         b.box_features, b.box_features_bf16 = bf.data_ptr(), None
     with _lib.on_device(dev):
         ws = _workspace(dev, int(plan.total_bytes), "train" if train else "eval")
@@ -506,7 +725,7 @@ def head_forward(ih, features3: Tensor, image_shapes, box_features: Tensor, boxe
         if train:
             run["_batch"] = type(b).from_buffer_copy(b)
         return run
-    run = _Run(ws, plan, seg=seg, NH=seg.total_humans, NB=seg.total_boxes, _keep=(f3, bf, boxes_cat, ent))
+    run = _Run(ws, plan, rows_plan=rows_plan, seg=seg, NH=seg.total_humans, NB=seg.total_boxes, _keep=(f3, bf, boxes_cat, ent))
     if train:                                        # what skg_head_backward is called with (train._StepRecord)
         run["_train"] = True; run["_flags"] = flags; run["_batch"] = type(b).from_buffer_copy(b)
     if profile:
@@ -835,6 +1054,8 @@ def interaction_head_from_pooled(ih, features, image_shapes, box_features, box_c
     if ih.training:
         assert targets is not None, "Targets should be passed during training"          # head.py:380-381
     meta, boxes_cat, labels_dev, scores_dev = _prep_inputs(G, features, box_features, box_coords, box_labels, box_scores, meta)
+    if run is None and targets is None and not ih.training and SESSION_PATH and CAPACITY_BUCKETS and sum(meta["n"]) > 0:
+        return _session_forward(ih, packed_head(ih), features["3"], image_shapes, box_features, boxes_cat, labels_dev, scores_dev, meta)
     if run is None:
         run = head_forward(ih, features["3"], image_shapes, box_features, boxes_cat, meta)
     seg: Segments = run["seg"]
@@ -954,7 +1175,9 @@ def results_to_host(ih, results: List[dict], wait: bool = True):
     device buffers, so the whole batch comes back with TWO pinned device->host copies and one synchronise instead of
     eight small copies per image."""
     flat = ih.__dict__.get("_skg_last_flat")
-    if flat is None or not results or results[0]["index"].untyped_storage().data_ptr() != flat["out_i"].untyped_storage().data_ptr():
+    if isinstance(results, LazyResults):
+        flat = results._flat
+    elif flat is None or not results or results[0]["index"].untyped_storage().data_ptr() != flat["out_i"].untyped_storage().data_ptr():
         out = [{k: v.cpu() for k, v in r.items()} for r in results]
         return out if wait else PendingResults(lambda: out, None)
     hi = torch.empty(flat["out_i"].shape, dtype=torch.int64, pin_memory=True)
@@ -977,7 +1200,8 @@ def _split_host_results(flat, hi, hf, results):
     if flat["train"]:
         for r, l_b, u_b in zip(out, sp(lab_e, esz), sp(unary, psz)):
             r["labels"] = l_b; r["unary_labels"] = u_b
-    out.extend(results[len(out):])            # the trailing loss dict (training) stays where it is
+    if not isinstance(results, LazyResults):
+        out.extend(results[len(out):])        # the trailing loss dict (training) stays where it is
     return out
 
 
@@ -1072,7 +1296,13 @@ def interaction_head_forward(ih, features, detections, image_shapes, targets=Non
         # inference: the pooled block goes straight into box_head's bf16 GEMM operand; the
         # [sum n, 256, 7, 7] fp32 tensor and its cast never reach HBM
         K0 = int(packed_head(ih).cw.K0)
-        box_features = torch.empty(sum(int(c.shape[0]) for c in coords), K0, dtype=torch.bfloat16, device=features["3"].device)
+        total = sum(int(c.shape[0]) for c in coords)
+        rows_cap = max((total + 127) // 128 * 128, 128)          # the capacity bucket's row count (skg_head_capacity)
+        buf = ih.__dict__.get("_skg_operand_buf")                # persistent: a stable address keeps the graph key stable
+        if buf is None or buf.shape[0] < rows_cap or buf.shape[1] != K0 or buf.device != features["3"].device:
+            buf = torch.zeros(rows_cap, K0, dtype=torch.bfloat16, device=features["3"].device)
+            ih.__dict__["_skg_operand_buf"] = buf
+        box_features = buf[:total]
         if K0 != pool.channels_times_bins(features):
             box_features.zero_()
         pool.pool(features, coords, image_shapes, want_f32=False, bf16_out=box_features)
