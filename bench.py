@@ -651,9 +651,10 @@ def measure_training(torch, dist, args, dev, rank, world, flush):
     from skghoi_b200 import engine
     meta = engine._host_meta(batch["box_labels"], batch["box_scores"], 49)
     params = [p for p in ih.parameters() if p.requires_grad]
-    opt = torch.optim.SGD(params, lr=1e-4, momentum=0.9)
-    buckets = shard.GradBuckets(params).attach()      # gradients live in flat buckets: stable .grad addresses for the native
-    #                                                   backward's unpack table, one all-reduce + one scale per bucket when N > 1
+    # gradients AND parameters live in flat buckets: stable .grad addresses for the native backward's unpack table, one
+    # all-reduce + one scale per bucket when N > 1, one fused SGD kernel per bucket instead of ~400 per-tensor updates
+    buckets = shard.GradBuckets(params).attach(flatten_params=True, module=ih)
+    opt = torch.optim.SGD(buckets.flat_params, lr=1e-4, momentum=0.9, fused=True)
 
     def step():
         buckets.zero_grad()

@@ -148,6 +148,28 @@ def _version_sum(params) -> int:
     return sum(map(_VERSION_OF, params))
 
 
+# Fused optimisers (``torch.optim.SGD / Adam(fused=True)``) update the parameters WITHOUT bumping their version counters,
+# so the packed operands also follow a process-wide count of optimiser steps (a global step post-hook: any optimiser step
+# invalidates them; the re-pack is one block-copy launch in training, one PackedHead rebuild in inference).
+_OPT_STEPS = [0]
+
+
+def _count_optimizer_step(*_args, **_kw):
+    _OPT_STEPS[0] += 1
+
+
+try:
+    from torch.optim.optimizer import register_optimizer_step_post_hook as _reg_opt_hook
+    _reg_opt_hook(_count_optimizer_step)
+except ImportError:                      # pragma: no cover  (torch < 2.0: version counters only)
+    pass
+
+
+def mark_parameters_updated() -> None:
+    """For parameter writes nothing can see (``p.data.copy_()``, a custom fused update): the next forward re-packs."""
+    _OPT_STEPS[0] += 1
+
+
 class PackedMBF:
     """Concatenated-branch bf16 operands of one MultiBranchFusion / MessageMBF (head.py:446-474).  The representation
     width is padded to a multiple of the narrowest GEMM N tile (128) with zero rows / columns, so any cardinality x
@@ -318,8 +340,11 @@ class PackedHead:
 
 def packed_head(ih) -> PackedHead:
     pk = ih.__dict__.get("_skg_packed")
-    if pk is None or pk.vsum != _version_sum(pk.params) or pk.ptr0 != (pk.params[0].data_ptr(), pk.params[-1].data_ptr()):
+    flats = ih.__dict__.get("_skg_flat_params")      # flat parameter buffers (shard.GradBuckets): updated through THEIR versions
+    vs = (_version_sum(pk.params) + (_version_sum(flats) if flats else 0), _OPT_STEPS[0]) if pk is not None else None
+    if pk is None or pk.vsum != vs or pk.ptr0 != (pk.params[0].data_ptr(), pk.params[-1].data_ptr()):
         pk = PackedHead(ih)
+        pk.vsum = (_version_sum(pk.params) + (_version_sum(flats) if flats else 0), _OPT_STEPS[0])
         ih.__dict__["_skg_packed"] = pk
     return pk
 
@@ -851,17 +876,22 @@ def _gt_labels(G, run: dict, tables, boxes_cat: Tensor, targets: List[dict]) -> 
     dev = seg.device
     Pn = seg.total_pairs
     counts = [int(t["boxes_h"].shape[0]) for t in targets]
-    gt_off = torch.tensor(np.concatenate([[0], np.cumsum(counts)]).astype(np.int32)).to(dev)
+    gt_off_h = torch.empty(len(counts) + 1, dtype=torch.int32, pin_memory=True)     # pinned: a truly asynchronous copy
+    gt_off_h[0] = 0
+    gt_off_h[1:] = torch.as_tensor(np.cumsum(counts), dtype=torch.int32)
+    gt_off = gt_off_h.to(dev, non_blocking=True)
     if sum(counts):
         gh = torch.cat([t["boxes_h"] for t in targets]).to(dev, torch.float32).contiguous()
         go = torch.cat([t["boxes_o"] for t in targets]).to(dev, torch.float32).contiguous()
         gv_host = [t["labels"] for t in targets if not t["labels"].is_cuda]
         gv = torch.cat([t["labels"] for t in targets]).to(dev, torch.int64).contiguous()
         # the reference indexes labels[x, target['labels'][y]] (head.py:717) and raises IndexError for a verb outside
-        # [0, num_cls); checked on whichever copy is cheapest (host tensors: no device round trip)
-        chk = torch.cat(gv_host) if len(gv_host) == len(targets) else gv
-        if chk.numel() and (int(chk.max()) >= G.num_cls or int(chk.min()) < -G.num_cls):
-            raise IndexError("target verb id out of range for %d classes" % G.num_cls)
+        # [0, num_cls).  Host-resident targets are checked here; device-resident ones are NOT read back (that would drain
+        # the stream every training step): the kernel skips out-of-range ids instead of writing out of bounds
+        if len(gv_host) == len(targets):
+            chk = torch.cat(gv_host)
+            if chk.numel() and (int(chk.max()) >= G.num_cls or int(chk.min()) < -G.num_cls):
+                raise IndexError("target verb id out of range for %d classes" % G.num_cls)
     else:
         gh = go = torch.zeros(1, 4, device=dev); gv = torch.zeros(1, dtype=torch.int64, device=dev)
     labels = torch.empty(Pn, G.num_cls, dtype=torch.float32, device=dev)
@@ -964,8 +994,12 @@ def select_negatives_device(labels: Tensor, pair_img: Tensor, num_images: int):
     first = torch.searchsorted(img_sorted, torch.arange(num_images + 1, device=dev))   # first sorted slot of every image
     rank = torch.arange(Pn * nc, device=dev) - first[img_sorted]
     n_pos_ext = torch.cat([n_pos_img, n_pos_img.new_zeros(1)])
-    neg_flat = order[finite & (rank < n_pos_ext[img_sorted])]
-    pos_flat = torch.nonzero(is_pos.view(-1)).squeeze(1)                             # host sync (sizes)
+    # ONE host sync for both index lists: every image has at least as many zero labels as positives (117 verbs per pair), so
+    # the combined mask holds k positives followed by k selected negatives
+    both = torch.nonzero(torch.cat([is_pos.view(-1), finite & (rank < n_pos_ext[img_sorted])])).squeeze(1)
+    k = both.numel() // 2
+    pos_flat = both[:k]
+    neg_flat = order[both[k:] - Pn * nc]
     return pos_flat, neg_flat
 
 

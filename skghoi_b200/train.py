@@ -169,6 +169,7 @@ class TrainState:
         self._build_pack_table(ih)
         self._unpack = None
         self._grad_key = None
+        self._grad_skey = None
         self.params = list(ih.parameters())
         self.vsum = -1
         self.refresh(force=True)                        # fills the transposed copies (and re-derives the operands)
@@ -245,7 +246,10 @@ class TrainState:
 
     def refresh(self, force: bool = False) -> None:
         from . import engine
-        vs = engine._version_sum(self.params)
+        flats = self.ih().__dict__.get("_skg_flat_params") if self.ih() is not None else None
+        # parameters living in flat buffers (shard.GradBuckets.attach(flatten_params=True)): an optimiser step on the flat
+        # tensors bumps THEIR version counters -- three reads instead of ~400
+        vs = (engine._version_sum(flats) if flats else engine._version_sum(self.params), engine._OPT_STEPS[0])
         if not force and vs == self.vsum:
             return
         for t in self._bsum:
@@ -256,14 +260,24 @@ class TrainState:
     # ---- gradients --------------------------------------------------------------------------------------------------
     def _ensure_unpack(self):
         params = self.params
+        # fast path: the unpack table stands while every .grad is the very tensor object it was built for (identity walk,
+        # no data_ptr calls) and a sample of them still sits at the same address
+        sample = params[::max(len(params) // 8, 1)] + params[-1:]
+        if self._unpack is not None and self._grad_skey is not None:
+            objs = self._grad_objs
+            if all(p.grad is g for p, g in zip(params, objs)) and \
+                    tuple(p.grad.data_ptr() if p.grad is not None else 0 for p in sample) == self._grad_skey:
+                return
         missing = [p for p in params if p.requires_grad and p.grad is None]
         if missing:
-            flat = torch.zeros(sum(p.numel() for p in missing), dtype=torch.float32, device=self.device)
+            flat = torch.zeros(sum((p.numel() + 63) // 64 * 64 for p in missing), dtype=torch.float32, device=self.device)
             o = 0
             for p in missing:
                 p.grad = flat[o:o + p.numel()].view_as(p)
-                o += p.numel()
+                o += (p.numel() + 63) // 64 * 64
         key = tuple(p.grad.data_ptr() if p.grad is not None else 0 for p in params)
+        self._grad_skey = tuple(p.grad.data_ptr() if p.grad is not None else 0 for p in sample)
+        self._grad_objs = [p.grad for p in params]
         if self._unpack is not None and key == self._grad_key:
             return
         ih = self.ih()
@@ -364,14 +378,11 @@ def training_forward(ih, features, image_shapes, box_features: Tensor, box_coord
     with torch.no_grad():
         run = engine.head_forward(ih, features["3"], image_shapes, box_features.detach(), boxes_cat, meta, precise_logits=False,
                                   graph=False, train=True, pk=ts.pk)
-    was_training = ih.training
-    ih.train()
-    try:
-        with torch.enable_grad():           # the TransH loss is differentiable w.r.t. the tables (kge autograd Functions)
-            results = engine.interaction_head_from_pooled(ih, features, image_shapes, box_features.detach(), box_coords,
-                                                          box_labels, box_scores, targets=targets, meta=meta, run=run)
-    finally:
-        ih.train(was_training)
+    # (called from forward_from_pooled only in training mode: no train() / eval() round trip over the ~470 sub-modules)
+    assert ih.training, "training_forward needs the head in training mode"
+    with torch.enable_grad():               # the TransH loss is differentiable w.r.t. the tables (kge autograd Functions)
+        results = engine.interaction_head_from_pooled(ih, features, image_shapes, box_features.detach(), box_coords,
+                                                      box_labels, box_scores, targets=targets, meta=meta, run=run)
     losses = results.pop()
     post = ih.__dict__["_skg_last_post"]
     rec = _StepRecord(ts, run, run["_batch"], run["_flags"], run._ws, post["tables"], post["gt"], post["n_p"],

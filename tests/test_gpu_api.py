@@ -340,3 +340,44 @@ def test_device_preprocess_matches_stock_torchvision(train):
     # the module method takes the device path for CUDA inputs
     via_method = ih.preprocess(dets, targets)
     assert all(torch.equal(a["boxes"], b_["boxes"]) for a, b_ in zip(via_method, got))
+
+
+def test_training_flat_params_fused_optimizer_tracks_updates():
+    """shard.GradBuckets.attach(flatten_params=True) + a FUSED optimiser over the flat buffers (what bench.py's training
+    leg runs): fused updates do not bump tensor version counters, the packed bf16 operands must still follow every step
+    (global optimiser-step hook) -- the loss trajectory equals the per-tensor SGD one, and an eval forward after training
+    sees the trained weights."""
+    from skghoi_b200 import shard
+    batch = synthetic.make_batch([(4, 9), (3, 7)], seed=5, with_targets=True)
+    d = _to_dev(batch)
+    traj = {}
+    for mode in ("per_tensor", "flat_fused"):
+        ih = _head(True)
+        ih.box_pair_head.transh_head.negatives_on_device = True
+        params = [p for p in ih.parameters() if p.requires_grad]
+        if mode == "flat_fused":
+            buckets = shard.GradBuckets(params).attach(flatten_params=True, module=ih)
+            opt = torch.optim.SGD(buckets.flat_params, lr=1e-2, momentum=0.9, fused=True)
+            zero = buckets.zero_grad
+        else:
+            opt = torch.optim.SGD(params, lr=1e-2, momentum=0.9)
+            zero = lambda: opt.zero_grad(set_to_none=False)           # noqa: E731
+        losses = []
+        for _ in range(4):
+            zero()
+            res = ih.forward_from_pooled(d["features"], d["image_shapes"], d["box_features"], d["box_coords"], d["box_labels"],
+                                         d["box_scores"], d["targets"])
+            tot = res[-1]["hoi_loss"] + res[-1]["interactiveness_loss"]
+            tot.backward()
+            opt.step()
+            losses.append(float(tot.detach()))
+        ih.eval()
+        with torch.no_grad():
+            ev = ih.forward_from_pooled(d["features"], d["image_shapes"], d["box_features"], d["box_coords"], d["box_labels"],
+                                        d["box_scores"])
+        traj[mode] = (losses, torch.cat([r["scores"] for r in ev]).cpu())
+    a, b = traj["per_tensor"], traj["flat_fused"]
+    assert a[0][-1] < a[0][0] and b[0][-1] < b[0][0], (a[0], b[0])          # both train
+    for x, y in zip(a[0], b[0]):
+        assert abs(x - y) <= 2e-2 * abs(x), (a[0], b[0])
+    assert float((a[1] - b[1]).abs().max()) <= 2e-2 * float(a[1].abs().max()) + 1e-6

@@ -100,3 +100,27 @@ def test_partition_properties():
     t = torch.tensor([2.0, 4.0])
     assert shard.average_normalisers(t) is t
     assert shard.max_over_ranks([3.0]) == [3.0]
+
+
+def test_flat_params_follow_a_fused_style_optimizer():
+    """GradBuckets.attach(flatten_params=True): parameters and gradients live in flat buffers, an optimiser over
+    ``flat_params`` gives the same update as the per-tensor one, and state_dict / module access are unchanged."""
+    import copy
+    torch.manual_seed(0)
+    net = torch.nn.Sequential(torch.nn.Linear(5, 7), torch.nn.ReLU(), torch.nn.Linear(7, 3))
+    ref = copy.deepcopy(net)
+    x = torch.randn(4, 5)
+    from skghoi_b200.shard import GradBuckets
+    holder = torch.nn.Module()
+    buckets = GradBuckets(net.parameters(), bucket_bytes=64).attach(flatten_params=True, module=holder)
+    assert len(buckets.flat_params) >= 2 and holder.__dict__["_skg_flat_params"] is buckets.flat_params
+    opt = torch.optim.SGD(buckets.flat_params, lr=0.1, momentum=0.9)
+    opt_ref = torch.optim.SGD(ref.parameters(), lr=0.1, momentum=0.9)
+    for _ in range(3):
+        buckets.zero_grad(); opt_ref.zero_grad()
+        net(x).pow(2).sum().backward(); ref(x).pow(2).sum().backward()
+        v0 = sum(f._version for f in buckets.flat_params)
+        opt.step(); opt_ref.step()
+        assert sum(f._version for f in buckets.flat_params) > v0          # the change detector of the packed operands
+    for (k, a), (_, b) in zip(net.state_dict().items(), ref.state_dict().items()):
+        torch.testing.assert_close(a, b, rtol=1e-6, atol=1e-7)

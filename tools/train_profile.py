@@ -1,5 +1,7 @@
-"""Where a training step spends its time (torch.profiler): python tools/train_profile.py  (on the GPU box)."""
-import os, sys, time
+"""Where a training step (bench.py's `training` leg: batch 16 x (16, 32), GradBuckets, SGD momentum) spends its time:
+host enqueue per phase, device->host synchronisations (torch sync debug mode), GPU time per kernel (torch.profiler).
+python tools/train_profile.py  (on the GPU box)."""
+import os, sys, time, warnings
 import torch
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
@@ -18,19 +20,22 @@ d = dict(f={"3": batch["features"]["3"].to(dev)}, bf=batch["box_features"].to(de
          targets=[{k: v.to(dev) for k, v in t.items()} for t in batch["targets"]])
 meta = engine._host_meta(batch["box_labels"], batch["box_scores"], 49)
 params = [p for p in ih.parameters() if p.requires_grad]
-opt = torch.optim.SGD(params, lr=1e-4, momentum=0.9)
+buckets = shard.GradBuckets(params).attach(flatten_params=True, module=ih)
+opt = torch.optim.SGD(buckets.flat_params, lr=1e-4, momentum=0.9, fused=True)
 T = {}
 
 
-def step(timed=False):
+def step(sync=False):
     def mark(k, t0):
-        if timed:
-            torch.cuda.synchronize(); T[k] = T.get(k, 0.0) + time.perf_counter() - t0
+        if sync:
+            torch.cuda.synchronize()
+        T[k] = T.get(k, 0.0) + time.perf_counter() - t0
         return time.perf_counter()
     t0 = time.perf_counter()
-    opt.zero_grad(set_to_none=True)
+    buckets.zero_grad()
+    t0 = mark("zero_grad", t0)
     res = ih.forward_from_pooled(d["f"], batch["image_shapes"], d["bf"], d["boxes"], d["labels"], d["scores"], d["targets"], meta=meta)
-    t0 = mark("forward (native + taped)", t0)
+    t0 = mark("forward + losses", t0)
     ls = res[-1]
     (ls["hoi_loss"] + ls["interactiveness_loss"] + ls["transH_loss"].sum()).backward()
     t0 = mark("backward", t0)
@@ -41,24 +46,32 @@ def step(timed=False):
 for _ in range(3):
     step()
 torch.cuda.synchronize()
-for _ in range(5):
-    step(True)
-print({k: "%.2f ms" % (v / 5 * 1e3) for k, v in T.items()})
-# split the forward
-import skghoi_b200.train as TR
-orig = engine.interaction_head_from_pooled
-acc = {"native": 0.0}
-def wrapped(*a, **k):
-    torch.cuda.synchronize(); t0 = time.perf_counter(); r = orig(*a, **k); torch.cuda.synchronize(); acc["native"] += time.perf_counter() - t0; return r
-engine.interaction_head_from_pooled = wrapped
-for _ in range(5):
+for sync in (False, True):
+    T.clear()
+    t0 = time.perf_counter()
+    for _ in range(10):
+        step(sync)
+    torch.cuda.synchronize()
+    print("%s: %.2f ms/step | " % ("phases with a synchronise after each" if sync else "host enqueue per phase (no synchronise)",
+                                     (time.perf_counter() - t0) / 10 * 1e3), {k: "%.2f ms" % (v / 10 * 1e3) for k, v in T.items()})
+print("---- device->host synchronisations of ONE step:")
+torch.cuda.set_sync_debug_mode("warn")
+with warnings.catch_warnings(record=True) as w:
+    warnings.simplefilter("always")
     step()
-print("native train-mode forward inside the step: %.2f ms" % (acc["native"] / 5 * 1e3))
-engine.interaction_head_from_pooled = orig
+torch.cuda.set_sync_debug_mode("default")
+import traceback
+for x in w:
+    print("  sync:", x.filename.replace(ROOT, "."), x.lineno)
 from torch.profiler import profile, ProfilerActivity
 with profile(activities=[ProfilerActivity.CPU, ProfilerActivity.CUDA]) as prof:
     for _ in range(3):
         step()
     torch.cuda.synchronize()
-print(prof.key_averages().table(sort_by="self_cpu_time_total", row_limit=18, max_name_column_width=50))
-print(prof.key_averages().table(sort_by="self_cuda_time_total", row_limit=14, max_name_column_width=70))
+print(prof.key_averages().table(sort_by="self_cuda_time_total", row_limit=30, max_name_column_width=90))
+import cProfile, pstats
+pr = cProfile.Profile(); pr.enable()
+for _ in range(10):
+    step()
+torch.cuda.synchronize(); pr.disable()
+pstats.Stats(pr, stream=sys.stdout).sort_stats("cumulative").print_stats(60)
