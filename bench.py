@@ -656,13 +656,18 @@ def measure_training(torch, dist, args, dev, rank, world, flush):
     buckets = shard.GradBuckets(params).attach(flatten_params=True, module=ih)
     opt = torch.optim.SGD(buckets.flat_params, lr=1e-4, momentum=0.9, fused=True)
 
+    if world > 1:
+        # the packed gradient groups are all-reduced INSIDE loss.backward(), each behind its stage event of
+        # skg_head_backward_staged, while the rest of the backward runs (train._GradAllReduce)
+        from skghoi_b200 import train as _train
+        _train.enable_gradient_allreduce(ih)
+
     def step():
         buckets.zero_grad()
         res = ih.forward_from_pooled(d["f"], batch["image_shapes"], d["bf"], d["boxes"], d["labels"], d["scores"],
                                      d["targets"], meta=meta)
         ls = res[-1]
         (ls["hoi_loss"] + ls["interactiveness_loss"] + ls["transH_loss"].sum()).backward()
-        buckets.allreduce()
         opt.step()
         return ls
     for _ in range(3):
@@ -683,8 +688,9 @@ def measure_training(torch, dist, args, dev, rank, world, flush):
             "value": pairs * world * args.train_steps / (t_ms * 1e-3), "unit": UNIT, "ms_per_step": t_ms / args.train_steps,
             "steps": args.train_steps, "n_gpus": world, "pairs_per_step_per_gpu": pairs,
             "negatives": "TransH negatives drawn on the device (uniform without replacement per image, as head.py:939)",
-            "step": "zero_grad + skg_head_forward(TRAIN) + post / losses + skg_head_backward (every dX / dW on the tcgen05 GEMM, trainops kernels) + gradient unpack + %s + SGD update"
-                    % ("bucketed NCCL gradient all-reduce (%d buckets)" % len(buckets.buckets) if world > 1 else "no all-reduce (1 GPU)"),
+            "step": "zero_grad + skg_head_forward(TRAIN) + post / losses + skg_head_backward (every dX / dW on the tcgen05 GEMM, trainops kernels) + %s + gradient unpack + fused SGD over flat parameter buffers"
+                    % ("NCCL all-reduce of the 3 packed gradient groups, each started behind its stage event inside the backward "
+                       "(the 81 MB node-side group overlaps the cell-side chain)" if world > 1 else "no all-reduce (1 GPU)"),
             "grad_bytes": sum(p.numel() * 4 for p in params),
             "final_losses": {k: float(v.detach().reshape(-1)[0]) for k, v in ls.items()}}
 

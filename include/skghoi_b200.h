@@ -536,6 +536,17 @@ typedef struct skg_head_loss_args {
 int skg_head_backward(const skg_head_weights* weights, const skg_head_weights_t* weights_t, const skg_head_batch* batch,
                       const skg_head_loss_args* loss, const skg_head_grads* grads, int flags, void* workspace,
                       int64_t workspace_bytes, cudaStream_t stream);
+/* The same with stage events for data-parallel training (reference: DDP's bucketed all-reduce overlapping backward,
+ * utils.py:200-229): stage_events[k] (cudaEvent_t handles, NULL entries skipped) is recorded on `stream` when the gradients of
+ * group k are final, so the caller can start that group's all-reduce on another stream while the backward continues:
+ *   0: Wpred bpred W3g b3g Wg1 bg1 ln_* W3os b3os W3so b3so w_adj b_adj W3att b3att
+ *   1: W_hproj b_hproj W_oproj b_oproj Wfc bfc Wb2 bb2 Wb1 bb1   (the node-side chain incl. box_head: 69 % of the bytes; it
+ *      runs BEFORE the cell-side chain so that its all-reduce is covered)
+ *   2: W2cat b2cat Wsp2 bsp2 Wsp1 bsp1 Wsp0 bsp0                 (the end of the backward) */
+#define SKG_HEAD_BACKWARD_STAGES 3
+int skg_head_backward_staged(const skg_head_weights* weights, const skg_head_weights_t* weights_t, const skg_head_batch* batch,
+                             const skg_head_loss_args* loss, const skg_head_grads* grads, int flags, void* workspace,
+                             int64_t workspace_bytes, cudaStream_t stream, void* const* stage_events, int num_stage_events);
 
 /* Host-side packing of the per-batch segment table every batched kernel consumes (all HOST pointers): n / n_h [B]
  * boxes and humans per image, hw [B,2] = (h, w) as doubles.  `out` receives

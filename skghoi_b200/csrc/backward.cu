@@ -60,6 +60,22 @@ using namespace skg;
 extern "C" int skg_head_backward(const skg_head_weights* wp, const skg_head_weights_t* wtp, const skg_head_batch* bp,
                                  const skg_head_loss_args* lp, const skg_head_grads* gp, int flags, void* workspace,
                                  int64_t workspace_bytes, cudaStream_t st) {
+  return skg_head_backward_staged(wp, wtp, bp, lp, gp, flags, workspace, workspace_bytes, st, nullptr, 0);
+}
+
+// Stage events (data-parallel training: the gradient all-reduce overlaps the rest of the backward).  stage_events[k] is
+// recorded on `st` when the gradients of group k are FINAL:
+//   0: predictor | suppressor, attention_head_g.fc_3 / fc_1, LayerNorms, message fc_3, adjacency, attention_head.fc_3
+//   1: the node-side chain -- per-node projections (attention_head.fc_1, sub_to_obj.fc_1, obj_to_sub.fc_1), fc_head | fc_tail,
+//      box_head (69 % of the bytes: it is scheduled BEFORE the cell-side chain so that its all-reduce has cover)
+//   2: the cell-side chain -- fused fc_2 of the four MBFs, spatial head (the end of the backward)
+extern "C" int skg_head_backward_staged(const skg_head_weights* wp, const skg_head_weights_t* wtp, const skg_head_batch* bp,
+                                        const skg_head_loss_args* lp, const skg_head_grads* gp, int flags, void* workspace,
+                                        int64_t workspace_bytes, cudaStream_t st, void* const* stage_events, int num_stage_events) {
+  auto stage_done = [&](int k) -> int {
+    if (stage_events && k < num_stage_events && stage_events[k]) SKG_CUDA(cudaEventRecord(reinterpret_cast<cudaEvent_t>(stage_events[k]), st));
+    return SKG_OK;
+  };
   SKG_REQUIRE(wp && wtp && bp && lp && gp && workspace, "null pointer argument");
   SKG_REQUIRE(flags & SKG_HEAD_TRAIN, "skg_head_backward needs the SKG_HEAD_TRAIN workspace layout");
   const skg_head_weights& w = *wp;
@@ -147,17 +163,10 @@ extern "C" int skg_head_backward(const skg_head_weights* wp, const skg_head_weig
                                          b.max_boxes_per_image, R, H(B_DPOS), H(B_DPSO), R, F(B_DADJH), F(B_DADJO), st));
   SKG_TRY(skg_adjacency_backward(F(B_DADJH), F(B_DADJO), H(B_WTS), R, w.w_adj, C, R, H(B_DWTS), R, d.w_adj, d.b_adj, st));
   SKG_TRY(wgrad(c, H(B_DWTS), R, R, H(B_HATT), R, R, nullptr, C, d.W3att, R, d.b3att, true));     // second use of attention_head.fc_3
+  SKG_TRY(stage_done(0));
   SKG_TRY(dgrad(c, H(B_DWTS), R, C, R, wt.W3attT, R, R, H(B_HATT), R, nullptr, 0, H(B_DPATT), R, nullptr, 0, nullptr));
   // ---- branch products of the first pass: dS (att | os | so) and the node-side sums dhproj / doproj
   SKG_TRY(skg_hadamard_backward(&hb, NH, 2, st));
-  // ---- fused fc_2 of the four MBFs, then the spatial head (head.py:662-669)
-  SKG_TRY(wgrad(c, H(B_DS), 4 * R, 4 * R, H(B_SP), R, R, nullptr, C, d.W2cat, R, d.b2cat, false));
-  SKG_TRY(dgrad(c, H(B_DS), 4 * R, C, 4 * R, wt.W2catT, 4 * R, R, H(B_SP), R, nullptr, 0, H(B_DSP), R, nullptr, 0, nullptr));
-  SKG_TRY(wgrad(c, H(B_DSP), R, R, H(B_S2), 256, 256, nullptr, C, d.Wsp2, 256, d.bsp2, false));
-  SKG_TRY(dgrad(c, H(B_DSP), R, C, R, wt.Wsp2T, R, 256, H(B_S2), 256, nullptr, 0, H(B_DS2), 256, nullptr, 0, nullptr));
-  SKG_TRY(wgrad(c, H(B_DS2), 256, 256, H(B_S1), 128, 128, nullptr, C, d.Wsp1, 128, d.bsp1, false));
-  SKG_TRY(dgrad(c, H(B_DS2), 256, C, 256, wt.Wsp1T, 256, 128, H(B_S1), 128, nullptr, 0, H(B_DS1), 128, nullptr, 0, nullptr));
-  SKG_TRY(skg_spatial_fc1_backward(F(B_ENC), H(B_DS1), C, 46, 128, d.Wsp0, d.bsp0, st));
   // ---- node projections [U_h | V_so] = hN W_hproj^T, [U_o | V_os] = oN W_oproj^T
   SKG_TRY(skg_cast_pad_bf16(F(B_DHPROJ), 2 * R, nullptr, 0, NH, 2 * R, n16, 2 * R, 2 * R, st));
   SKG_TRY(skg_cast_pad_bf16(F(B_DOPROJ), 2 * R, nullptr, 0, NB, 2 * R, n16_o, 2 * R, 2 * R, st));
@@ -173,5 +182,16 @@ extern "C" int skg_head_backward(const skg_head_weights* wp, const skg_head_weig
   SKG_TRY(wgrad(c, H(B_DX2), E, E, H(B_X1), E, E, nullptr, NB, d.Wb2, E, d.bb2, false));
   SKG_TRY(dgrad(c, H(B_DX2), E, NB, E, wt.Wb2T, E, E, H(B_X1), E, nullptr, 0, H(B_DX1), E, nullptr, 0, nullptr));
   SKG_TRY(wgrad(c, H(B_DX1), E, E, xb, w.K0, w.K0, nullptr, NB, d.Wb1, w.K0, d.bb1, false));
+  SKG_TRY(stage_done(1));
+  // ---- fused fc_2 of the four MBFs, then the spatial head (head.py:662-669): the cell-side chain, independent of the
+  //      node-side chain above once the Hadamard backward has split dS from dhproj / doproj
+  SKG_TRY(wgrad(c, H(B_DS), 4 * R, 4 * R, H(B_SP), R, R, nullptr, C, d.W2cat, R, d.b2cat, false));
+  SKG_TRY(dgrad(c, H(B_DS), 4 * R, C, 4 * R, wt.W2catT, 4 * R, R, H(B_SP), R, nullptr, 0, H(B_DSP), R, nullptr, 0, nullptr));
+  SKG_TRY(wgrad(c, H(B_DSP), R, R, H(B_S2), 256, 256, nullptr, C, d.Wsp2, 256, d.bsp2, false));
+  SKG_TRY(dgrad(c, H(B_DSP), R, C, R, wt.Wsp2T, R, 256, H(B_S2), 256, nullptr, 0, H(B_DS2), 256, nullptr, 0, nullptr));
+  SKG_TRY(wgrad(c, H(B_DS2), 256, 256, H(B_S1), 128, 128, nullptr, C, d.Wsp1, 128, d.bsp1, false));
+  SKG_TRY(dgrad(c, H(B_DS2), 256, C, 256, wt.Wsp1T, 256, 128, H(B_S1), 128, nullptr, 0, H(B_DS1), 128, nullptr, 0, nullptr));
+  SKG_TRY(skg_spatial_fc1_backward(F(B_ENC), H(B_DS1), C, 46, 128, d.Wsp0, d.bsp0, st));
+  SKG_TRY(stage_done(2));
   return SKG_OK;
 }

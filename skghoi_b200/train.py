@@ -16,6 +16,7 @@ tables).  Gradients of the head's parameters w.r.t. ``hoi_loss`` and ``interacti
 that enter fc_head / fc_tail are constants of the step (the reference re-draws the tables on every call, head.py:574-578).
 """
 import ctypes
+import os
 import weakref
 from typing import List, Optional
 
@@ -45,6 +46,15 @@ class HeadWeightsT(ctypes.Structure):
 _GRAD_FIELDS = ("Wb1", "bb1", "Wb2", "bb2", "Wsp0", "bsp0", "Wsp1", "bsp1", "Wsp2", "bsp2", "Wfc", "bfc", "W_hproj", "b_hproj",
                 "W_oproj", "b_oproj", "Wg1", "bg1", "W2cat", "b2cat", "W3att", "b3att", "W3os", "b3os", "W3so", "b3so", "W3g",
                 "b3g", "w_adj", "b_adj", "ln_h_w", "ln_h_b", "ln_o_w", "ln_o_b", "Wpred", "bpred")
+
+
+# gradient groups in the order skg_head_backward_staged finishes them: the packed gradient buffer is laid out group by group,
+# so every group is ONE contiguous range to all-reduce as soon as its stage event has fired
+_GRAD_STAGES = (("Wpred", "bpred", "W3g", "b3g", "Wg1", "bg1", "ln_h_w", "ln_h_b", "ln_o_w", "ln_o_b", "W3os", "b3os", "W3so", "b3so",
+                 "w_adj", "b_adj", "W3att", "b3att"),
+                ("W_hproj", "b_hproj", "W_oproj", "b_oproj", "Wfc", "bfc", "Wb2", "bb2", "Wb1", "bb1"),
+                ("W2cat", "b2cat", "Wsp2", "bsp2", "Wsp1", "bsp1", "Wsp0", "bsp0"))
+assert sorted(k for g in _GRAD_STAGES for k in g) == sorted(_GRAD_FIELDS)
 
 
 class HeadGrads(ctypes.Structure):
@@ -161,11 +171,16 @@ class TrainState:
         self.g = {}
         self.cg = HeadGrads()
         o = 0
-        for k in _GRAD_FIELDS:
-            n = int(np.prod(shapes[k]))
-            self.g[k] = self.gflat[o:o + n].view(*shapes[k])
-            setattr(self.cg, k, self.g[k].data_ptr())
-            o += (n + 63) // 64 * 64
+        self.stage_ranges = []                          # (begin, end) element ranges of the gradient groups inside gflat
+        for group in _GRAD_STAGES:
+            o0 = o
+            for k in group:
+                n = int(np.prod(shapes[k]))
+                self.g[k] = self.gflat[o:o + n].view(*shapes[k])
+                setattr(self.cg, k, self.g[k].data_ptr())
+                o += (n + 63) // 64 * 64
+            self.stage_ranges.append((o0, o))
+        self.dist = None                                # set by enable_gradient_allreduce
         self._build_pack_table(ih)
         self._unpack = None
         self._grad_key = None
@@ -282,20 +297,22 @@ class TrainState:
             return
         ih = self.ih()
         tab = _BlockTable(self.device)
+        scale = 1.0 / self.dist.world if self.dist is not None else 1.0      # rank mean of the all-reduced packed gradients
+        self._unpack_scale = scale
         for p, name, r0, c0, tname, kind in self._blocks(ih):
             base = p._base if p._base is not None else p
             if not getattr(base, "requires_grad", False) or base.grad is None:
                 continue
             if name in ("Wfh_ent", "bfh"):               # fc_head bias / entity columns: both come from dbfc[:R]
                 if name == "bfh":
-                    tab.add(self.g["bfc"].reshape(1, -1)[:, :p.shape[1]], base.grad.reshape(1, -1), None, flags=_ACC)
+                    tab.add(self.g["bfc"].reshape(1, -1)[:, :p.shape[1]], base.grad.reshape(1, -1), None, flags=_ACC, scale=scale)
                 continue
             gsrc = self.g[name] if self.g[name].dim() > 1 else _v(self.g[name])
             rows, cols = p.shape
             src = gsrc[r0:r0 + rows, c0:c0 + cols]
             # the parameter view p (a slice / reshape of the parameter) maps onto the same slice of its .grad
             gview = base.grad.as_strided(p.shape, p.stride(), base.grad.storage_offset() + p.storage_offset() - base.storage_offset())
-            tab.add(src, gview, None, flags=_ACC)
+            tab.add(src, gview, None, flags=_ACC, scale=scale)
         self._unpack = tab.finalize()
         self._grad_key = key
 
@@ -309,7 +326,50 @@ class TrainState:
         if fh.requires_grad and fh.grad is not None:
             ent = G.transh_head.transh.ent_embeddings.weight.detach()
             # d fc_head.weight[:, E:] = sum_rows g_row (x) E[human_idx] = dbias (x) E[human_idx]   (head_stack rows are constant)
-            fh.grad[:, self.pk.E:].addmm_(self.g["bfc"][:self.pk.R].unsqueeze(1), ent[G.human_idx].float().unsqueeze(0))
+            fh.grad[:, self.pk.E:].addmm_(self.g["bfc"][:self.pk.R].unsqueeze(1), ent[G.human_idx].float().unsqueeze(0),
+                                          alpha=getattr(self, "_unpack_scale", 1.0))
+
+
+class _GradAllReduce:
+    """Overlapped gradient averaging of the native training step (the reference trains under DDP, utils.py:200-229): one
+    all-reduce per gradient group of skg_head_backward_staged on the PACKED gradient buffer (identical layout on every rank),
+    started behind the group's stage event on a side stream while the backward continues; the unpack that follows scales by
+    1 / world.  NCCL on the box, gloo in the CPU tests of the host logic."""
+
+    def __init__(self, ts: "TrainState", group=None):
+        import torch.distributed as dist
+        self.group = group
+        self.world = dist.get_world_size(group)
+        dev = ts.device
+        self.side = torch.cuda.Stream(dev)
+        self.events = [torch.cuda.Event() for _ in range(len(ts.stage_ranges))]
+        for e in self.events:
+            e.record(torch.cuda.current_stream(dev))         # materialises the cudaEvent_t handle
+        self.event_array = (ctypes.c_void_p * len(self.events))(*[e.cuda_event for e in self.events])
+        self.work = []
+
+    def launch(self, ts: "TrainState") -> None:
+        import torch.distributed as dist
+        self.work = []
+        if os.environ.get("SKG_DIST_SYNC"):                  # diagnostics: no overlap, collectives after the whole backward
+            torch.cuda.synchronize(ts.device)
+        with torch.cuda.stream(self.side):
+            for ev, (a, b) in zip(self.events, ts.stage_ranges):
+                self.side.wait_event(ev)
+                self.work.append(dist.all_reduce(ts.gflat[a:b], group=self.group, async_op=True))
+        for w in self.work:
+            w.wait()                                         # the current stream waits for the collective, not the host
+        self.work = []
+        ts.gflat.record_stream(self.side)
+
+
+def enable_gradient_allreduce(ih, group=None) -> None:
+    """Data-parallel training of the head: from the next backward on, the packed parameter gradients are averaged over the
+    ranks of ``group`` INSIDE ``loss.backward()`` (overlapped with it) -- do not all-reduce the head's ``p.grad`` again."""
+    ts = train_state(ih)
+    ts.dist = _GradAllReduce(ts, group)
+    ts._unpack = None                                        # rebuild the unpack table with the 1 / world scale
+    ts._grad_key = ts._grad_skey = None
 
 
 def train_state(ih) -> TrainState:
@@ -340,10 +400,19 @@ class _StepRecord:
         la = HeadLossArgs()
         la.tables = ctypes.pointer(self.tables)
         la.gt_labels, la.n_p, la.g_hoi, la.g_int, la.prior_power = self.gt.data_ptr(), self.n_p.data_ptr(), gh.data_ptr(), gi.data_ptr(), 1.0
+        dd = ts.dist
         with _lib.on_device(dev):
             ts.gflat.zero_()
-            _lib.call("skg_head_backward", ctypes.byref(ts.pk.cw), ctypes.byref(ts.wt), ctypes.byref(self.b), ctypes.byref(la),
-                      ctypes.byref(ts.cg), self.flags, _lib.ptr(self.ws), self.ws.numel(), _lib.stream_ptr(dev))
+            if dd is None:
+                _lib.call("skg_head_backward", ctypes.byref(ts.pk.cw), ctypes.byref(ts.wt), ctypes.byref(self.b), ctypes.byref(la),
+                          ctypes.byref(ts.cg), self.flags, _lib.ptr(self.ws), self.ws.numel(), _lib.stream_ptr(dev))
+            else:
+                # data parallel: the packed gradient groups are all-reduced as the backward finishes them (stage events recorded
+                # inside the C call; the collectives are issued behind them on a side stream) and averaged by the unpack's scale
+                _lib.call("skg_head_backward_staged", ctypes.byref(ts.pk.cw), ctypes.byref(ts.wt), ctypes.byref(self.b), ctypes.byref(la),
+                          ctypes.byref(ts.cg), self.flags, _lib.ptr(self.ws), self.ws.numel(), _lib.stream_ptr(dev), dd.event_array,
+                          len(dd.events))
+                dd.launch(ts)
         ts.grads_into_params()
         self.done = True
 
