@@ -644,9 +644,11 @@ def measure_training(torch, dist, args, dev, rank, world, flush):
     ih.box_pair_head.transh_head.negatives_on_device = True     # same distribution as head.py:939, device generator, batched
     n_img = args.train_images
     batch = synthetic.make_batch([(args.humans, args.boxes)] * n_img, seed=1042 + rank, with_targets=True)
+    n_per = [int(b.shape[0]) for b in batch["box_coords"]]
+    # detections as per-image views of three packed device tensors (what preprocess_detections_device hands out)
     d = dict(f={"3": batch["features"]["3"].to(dev)}, bf=batch["box_features"].to(dev),
-             boxes=[b.to(dev) for b in batch["box_coords"]], labels=[l.to(dev) for l in batch["box_labels"]],
-             scores=[s_.to(dev) for s_ in batch["box_scores"]],
+             boxes=list(torch.cat(batch["box_coords"]).to(dev).split(n_per)), labels=list(torch.cat(batch["box_labels"]).to(dev).split(n_per)),
+             scores=list(torch.cat(batch["box_scores"]).to(dev).split(n_per)),
              targets=[{k: v.to(dev) for k, v in t.items()} for t in batch["targets"]])
     from skghoi_b200 import engine
     meta = engine._host_meta(batch["box_labels"], batch["box_scores"], 49)

@@ -543,6 +543,10 @@ int skg_head_backward(const skg_head_weights* weights, const skg_head_weights_t*
  *   1: W_hproj b_hproj W_oproj b_oproj Wfc bfc Wb2 bb2 Wb1 bb1   (the node-side chain incl. box_head: 69 % of the bytes; it
  *      runs BEFORE the cell-side chain so that its all-reduce is covered)
  *   2: W2cat b2cat Wsp2 bsp2 Wsp1 bsp1 Wsp0 bsp0                 (the end of the backward) */
+/* flags | SKG_HEAD_GRAPH: the launch sequence is replayed as a CUDA graph when every byte that reaches a launch repeats
+ * (weights, batch geometry, loss-argument / gradient addresses, workspace, stage events): first sighting plain launches,
+ * second capture, then replays; skg_head_backward_graph_stats counts them for this thread */
+void skg_head_backward_graph_stats(long long* replays, long long* captures, long long* plain);
 #define SKG_HEAD_BACKWARD_STAGES 3
 int skg_head_backward_staged(const skg_head_weights* weights, const skg_head_weights_t* weights_t, const skg_head_batch* batch,
                              const skg_head_loss_args* loss, const skg_head_grads* grads, int flags, void* workspace,

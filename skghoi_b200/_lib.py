@@ -286,6 +286,7 @@ _SIGNATURES["skg_kg_sample"] = (I, [P, P, P, P, P, P, P, P, L, L, P, P, I, L, I,
 # ---- training step (csrc/trainops.cu, csrc/backward.cu); struct pointers travel as void* (ctypes.byref) -------------
 _SIGNATURES["skg_block_copy"] = (I, [P, P, I, P])
 _SIGNATURES["skg_head_backward"] = (I, [P, P, P, P, P, I, P, L, P])
+_SIGNATURES["skg_head_backward_graph_stats"] = (None, [ctypes.POINTER(ctypes.c_longlong)] * 3)
 _SIGNATURES["skg_head_backward_staged"] = (I, [P, P, P, P, P, I, P, L, P, P, I])
 _SIGNATURES["skg_transpose_bf16"] = (I, [P, L, L, I, P, P, L, P, P])
 _SIGNATURES["skg_hum2box"] = (I, [P, I, P, P])

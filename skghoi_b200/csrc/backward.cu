@@ -13,8 +13,11 @@
 #include "common.cuh"
 #include "skghoi_b200.h"
 #include "head_plan.cuh"
+#include "graph_cache.cuh"
 
 namespace skg {
+
+static thread_local GraphCache g_bwd_graphs;
 
 struct BwdCtx {
   uint8_t* base;
@@ -69,11 +72,47 @@ extern "C" int skg_head_backward(const skg_head_weights* wp, const skg_head_weig
 //   1: the node-side chain -- per-node projections (attention_head.fc_1, sub_to_obj.fc_1, obj_to_sub.fc_1), fc_head | fc_tail,
 //      box_head (69 % of the bytes: it is scheduled BEFORE the cell-side chain so that its all-reduce has cover)
 //   2: the cell-side chain -- fused fc_2 of the four MBFs, spatial head (the end of the backward)
+static int backward_enqueue(const skg_head_weights* wp, const skg_head_weights_t* wtp, const skg_head_batch* bp,
+                            const skg_head_loss_args* lp, const skg_head_grads* gp, int flags, void* workspace,
+                            int64_t workspace_bytes, cudaStream_t st, void* const* stage_events, int num_stage_events, bool capturing);
+
+extern "C" void skg_head_backward_graph_stats(long long* replays, long long* captures, long long* plain) {
+  if (replays) *replays = g_bwd_graphs.stats[0];
+  if (captures) *captures = g_bwd_graphs.stats[1];
+  if (plain) *plain = g_bwd_graphs.stats[2];
+}
+
 extern "C" int skg_head_backward_staged(const skg_head_weights* wp, const skg_head_weights_t* wtp, const skg_head_batch* bp,
                                         const skg_head_loss_args* lp, const skg_head_grads* gp, int flags, void* workspace,
                                         int64_t workspace_bytes, cudaStream_t st, void* const* stage_events, int num_stage_events) {
+  SKG_REQUIRE(wp && wtp && bp && lp && gp && workspace, "null pointer argument");
+  if (!(flags & SKG_HEAD_GRAPH))
+    return backward_enqueue(wp, wtp, bp, lp, gp, flags, workspace, workspace_bytes, st, stage_events, num_stage_events, false);
+  // SKG_HEAD_GRAPH: the ~130 launches replayed as one graph when every byte that reaches a launch repeats (weights, batch
+  // geometry, loss-argument and gradient ADDRESSES, workspace, stage events) -- a training loop over a fixed batch geometry
+  // with stable buffers; anything else takes the plain launches
+  SKG_REQUIRE(lp->tables, "incomplete loss arguments");
+  KeyBuilder kb;
+  int dev = 0;
+  SKG_CUDA(cudaGetDevice(&dev));
+  kb.add(dev); kb.add(*wp); kb.add(*wtp); kb.add(*bp); kb.add(*lp->tables); kb.add(lp->gt_labels); kb.add(lp->n_p); kb.add(lp->g_hoi);
+  kb.add(lp->g_int); kb.add(lp->prior_power); kb.add(*gp); kb.add(flags); kb.add(workspace); kb.add(workspace_bytes);
+  for (int k = 0; k < num_stage_events; ++k) kb.add(stage_events ? stage_events[k] : nullptr);
+  return graph_cached_run(g_bwd_graphs, kb.bytes, st, [&](cudaStream_t s, bool capturing) {
+    return backward_enqueue(wp, wtp, bp, lp, gp, flags, workspace, workspace_bytes, s, stage_events, num_stage_events, capturing);
+  });
+}
+
+static int backward_enqueue(const skg_head_weights* wp, const skg_head_weights_t* wtp, const skg_head_batch* bp,
+                            const skg_head_loss_args* lp, const skg_head_grads* gp, int flags, void* workspace,
+                            int64_t workspace_bytes, cudaStream_t st, void* const* stage_events, int num_stage_events, bool capturing) {
   auto stage_done = [&](int k) -> int {
-    if (stage_events && k < num_stage_events && stage_events[k]) SKG_CUDA(cudaEventRecord(reinterpret_cast<cudaEvent_t>(stage_events[k]), st));
+    if (stage_events && k < num_stage_events && stage_events[k]) {
+      // inside a capture the record must become an EXTERNAL event-record node: it then fires at every replay and streams
+      // outside the graph can wait on it
+      if (capturing) SKG_CUDA(cudaEventRecordWithFlags(reinterpret_cast<cudaEvent_t>(stage_events[k]), st, cudaEventRecordExternal));
+      else SKG_CUDA(cudaEventRecord(reinterpret_cast<cudaEvent_t>(stage_events[k]), st));
+    }
     return SKG_OK;
   };
   SKG_REQUIRE(wp && wtp && bp && lp && gp && workspace, "null pointer argument");

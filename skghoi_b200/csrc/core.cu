@@ -28,6 +28,7 @@ int check_launch(const char* what) {
 }
 
 void add_launches(long long n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
+long long launch_count_now() { return g_launches.load(std::memory_order_relaxed); }
 
 int num_sms() {
   static thread_local int cached_dev = -1, cached = 0;

@@ -659,12 +659,11 @@ def head_forward(ih, features3: Tensor, image_shapes, box_features: Tensor, boxe
     flags = (_lib.HEAD_PRECISE_LOGITS if precise_logits else 0) | (_lib.HEAD_WANT_TAPS if want_taps else 0)
     if train:
         flags = (flags & ~_lib.HEAD_PRECISE_LOGITS) | _lib.HEAD_TRAIN
-        graph = False
     if profile:
         flags |= _lib.HEAD_PROFILE
     elif graph:
         flags |= _lib.HEAD_GRAPH
-        if CAPACITY_BUCKETS and not want_taps:
+        if CAPACITY_BUCKETS and not want_taps and not train:
             # launches sized by a capacity bucket, true counts + input addresses read from the segment table on the device:
             # ONE captured graph per bucket serves every batch geometry and every set of input buffers
             flags |= _lib.HEAD_CAPACITY
@@ -894,7 +893,9 @@ def _gt_labels(G, run: dict, tables, boxes_cat: Tensor, targets: List[dict]) -> 
                 raise IndexError("target verb id out of range for %d classes" % G.num_cls)
     else:
         gh = go = torch.zeros(1, 4, device=dev); gv = torch.zeros(1, dtype=torch.int64, device=dev)
-    labels = torch.empty(Pn, G.num_cls, dtype=torch.float32, device=dev)
+    labels = run.get("_gt_out")                          # the training step's persistent buffer (stable address), else fresh
+    if labels is None or tuple(labels.shape) != (Pn, G.num_cls):
+        labels = torch.empty(Pn, G.num_cls, dtype=torch.float32, device=dev)
     with torch.cuda.device(dev):
         _lib.call("skg_associate_gt", _lib.ptr(boxes_cat), ctypes_byref(tables), Pn, G.num_cls, _lib.ptr(gt_off),
                   _lib.ptr(gh), _lib.ptr(go), _lib.ptr(gv), float(G.fg_iou_thresh), _lib.ptr(labels), _lib.stream_ptr(dev))

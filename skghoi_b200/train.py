@@ -181,6 +181,10 @@ class TrainState:
                 o += (n + 63) // 64 * 64
             self.stage_ranges.append((o0, o))
         self.dist = None                                # set by enable_gradient_allreduce
+        self.graph = True                               # forward / backward launch sequences replayed as CUDA graphs when their
+        #                                                 keys repeat (fixed batch geometry, stable buffers); else plain launches
+        self.loss_scalars = torch.zeros(4, dtype=torch.float32, device=dev)
+        self._gt_buf = None
         self._build_pack_table(ih)
         self._unpack = None
         self._grad_key = None
@@ -189,6 +193,13 @@ class TrainState:
         self.vsum = -1
         self.refresh(force=True)                        # fills the transposed copies (and re-derives the operands)
         self.anchor = torch.zeros(1, device=dev, requires_grad=True)
+
+    def gt_buffer(self, pairs: int, num_cls: int) -> Tensor:
+        """Persistent [pairs, num_cls] label buffer (a stable address for the backward's graph key)."""
+        n = max(pairs, 1) * num_cls
+        if self._gt_buf is None or self._gt_buf.numel() < n:
+            self._gt_buf = torch.empty(int(n * 1.25) + 64, dtype=torch.float32, device=self.device)
+        return self._gt_buf[:pairs * num_cls].view(pairs, num_cls)
 
     # ---- parameter -> operand map (the inverse, operand gradient -> parameter gradient, is built from the same list) ----
     def _blocks(self, ih):
@@ -395,22 +406,26 @@ class _StepRecord:
         zero = None
         if g_hoi is None or g_int is None:
             zero = torch.zeros(1, dtype=torch.float32, device=dev)
-        gh = (g_hoi if g_hoi is not None else zero).reshape(-1).float().contiguous()
-        gi = (g_int if g_int is not None else zero).reshape(-1).float().contiguous()
+        gh = (g_hoi if g_hoi is not None else zero).reshape(-1).float()
+        gi = (g_int if g_int is not None else zero).reshape(-1).float()
+        # normalisers and upstream gradients into ONE persistent 4-float buffer: stable addresses for the backward's graph key
+        sc = ts.loss_scalars
+        torch.cat([self.n_p.reshape(-1), gh, gi], out=sc)
         la = HeadLossArgs()
         la.tables = ctypes.pointer(self.tables)
-        la.gt_labels, la.n_p, la.g_hoi, la.g_int, la.prior_power = self.gt.data_ptr(), self.n_p.data_ptr(), gh.data_ptr(), gi.data_ptr(), 1.0
+        la.gt_labels, la.n_p, la.g_hoi, la.g_int, la.prior_power = self.gt.data_ptr(), sc.data_ptr(), sc[2:].data_ptr(), sc[3:].data_ptr(), 1.0
+        bflags = self.flags | (_lib.HEAD_GRAPH if ts.graph else 0)
         dd = ts.dist
         with _lib.on_device(dev):
             ts.gflat.zero_()
             if dd is None:
-                _lib.call("skg_head_backward", ctypes.byref(ts.pk.cw), ctypes.byref(ts.wt), ctypes.byref(self.b), ctypes.byref(la),
-                          ctypes.byref(ts.cg), self.flags, _lib.ptr(self.ws), self.ws.numel(), _lib.stream_ptr(dev))
+                _lib.call("skg_head_backward_staged", ctypes.byref(ts.pk.cw), ctypes.byref(ts.wt), ctypes.byref(self.b), ctypes.byref(la),
+                          ctypes.byref(ts.cg), bflags, _lib.ptr(self.ws), self.ws.numel(), _lib.stream_ptr(dev), None, 0)
             else:
                 # data parallel: the packed gradient groups are all-reduced as the backward finishes them (stage events recorded
                 # inside the C call; the collectives are issued behind them on a side stream) and averaged by the unpack's scale
                 _lib.call("skg_head_backward_staged", ctypes.byref(ts.pk.cw), ctypes.byref(ts.wt), ctypes.byref(self.b), ctypes.byref(la),
-                          ctypes.byref(ts.cg), self.flags, _lib.ptr(self.ws), self.ws.numel(), _lib.stream_ptr(dev), dd.event_array,
+                          ctypes.byref(ts.cg), bflags, _lib.ptr(self.ws), self.ws.numel(), _lib.stream_ptr(dev), dd.event_array,
                           len(dd.events))
                 dd.launch(ts)
         ts.grads_into_params()
@@ -446,7 +461,8 @@ def training_forward(ih, features, image_shapes, box_features: Tensor, box_coord
     ts = train_state(ih)
     with torch.no_grad():
         run = engine.head_forward(ih, features["3"], image_shapes, box_features.detach(), boxes_cat, meta, precise_logits=False,
-                                  graph=False, train=True, pk=ts.pk)
+                                  graph=ts.graph, train=True, pk=ts.pk)
+        dict.__setitem__(run, "_gt_out", ts.gt_buffer(int(run["seg"].total_pairs), G.num_cls))
     # (called from forward_from_pooled only in training mode: no train() / eval() round trip over the ~470 sub-modules)
     assert ih.training, "training_forward needs the head in training mode"
     with torch.enable_grad():               # the TransH loss is differentiable w.r.t. the tables (kge autograd Functions)

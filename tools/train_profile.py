@@ -15,8 +15,9 @@ ih.box_pair_head.transh_head.set_tables(*synthetic.make_transh_tables(42))
 ih = ih.to(dev).train(); ih.box_pair_head.transh_head.transh.to(dev)
 ih.box_pair_head.transh_head.negatives_on_device = True
 batch = synthetic.make_batch([(16, 32)] * 16, seed=1042, with_targets=True)
-d = dict(f={"3": batch["features"]["3"].to(dev)}, bf=batch["box_features"].to(dev), boxes=[b.to(dev) for b in batch["box_coords"]],
-         labels=[l.to(dev) for l in batch["box_labels"]], scores=[s.to(dev) for s in batch["box_scores"]],
+n_per = [int(b.shape[0]) for b in batch["box_coords"]]
+d = dict(f={"3": batch["features"]["3"].to(dev)}, bf=batch["box_features"].to(dev), boxes=list(torch.cat(batch["box_coords"]).to(dev).split(n_per)),
+         labels=list(torch.cat(batch["box_labels"]).to(dev).split(n_per)), scores=list(torch.cat(batch["box_scores"]).to(dev).split(n_per)),
          targets=[{k: v.to(dev) for k, v in t.items()} for t in batch["targets"]])
 meta = engine._host_meta(batch["box_labels"], batch["box_scores"], 49)
 params = [p for p in ih.parameters() if p.requires_grad]
@@ -54,6 +55,11 @@ for sync in (False, True):
     torch.cuda.synchronize()
     print("%s: %.2f ms/step | " % ("phases with a synchronise after each" if sync else "host enqueue per phase (no synchronise)",
                                      (time.perf_counter() - t0) / 10 * 1e3), {k: "%.2f ms" % (v / 10 * 1e3) for k, v in T.items()})
+import ctypes
+from skghoi_b200 import _lib
+a, b_, c = ctypes.c_longlong(), ctypes.c_longlong(), ctypes.c_longlong()
+_lib.lib().skg_head_backward_graph_stats(ctypes.byref(a), ctypes.byref(b_), ctypes.byref(c))
+print("backward graph cache (replays, captures, plain):", a.value, b_.value, c.value, "| forward:", _lib.graph_stats())
 print("---- device->host synchronisations of ONE step:")
 torch.cuda.set_sync_debug_mode("warn")
 with warnings.catch_warnings(record=True) as w:
