@@ -263,7 +263,7 @@ class TrainState:
                 continue                                 # the operand aliases the parameter (fp32 biases, LayerNorm affine)
             dst_t = self.T[tname][c0:c0 + cols, r0:r0 + rows] if tname else None
             if kind == "bsum":
-                if not any(d is dst_full for d in self._bsum):
+                if not any(d.data_ptr() == dst_full.data_ptr() for d in self._bsum):     # (_operand hands out a fresh view per call)
                     self._bsum.append(dst_full)
                 tab.add(src, dst, None, flags=_ACC)
             else:
