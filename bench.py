@@ -50,6 +50,7 @@ def parse_args():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-rooflines", action="store_true")
     ap.add_argument("--no-train", action="store_true", help="skip the supplementary training-step line (configs[2])")
+    ap.add_argument("--no-sweep", action="store_true", help="skip the C5 pair-count stress sweep (BASELINE configs[4])")
     ap.add_argument("--no-varying", action="store_true", help="skip the varying-geometry leg (fresh batch geometry every step)")
     ap.add_argument("--train-images", type=int, default=16, help="images per training step per GPU (configs[2]: 16)")
     ap.add_argument("--train-steps", type=int, default=10)
@@ -429,6 +430,9 @@ def run_b200(args):
     varying = None
     if not args.no_varying:
         varying = measure_varying_geometry(torch, dist, args, ih, dev, rank, world)
+    sweep = None
+    if not args.no_sweep:
+        sweep = measure_c5_sweep(torch, dist, args, ih, dev, rank, world, flush)
     train = None
     if not args.no_train:
         train = measure_training(torch, dist, args, dev, rank, world, flush)
@@ -468,6 +472,8 @@ def run_b200(args):
         line.update(extra_roofs)
         if varying is not None:
             line["varying_geometry"] = varying
+        if sweep is not None:
+            line["c5_sweep"] = sweep
         if train is not None:
             line["training"] = train
         if kg is not None:
@@ -565,6 +571,55 @@ def measure_varying_geometry(torch, dist, args, ih, dev, rank, world):
                    "counts and input addresses read from the segment table on the device); cycle_exact: one graph per exact "
                    "geometry on a 16-batch cycle (no padding, the headline's best case at this batch size)"}
     return out if rank == 0 else None
+
+
+def measure_c5_sweep(torch, dist, args, ih, dev, rank, world, flush):
+    """BASELINE configs[4]: pair-count stress sweep up to 64 x 64 detections per image (4096 cells), every rank its own
+    batch (weak scaling, no data-path collective), device-resident inputs, CUDA events per step, L2 flushed between steps,
+    max over ranks.  Also (16, 32) x 512 images: the same 262 144 cells as 64 x (64, 64) spread over 8 x more images
+    (VERDICT r1 'batch-512 regression': 4 x more boxes through box_head plus per-image host work)."""
+    from skghoi_b200 import engine, shard, synthetic
+    gd = torch.Generator(device=dev).manual_seed(4242 + rank)
+    g = torch.Generator().manual_seed(777 + rank)
+    rows = []
+    for nh, n, B in ((32, 64, 8), (32, 64, 64), (40, 80, 8), (40, 80, 64), (64, 64, 8), (64, 64, 64), (16, 32, 512)):
+        shapes = [(nh, n)] * B
+        img_shapes = [(800, 1216)] * B
+        boxes, labels, scores = synthetic.make_detections(shapes, img_shapes, g)
+        n_per = [n] * B
+        d = dict(f3={"3": torch.randn(B, 256, 25, 38, device=dev, generator=gd)},
+                 bf=torch.randn(B * n, 256, 7, 7, device=dev, generator=gd),
+                 boxes=list(torch.cat(boxes).to(dev).split(n_per)), labels=list(torch.cat(labels).to(dev).split(n_per)),
+                 scores=list(torch.cat(scores).to(dev).split(n_per)))
+        meta = engine._host_meta(labels, scores, 49)
+
+        def step():
+            with torch.no_grad():
+                return engine.interaction_head_from_pooled(ih, d["f3"], img_shapes, d["bf"], d["boxes"], d["labels"], d["scores"], meta=meta)
+        for _ in range(3):
+            step(); flush.zero_()
+        torch.cuda.synchronize(dev)
+        if world > 1:
+            dist.barrier()
+        K = 5
+        ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(K)]
+        t0 = time.perf_counter()
+        for s_, e in ev:
+            s_.record(); step(); e.record(); flush.zero_()
+        host_ms = (time.perf_counter() - t0) / K * 1e3
+        torch.cuda.synchronize(dev)
+        ms = sum(s_.elapsed_time(e) for s_, e in ev) / K
+        ms = shard.max_over_ranks([ms], device=dev)[0] if world > 1 else ms
+        cells, pairs = B * nh * n, B * nh * (n - 1)
+        flops = 2.0 * (cells * (128 * 256 + 256 * 1024 + 1024 * 4096 + 2 * 1024 * 1024) + pairs * (2 * 1024 * 1024 + 6144 * 128)
+                       + B * n * (12544 * 1024 + 1024 * 1024 + 2 * 1088 * 1024 + 4 * 1024 * 1024))
+        rows.append({"n_h": nh, "n": n, "images_per_gpu": B, "cells_per_gpu": cells, "pairs_per_gpu": pairs, "ms_per_step": ms,
+                     "value": pairs * world / (ms * 1e-3), "unit": UNIT, "gemm_tflops_issued_per_gpu": flops / (ms * 1e-3) / 1e12,
+                     "host_loop_ms_per_step": host_ms})
+        del d
+        torch.cuda.empty_cache()
+    return {"workload": "pair-count stress sweep (BASELINE configs[4]), per GPU: (n_h, n) x images per step; weak scaling over %d GPU(s)" % world,
+            "rows": rows} if rank == 0 else None
 
 
 def measure_kg(torch, dist, dev, rank, world):
@@ -691,7 +746,7 @@ def measure_training(torch, dist, args, dev, rank, world, flush):
             "steps": args.train_steps, "n_gpus": world, "pairs_per_step_per_gpu": pairs,
             "negatives": "TransH negatives drawn on the device (uniform without replacement per image, as head.py:939)",
             "step": "zero_grad + skg_head_forward(TRAIN) + post / losses + skg_head_backward (every dX / dW on the tcgen05 GEMM, trainops kernels) + %s + gradient unpack + fused SGD over flat parameter buffers"
-                    % ("NCCL all-reduce of the 3 packed gradient groups, each started behind its stage event inside the backward "
+                    % ("NCCL all-reduce of the 4 packed gradient groups, each started behind its stage event inside the backward "
                        "(the 81 MB node-side group overlaps the cell-side chain)" if world > 1 else "no all-reduce (1 GPU)"),
             "grad_bytes": sum(p.numel() * 4 for p in params),
             "final_losses": {k: float(v.detach().reshape(-1)[0]) for k, v in ls.items()}}
@@ -743,9 +798,10 @@ def measure_rooflines(torch, _lib, engine, ih, dev, flush, hbm_peak, tf_peak, pe
             "us_per_launch_l2_flushed_single": sec_flush * 1e6,
             "frac_l2_flushed_single": g["flops"] / sec_flush / 1e12 / tf_peak}
     extra = {}
-    # spatial encoding at >= 2^20 cells: enc + x_keep/y_keep only
+    # spatial encoding at 2^23 cells (SURVEY 8(d) asks >= 2^20): enc + x_keep/y_keep only; ONE launch writes 1.7 GB, 13 x the
+    # 126 MB L2, so write absorption by the L2 cannot flatter the number
     from skghoi_b200 import synthetic
-    B = 2048
+    B = 16384
     gen = torch.Generator().manual_seed(1)
     bx, _, _ = synthetic.make_detections([(16, 32)], [(800, 1216)], gen)
     boxes = bx[0].repeat(B, 1).to(dev)

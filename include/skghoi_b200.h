@@ -151,6 +151,12 @@ int skg_gemm_bf16(const void* A, int64_t lda, const void* B, int64_t ldb, int M,
 int skg_gemm_bf16_splitk(const void* A, int64_t lda, const void* B, int64_t ldb, int M, int N, int K,
                          const skg_epilogue_group* groups, int num_groups, int block_n, void* scratch,
                          int64_t scratch_bytes, cudaStream_t stream);
+/* The same with A read CYCLICALLY along K: A has a_k_wrap columns (a multiple of 64, <= K; 0 = plain) and k-block kb reads
+ * columns (64 kb) mod a_k_wrap -- the split-bf16 predictor [hi | lo | hi] x [W_hi | W_hi | W_lo]^T as ONE K = 6R launch over
+ * the [hi | lo] feature rows (head.py:410-411 in ~fp32 precision, 3 bf16 passes). */
+int skg_gemm_bf16_wrapk(const void* A, int64_t lda, int a_k_wrap, const void* B, int64_t ldb, int M, int N, int K,
+                        const skg_epilogue_group* groups, int num_groups, int block_n, void* scratch,
+                        int64_t scratch_bytes, cudaStream_t stream);
 int64_t skg_gemm_splitk_scratch_bytes(int max_tiles_m, int max_n);
 
 /* ---- glue kernels between the GEMMs (csrc/headops.cu) ---------------------------------------- */
@@ -383,6 +389,8 @@ typedef struct skg_head_weights {
   const void* Wpred; const float* bpred;      /* [n_logit_pad, 2R] predictor rows then the suppressor row (models.py:176-177) */
   const void* Wpred_hh; const void* Wpred_lo; /* split-bf16 predictor operands ([hi | hi] and lo), NULL -> single bf16 pass */
   const float* ent;                           /* TransH entity table [ent_tot, ent_dim] (head.py:574-578) */
+  const void* Wpred_hhl;                      /* [n_logit_pad, 6R] = [W_hi | W_hi | W_lo]: the split-bf16 predictor as one launch
+                                                 against the cyclically read [hi | lo] features; NULL -> the two-launch form */
   const float* Wfh_ent;                       /* fc_head.0.weight[:, E:] fp32 [R, ent_dim]: when set, every forward re-folds
                                                  bfc[:R] = bfh[:R] + Wfh_ent @ ent[human_idx] ON THE DEVICE (bfc is then
                                                  written by the library), so the constant human-side entity term follows the
@@ -542,12 +550,13 @@ int skg_head_backward(const skg_head_weights* weights, const skg_head_weights_t*
  *   0: Wpred bpred W3g b3g Wg1 bg1 ln_* W3os b3os W3so b3so w_adj b_adj W3att b3att
  *   1: W_hproj b_hproj W_oproj b_oproj Wfc bfc Wb2 bb2 Wb1 bb1   (the node-side chain incl. box_head: 69 % of the bytes; it
  *      runs BEFORE the cell-side chain so that its all-reduce is covered)
- *   2: W2cat b2cat Wsp2 bsp2 Wsp1 bsp1 Wsp0 bsp0                 (the end of the backward) */
+ *   2: W2cat b2cat                                               (fused fc_2 of the four MBFs, 16.8 MB)
+ *   3: Wsp2 bsp2 Wsp1 bsp1 Wsp0 bsp0                             (spatial head, 1.2 MB: the end of the backward) */
 /* flags | SKG_HEAD_GRAPH: the launch sequence is replayed as a CUDA graph when every byte that reaches a launch repeats
  * (weights, batch geometry, loss-argument / gradient addresses, workspace, stage events): first sighting plain launches,
  * second capture, then replays; skg_head_backward_graph_stats counts them for this thread */
 void skg_head_backward_graph_stats(long long* replays, long long* captures, long long* plain);
-#define SKG_HEAD_BACKWARD_STAGES 3
+#define SKG_HEAD_BACKWARD_STAGES 4
 int skg_head_backward_staged(const skg_head_weights* weights, const skg_head_weights_t* weights_t, const skg_head_batch* batch,
                              const skg_head_loss_args* loss, const skg_head_grads* grads, int flags, void* workspace,
                              int64_t workspace_bytes, cudaStream_t stream, void* const* stage_events, int num_stage_events);

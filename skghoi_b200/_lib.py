@@ -29,6 +29,7 @@ _SIGNATURES = {
     "skg_margin_loss": (I, [P, P, L, L, F, F, I, P, P, P, F, P]),
     "skg_focal_loss": (I, [P, P, L, F, F, F, P, P, P, P]),
     "skg_cast_pad_bf16": (I, [P, L, P, I, L, I, P, L, I, P]),
+    "skg_gemm_bf16_wrapk": (I, [P, L, I, P, L, I, I, I, P, I, I, P, L, P]),
     "skg_spatial_fc1": (I, [P, P, P, L, I, I, P, P]),
     "skg_node_inputs": (I, [P, I, P, I, I, I, P, P, I, I, I, P, P, I, P]),
     "skg_global_pool": (I, [P, L, I, P, P, P]),
@@ -217,7 +218,7 @@ class HeadWeights(ctypes.Structure):
         ("w_adj", c_void_p), ("b_adj", c_float),
         ("ln_h_w", c_void_p), ("ln_h_b", c_void_p), ("ln_o_w", c_void_p), ("ln_o_b", c_void_p), ("ln_eps", c_float),
         ("Wpred", c_void_p), ("bpred", c_void_p), ("Wpred_hh", c_void_p), ("Wpred_lo", c_void_p),
-        ("ent", c_void_p), ("Wfh_ent", c_void_p)]
+        ("ent", c_void_p), ("Wpred_hhl", c_void_p), ("Wfh_ent", c_void_p)]
 
 
 class HeadBatch(ctypes.Structure):

@@ -71,7 +71,8 @@ extern "C" int skg_head_backward(const skg_head_weights* wp, const skg_head_weig
 //   0: predictor | suppressor, attention_head_g.fc_3 / fc_1, LayerNorms, message fc_3, adjacency, attention_head.fc_3
 //   1: the node-side chain -- per-node projections (attention_head.fc_1, sub_to_obj.fc_1, obj_to_sub.fc_1), fc_head | fc_tail,
 //      box_head (69 % of the bytes: it is scheduled BEFORE the cell-side chain so that its all-reduce has cover)
-//   2: the cell-side chain -- fused fc_2 of the four MBFs, spatial head (the end of the backward)
+//   2: fused fc_2 of the four MBFs (16.8 MB), as soon as its weight gradient is done
+//   3: spatial head (1.2 MB: the only group whose all-reduce has no cover -- the end of the backward)
 static int backward_enqueue(const skg_head_weights* wp, const skg_head_weights_t* wtp, const skg_head_batch* bp,
                             const skg_head_loss_args* lp, const skg_head_grads* gp, int flags, void* workspace,
                             int64_t workspace_bytes, cudaStream_t st, void* const* stage_events, int num_stage_events, bool capturing);
@@ -225,12 +226,13 @@ static int backward_enqueue(const skg_head_weights* wp, const skg_head_weights_t
   // ---- fused fc_2 of the four MBFs, then the spatial head (head.py:662-669): the cell-side chain, independent of the
   //      node-side chain above once the Hadamard backward has split dS from dhproj / doproj
   SKG_TRY(wgrad(c, H(B_DS), 4 * R, 4 * R, H(B_SP), R, R, nullptr, C, d.W2cat, R, d.b2cat, false));
+  SKG_TRY(stage_done(2));
   SKG_TRY(dgrad(c, H(B_DS), 4 * R, C, 4 * R, wt.W2catT, 4 * R, R, H(B_SP), R, nullptr, 0, H(B_DSP), R, nullptr, 0, nullptr));
   SKG_TRY(wgrad(c, H(B_DSP), R, R, H(B_S2), 256, 256, nullptr, C, d.Wsp2, 256, d.bsp2, false));
   SKG_TRY(dgrad(c, H(B_DSP), R, C, R, wt.Wsp2T, R, 256, H(B_S2), 256, nullptr, 0, H(B_DS2), 256, nullptr, 0, nullptr));
   SKG_TRY(wgrad(c, H(B_DS2), 256, 256, H(B_S1), 128, 128, nullptr, C, d.Wsp1, 128, d.bsp1, false));
   SKG_TRY(dgrad(c, H(B_DS2), 256, C, 256, wt.Wsp1T, 256, 128, H(B_S1), 128, nullptr, 0, H(B_DS1), 128, nullptr, 0, nullptr));
   SKG_TRY(skg_spatial_fc1_backward(F(B_ENC), H(B_DS1), C, 46, 128, d.Wsp0, d.bsp0, st));
-  SKG_TRY(stage_done(2));
+  SKG_TRY(stage_done(3));
   return SKG_OK;
 }

@@ -396,7 +396,13 @@ static int enqueue_forward(const skg_head_weights* wp, const skg_head_batch* bp,
   const int64_t LR = train ? C : P;      // logit rows: pair-compacted, or cell rows in training
   if (LR > 0) {
     g = group0();
-    if (precise) {   // split bf16: logits = [hi | lo] x [W_hi | W_hi]^T + hi x W_lo^T   (3 bf16 passes ~ fp32 product)
+    if (precise && w.Wpred_hhl) {
+      // split bf16 as ONE launch: logits = [hi | lo | hi] x [W_hi | W_hi | W_lo]^T (3 bf16 passes ~ fp32 product), A = the
+      // [hi | lo] feature rows read cyclically along K = 6R; the skinny N = 128 problem fills the SMs through split-K
+      g.bias = w.bpred; g.out_f32 = F(B_LOGITS); g.ld_of = w.n_logit;
+      SKG_TRY(skg_gemm_bf16_wrapk(H(B_FEAT), feat_ld, 4 * R, w.Wpred_hhl, 6 * R, (int)LR, w.n_logit, 6 * R, &g, 1, 0, H(B_SPLITK0), sk_bytes, st));
+      MARK("gemm predictor [hi|lo|hi]x[Whi|Whi|Wlo]", st);
+    } else if (precise) {   // two launches: logits = [hi | lo] x [W_hi | W_hi]^T + hi x W_lo^T
       g.bias = w.bpred; g.out_f32 = F(B_TMP); g.ld_of = w.n_logit_pad;
       SKG_TRY(skg_gemm_bf16(H(B_FEAT), feat_ld, w.Wpred_hh, 4 * R, (int)LR, w.n_logit, 4 * R, &g, 1, 0, st));
       MARK("gemm predictor [hi|lo]x[Whi|Whi]", st);

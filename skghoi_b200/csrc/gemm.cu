@@ -160,7 +160,7 @@ struct GemmSmem {
 template <int BN, uint32_t FEAT, bool SK>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, int M, int N, int K,
-                 const __grid_constant__ EpiGroups epi, int splits, float* __restrict__ sk_ws, int* __restrict__ sk_cnt) {
+                 const __grid_constant__ EpiGroups epi, int splits, float* __restrict__ sk_ws, int* __restrict__ sk_cnt, int a_k_wrap) {
   using S = GemmSmem<BN, (FEAT & (F_P | F_Q)) != 0 && FEAT != F_ALL>;
   constexpr int kStages = S::kStages;
   extern __shared__ uint8_t smem_raw[];
@@ -217,7 +217,9 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           uint8_t* sa = smem + stage * S::kStageBytes;
           uint8_t* sb = sa + S::kABytes;
           mbar_arrive_expect_tx(full_bar + stage, S::kStageBytes);
-          tma_load_2d(&tmA, full_bar + stage, sa, kb * BK, m0);
+          // a_k_wrap: A holds only a_k_wrap columns and is read cyclically along K (split-bf16 predictor: [hi | lo | hi])
+          const int ka = (a_k_wrap > 0) ? (kb * BK) % a_k_wrap : kb * BK;
+          tma_load_2d(&tmA, full_bar + stage, sa, ka, m0);
           tma_load_2d(&tmB, full_bar + stage, sb, kb * BK, n0);
           if (++stage == kStages) { stage = 0; phase ^= 1; }
         }
@@ -574,11 +576,13 @@ struct SplitK {
   int splits;
   float* ws;
   int* cnt;
+  int a_k_wrap = 0;
 };
 
 template <int BN, uint32_t FEAT, bool SK>
 static int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, int M, int N, int K, const EpiGroups& epi,
                        const SplitK& sk, cudaStream_t stream) {
+  const int a_k_wrap = sk.a_k_wrap;
   using S = GemmSmem<BN, (FEAT & (F_P | F_Q)) != 0 && FEAT != F_ALL>;
   auto kern = gemm_bf16_kernel<BN, FEAT, SK>;
   static bool attr_set = false;
@@ -596,9 +600,9 @@ static int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, int M, in
     at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     at[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = at; cfg.numAttrs = 1;
-    SKG_CUDA(cudaLaunchKernelEx(&cfg, kern, tmA, tmB, M, N, K, epi, sk.splits, sk.ws, sk.cnt));
+    SKG_CUDA(cudaLaunchKernelEx(&cfg, kern, tmA, tmB, M, N, K, epi, sk.splits, sk.ws, sk.cnt, a_k_wrap));
   } else {
-    kern<<<grid, kGemmThreads, S::kTotal, stream>>>(tmA, tmB, M, N, K, epi, sk.splits, sk.ws, sk.cnt);
+    kern<<<grid, kGemmThreads, S::kTotal, stream>>>(tmA, tmB, M, N, K, epi, sk.splits, sk.ws, sk.cnt, a_k_wrap);
   }
   return check_launch("gemm_bf16_kernel");
 }
@@ -640,11 +644,19 @@ extern "C" int skg_gemm_bf16(const void* A, int64_t lda, const void* B, int64_t 
 extern "C" int skg_gemm_bf16_splitk(const void* A, int64_t lda, const void* B, int64_t ldb, int M, int N, int K,
                                     const skg_epilogue_group* groups, int num_groups, int block_n, void* scratch,
                                     int64_t scratch_bytes, cudaStream_t stream) {
+  return skg_gemm_bf16_wrapk(A, lda, 0, B, ldb, M, N, K, groups, num_groups, block_n, scratch, scratch_bytes, stream);
+}
+
+extern "C" int skg_gemm_bf16_wrapk(const void* A, int64_t lda, int a_k_wrap, const void* B, int64_t ldb, int M, int N, int K,
+                                   const skg_epilogue_group* groups, int num_groups, int block_n, void* scratch,
+                                   int64_t scratch_bytes, cudaStream_t stream) {
   SKG_REQUIRE(M >= 0 && N > 0 && K > 0, "bad GEMM shape M=%d N=%d K=%d", M, N, K);
+  SKG_REQUIRE(a_k_wrap == 0 || (a_k_wrap % BK == 0 && a_k_wrap > 0 && a_k_wrap <= K), "a_k_wrap must be a multiple of %d within K", BK);
+  const int KA = a_k_wrap > 0 ? a_k_wrap : K;      // columns A really has
   if (M == 0) return SKG_OK;
   SKG_REQUIRE(A && B && groups, "null pointer argument");
   SKG_REQUIRE(num_groups >= 1 && num_groups <= kMaxGroups, "num_groups must be in [1, %d]", kMaxGroups);
-  SKG_REQUIRE((lda % 8) == 0 && (ldb % 8) == 0 && lda >= K && ldb >= K, "lda/ldb must be >= K and multiples of 8 elements");
+  SKG_REQUIRE((lda % 8) == 0 && (ldb % 8) == 0 && lda >= KA && ldb >= K, "lda/ldb must be >= K and multiples of 8 elements");
   SKG_REQUIRE(((reinterpret_cast<uintptr_t>(A) | reinterpret_cast<uintptr_t>(B)) & 15u) == 0, "A and B must be 16-byte aligned");
   if (block_n == 0) {
     // widest tile that still spreads the problem over the SMs: node-row GEMMs (M = humans / boxes of the batch,
@@ -679,11 +691,12 @@ extern "C" int skg_gemm_bf16_splitk(const void* A, int64_t lda, const void* B, i
   }
   // bias / tables are read in 32-column chunks up to the padded width: callers pad them to block_n multiples
   CUtensorMap tmA, tmB;
-  int rc = make_tmap(&tmA, A, M, K, lda, BM);
+  int rc = make_tmap(&tmA, A, M, KA, lda, BM);
   if (rc) return rc;
   rc = make_tmap(&tmB, B, N, K, ldb, block_n);
   if (rc) return rc;
   SplitK sk{1, nullptr, nullptr};
+  sk.a_k_wrap = a_k_wrap;
   if (scratch) {
     SKG_REQUIRE((reinterpret_cast<uintptr_t>(scratch) & 15u) == 0, "split-K scratch must be 16-byte aligned");
     sk.splits = block_n == 64 ? 1 : choose_splits(M, N, K, block_n, scratch_bytes);

@@ -4,9 +4,11 @@
 // numbered consecutively (cell r of image b = cell_off[b] + i*n + j, row-major like
 // torch.meshgrid(indexing='ij')), one thread per cell.  The kernel is HBM-write bound
 // (46 fp32 = 184 B per cell): each CTA stages a 128-cell tile in shared memory laid out exactly
-// like the output rows and drains it with ONE bulk asynchronous copy (cp.async.bulk, the 1-D TMA
-// path, SASS UBLKCP) so the global writes are perfectly coalesced 128-byte lines regardless of
-// the 184-byte row pitch; the next tile is computed into the other buffer meanwhile.
+// like the output rows and drains it with coalesced 16-byte streaming stores issued by all 128
+// threads (st.global.cs.v4: consecutive lanes on consecutive addresses, full 128-byte lines
+// regardless of the 184-byte row pitch).  kDrainBulk = true selects the earlier drain, one
+// cp.async.bulk per tile (1-D TMA, SASS UBLKCP): it left the CTA waiting on the bulk engine's
+// shared-memory read (0.64 vs 0.76 of copy peak) and is kept for comparison only.
 //
 // Valid-pair compaction (torch.nonzero(x != y), head.py:852): in row i exactly the cell j == i is
 // dropped (i < n_h <= n), so the row-major rank of a kept cell is p = i*(n-1) + j - (j > i):
@@ -146,9 +148,9 @@ template <int F>
 __global__ void __launch_bounds__(kTileCells, 8) pairs_spatial_kernel(const float4* __restrict__ boxes, SegTable seg,
                                                                       int64_t total_cells, float eps, PairOutputs o,
                                                                       const unsigned long long* __restrict__ boxes_slot) {
-  // One 128-cell tile per CTA iteration, staged in shared memory in the exact output layout (23.5 KB) and drained by one
-  // bulk asynchronous copy; 8 CTAs per SM (188 KB of shared memory, <= 64 registers) keep 32 warps of MUFU / store
-  // work in flight, so the drain of one CTA's tile overlaps the arithmetic of the seven others.
+  // One 128-cell tile per CTA iteration, staged in shared memory in the exact output layout (23.5 KB) and drained by all
+  // threads as coalesced 16-byte streaming stores; 8 CTAs per SM (188 KB of shared memory, <= 64 registers) keep 32 warps
+  // of MUFU / store work in flight, so the drain of one CTA's tile overlaps the arithmetic of the seven others.
   constexpr int W = 2 * F;
   __shared__ __align__(128) float tile[kTileCells * W];
   const int tid = threadIdx.x;

@@ -317,6 +317,7 @@ class PackedHead:
         hi = Wp.to(torch.bfloat16); lo = (Wp - hi.float()).to(torch.bfloat16)
         self.Wpred_hh = _bf16(torch.cat([hi.float(), hi.float()], 1), pad_rows=128)     # [128, 2*2R] against [hi | lo]
         self.Wpred_lo = _bf16(lo.float(), pad_rows=128)                                 # [128, 2R]   against hi
+        self.Wpred_hhl = _bf16(torch.cat([hi.float(), hi.float(), lo.float()], 1), pad_rows=128)   # one K = 6R launch, A read cyclically
         self.cw = self._c_struct(G)
 
     def _c_struct(self, G):
@@ -330,7 +331,7 @@ class PackedHead:
         for name in ("Wb1", "bb1", "Wb2", "bb2", "Wsp0", "bsp0", "Wsp1", "bsp1", "Wsp2", "bsp2", "Wfh", "bfh", "Wft", "bft",
                      "Wfc", "bfc", "Wfh_ent",
                      "W_hproj", "b_hproj", "W_oproj", "b_oproj", "Wg1", "bg1", "W2cat", "b2cat", "W3att", "b3att",
-                     "W3os", "b3os", "W3so", "b3so", "W3g", "b3g", "w_adj", "Wpred", "bpred", "Wpred_hh", "Wpred_lo"):
+                     "W3os", "b3os", "W3so", "b3so", "W3g", "b3g", "w_adj", "Wpred", "bpred", "Wpred_hh", "Wpred_lo", "Wpred_hhl"):
             setattr(w, name, getattr(self, name).data_ptr())
         w.b_adj = self.b_adj
         w.ln_h_w, w.ln_h_b, w.ln_o_w, w.ln_o_b = (t.data_ptr() for t in self.ln)

@@ -53,7 +53,8 @@ _GRAD_FIELDS = ("Wb1", "bb1", "Wb2", "bb2", "Wsp0", "bsp0", "Wsp1", "bsp1", "Wsp
 _GRAD_STAGES = (("Wpred", "bpred", "W3g", "b3g", "Wg1", "bg1", "ln_h_w", "ln_h_b", "ln_o_w", "ln_o_b", "W3os", "b3os", "W3so", "b3so",
                  "w_adj", "b_adj", "W3att", "b3att"),
                 ("W_hproj", "b_hproj", "W_oproj", "b_oproj", "Wfc", "bfc", "Wb2", "bb2", "Wb1", "bb1"),
-                ("W2cat", "b2cat", "Wsp2", "bsp2", "Wsp1", "bsp1", "Wsp0", "bsp0"))
+                ("W2cat", "b2cat"),
+                ("Wsp2", "bsp2", "Wsp1", "bsp1", "Wsp0", "bsp0"))
 assert sorted(k for g in _GRAD_STAGES for k in g) == sorted(_GRAD_FIELDS)
 
 
