@@ -409,6 +409,10 @@ typedef struct skg_head_batch {
   const void* box_features_bf16;  /* optional [boxes, K0] bf16 rows (K0 = pool_k rounded up to 8, zero padded): the pooled
                                      features already in the first GEMM's operand layout, e.g. written by
                                      skg_multiscale_roi_align; when set, box_features is ignored and may be NULL */
+  void* maps_ready_event;         /* optional cudaEvent_t recorded right after the pair enumeration (the FIRST kernel of the
+                                     step): x / y / x_keep / y_keep / cell and pair maps are then final, so work that needs only
+                                     the batch geometry (GT association, loss normalisers, TransH selection: head.py:926-963)
+                                     can run on another stream under the GEMM chain; NULL = none */
 } skg_head_batch;
 
 #define SKG_HEAD_NUM_BUFFERS 96
@@ -453,6 +457,23 @@ int skg_head_profile_get(int i, const char** name, int* stream_id, float* us);
 void skg_head_graph_stats(long long* replays, long long* captures, long long* plain);
 int skg_head_forward(const skg_head_weights* weights, const skg_head_batch* batch, int flags, void* workspace,
                      int64_t workspace_bytes, cudaStream_t stream);
+
+/* n_p of the two focal losses from the GT labels alone (head.py:167-205: number of positive entry labels, number of pairs
+ * with any positive label) -- what `(labels != 0).sum()` / `(unary_labels != 0).sum()` give after skg_head_post, computable
+ * before the GEMM chain has produced a single logit.  gt_labels [pairs, num_cls], out [2] fp32 (zeroed here). */
+int skg_loss_normalisers(const float* gt_labels, const skg_post_tables* tables, int64_t pairs, int num_cls, float* out,
+                         cudaStream_t stream);
+
+/* TransH positive / negative selection of the training loss on the device (head.py:926-963): per image b -- the label rows
+ * [pair_off[b], pair_off[b+1]) of gt_labels [P, num_cls] -- skg_select_count writes the number of positive labels to
+ * n_pos[b] and their total to n_pos[num_images]; after the caller has sized the outputs from that total, skg_select_fill
+ * writes the positives' flat indices (p * num_cls + verb, flat order, image by image) and, aligned with them, as many
+ * zero-label flat indices of the SAME image drawn uniformly without replacement (the distribution of
+ * randperm(#zeros)[:#pos], head.py:939; counter-hash generator seeded by `seed`). */
+int skg_select_count(const float* gt_labels, const int64_t* pair_off, int num_images, int num_cls, int32_t* n_pos,
+                     cudaStream_t stream);
+int skg_select_fill(const float* gt_labels, const int64_t* pair_off, int num_images, int num_cls, const int32_t* n_pos,
+                    unsigned long long seed, int64_t* pos_flat, int64_t* neg_flat, cudaStream_t stream);
 
 /* ---- per-head serving session (csrc/session.cu) ----------------------------------------------------------------------------
  * The opaque handle of SURVEY 8(b): it owns a copy of the packed-weight descriptor (the bf16 operands stay owned by the

@@ -226,7 +226,7 @@ class HeadBatch(ctypes.Structure):
     _fields_ = [(k, ctypes.c_int32) for k in ("num_images", "total_boxes", "total_humans", "max_boxes_per_image", "feat_hw")] + \
                [("total_cells", c_int64), ("total_pairs", c_int64), ("seg_bytes", c_int64)] + \
                [(k, c_void_p) for k in ("features3", "box_features", "boxes", "box_off", "n_h", "hum_off", "cell_off",
-                                        "pair_off", "hw", "box_features_bf16")]
+                                        "pair_off", "hw", "box_features_bf16", "maps_ready_event")]
 
 
 HEAD_NUM_BUFFERS = 96
@@ -290,6 +290,9 @@ _SIGNATURES["skg_head_backward"] = (I, [P, P, P, P, P, I, P, L, P])
 _SIGNATURES["skg_head_backward_graph_stats"] = (None, [ctypes.POINTER(ctypes.c_longlong)] * 3)
 _SIGNATURES["skg_head_backward_staged"] = (I, [P, P, P, P, P, I, P, L, P, P, I])
 _SIGNATURES["skg_transpose_bf16"] = (I, [P, L, L, I, P, P, L, P, P])
+_SIGNATURES["skg_select_count"] = (I, [P, P, I, I, P, P])
+_SIGNATURES["skg_select_fill"] = (I, [P, P, I, I, P, ctypes.c_ulonglong, P, P, P])
+_SIGNATURES["skg_loss_normalisers"] = (I, [P, P, L, I, P, P])
 _SIGNATURES["skg_hum2box"] = (I, [P, I, P, P])
 _SIGNATURES["skg_head_loss_backward"] = (I, [P, I, I, P, P, L, F, P, P, P, P, P, I, P])
 _SIGNATURES["skg_hadamard_backward"] = (I, [P, I, I, P])

@@ -317,6 +317,14 @@ static int enqueue_forward(const skg_head_weights* wp, const skg_head_batch* bp,
                                     b.hw, B, C, 23, 1e-10f, 1, F(B_ENC), I64(B_X), I64(B_Y), I64(B_XKEEP), I64(B_YKEEP), I32(B_CELL2PAIR),
                                     I32(B_CELL_HROW), I32(B_CELL_OROW), I32(B_CELL_IMG), I32(B_PAIR2CELL), I32(B_NANFLAG), st));
   MARK("pairs_spatial_encode", st);
+  if (b.maps_ready_event) {   // geometry-only work of the caller (labels, normalisers, TransH selection) may start on another stream
+    cudaStreamCaptureStatus cst = cudaStreamCaptureStatusNone;
+    SKG_CUDA(cudaStreamIsCapturing(st, &cst));
+    if (cst != cudaStreamCaptureStatusNone)
+      SKG_CUDA(cudaEventRecordWithFlags(reinterpret_cast<cudaEvent_t>(b.maps_ready_event), st, cudaEventRecordExternal));
+    else
+      SKG_CUDA(cudaEventRecord(reinterpret_cast<cudaEvent_t>(b.maps_ready_event), st));
+  }
   SKG_TRY(skg_spatial_fc1(F(B_ENC), w.Wsp0, w.bsp0, C, 46, 128, H(B_S1), st));
   MARK("spatial_fc1", st);
   g = group0(); g.flags = SKG_EPI_RELU; g.bias = w.bsp1; g.out_bf16 = H(B_S2); g.ld_ob = 256;

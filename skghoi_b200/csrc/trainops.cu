@@ -470,6 +470,102 @@ __global__ void __launch_bounds__(OUT) spatial_fc1_backward_kernel(const float* 
 }
 
 // hum2box[box2hum[k]] = k for the human boxes (inverse of the map node_prep_kernel builds)
+// n_p of the focal losses straight from the GT labels: one warp per valid pair
+__global__ void loss_normalisers_kernel(const float* __restrict__ gt, LossTables t, int64_t pairs, int num_cls, float* __restrict__ out) {
+  const int lane = threadIdx.x & 31;
+  const int64_t p = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
+  if (p >= pairs) return;
+  const int cell = __ldg(t.pair2cell + p);
+  const int hr = __ldg(t.cell_hrow + cell), orow = __ldg(t.cell_orow + cell), b = __ldg(t.cell_img + cell);
+  const int boff = __ldg(t.box_off + b);
+  const int i = hr - __ldg(t.hum_off + b);
+  float s = 0.f;
+  for (int v = lane; v < num_cls; v += 32) s += gt[p * num_cls + v];
+  s = warp_sum(s);
+  float e = 0.f;
+  if (__ldg(t.scores + boff + i) > 0.f) {           // the pair's entries exist only for a positive human score (head.py:315)
+    const int64_t lab_o = __ldg(t.labels + orow);
+    const int v0 = __ldg(t.verb_off + lab_o), v1 = __ldg(t.verb_off + lab_o + 1);
+    for (int k = v0 + lane; k < v1; k += 32) e += (gt[p * num_cls + __ldg(t.verb_idx + k)] != 0.f) ? 1.f : 0.f;
+  }
+  e = warp_sum(e);
+  if (lane == 0) {
+    if (e != 0.f) atomicAdd(out, e);
+    if (s != 0.f) atomicAdd(out + 1, 1.f);
+  }
+}
+
+// ---- TransH positive / negative selection (head.py:926-963, device form): per image, the positives of the GT label block
+// in flat order and as many zero-label entries drawn uniformly without replacement (rejection sampling from a counter-hash
+// generator -- uniform over the image's zero labels, the distribution of randperm(#zeros)[:#pos], head.py:939).
+__global__ void __launch_bounds__(256) select_count_kernel(const float* __restrict__ gt, const int64_t* __restrict__ pair_off,
+                                                           int num_cls, int32_t* __restrict__ n_pos, int32_t* __restrict__ total) {
+  __shared__ int red[8];
+  const int b = blockIdx.x;
+  const int64_t lo = __ldg(pair_off + b) * num_cls, hi = __ldg(pair_off + b + 1) * num_cls;
+  int c = 0;
+  for (int64_t e = lo + threadIdx.x; e < hi; e += 256) c += (__ldg(gt + e) != 0.f) ? 1 : 0;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = c;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    int s = 0;
+    for (int k = 0; k < 8; ++k) s += red[k];
+    n_pos[b] = s;
+    atomicAdd(total, s);
+  }
+}
+
+__device__ __forceinline__ uint64_t splitmix64(uint64_t& x) {
+  uint64_t z = (x += 0x9E3779B97F4A7C15ull);
+  z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+  z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+  return z ^ (z >> 31);
+}
+
+constexpr int kSelMaxChosen = 2048;
+__global__ void __launch_bounds__(256) select_fill_kernel(const float* __restrict__ gt, const int64_t* __restrict__ pair_off, int num_images,
+                                                          int num_cls, const int32_t* __restrict__ n_pos, unsigned long long seed,
+                                                          int64_t* __restrict__ pos_flat, int64_t* __restrict__ neg_flat) {
+  __shared__ int cnt[256];
+  __shared__ int64_t chosen[kSelMaxChosen];
+  const int b = blockIdx.x, tid = threadIdx.x;
+  const int k = __ldg(n_pos + b);
+  if (k == 0) return;
+  int64_t out0 = 0;
+  for (int i = 0; i < b; ++i) out0 += __ldg(n_pos + i);
+  const int64_t lo = __ldg(pair_off + b) * num_cls, hi = __ldg(pair_off + b + 1) * num_cls, len = hi - lo;
+  // positives in flat order: contiguous chunk per thread, block-wide exclusive scan of the chunk counts
+  const int64_t c0 = lo + len * tid / 256, c1 = lo + len * (tid + 1) / 256;
+  int c = 0;
+  for (int64_t e = c0; e < c1; ++e) c += (__ldg(gt + e) != 0.f) ? 1 : 0;
+  cnt[tid] = c;
+  __syncthreads();
+  if (tid == 0) { int run = 0; for (int i = 0; i < 256; ++i) { const int v = cnt[i]; cnt[i] = run; run += v; } }
+  __syncthreads();
+  int64_t w = out0 + cnt[tid];
+  for (int64_t e = c0; e < c1; ++e) if (__ldg(gt + e) != 0.f) pos_flat[w++] = e;
+  // negatives: one thread, k draws, rejecting positives and repeats
+  if (tid == 0) {
+    uint64_t st = seed ^ (0xD1B54A32D192ED03ull * (uint64_t)(b + 1));
+    for (int j = 0; j < k; ++j) {
+      int64_t pick = lo;
+      for (int tries = 0; tries < 4096; ++tries) {
+        const int64_t cand = lo + (int64_t)(splitmix64(st) % (uint64_t)len);
+        pick = cand;
+        if (__ldg(gt + cand) != 0.f) continue;
+        bool dup = false;
+        const int seen = j < kSelMaxChosen ? j : kSelMaxChosen;
+        for (int q = 0; q < seen; ++q) if (chosen[q] == cand) { dup = true; break; }
+        if (!dup) break;
+      }
+      if (j < kSelMaxChosen) chosen[j] = pick;
+      neg_flat[out0 + j] = pick;
+    }
+  }
+}
+
 __global__ void hum2box_kernel(const int32_t* __restrict__ box2hum, int total_boxes, int32_t* __restrict__ hum2box) {
   const int k = blockIdx.x * blockDim.x + threadIdx.x;
   if (k >= total_boxes) return;
@@ -546,6 +642,38 @@ extern "C" int skg_head_loss_backward(const float* logits, int ld_logits, int nu
                                                                                   prior_power, gt_labels, n_p, g_hoi, g_int, 0.5f, 0.2f,
                                                                                   2.0f, 1e-6f, (__nv_bfloat16*)dlogits_bf16, ld_d);
   return check_launch("head_loss_backward_kernel");
+}
+
+extern "C" int skg_loss_normalisers(const float* gt_labels, const skg_post_tables* tables, int64_t pairs, int num_cls, float* out,
+                                    cudaStream_t stream) {
+  SKG_REQUIRE(out, "null output pointer");
+  SKG_CUDA(cudaMemsetAsync(out, 0, 2 * sizeof(float), stream));
+  if (pairs == 0) return SKG_OK;
+  SKG_REQUIRE(gt_labels && tables && num_cls > 0, "bad loss_normalisers arguments");
+  LossTables t{tables->verb_off, tables->verb_idx, tables->pair2cell, tables->cell_hrow, tables->cell_orow, tables->cell_img,
+               tables->hum_off, tables->box_off, tables->labels, tables->scores};
+  SKG_REQUIRE(t.verb_off && t.verb_idx && t.pair2cell && t.cell_hrow && t.cell_orow && t.cell_img && t.hum_off && t.box_off && t.labels && t.scores,
+              "incomplete post tables");
+  loss_normalisers_kernel<<<(int)ceil_div64(pairs * 32, 256), 256, 0, stream>>>(gt_labels, t, pairs, num_cls, out);
+  return check_launch("loss_normalisers_kernel");
+}
+
+extern "C" int skg_select_count(const float* gt_labels, const int64_t* pair_off, int num_images, int num_cls, int32_t* n_pos,
+                                cudaStream_t stream) {
+  SKG_REQUIRE(n_pos && num_images >= 0, "bad select_count arguments");
+  SKG_CUDA(cudaMemsetAsync(n_pos, 0, sizeof(int32_t) * (num_images + 1), stream));
+  if (num_images == 0) return SKG_OK;
+  SKG_REQUIRE(gt_labels && pair_off && num_cls > 0, "null pointer argument");
+  select_count_kernel<<<num_images, 256, 0, stream>>>(gt_labels, pair_off, num_cls, n_pos, n_pos + num_images);
+  return check_launch("select_count_kernel");
+}
+
+extern "C" int skg_select_fill(const float* gt_labels, const int64_t* pair_off, int num_images, int num_cls, const int32_t* n_pos,
+                               unsigned long long seed, int64_t* pos_flat, int64_t* neg_flat, cudaStream_t stream) {
+  if (num_images == 0) return SKG_OK;
+  SKG_REQUIRE(gt_labels && pair_off && n_pos && pos_flat && neg_flat && num_cls > 0, "null pointer argument");
+  select_fill_kernel<<<num_images, 256, 0, stream>>>(gt_labels, pair_off, num_images, num_cls, n_pos, seed, pos_flat, neg_flat);
+  return check_launch("select_fill_kernel");
 }
 
 extern "C" int skg_hadamard_backward(const skg_hadamard_bwd* a, int total_humans, int phase, cudaStream_t stream) {

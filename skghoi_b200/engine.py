@@ -636,7 +636,7 @@ def _session_forward(ih, pk, features3: Tensor, image_shapes, box_features: Tens
 
 def head_forward(ih, features3: Tensor, image_shapes, box_features: Tensor, boxes_cat: Tensor, meta: dict,
                  want_taps: bool = False, precise_logits: bool = True, profile: bool = False, graph: bool = True,
-                 train: bool = False, pk=None) -> dict:
+                 train: bool = False, pk=None, maps_event: int = 0) -> dict:
     """Runs the whole pair path for a batch through ONE C-ABI call (skg_head_forward, csrc/forward.cu).
     Inputs: features['3'] [B,256,h,w] fp32, pooled box features [sum n, 256, 7, 7] fp32, concatenated boxes
     [sum n, 4] fp32 (all CUDA), host ``meta``.  Returns named views into the step's workspace: logits [P,118]
@@ -720,6 +720,7 @@ def head_forward(ih, features3: Tensor, image_shapes, box_features: Tensor, boxe
     _lib.require_cuda(f3, bf, boxes_cat)
     w = pk.cw
     w.ent = ent.data_ptr()
+    b.maps_ready_event = maps_event or None          # cudaEvent_t recorded after the pair enumeration (train._prepass)
     if not cap_mode:
         b.features3, b.boxes = f3.data_ptr(), boxes_cat.data_ptr()
     if bf.dtype == torch.bfloat16:                   # operand rows written by the native RoIAlign (roi.py)
@@ -1005,6 +1006,25 @@ def select_negatives_device(labels: Tensor, pair_img: Tensor, num_images: int):
     return pos_flat, neg_flat
 
 
+def select_negatives_cuda(labels: Tensor, pair_off_dev: Tensor, num_images: int):
+    """CUDA form of ``select_negatives_device`` (skg_select_count / skg_select_fill, csrc/trainops.cu): two launches and ONE
+    small device->host read (the total, which sizes the outputs) instead of ~25 ATen ops with a 10^6-key sort.  The seed of
+    the counter-hash generator is drawn from torch's CPU generator (``torch.manual_seed`` reproduces the draw)."""
+    Pn, nc = labels.shape
+    dev = labels.device
+    n_pos = torch.empty(num_images + 1, dtype=torch.int32, device=dev)
+    with _lib.on_device(dev):
+        _lib.call("skg_select_count", _lib.ptr(labels), _lib.ptr(pair_off_dev), num_images, nc, _lib.ptr(n_pos), _lib.stream_ptr(dev))
+        k = int(n_pos[num_images:].cpu())                                        # the step's one host synchronisation
+        pos = torch.empty(k, dtype=torch.int64, device=dev)
+        neg = torch.empty(k, dtype=torch.int64, device=dev)
+        if k:
+            seed = int(torch.randint(0, 2 ** 62, (1,)))
+            _lib.call("skg_select_fill", _lib.ptr(labels), _lib.ptr(pair_off_dev), num_images, nc, _lib.ptr(n_pos), seed,
+                      _lib.ptr(pos), _lib.ptr(neg), _lib.stream_ptr(dev))
+    return pos, neg
+
+
 def _transh_pos_neg_device(G, run, labels: Tensor):
     """Batched form of the selection above for ``transH_head.negatives_on_device``: per image, as many negatives as
     positives, drawn uniformly without replacement among that image's zero labels -- the same distribution as
@@ -1017,8 +1037,11 @@ def _transh_pos_neg_device(G, run, labels: Tensor):
     Pn = seg.total_pairs
     if Pn == 0:
         return [], [], [], [], [], []
-    pair_img = run["cell_img"].long()[run["pair2cell"].long()]                       # image of every valid pair
-    pos_flat, neg_flat = select_negatives_device(labels, pair_img, seg.B)
+    if labels.is_cuda and labels.is_contiguous():
+        pos_flat, neg_flat = select_negatives_cuda(labels, seg.d_pair_off, seg.B)
+    else:
+        pair_img = run["cell_img"].long()[run["pair2cell"].long()]                   # image of every valid pair
+        pos_flat, neg_flat = select_negatives_device(labels, pair_img, seg.B)
     sel = torch.cat([pos_flat, neg_flat])
     pair_idx = torch.div(sel, nc, rounding_mode="floor"); verb = sel - pair_idx * nc
     tails = run["y_keep"][pair_idx]
@@ -1079,11 +1102,33 @@ def _shell_for(G):
     return sh
 
 
+def _run_post_tables(G, run, labels_dev: Tensor, scores_dev: Tensor):
+    """skg_post_tables over the maps of ``run`` (cached on the run object while the label / score buffers stay put)."""
+    seg: Segments = run["seg"]
+    vt = _verb_table(G, seg.device)
+    tkey = (labels_dev.data_ptr(), scores_dev.data_ptr(), run["pair2cell"].data_ptr(), seg.d_hum_off.data_ptr())
+    tc = run.get("_post_tables")
+    if tc is not None and tc[0] == tkey:
+        return tc[1]                                 # same run views, same label / score buffers: the descriptor stands
+    tables = _lib.PostTables()
+    tables.verb_off, tables.verb_idx = vt.d_off.data_ptr(), vt.d_idx.data_ptr()
+    tables.pair2cell, tables.cell_hrow = run["pair2cell"].data_ptr(), run["cell_hrow"].data_ptr()
+    tables.cell_orow, tables.cell_img = run["cell_orow"].data_ptr(), run["cell_img"].data_ptr()
+    tables.hum_off, tables.box_off, tables.pair_off = seg.d_hum_off.data_ptr(), seg.d_box_off.data_ptr(), seg.d_pair_off.data_ptr()
+    tables.labels, tables.scores = labels_dev.data_ptr(), scores_dev.data_ptr()
+    if run.get("_train"):
+        tables.logit_row = run["pair2cell"].data_ptr()             # training layout: logits live in cell rows
+    dict.__setitem__(run, "_post_tables", (tkey, tables))
+    return tables
+
+
 def interaction_head_from_pooled(ih, features, image_shapes, box_features, box_coords, box_labels, box_scores,
-                                 targets=None, meta=None, run=None) -> List[dict]:
+                                 targets=None, meta=None, run=None, pre=None) -> List[dict]:
     """InteractionHead.forward from the pooled box features on (head.py:389-427).  ``run`` (training pass): pair maps,
     segment table and logits computed by the caller -- the native GEMM chain is then skipped and only the
-    post-processing / GT association / loss kernels run."""
+    post-processing / GT association / loss kernels run.  ``pre`` (training pass): what depends on the batch geometry and
+    the targets only -- GT labels, loss normalisers, the TransH loss -- already computed on a side stream under the GEMM
+    chain (train._prepass)."""
     from . import ops
     from .kge import MarginLoss, NegativeSampling
     G = ih.box_pair_head
@@ -1099,20 +1144,7 @@ def interaction_head_from_pooled(ih, features, image_shapes, box_features, box_c
     Pn = seg.total_pairs
     nc = G.num_cls
     vt = _verb_table(G, dev)
-    tkey = (labels_dev.data_ptr(), scores_dev.data_ptr(), run["pair2cell"].data_ptr(), seg.d_hum_off.data_ptr())
-    tc = run.get("_post_tables")
-    if tc is not None and tc[0] == tkey:
-        tables = tc[1]                               # same run views, same label / score buffers: the descriptor stands
-    else:
-        tables = _lib.PostTables()
-        tables.verb_off, tables.verb_idx = vt.d_off.data_ptr(), vt.d_idx.data_ptr()
-        tables.pair2cell, tables.cell_hrow = run["pair2cell"].data_ptr(), run["cell_hrow"].data_ptr()
-        tables.cell_orow, tables.cell_img = run["cell_orow"].data_ptr(), run["cell_img"].data_ptr()
-        tables.hum_off, tables.box_off, tables.pair_off = seg.d_hum_off.data_ptr(), seg.d_box_off.data_ptr(), seg.d_pair_off.data_ptr()
-        tables.labels, tables.scores = labels_dev.data_ptr(), scores_dev.data_ptr()
-        if run.get("_train"):
-            tables.logit_row = run["pair2cell"].data_ptr()         # training layout: logits live in cell rows
-        dict.__setitem__(run, "_post_tables", (tkey, tables))
+    tables = pre["tables"] if pre is not None else _run_post_tables(G, run, labels_dev, scores_dev)
     # entries per image (sizes the outputs): closed form on the host, no device round trip
     pc = meta.get("_skg_post")
     if pc is None or pc[0] is not seg:
@@ -1135,7 +1167,10 @@ def interaction_head_from_pooled(ih, features, image_shapes, box_features, box_c
         if len(seg.post_cache) >= 16:
             seg.post_cache.clear()
         seg.post_cache[pkey] = meta["_skg_post"]
-    gt = _gt_labels(G, run, tables, boxes_cat, targets) if targets is not None else None
+    if pre is not None:
+        gt = pre["gt"]
+    else:
+        gt = _gt_labels(G, run, tables, boxes_cat, targets) if targets is not None else None
     # two allocations hold every output of the batch; the per-image results are views into them
     out_i = torch.empty(2 * L + Pn, dtype=torch.int64, device=dev)
     out_f = torch.empty(_flat_f_size(L, Pn, gt is not None), dtype=torch.float32, device=dev)
@@ -1159,20 +1194,34 @@ def interaction_head_from_pooled(ih, features, image_shapes, box_features, box_c
     ih.__dict__["_skg_last_run"] = run
     if ih.training:
         # losses (head.py:153-235); n_p averaged over ranks when distributed (one 2-float all-reduce, no barriers)
-        n_p = torch.stack([(lab_e != 0).sum(), (unary != 0).sum()]).float()
-        if ih.distributed:
-            from .shard import average_normalisers
-            n_p = average_normalisers(n_p)
+        if pre is not None:
+            n_p, transh = pre["n_p"], None
+        else:
+            n_p = torch.stack([(lab_e != 0).sum(), (unary != 0).sum()]).float()
+            if ih.distributed:
+                from .shard import average_normalisers
+                n_p = average_normalisers(n_p)
         hoi = ops.binary_focal_loss(scores, lab_e, reduction="sum", gamma=0.2) / n_p[0]
         inter = ops.binary_focal_loss(weights, unary, reduction="sum", gamma=2.0) / n_p[1]
-        pos, neg, eh, et, rl, rn = _transh_pos_neg(G, run, gt, targets)
-        ns = ih.__dict__.get("_skg_ns")                      # built once per head (head.py:229-231 builds it per call)
-        if ns is None or ns[0] != dev:
-            ns = ih.__dict__["_skg_ns"] = (dev, NegativeSampling(loss=MarginLoss(margin=1), batch_size=256).to(dev))
-        transh = ns[1](pos, neg, eh, rl, rn, et) / n_p[1]
+        if pre is not None:
+            transh = pre["transh"]
+        else:
+            transh = transh_loss(ih, run, gt, targets) / n_p[1]
         ih.__dict__["_skg_last_post"] = dict(tables=tables, gt=gt, n_p=n_p, keep=(labels_dev, scores_dev, boxes_cat))
         results.append(dict(hoi_loss=hoi, interactiveness_loss=inter, transH_loss=transh))
     return results
+
+
+def transh_loss(ih, run, gt: Tensor, targets) -> Tensor:
+    """compute_transH_loss before the division by the normaliser (head.py:207-235, 926-963)."""
+    from .kge import MarginLoss, NegativeSampling
+    G = ih.box_pair_head
+    dev = gt.device
+    pos, neg, eh, et, rl, rn = _transh_pos_neg(G, run, gt, targets)
+    ns = ih.__dict__.get("_skg_ns")                          # built once per head (head.py:229-231 builds it per call)
+    if ns is None or ns[0] != dev:
+        ns = ih.__dict__["_skg_ns"] = (dev, NegativeSampling(loss=MarginLoss(margin=1), batch_size=256).to(dev))
+    return ns[1](pos, neg, eh, rl, rn, et)
 
 
 def _flat_f_size(L: int, Pn: int, train: bool) -> int:

@@ -186,6 +186,11 @@ class TrainState:
         #                                                 keys repeat (fixed batch geometry, stable buffers); else plain launches
         self.loss_scalars = torch.zeros(4, dtype=torch.float32, device=dev)
         self._gt_buf = None
+        # side stream of the pre-pass (labels, normalisers, TransH loss: geometry + targets only) and its two events
+        self.side = torch.cuda.Stream(dev, priority=-1)          # high priority: its small kernels slot in between the GEMMs
+        self.ev_maps, self.ev_pre = torch.cuda.Event(), torch.cuda.Event()
+        self.ev_maps.record(torch.cuda.current_stream(dev))      # materialises the cudaEvent_t handle
+        self.prepass = True
         self._build_pack_table(ih)
         self._unpack = None
         self._grad_key = None
@@ -449,6 +454,36 @@ class _HeadLossFn(torch.autograd.Function):
         return None, None, None, None
 
 
+def _prepass(ih, ts: "TrainState", run, boxes_cat: Tensor, labels_dev: Tensor, scores_dev: Tensor, targets) -> dict:
+    """Everything of the training step that depends on the batch geometry and the targets only -- GT association
+    (head.py:703-719), the loss normalisers (head.py:167-205, with their rank average), TransH positive / negative selection
+    and the margin loss (head.py:207-235, 926-963) -- on a side stream behind the pair-enumeration event of the forward, so
+    it runs UNDER the GEMM chain.  The one host synchronisation of the step (the selection's sizes) then waits for this side
+    stream only: the main stream keeps the whole forward queued, and the rank average of the normalisers has the forward
+    as cover instead of sitting between the loss and the backward."""
+    from . import engine
+    G = ih.box_pair_head
+    dev = ts.device
+    cur = torch.cuda.current_stream(dev)
+    tables = engine._run_post_tables(G, run, labels_dev, scores_dev)
+    Pn = int(run["seg"].total_pairs)
+    with torch.cuda.stream(ts.side):
+        ts.side.wait_event(ts.ev_maps)
+        gt = engine._gt_labels(G, run, tables, boxes_cat, targets)
+        n_p = torch.empty(2, dtype=torch.float32, device=dev)
+        with _lib.on_device(dev):
+            _lib.call("skg_loss_normalisers", _lib.ptr(gt), ctypes.byref(tables), Pn, G.num_cls, _lib.ptr(n_p), _lib.stream_ptr(dev))
+        if ih.distributed:
+            from .shard import average_normalisers
+            n_p = average_normalisers(n_p)
+        with torch.enable_grad():
+            transh = engine.transh_loss(ih, run, gt, targets) / n_p[1]
+        ts.ev_pre.record(ts.side)
+    cur.wait_event(ts.ev_pre)
+    n_p.record_stream(cur); transh.record_stream(cur)
+    return dict(tables=tables, gt=gt, n_p=n_p, transh=transh)
+
+
 def training_forward(ih, features, image_shapes, box_features: Tensor, box_coords: List[Tensor], box_labels, box_scores,
                      targets, meta=None) -> List[dict]:
     """InteractionHead.forward in training mode from the pooled box features on (head.py:389-427): the per-image
@@ -462,13 +497,14 @@ def training_forward(ih, features, image_shapes, box_features: Tensor, box_coord
     ts = train_state(ih)
     with torch.no_grad():
         run = engine.head_forward(ih, features["3"], image_shapes, box_features.detach(), boxes_cat, meta, precise_logits=False,
-                                  graph=ts.graph, train=True, pk=ts.pk)
+                                  graph=ts.graph, train=True, pk=ts.pk, maps_event=ts.ev_maps.cuda_event if ts.prepass else 0)
         dict.__setitem__(run, "_gt_out", ts.gt_buffer(int(run["seg"].total_pairs), G.num_cls))
     # (called from forward_from_pooled only in training mode: no train() / eval() round trip over the ~470 sub-modules)
     assert ih.training, "training_forward needs the head in training mode"
+    pre = _prepass(ih, ts, run, boxes_cat, labels_dev, scores_dev, targets) if ts.prepass and int(run["seg"].total_pairs) > 0 else None
     with torch.enable_grad():               # the TransH loss is differentiable w.r.t. the tables (kge autograd Functions)
         results = engine.interaction_head_from_pooled(ih, features, image_shapes, box_features.detach(), box_coords,
-                                                      box_labels, box_scores, targets=targets, meta=meta, run=run)
+                                                      box_labels, box_scores, targets=targets, meta=meta, run=run, pre=pre)
     losses = results.pop()
     post = ih.__dict__["_skg_last_post"]
     rec = _StepRecord(ts, run, run["_batch"], run["_flags"], run._ws, post["tables"], post["gt"], post["n_p"],

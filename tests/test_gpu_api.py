@@ -381,3 +381,33 @@ def test_training_flat_params_fused_optimizer_tracks_updates():
     for x, y in zip(a[0], b[0]):
         assert abs(x - y) <= 2e-2 * abs(x), (a[0], b[0])
     assert float((a[1] - b[1]).abs().max()) <= 2e-2 * float(a[1].abs().max()) + 1e-6
+
+
+def test_training_prepass_matches_inline_losses():
+    """The side-stream pre-pass (GT labels, normalisers from skg_loss_normalisers, TransH loss under the GEMM chain) gives the
+    losses and gradients of the in-line order (normalisers counted from the post-processed labels, head.py:167-205)."""
+    from skghoi_b200 import train
+    batch = synthetic.make_batch([(4, 9), (3, 7), (6, 6)], seed=15, with_targets=True)
+    d = _to_dev(batch)
+    out = {}
+    for mode in (True, False):
+        ih = _head(True)
+        ts = train.train_state(ih)
+        ts.prepass = mode
+        vals = []
+        for _ in range(3):                       # three steps: plain launches, graph capture, graph replay
+            ih.zero_grad(set_to_none=False)
+            res = ih.forward_from_pooled(d["features"], d["image_shapes"], d["box_features"], d["box_coords"], d["box_labels"],
+                                         d["box_scores"], d["targets"])
+            ls = res[-1]
+            (ls["hoi_loss"] + ls["interactiveness_loss"]).backward()
+            torch.cuda.synchronize()
+            vals.append((float(ls["hoi_loss"]), float(ls["interactiveness_loss"]), float(ls["transH_loss"].sum())))
+        out[mode] = (vals, [p.grad.detach().clone() for p in ih.parameters()],
+                     ih.__dict__["_skg_last_post"]["n_p"].cpu().clone())
+    assert torch.equal(out[True][2], out[False][2]), (out[True][2], out[False][2])          # the normalisers themselves
+    for a, b in zip(out[True][0], out[False][0]):
+        assert abs(a[0] - b[0]) <= 1e-3 * abs(b[0]) and abs(a[1] - b[1]) <= 1e-3 * abs(b[1]), (a, b)
+        assert abs(a[2] - b[2]) <= 1e-4 * max(1.0, abs(b[2])), (a, b)      # CPU-seeded negatives differ run to run only by RNG state
+    tot_a = torch.cat([g.flatten() for g in out[True][1]]); tot_b = torch.cat([g.flatten() for g in out[False][1]])
+    assert float((tot_a - tot_b).norm()) <= 2e-2 * float(tot_b.norm())

@@ -18,4 +18,4 @@ def test_staged_allreduce_equals_rank_mean():
            "--master-port", "29541", os.path.join(ROOT, "tools", "dist_train_check.py")]
     out = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
     assert out.returncode == 0, out.stdout[-2000:] + out.stderr[-2000:]
-    assert "\nOK" in out.stdout, out.stdout[-2000:]
+    assert "\nOK" in out.stdout and "TRAIN_OK" in out.stdout, out.stdout[-2000:]

@@ -250,3 +250,39 @@ def test_head_loss_backward_vs_autograd():
     assert float((got - ref).abs().max()) <= 1e-2 * scale, (float((got - ref).abs().max()), scale)
     diag = torch.ones(C, dtype=torch.bool, device=DEV); diag[p2c] = False
     assert float(got[diag].abs().max()) == 0.0          # cells i == j carry no gradient
+
+
+def test_select_negatives_cuda_counts_validity_and_randomness():
+    """skg_select_count / skg_select_fill: positives in flat order image by image, per image as many DISTINCT zero-label
+    entries of the same image, a new draw per call (head.py:926-963 in its device form)."""
+    from skghoi_b200 import engine
+    torch.manual_seed(0)
+    nc = 117
+    per_img = [10, 25, 0, 5, 300]
+    P = sum(per_img)
+    pair_off = torch.tensor([0] + list(torch.tensor(per_img).cumsum(0)), dtype=torch.int64, device=DEV)
+    labels = (torch.rand(P, nc) > 0.97).float()
+    labels[35:40] = 0; labels[36, 5] = 1
+    lab = labels.to(DEV)
+    pos, neg = engine.select_negatives_cuda(lab, pair_off, len(per_img))
+    flat = labels.view(-1)
+    assert torch.equal(pos.cpu(), torch.nonzero(flat).squeeze(1))
+    negc = neg.cpu()
+    assert bool((flat[negc] == 0).all()) and negc.unique().numel() == negc.numel()
+    img_of = torch.repeat_interleave(torch.arange(len(per_img)), torch.tensor(per_img))
+    assert torch.equal(img_of[pos.cpu() // nc], img_of[negc // nc])            # negative i comes from the image of positive i
+    _, neg2 = engine.select_negatives_cuda(lab, pair_off, len(per_img))
+    assert neg2.numel() == neg.numel() and not torch.equal(neg2.cpu().sort().values, negc.sort().values)
+    # uniformity over the zero labels of a small image: 2 positives among 12 entries, many draws
+    small = torch.zeros(2, 6); small[0, 1] = 1; small[1, 4] = 1
+    sm = small.to(DEV); off = torch.tensor([0, 2], dtype=torch.int64, device=DEV)
+    hits = torch.zeros(12)
+    for _ in range(600):
+        _, n = engine.select_negatives_cuda(sm, off, 1)
+        hits[n.cpu()] += 1
+    assert hits[1] == 0 and hits[10] == 0
+    z = hits[[0, 2, 3, 4, 5, 6, 7, 8, 9, 11]]
+    assert float(z.min()) > 0.6 * float(z.mean()) and float(z.max()) < 1.4 * float(z.mean()), z
+    empty = torch.zeros(6, nc, device=DEV)
+    p0, n0 = engine.select_negatives_cuda(empty, torch.tensor([0, 6], dtype=torch.int64, device=DEV), 1)
+    assert p0.numel() == 0 and n0.numel() == 0
