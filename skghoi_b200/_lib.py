@@ -12,7 +12,7 @@ from ctypes import c_char_p, c_float, c_int, c_int64, c_void_p
 import torch
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libskghoi_b200.so")
+LIB_PATH = os.environ.get("SKG_LIB_PATH") or os.path.join(_HERE, "libskghoi_b200.so")   # (override: kernel experiments only)
 
 P, I, L, F = c_void_p, c_int, c_int64, c_float
 

@@ -23,7 +23,14 @@ namespace skg {
 constexpr int BM = 128;            // UMMA M (cta_group::1)
 constexpr int BK = 64;             // 64 bf16 = 128 B = one swizzle-128B atom row
 constexpr int UMMA_K = 16;
-constexpr int kEpiWarps = 8;       // kEpiParts per TMEM lane quadrant
+#ifndef SKG_EPI_WARPS
+#define SKG_EPI_WARPS 8
+#endif
+constexpr int kEpiWarps = SKG_EPI_WARPS;   // kEpiParts per TMEM lane quadrant (8 or 16)
+// gathered operands software-pipelined one block ahead (costs ~40 registers).  Measured on B200 (tools/gemm_bench.py --epi,
+// fused fc_2 shape 4096 x 4096 x 1024, flushed single launches): 8 warps + prefetch 49.9 us, 16 warps without it (the
+// register budget of 640 threads leaves no room) 58.2 us -- latency hiding by prefetch beats latency hiding by occupancy
+constexpr bool kEpiPrefetch = kEpiWarps <= 8;
 constexpr int kEpiParts = kEpiWarps / 4;   // column parts of a tile, one epilogue warp each per quadrant
 constexpr int kGemmThreads = 32 * (4 + kEpiWarps);  // warps: 0 TMA, 1 MMA, 2 TMEM alloc, 3 idle, 4..19 epilogue
 // epilogue features (compile-time mask FEAT of gemm_bf16_kernel; bias / ReLU / out_row are always available)
@@ -444,10 +451,13 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             }
           }
         };
-        if (kBlocks == 1) {
+        if (kBlocks == 1 || !kEpiPrefetch) {
           Tabs T0;
-          load_tabs(0, T0);
-          process(0, T0);
+#pragma unroll 1
+          for (int blk = 0; blk < kBlocks; ++blk) {
+            load_tabs(blk, T0);
+            process(blk, T0);
+          }
         } else {
           Tabs T0, T1;
           load_tabs(0, T0);

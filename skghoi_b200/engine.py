@@ -1134,7 +1134,10 @@ def interaction_head_from_pooled(ih, features, image_shapes, box_features, box_c
     G = ih.box_pair_head
     if ih.training:
         assert targets is not None, "Targets should be passed during training"          # head.py:380-381
-    meta, boxes_cat, labels_dev, scores_dev = _prep_inputs(G, features, box_features, box_coords, box_labels, box_scores, meta)
+    if pre is not None and "prepped" in pre:
+        meta, boxes_cat, labels_dev, scores_dev = pre["prepped"]      # the training pass has packed the inputs already
+    else:
+        meta, boxes_cat, labels_dev, scores_dev = _prep_inputs(G, features, box_features, box_coords, box_labels, box_scores, meta)
     if run is None and targets is None and not ih.training and SESSION_PATH and CAPACITY_BUCKETS and sum(meta["n"]) > 0:
         return _session_forward(ih, packed_head(ih), features["3"], image_shapes, box_features, boxes_cat, labels_dev, scores_dev, meta)
     if run is None:

@@ -502,6 +502,8 @@ def training_forward(ih, features, image_shapes, box_features: Tensor, box_coord
     # (called from forward_from_pooled only in training mode: no train() / eval() round trip over the ~470 sub-modules)
     assert ih.training, "training_forward needs the head in training mode"
     pre = _prepass(ih, ts, run, boxes_cat, labels_dev, scores_dev, targets) if ts.prepass and int(run["seg"].total_pairs) > 0 else None
+    if pre is not None:
+        pre["prepped"] = (meta, boxes_cat, labels_dev, scores_dev)
     with torch.enable_grad():               # the TransH loss is differentiable w.r.t. the tables (kge autograd Functions)
         results = engine.interaction_head_from_pooled(ih, features, image_shapes, box_features.detach(), box_coords,
                                                       box_labels, box_scores, targets=targets, meta=meta, run=run, pre=pre)
