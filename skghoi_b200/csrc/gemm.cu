@@ -17,6 +17,7 @@
 #include "common.cuh"
 #include "skghoi_b200.h"
 #include <cuda.h>
+#include <stdlib.h>
 
 namespace skg {
 
@@ -31,6 +32,10 @@ constexpr int kEpiWarps = SKG_EPI_WARPS;   // kEpiParts per TMEM lane quadrant (
 // fused fc_2 shape 4096 x 4096 x 1024, flushed single launches): 8 warps + prefetch 49.9 us, 16 warps without it (the
 // register budget of 640 threads leaves no room) 58.2 us -- latency hiding by prefetch beats latency hiding by occupancy
 constexpr bool kEpiPrefetch = kEpiWarps <= 8;
+#ifndef SKG_EPI_L1_PREFETCH
+#define SKG_EPI_L1_PREFETCH 1
+#endif
+constexpr bool kEpiL1Prefetch = SKG_EPI_L1_PREFETCH != 0;
 constexpr int kEpiParts = kEpiWarps / 4;   // column parts of a tile, one epilogue warp each per quadrant
 constexpr int kGemmThreads = 32 * (4 + kEpiWarps);  // warps: 0 TMA, 1 MMA, 2 TMEM alloc, 3 idle, 4..19 epilogue
 // epilogue features (compile-time mask FEAT of gemm_bf16_kernel; bias / ReLU / out_row are always available)
@@ -92,6 +97,49 @@ __device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t desc_a, uint
       "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
       : "memory");
 }
+// ---- CTA pair (cta_group::2): the two CTAs of a cluster run ONE M = 256 MMA; each loads its own 128 rows of A and HALF of
+// the B tile, so the operand traffic per output element drops by a third (the fused fc_2 shape is bound by the L2 -> SM
+// operand stream: 403 MB per launch at ~12 TB/s of L2 read throughput with 128 x 256 tiles per CTA)
+constexpr uint32_t kPeerBitMask = 0xFEFFFFFFu;   // shared::cluster address of the same offset in the pair's even (leader) CTA
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;\n" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;\n" ::: "memory");
+  asm volatile("barrier.cluster.wait.acquire.aligned;\n" ::: "memory");
+}
+// TMA load whose completion bytes are credited to the LEADER CTA's mbarrier (executed by both CTAs of the pair)
+__device__ __forceinline__ void tma_load_2d_pair(const CUtensorMap* map, uint64_t* bar, void* smem_dst, int c_inner, int c_outer) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];\n" ::"r"(
+          smem_u32(smem_dst)),
+      "l"(map), "r"(smem_u32(bar) & kPeerBitMask), "r"(c_inner), "r"(c_outer)
+      : "memory");
+}
+__device__ __forceinline__ void umma_bf16_pair(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "setp.ne.b32 p, %4, 0;\n"
+      "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n"
+      "}\n" ::"r"(tmem_d),
+      "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+// commit of the pair's MMAs: arrives on the barrier at this offset in BOTH CTAs
+__device__ __forceinline__ void tcgen05_commit_pair(uint64_t* bar) {
+  asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;\n" ::"r"(
+                   smem_u32(bar)),
+               "h"((uint16_t)3)
+               : "memory");
+}
+// arrive on the LEADER CTA's barrier at this offset (from either CTA of the pair)
+__device__ __forceinline__ void mbar_arrive_leader(uint64_t* bar) {
+  asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];\n" ::"r"(smem_u32(bar) & kPeerBitMask) : "memory");
+}
+
 __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
   asm volatile(
       "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
@@ -154,21 +202,34 @@ __device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
 // GATHER: the epilogue multiplies by row-gathered tables.  Those launches trade one pipeline stage (48 KB) for L1 capacity:
 // the carve-out drops from 228 KB to 164 KB, the tile's table rows (32 KB at n = 32) then stay L1-resident across the four
 // lane quadrants; plain launches keep the deeper pipeline (measured: 4 -> 3 stages costs the mainloop 3 us at K = 1024).
-template <int BN, bool GATHER>
+template <int BN, bool GATHER, bool TWO = false>
 struct GemmSmem {
-  static constexpr int kStages = (BN == 256) ? (GATHER ? 3 : 4) : (BN == 128 ? 6 : 7);
+#ifndef SKG_PAIR_STAGES
+#define SKG_PAIR_STAGES 5
+#endif
+#ifndef SKG_PAIR_STAGES_GATHER
+#define SKG_PAIR_STAGES_GATHER 4
+#endif
+  static constexpr int kStages = TWO ? (GATHER ? SKG_PAIR_STAGES_GATHER : SKG_PAIR_STAGES) : (BN == 256) ? (GATHER ? 3 : 4) : (BN == 128 ? 6 : 7);
   static constexpr int kABytes = BM * BK * 2;
-  static constexpr int kBBytes = BN * BK * 2;
+  static constexpr int kBRows = TWO ? BN / 2 : BN;     // CTA pair: each CTA stages half of the B tile
+  static constexpr int kBBytes = kBRows * BK * 2;
   static constexpr int kStageBytes = kABytes + kBBytes;
   static constexpr int kStagingBytes = kEpiWarps * 2048;   // one swizzled 32 x 16 fp32 patch per epilogue warp
   static constexpr int kTotal = kStages * kStageBytes + 1024 /*align slack*/ + 256 /*barriers*/ + kStagingBytes;
 };
 
-template <int BN, uint32_t FEAT, bool SK>
+template <int BN, uint32_t FEAT, bool SK, bool TWO = false>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, int M, int N, int K,
                  const __grid_constant__ EpiGroups epi, int splits, float* __restrict__ sk_ws, int* __restrict__ sk_cnt, int a_k_wrap) {
-  using S = GemmSmem<BN, (FEAT & (F_P | F_Q)) != 0 && FEAT != F_ALL>;
+  static_assert(!TWO || (BN == 256 && !SK), "the CTA-pair variant is the 256 x 256 pair tile without split-K");
+  using S = GemmSmem<BN, (FEAT & (F_P | F_Q)) != 0 && FEAT != F_ALL, TWO>;
+  constexpr int TM = TWO ? 2 * BM : BM;                 // rows of a work item (pair tile: 256, 128 per CTA)
+  const uint32_t cta_rank = TWO ? cluster_ctarank() : 0u;
+  const bool leader = cta_rank == 0;
+  const int first_item = TWO ? (int)(blockIdx.x >> 1) : (int)blockIdx.x;
+  const int item_stride = TWO ? (int)(gridDim.x >> 1) : (int)gridDim.x;
   constexpr int kStages = S::kStages;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
@@ -182,7 +243,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   volatile int* sk_flag = reinterpret_cast<volatile int*>(tmem_base_slot + 1);   // split-K: 'this CTA owns the epilogue'
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int num_m = (M + BM - 1) / BM, num_n = (N + BN - 1) / BN;
+  const int num_m = (M + TM - 1) / TM, num_n = (N + BN - 1) / BN;
   const int num_tiles = num_m * num_n;
   const int num_k = (K + BK - 1) / BK;
   // split-K: work item = (tile, split); the splits of one tile sit on adjacent CTAs and reduce through fp32
@@ -198,15 +259,21 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   }
   if (warp == 1 && lane == 0) {
     for (int s = 0; s < kStages; ++s) { mbar_init(full_bar + s, 1); mbar_init(empty_bar + s, 1); }
-    for (int a = 0; a < 2; ++a) { mbar_init(tmem_full + a, 1); mbar_init(tmem_empty + a, kEpiWarps); }
+    // pair: the leader's tmem_empty barriers collect the epilogue warps of BOTH CTAs
+    for (int a = 0; a < 2; ++a) { mbar_init(tmem_full + a, 1); mbar_init(tmem_empty + a, TWO ? 2 * kEpiWarps : kEpiWarps); }
     asm volatile("fence.mbarrier_init.release.cluster;\n" ::: "memory");
   }
-  if (warp == 2) {   // 2 x BN fp32 accumulator columns (power of two >= 32)
-    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;\n" ::"r"(smem_u32(tmem_base_slot)), "r"(2 * BN));
-    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;\n" ::: "memory");
+  if (warp == 2) {   // 2 x BN fp32 accumulator columns (power of two >= 32); pair: the same warp of both CTAs, same columns
+    if (TWO) {
+      asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;\n" ::"r"(smem_u32(tmem_base_slot)), "r"(2 * BN));
+      asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;\n" ::: "memory");
+    } else {
+      asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;\n" ::"r"(smem_u32(tmem_base_slot)), "r"(2 * BN));
+      asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;\n" ::: "memory");
+    }
   }
   tcgen05_fence_before();
-  __syncthreads();
+  if (TWO) cluster_sync_all(); else __syncthreads();   // pair: nobody signals a peer barrier before it is initialised
   tcgen05_fence_after();
   const uint32_t tmem_base = *tmem_base_slot;
   asm volatile("griddepcontrol.wait;\n" ::: "memory");   // every predecessor grid has completed, its writes are visible
@@ -215,30 +282,37 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     // ===================== TMA producer =====================
     if (lane == 0) {
       int stage = 0; uint32_t phase = 0;
-      for (int item = blockIdx.x; item < num_items; item += gridDim.x) {
+      for (int item = first_item; item < num_items; item += item_stride) {
         const int tile = item / splits, split = item - tile * splits;
-        const int m0 = (tile / num_n) * BM, n0 = (tile % num_n) * BN;
+        const int m0 = (tile / num_n) * TM + (int)cta_rank * BM, n0 = (tile % num_n) * BN;
         const int kb0 = (int)((long long)split * num_k / splits), kb1 = (int)((long long)(split + 1) * num_k / splits);
         for (int kb = kb0; kb < kb1; ++kb) {
           mbar_wait(empty_bar + stage, phase ^ 1);
           uint8_t* sa = smem + stage * S::kStageBytes;
           uint8_t* sb = sa + S::kABytes;
-          mbar_arrive_expect_tx(full_bar + stage, S::kStageBytes);
           // a_k_wrap: A holds only a_k_wrap columns and is read cyclically along K (split-bf16 predictor: [hi | lo | hi])
           const int ka = (a_k_wrap > 0) ? (kb * BK) % a_k_wrap : kb * BK;
-          tma_load_2d(&tmA, full_bar + stage, sa, ka, m0);
-          tma_load_2d(&tmB, full_bar + stage, sb, kb * BK, n0);
+          if (TWO) {
+            // both CTAs load (own A rows, own half of the B tile); all four copies complete on the LEADER's full barrier
+            if (leader) mbar_arrive_expect_tx(full_bar + stage, 2 * S::kStageBytes);
+            tma_load_2d_pair(&tmA, full_bar + stage, sa, ka, m0);
+            tma_load_2d_pair(&tmB, full_bar + stage, sb, kb * BK, n0 + (int)cta_rank * S::kBRows);
+          } else {
+            mbar_arrive_expect_tx(full_bar + stage, S::kStageBytes);
+            tma_load_2d(&tmA, full_bar + stage, sa, ka, m0);
+            tma_load_2d(&tmB, full_bar + stage, sb, kb * BK, n0);
+          }
           if (++stage == kStages) { stage = 0; phase ^= 1; }
         }
       }
     }
   } else if (warp == 1) {
     // ===================== MMA issuer =====================
-    if (lane == 0) {
-      constexpr uint32_t idesc = make_idesc(BM, BN);
+    if (lane == 0 && leader) {
+      constexpr uint32_t idesc = make_idesc(TM, BN);
       int stage = 0; uint32_t phase = 0;
       int acc = 0; uint32_t acc_phase = 0;
-      for (int item = blockIdx.x; item < num_items; item += gridDim.x) {
+      for (int item = first_item; item < num_items; item += item_stride) {
         const int split = item % splits;
         const int kb0 = (int)((long long)split * num_k / splits), kb1 = (int)((long long)(split + 1) * num_k / splits);
         mbar_wait(tmem_empty + acc, acc_phase ^ 1);      // epilogue has drained this accumulator
@@ -253,12 +327,15 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           for (int k = 0; k < BK / UMMA_K; ++k) {
             const uint64_t da = make_smem_desc(sa + k * UMMA_K * 2);
             const uint64_t db = make_smem_desc(sb + k * UMMA_K * 2);
-            umma_bf16(d_tmem, da, db, idesc, (kb > kb0 || k != 0) ? 1u : 0u);
+            if (TWO) umma_bf16_pair(d_tmem, da, db, idesc, (kb > kb0 || k != 0) ? 1u : 0u);
+            else umma_bf16(d_tmem, da, db, idesc, (kb > kb0 || k != 0) ? 1u : 0u);
           }
-          tcgen05_commit(empty_bar + stage);              // smem slot free once these MMAs retire
+          if (TWO) tcgen05_commit_pair(empty_bar + stage); // pair: frees the slot in BOTH CTAs
+          else tcgen05_commit(empty_bar + stage);          // smem slot free once these MMAs retire
           if (++stage == kStages) { stage = 0; phase ^= 1; }
         }
-        tcgen05_commit(tmem_full + acc);                  // accumulator complete -> epilogue
+        if (TWO) tcgen05_commit_pair(tmem_full + acc);    // accumulator complete -> the epilogue warps of both CTAs
+        else tcgen05_commit(tmem_full + acc);             // accumulator complete -> epilogue
         if (++acc == 2) { acc = 0; acc_phase ^= 1; }
       }
     }
@@ -279,10 +356,10 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     constexpr int kBlocks = BN / (16 * kEpiParts);        // 16-column blocks per warp (even, or 1)
     static_assert(kBlocks == 1 || kBlocks % 2 == 0, "the pipelined epilogue walks the blocks in pairs");
     int acc = 0; uint32_t acc_phase = 0;
-    for (int item = blockIdx.x; item < num_items; item += gridDim.x) {
+    for (int item = first_item; item < num_items; item += item_stride) {
       const int tile = item / splits;
       const int m_blk = tile / num_n, n_blk = tile % num_n;
-      const int m0 = m_blk * BM, n0 = n_blk * BN;
+      const int m0 = m_blk * TM + (int)cta_rank * BM, n0 = n_blk * BN;
       int gi = 0;
       for (int q = 1; q < epi.num; ++q) if (n0 >= epi.g[q].n_begin) gi = q;
       const skg_epilogue_group& G = epi.g[gi];
@@ -314,6 +391,22 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           if (G.out_row) ro = __ldg(G.out_row + row);
         } else {
           rp = rq = rr = 0; ro = -1;
+        }
+        // The gathered table rows of this tile are first-touch L2 hits (~1 us under load) and the one-block-ahead register
+        // prefetch below covers ~300 cycles of them: pull the tile's table lines into L1 NOW, one row per lane, while the
+        // warp would otherwise sit waiting for the accumulator (ncu: stall_long_sb on the first use of the gathered operands
+        // was 20 % of the kernel's active samples)
+        if (kEpiL1Prefetch && row_ok) {
+          constexpr int kLines = (BN / kEpiParts) / 32;          // 128-byte lines of this warp's column part per row
+          const int lc0 = n0 - n_begin + part * (BN / kEpiParts);
+          if (n0 + part * (BN / kEpiParts) < N) {
+#pragma unroll
+            for (int j = 0; j < kLines; ++j) {
+              if ((FEAT & F_P) && g_p) asm volatile("prefetch.global.L1 [%0];\n" ::"l"(g_p + (int64_t)rp * ld_p + lc0 + j * 32));
+              if ((FEAT & F_Q) && g_q) asm volatile("prefetch.global.L1 [%0];\n" ::"l"(g_q + (int64_t)rq * ld_q + lc0 + j * 32));
+              if ((FEAT & F_RES) && g_res) asm volatile("prefetch.global.L1 [%0];\n" ::"l"(g_res + (int64_t)rr * ld_r + lc0 + j * 32));
+            }
+          }
         }
 #pragma unroll
         for (int it = 0; it < 4; ++it) {
@@ -477,7 +570,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           // accumulator drained: hand the TMEM buffer back to the MMA warp
           tcgen05_fence_before();
           __syncwarp();
-          if (lane == 0) mbar_arrive(tmem_empty + acc);
+          if (lane == 0) { if (TWO) mbar_arrive_leader(tmem_empty + acc); else mbar_arrive(tmem_empty + acc); }
           if (split_mode) {                            // threadfence-reduction: who adds the last partial owns the epilogue
             __threadfence();
             asm volatile("bar.sync 1, %0;\n" ::"n"(kEpiWarps * 32) : "memory");
@@ -513,10 +606,11 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   }
 
   tcgen05_fence_before();
-  __syncthreads();
+  if (TWO) cluster_sync_all(); else __syncthreads();   // pair: neither CTA leaves while the other may still read its smem / signal it
   if (warp == 2) {
     tcgen05_fence_after();
-    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;\n" ::"r"(tmem_base), "r"(2 * BN));
+    if (TWO) asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;\n" ::"r"(tmem_base), "r"(2 * BN));
+    else asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;\n" ::"r"(tmem_base), "r"(2 * BN));
   }
 }
 
@@ -589,27 +683,37 @@ struct SplitK {
   int a_k_wrap = 0;
 };
 
-template <int BN, uint32_t FEAT, bool SK>
+template <int BN, uint32_t FEAT, bool SK, bool TWO = false>
 static int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, int M, int N, int K, const EpiGroups& epi,
                        const SplitK& sk, cudaStream_t stream) {
   const int a_k_wrap = sk.a_k_wrap;
-  using S = GemmSmem<BN, (FEAT & (F_P | F_Q)) != 0 && FEAT != F_ALL>;
-  auto kern = gemm_bf16_kernel<BN, FEAT, SK>;
+  using S = GemmSmem<BN, (FEAT & (F_P | F_Q)) != 0 && FEAT != F_ALL, TWO>;
+  auto kern = gemm_bf16_kernel<BN, FEAT, SK, TWO>;
   static bool attr_set = false;
   if (!attr_set) {
     SKG_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, S::kTotal));
     attr_set = true;
   }
-  const int items = ceil_div(M, BM) * ceil_div(N, BN) * sk.splits;
-  const int grid = items < num_sms() ? items : num_sms();
+  const int items = ceil_div(M, TWO ? 2 * BM : BM) * ceil_div(N, BN) * sk.splits;
+  int grid = items < num_sms() ? items : num_sms();
+  if (TWO) { const int pairs = num_sms() / 2; grid = 2 * (items < pairs ? items : pairs); }   // one cluster of two CTAs per pair tile
   static const bool pdl = [] { const char* e = getenv("SKG_GEMM_PDL"); return !(e && e[0] == '0'); }();
-  if (pdl) {
+  if (pdl || TWO) {
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(grid); cfg.blockDim = dim3(kGemmThreads); cfg.dynamicSmemBytes = S::kTotal; cfg.stream = stream;
-    cudaLaunchAttribute at[1];
-    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-    at[0].val.programmaticStreamSerializationAllowed = 1;
-    cfg.attrs = at; cfg.numAttrs = 1;
+    cudaLaunchAttribute at[2];
+    int na = 0;
+    if (pdl) {
+      at[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+      at[na].val.programmaticStreamSerializationAllowed = 1;
+      ++na;
+    }
+    if (TWO) {
+      at[na].id = cudaLaunchAttributeClusterDimension;
+      at[na].val.clusterDim.x = 2; at[na].val.clusterDim.y = 1; at[na].val.clusterDim.z = 1;
+      ++na;
+    }
+    cfg.attrs = at; cfg.numAttrs = na;
     SKG_CUDA(cudaLaunchKernelEx(&cfg, kern, tmA, tmB, M, N, K, epi, sk.splits, sk.ws, sk.cnt, a_k_wrap));
   } else {
     kern<<<grid, kGemmThreads, S::kTotal, stream>>>(tmA, tmB, M, N, K, epi, sk.splits, sk.ws, sk.cnt, a_k_wrap);
@@ -700,11 +804,6 @@ extern "C" int skg_gemm_bf16_wrapk(const void* A, int64_t lda, int a_k_wrap, con
     epi.g[i] = g;
   }
   // bias / tables are read in 32-column chunks up to the padded width: callers pad them to block_n multiples
-  CUtensorMap tmA, tmB;
-  int rc = make_tmap(&tmA, A, M, KA, lda, BM);
-  if (rc) return rc;
-  rc = make_tmap(&tmB, B, N, K, ldb, block_n);
-  if (rc) return rc;
   SplitK sk{1, nullptr, nullptr};
   sk.a_k_wrap = a_k_wrap;
   if (scratch) {
@@ -715,6 +814,22 @@ extern "C" int skg_gemm_bf16_wrapk(const void* A, int64_t lda, int a_k_wrap, con
       sk.ws = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(scratch) + kSplitKCounters * 4);
     }
   }
+  // CTA pairs (cta_group::2, 256 x 256 pair tiles) for the wide cell-row problems: enough pair tiles to fill the 74 SM pairs
+  // and no split-K; SKG_GEMM_PAIR=0 keeps every launch on single CTAs (A/B measurements)
+  // Measured on B200 (tools/gemm_bench.py --epi, 4096 x 4096 x 1024, flushed single launches): plain epilogue 37.0 us as
+  // pairs vs 37.3-38.5 us on single CTAs; the gather epilogue (fused fc_2) 48.8 vs 47.2 us -- it is bound by its own
+  // instruction path, not by the operand stream, and loses L1 to the deeper pipeline -- so it stays on single CTAs
+  // (SKG_GEMM_PAIR=2 forces pairs there too).
+  static const int pair_mode = [] { const char* e = getenv("SKG_GEMM_PAIR"); return e ? atoi(e) : 1; }();
+  bool gather = false;
+  for (int i = 0; i < num_groups; ++i) gather |= (groups[i].mul_p != nullptr);
+  const bool use_pair = pair_mode > 0 && (pair_mode > 1 || !gather) && block_n == 256 && sk.splits == 1 && a_k_wrap == 0 && N % 256 == 0 &&
+                        (int64_t)ceil_div(M, 2 * BM) * (N / 256) >= num_sms() / 2;
+  CUtensorMap tmA, tmB;
+  int rc = make_tmap(&tmA, A, M, KA, lda, BM);
+  if (rc) return rc;
+  rc = make_tmap(&tmB, B, N, K, ldb, use_pair ? block_n / 2 : block_n);
+  if (rc) return rc;
   // pick the leanest compiled epilogue whose feature set covers what the groups ask for
   uint32_t need = 0;
   for (int i = 0; i < num_groups; ++i) {
@@ -736,27 +851,31 @@ extern "C" int skg_gemm_bf16_wrapk(const void* A, int64_t lda, int a_k_wrap, con
   SKG_GEMM_CASE64(F_RES | F_MASK | F_OB)
   SKG_GEMM_CASE64(F_ALL)
 #undef SKG_GEMM_CASE64
-#define SKG_GEMM_CASE(F, SKV)                                                                 \
+#define SKG_GEMM_CASE(F, SKV, PAIR)                                                           \
   if ((need & ~(uint32_t)(F)) == 0) {                                                      \
     if (SKV && sk.splits > 1) {                                                                   \
       if (block_n == 256) return launch_gemm<256, (F), SKV>(tmA, tmB, M, N, K, epi, sk, stream);  \
       return launch_gemm<128, (F), SKV>(tmA, tmB, M, N, K, epi, sk, stream);                      \
     }                                                                                             \
     sk.splits = 1;                                                                                \
-    if (block_n == 256) return launch_gemm<256, (F), false>(tmA, tmB, M, N, K, epi, sk, stream);  \
+    if (block_n == 256) {                                                                         \
+      if (PAIR && use_pair) return launch_gemm<256, (F), false, PAIR>(tmA, tmB, M, N, K, epi, sk, stream); \
+      if (use_pair) { rc = make_tmap(&tmB, B, N, K, ldb, block_n); if (rc) return rc; }           \
+      return launch_gemm<256, (F), false>(tmA, tmB, M, N, K, epi, sk, stream);                    \
+    }                                                                                             \
     return launch_gemm<128, (F), false>(tmA, tmB, M, N, K, epi, sk, stream);                      \
   }
-  SKG_GEMM_CASE(F_OB, true)                    // bias (+ReLU) -> bf16: spatial_head, box_head
-  SKG_GEMM_CASE(F_OF, true)                    // -> fp32: per-node projections
-  SKG_GEMM_CASE(F_OB | F_OF, true)                // fc_head / fc_tail
-  SKG_GEMM_CASE(F_P | F_Q | F_RAW | F_OB, false)    // fused fc_2 of the MBFs (Hadamard with gathered tables)
-  SKG_GEMM_CASE(F_DOT, false)                  // attention weights -> adjacency row-dot
-  SKG_GEMM_CASE(F_RES | F_OF, true)                // message fc_3 + residual, split-bf16 predictor second pass
-  SKG_GEMM_CASE(F_OB | F_LO, false)                // final pair features with rounding residual
-  SKG_GEMM_CASE(F_MASK | F_OB, false)              // training: dX = (G W) gated by the ReLU mask of the layer's input
-  SKG_GEMM_CASE(F_RES | F_MASK | F_OB, false)      // training: dX + the residual path's gradient, gated
-  SKG_GEMM_CASE(F_DOT | F_OB, false)               // training forward: adjacency row-dot that also keeps the weights
-  SKG_GEMM_CASE(F_ALL, true)
+  SKG_GEMM_CASE(F_OB, true, true)                   // bias (+ReLU) -> bf16: spatial_head, box_head
+  SKG_GEMM_CASE(F_OF, true, false)                  // -> fp32: per-node projections
+  SKG_GEMM_CASE(F_OB | F_OF, true, false)           // fc_head / fc_tail
+  SKG_GEMM_CASE(F_P | F_Q | F_RAW | F_OB, false, true)   // fused fc_2 of the MBFs (Hadamard with gathered tables)
+  SKG_GEMM_CASE(F_DOT, false, true)                 // attention weights -> adjacency row-dot
+  SKG_GEMM_CASE(F_RES | F_OF, true, false)          // message fc_3 + residual, split-bf16 predictor second pass
+  SKG_GEMM_CASE(F_OB | F_LO, false, true)           // final pair features with rounding residual
+  SKG_GEMM_CASE(F_MASK | F_OB, false, true)         // training: dX = (G W) gated by the ReLU mask of the layer's input
+  SKG_GEMM_CASE(F_RES | F_MASK | F_OB, false, true) // training: dX + the residual path's gradient, gated
+  SKG_GEMM_CASE(F_DOT | F_OB, false, true)          // training forward: adjacency row-dot that also keeps the weights
+  SKG_GEMM_CASE(F_ALL, true, true)
 #undef SKG_GEMM_CASE
   set_error("no epilogue variant");
   return SKG_ERR_UNSUPPORTED;
