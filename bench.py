@@ -510,10 +510,13 @@ def measure_varying_geometry(torch, dist, args, ih, dev, rank, world):
         shapes = draw()
         boxes, labels, scores = synthetic.make_detections(shapes, img_shapes, g)
         tot = sum(n for _, n in shapes)
+        n_per = [n for _, n in shapes]
+        # detections as per-image views of three packed device tensors (what preprocess_detections_device hands out)
         batches.append(dict(shapes=shapes, pairs=sum(h * (n - 1) for h, n in shapes), cells=sum(h * n for h, n in shapes),
                             f3={"3": torch.randn(n_img, 256, 25, 38, device=dev, generator=gd)},
                             bf=torch.randn(tot, 256, 7, 7, device=dev, generator=gd),
-                            boxes=[b.to(dev) for b in boxes], labels=[l.to(dev) for l in labels], scores=[x.to(dev) for x in scores],
+                            boxes=list(torch.cat(boxes).to(dev).split(n_per)), labels=list(torch.cat(labels).to(dev).split(n_per)),
+                            scores=list(torch.cat(scores).to(dev).split(n_per)),
                             meta=engine._host_meta(labels, scores, 49)))
 
     def step(bt):
