@@ -695,7 +695,9 @@ def measure_training(torch, dist, args, dev, rank, world, flush):
     from skghoi_b200 import shard, synthetic
     from skghoi_b200.head import build_interaction_head
     otv = synthetic.hico_object_to_verb()
-    ih = build_interaction_head(otv, seed=42, distributed=world > 1)
+    # (diagnostic knobs, tools/ only: SKG_BENCH_NO_NP_AR drops the rank average of the loss normalisers,
+    #  SKG_BENCH_NO_GRAD_AR the gradient all-reduce -- to attribute the N > 1 step time)
+    ih = build_interaction_head(otv, seed=42, distributed=world > 1 and not os.environ.get("SKG_BENCH_NO_NP_AR"))
     ih.box_pair_head.transh_head.set_tables(*synthetic.make_transh_tables(42))
     ih = ih.to(dev).train()
     ih.box_pair_head.transh_head.transh.to(dev)
@@ -716,7 +718,7 @@ def measure_training(torch, dist, args, dev, rank, world, flush):
     buckets = shard.GradBuckets(params).attach(flatten_params=True, module=ih)
     opt = torch.optim.SGD(buckets.flat_params, lr=1e-4, momentum=0.9, fused=True)
 
-    if world > 1:
+    if world > 1 and not os.environ.get("SKG_BENCH_NO_GRAD_AR"):
         # the packed gradient groups are all-reduced INSIDE loss.backward(), each behind its stage event of
         # skg_head_backward_staged, while the rest of the backward runs (train._GradAllReduce)
         from skghoi_b200 import train as _train
