@@ -20,7 +20,7 @@ namespace skg {
 
 // library-owned side streams + an event pool for fork / join (per host thread and device)
 struct SideStream {
-  static constexpr int kStreams = 4, kEvents = 18;   // s[3] stands in for the legacy default stream (cannot be captured)
+  static constexpr int kStreams = 4, kEvents = 24;   // s[3] stands in for the legacy default stream (cannot be captured)
   int dev = -1;
   cudaStream_t s[kStreams] = {};
   cudaEvent_t ev[kEvents] = {};
@@ -257,14 +257,17 @@ static int enqueue_forward(const skg_head_weights* wp, const skg_head_batch* bp,
   // ================= fork: node-row chain on sa, global-feature chain on sb
   SKG_TRY(stream_dep(side, st, sa));
   SKG_TRY(stream_dep(side, st, sb));
-  MARK("start", sa); MARK("start", sb);
-  // ---- sa: box head (head.py:635-641, 812); its second layer writes straight into the fc input rows
-  SKG_TRY(skg_node_prep(w.ent, w.ent_dim, w.ent_tot, b.box_off, b.n_h, b.hum_off, B, NB, H(B_OIN), w.fc_k, E, I32(B_BOX2HUM), sa));
-  MARK("node_prep", sa);
+  SKG_TRY(stream_dep(side, st, sc));
+  MARK("start", sa); MARK("start", sb); MARK("start", sc);
+  // ---- sc: the two small preparations of the fc_head | fc_tail GEMM run beside the box head instead of in front of it
+  //      (they were ~15 us at the head of the step's critical path)
+  SKG_TRY(skg_node_prep(w.ent, w.ent_dim, w.ent_tot, b.box_off, b.n_h, b.hum_off, B, NB, H(B_OIN), w.fc_k, E, I32(B_BOX2HUM), sc));
+  MARK("node_prep", sc);
   if (w.Wfh_ent) {   // constant human-side entity term of fc_head, re-folded from the table's CURRENT contents
-    SKG_TRY(skg_fc_bias_fold(w.bfh, w.Wfh_ent, w.ent, w.ent_dim, w.human_idx, R, const_cast<float*>(w.bfc), sa));
-    MARK("fc_bias_fold", sa);
+    SKG_TRY(skg_fc_bias_fold(w.bfh, w.Wfh_ent, w.ent, w.ent_dim, w.human_idx, R, const_cast<float*>(w.bfc), sc));
+    MARK("fc_bias_fold", sc);
   }
+  // ---- sa: box head (head.py:635-641, 812); its second layer writes straight into the fc input rows
   const void* xb = b.box_features_bf16;            // pooled features already in operand layout (native RoIAlign)
   if (!xb) {
     if (cap) SKG_TRY(cast_pad_bf16_indirect(slots + 1, w.pool_k, b.box_off + B, NB, w.pool_k, H(B_XB), w.K0, w.K0, sa));
@@ -280,6 +283,7 @@ static int enqueue_forward(const skg_head_weights* wp, const skg_head_batch* bp,
   MARK("gemm box_head.3", sa);
   // ---- sa: fc_head and fc_tail as ONE GEMM over all boxes with stacked weights (head.py:875-885): only n_h (resp. n)
   //      rows of the reference's [N2, 1074] inputs are distinct; human rows are compacted through box2hum
+  SKG_TRY(stream_dep(side, sc, sa));   // entity columns, box -> human map and the folded bias are in place
   {
     skg_epilogue_group gg[2];
     gg[0] = group0(); gg[0].flags = SKG_EPI_RELU; gg[0].bias = w.bfc; gg[0].out_f32 = F(B_HN32); gg[0].ld_of = R;
