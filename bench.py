@@ -682,6 +682,18 @@ def measure_kg(torch, dist, dev, rank, world):
         smp.sample()
     e1.record(); torch.cuda.synchronize(dev)
     us = e0.elapsed_time(e1) / 20 * 1e3
+    # ... and as ONE persistent cooperative kernel (Trainer(fused=True), csrc/kgtrain.cu): 500 steps per launch
+    trf = Trainer(strat, loader, train_times=500, alpha=0.5, optimizer=tr.optimizer, fused=True, distributed=False)
+    trf.run(); torch.cuda.synchronize(dev)
+    e0.record(); hist_f = trf.run(); e1.record(); torch.cuda.synchronize(dev)
+    ms_f = e0.elapsed_time(e1) / 500
+    out["fused_kernel"] = {"ms_per_step": ms_f, "value": trip / (ms_f * 1e-3), "unit": "triples/s", "steps": 500,
+                           "loss_last": float(hist_f[-1]),
+                           "roofline": {"bound": "latency (4 grid-wide barriers per step; tables and gradients in shared memory)",
+                                        "bytes_per_triple": bytes_per_triple, "achieved": trip * bytes_per_triple / (ms_f * 1e-3) / 1e9,
+                                        "unit": "GB/s"},
+                           "note": "skg_kg_train_steps: sampler + TransH forward + margin loss + backward + SGD for every step "
+                                   "inside one launch; same batches as the eager loop, updates equal up to fp32 atomic order"}
     out["graph_replay"] = {"ms_per_step": ms_g, "value": trip / (ms_g * 1e-3), "steps": 500, "loss_last": float(hist_g[-1]),
                            "note": "Trainer(graph=True): two steps per CUDA graph, wall clock incl. warm-up steps and capture"}
     out["sampler_alone"] = {"batch": bs, "neg_rate": 25, "us_per_call": us, "triples_per_s": bs * 26 / (us * 1e-6)}

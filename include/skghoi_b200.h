@@ -640,6 +640,29 @@ int skg_kg_sample(const int64_t* head_hrt, const int64_t* tail_hrt, const int64_
                   int64_t batch_size, int neg_rate, int mode, int64_t* batch_h, int64_t* batch_t, int64_t* batch_r,
                   float* batch_y, cudaStream_t stream);
 
+/* TransH knowledge-graph training as ONE persistent cooperative kernel (csrc/kgtrain.cu): `num_steps` optimiser steps of
+ * the reference loop OpenKE/openke/config/Trainer.py:43-99 -- negative sampling (the sampler above: same per-worker LCG
+ * streams, same batches), TransH scores (heads/TransH/TransH.py:56-106), MarginLoss without the adversarial weighting
+ * (heads/MarginLoss.py:28-36), NegativeSampling strategy with regul_rate = 0, backward, plain SGD -- per launch, the phases of
+ * a step separated by grid-wide barriers; the three tables and their gradients live in shared memory (graphs whose tables
+ * exceed 100 KB take the eager Trainer).  seeds: [2, work_threads], the seeds of the first step in row 0; after the call the
+ * current seeds sit in row num_steps & 1.  ent / rel / nrm are updated in place; loss_out[s] = the loss of step s. */
+typedef struct skg_kg_train_args {
+  const int64_t* head_hrt; const int64_t* tail_hrt;       /* [3, T] rows h | r | t in head order / tail order (skg_kg_sample) */
+  const int64_t* lef_head; const int64_t* rig_head; const int64_t* lef_tail; const int64_t* rig_tail;   /* [E] */
+  const float* left_mean; const float* right_mean;         /* [R] bern statistics, or both NULL */
+  int64_t train_total, ent_total, rel_total;
+  uint64_t* seeds;
+  int32_t work_threads; int32_t neg_rate; int32_t mode; int32_t dim; int32_t p_norm; int32_t norm_flag; int32_t num_steps; int32_t pad_;
+  int64_t batch_size;
+  float* ent; float* rel; float* nrm;                       /* [E, dim], [R, dim], [R, dim] fp32 */
+  float margin, lr;
+  float* loss_out;                                          /* [num_steps] */
+  void* scratch; int64_t scratch_bytes;                     /* >= skg_kg_train_scratch_bytes, 256-byte aligned */
+} skg_kg_train_args;
+int64_t skg_kg_train_scratch_bytes(int64_t batch_size, int neg_rate, int64_t ent_total, int64_t rel_total, int dim);
+int skg_kg_train_steps(const skg_kg_train_args* args, cudaStream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

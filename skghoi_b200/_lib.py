@@ -284,6 +284,18 @@ _SIGNATURES["skg_preprocess_detections"] = (I, [P, P, P, P, I, I, F, F, I, I, I,
 
 _SIGNATURES["skg_kg_sample"] = (I, [P, P, P, P, P, P, P, P, L, L, P, P, I, L, I, I, P, P, P, P, P])
 
+class KgTrainArgs(ctypes.Structure):
+    """Mirror of ``skg_kg_train_args``."""
+    _fields_ = [(k, c_void_p) for k in ("head_hrt", "tail_hrt", "lef_head", "rig_head", "lef_tail", "rig_tail", "left_mean", "right_mean")] + \
+               [("train_total", c_int64), ("ent_total", c_int64), ("rel_total", c_int64), ("seeds", c_void_p)] + \
+               [(k, ctypes.c_int32) for k in ("work_threads", "neg_rate", "mode", "dim", "p_norm", "norm_flag", "num_steps", "pad_")] + \
+               [("batch_size", c_int64), ("ent", c_void_p), ("rel", c_void_p), ("nrm", c_void_p), ("margin", c_float), ("lr", c_float),
+                ("loss_out", c_void_p), ("scratch", c_void_p), ("scratch_bytes", c_int64)]
+
+
+_SIGNATURES["skg_kg_train_scratch_bytes"] = (c_int64, [L, I, L, L, I])
+_SIGNATURES["skg_kg_train_steps"] = (I, [ctypes.POINTER(KgTrainArgs), P])
+
 # ---- training step (csrc/trainops.cu, csrc/backward.cu); struct pointers travel as void* (ctypes.byref) -------------
 _SIGNATURES["skg_block_copy"] = (I, [P, P, I, P])
 _SIGNATURES["skg_head_backward"] = (I, [P, P, P, P, P, I, P, L, P])

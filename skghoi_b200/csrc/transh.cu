@@ -16,47 +16,6 @@ namespace skg {
 constexpr int kTranshThreads = 256;
 constexpr int kTranshWarps = kTranshThreads / 32;
 
-struct TranshTriple {   // per-lane slice of one triple's intermediate state
-  float inv_w, a_h, a_t, inv_h, inv_t, inv_r, nrm_s;
-};
-
-// Forward math for one triple held EPL-elements-per-lane.  Returns the score (all lanes).
-template <int EPL>
-__device__ __forceinline__ float transh_triple_fwd(const float (&h)[EPL], const float (&t)[EPL], const float (&r)[EPL],
-                                                   const float (&w)[EPL], int p_norm, int norm_flag, float (&s)[EPL],
-                                                   TranshTriple& st) {
-  float ww = 0.f, hw = 0.f, tw = 0.f, rr = 0.f;
-#pragma unroll
-  for (int e = 0; e < EPL; ++e) { ww += w[e] * w[e]; hw += h[e] * w[e]; tw += t[e] * w[e]; rr += r[e] * r[e]; }
-  ww = warp_sum(ww); hw = warp_sum(hw); tw = warp_sum(tw); rr = warp_sum(rr);
-  const float inv_w = 1.f / fmaxf(sqrtf(ww), 1e-12f);      // F.normalize(norm, 2, -1)  TransH.py:76
-  const float a_h = hw * inv_w, a_t = tw * inv_w;            // sum(e * w_hat)           TransH.py:85
-  float hp[EPL], tp[EPL];
-  float hh = 0.f, tt = 0.f;
-#pragma unroll
-  for (int e = 0; e < EPL; ++e) {
-    const float wn = w[e] * inv_w;
-    hp[e] = h[e] - a_h * wn; tp[e] = t[e] - a_t * wn;
-    hh += hp[e] * hp[e]; tt += tp[e] * tp[e];
-  }
-  float inv_h = 1.f, inv_t = 1.f, inv_r = 1.f;
-  if (norm_flag) {                                           // TransH.py:57-60
-    hh = warp_sum(hh); tt = warp_sum(tt);
-    inv_h = 1.f / fmaxf(sqrtf(hh), 1e-12f); inv_t = 1.f / fmaxf(sqrtf(tt), 1e-12f);
-    inv_r = 1.f / fmaxf(sqrtf(rr), 1e-12f);
-  }
-  float acc = 0.f;
-#pragma unroll
-  for (int e = 0; e < EPL; ++e) {
-    s[e] = (hp[e] * inv_h + r[e] * inv_r) - tp[e] * inv_t;   // (h + r) - t   TransH.py:68
-    acc += (p_norm == 1) ? fabsf(s[e]) : s[e] * s[e];
-  }
-  acc = warp_sum(acc);
-  const float score = (p_norm == 1) ? acc : sqrtf(acc);      // torch.norm(score, p, -1)  TransH.py:70
-  st.inv_w = inv_w; st.a_h = a_h; st.a_t = a_t; st.inv_h = inv_h; st.inv_t = inv_t; st.inv_r = inv_r; st.nrm_s = score;
-  return score;
-}
-
 // d(tables) += d(score) * d score / d tables.  Gradients accumulate into fp32 tables with atomics;
 // when the tables fit they are privatised per CTA in shared memory and flushed once.
 template <int EPL, bool SMEM_TABLES>
@@ -90,56 +49,16 @@ __global__ void __launch_bounds__(kTranshThreads) transh_backward_kernel(
     }
     TranshTriple st;
     transh_triple_fwd<EPL>(h, tl, r, w, p_norm, norm_flag, s, st);
-    // g_s = g * d||s||_p / ds   (zero sub-gradient at s == 0, as torch.norm)
-    float gs[EPL];
-#pragma unroll
-    for (int e = 0; e < EPL; ++e) {
-      if (p_norm == 1) gs[e] = g * ((s[e] > 0.f) - (s[e] < 0.f));
-      else gs[e] = st.nrm_s > 0.f ? g * s[e] / st.nrm_s : 0.f;
-    }
-    // unit vectors u = hp*inv_h, q = r*inv_r, v = tp*inv_t ;  s = u + q - v
-    float wn[EPL], hp[EPL], tp[EPL];
-    float ugs = 0.f, vgs = 0.f, qgs = 0.f;
-#pragma unroll
-    for (int e = 0; e < EPL; ++e) {
-      wn[e] = w[e] * st.inv_w;
-      hp[e] = h[e] - st.a_h * wn[e]; tp[e] = tl[e] - st.a_t * wn[e];
-      ugs += hp[e] * st.inv_h * gs[e]; vgs += tp[e] * st.inv_t * gs[e]; qgs += r[e] * st.inv_r * gs[e];
-    }
-    float g_hp[EPL], g_tp[EPL], g_r[EPL];
-    if (norm_flag) {
-      ugs = warp_sum(ugs); vgs = warp_sum(vgs); qgs = warp_sum(qgs);
-#pragma unroll
-      for (int e = 0; e < EPL; ++e) {
-        g_hp[e] = (gs[e] - hp[e] * st.inv_h * ugs) * st.inv_h;
-        g_tp[e] = -(gs[e] - tp[e] * st.inv_t * vgs) * st.inv_t;
-        g_r[e] = (gs[e] - r[e] * st.inv_r * qgs) * st.inv_r;
-      }
-    } else {
-#pragma unroll
-      for (int e = 0; e < EPL; ++e) { g_hp[e] = gs[e]; g_tp[e] = -gs[e]; g_r[e] = gs[e]; }
-    }
-    // hp = h - (h.wn) wn  ->  g_h = g_hp - (g_hp.wn) wn ;  g_wn += -(a_h g_hp + (g_hp.wn) h)   (same for t)
-    float bh = 0.f, bt = 0.f;
-#pragma unroll
-    for (int e = 0; e < EPL; ++e) { bh += g_hp[e] * wn[e]; bt += g_tp[e] * wn[e]; }
-    bh = warp_sum(bh); bt = warp_sum(bt);
-    float g_wn[EPL];
-    float wg = 0.f;
-#pragma unroll
-    for (int e = 0; e < EPL; ++e) {
-      g_wn[e] = -(st.a_h * g_hp[e] + bh * h[e]) - (st.a_t * g_tp[e] + bt * tl[e]);
-      wg += wn[e] * g_wn[e];
-    }
-    wg = warp_sum(wg);
+    float g_h[EPL], g_t[EPL], g_r[EPL], g_w[EPL];
+    transh_triple_bwd<EPL>(h, tl, r, w, s, st, g, p_norm, norm_flag, g_h, g_t, g_r, g_w);
 #pragma unroll
     for (int e = 0; e < EPL; ++e) {
       const int d = lane + 32 * e;
       if (d < dim) {
-        atomicAdd(gE + hi * dim + d, g_hp[e] - bh * wn[e]);
-        atomicAdd(gE + ti * dim + d, g_tp[e] - bt * wn[e]);
+        atomicAdd(gE + hi * dim + d, g_h[e]);
+        atomicAdd(gE + ti * dim + d, g_t[e]);
         atomicAdd(gR + ri * dim + d, g_r[e]);
-        atomicAdd(gW + ri * dim + d, (g_wn[e] - wn[e] * wg) * st.inv_w);   // w_hat = w / ||w||
+        atomicAdd(gW + ri * dim + d, g_w[e]);
       }
     }
   }

@@ -76,9 +76,10 @@ class Trainer:
 
     def __init__(self, model: nn.Module, data_loader, train_times: int = 1000, alpha: float = 0.5, opt_method: str = "sgd",
                  weight_decay: float = 0.0, lr_decay: float = 0.0, optimizer=None, graph: bool = False,
-                 distributed: Optional[bool] = None, group=None):
+                 distributed: Optional[bool] = None, group=None, fused: bool = False):
         self.model, self.data_loader, self.train_times = model, data_loader, int(train_times)
         self.graph = bool(graph)      # replay whole epochs as one CUDA graph (sampler + forward + loss + backward + update)
+        self.fused = bool(fused)      # the whole run as ONE persistent cooperative kernel (skg_kg_train_steps, csrc/kgtrain.cu)
         self.alpha, self.opt_method, self.weight_decay, self.lr_decay, self.optimizer = alpha, opt_method, weight_decay, lr_decay, optimizer
         self.group = group
         if distributed is None:
@@ -157,6 +158,12 @@ class Trainer:
                                                   capturable=bool(self.graph and on_gpu))
             else:
                 self.optimizer = torch.optim.SGD(p, lr=self.alpha, weight_decay=self.weight_decay)
+        if self.fused:
+            why = self._fused_blocker()
+            if why is None:
+                return self._run_fused()
+            import warnings
+            warnings.warn("Trainer(fused=True): %s -- running the eager loop instead" % why)
         if self.distributed and self._buckets is None:
             self._setup_shards()
         if self.graph and next(self.model.parameters()).is_cuda:
@@ -168,6 +175,68 @@ class Trainer:
             else:
                 return self._run_graphed()
         return [float(self._epoch()) for _ in range(self.train_times)]
+
+    # ---- the fused trainer ------------------------------------------------------------------------------------------
+    def _fused_blocker(self) -> Optional[str]:
+        """None when the run is the configuration skg_kg_train_steps implements, else the reason it is not."""
+        st, o = self.model, self.optimizer
+        if self.distributed:
+            return "the fused kernel is single-GPU"
+        if not isinstance(st, NegativeSamplingStrategy) or not isinstance(st.model, TransH) or not isinstance(self.data_loader, TrainDataLoader):
+            return "it needs NegativeSamplingStrategy(TransH) over a TrainDataLoader"
+        if not isinstance(st.loss, MarginLoss) or st.loss.adv_flag or st.regul_rate != 0 or st.model.margin_flag:
+            return "it implements the plain MarginLoss without regulariser"
+        if not isinstance(o, torch.optim.SGD) or any(g["momentum"] or g["weight_decay"] or g["nesterov"] or g["dampening"] or g.get("maximize")
+                                                      for g in o.param_groups):
+            return "it implements plain SGD"
+        m = st.model
+        tabs = (m.ent_embeddings.weight, m.rel_embeddings.weight, m.norm_vector.weight)
+        if not all(t.is_cuda and t.dtype == torch.float32 and t.is_contiguous() for t in tabs):
+            return "the tables must be contiguous fp32 CUDA tensors"
+        if sum(t.numel() for t in tabs) * 8 > 200 * 1024:
+            return "the tables and their gradients must fit in 200 KB of shared memory"
+        if int(st.batch_size) != int(self.data_loader.get_batch_size()):
+            return "the strategy's batch_size must be the loader's"
+        return None
+
+    def _run_fused(self) -> List[float]:
+        """``train_times`` epochs of ``nbatches`` steps as one launch of the persistent cooperative kernel: the same batches
+        (the sampler's LCG streams continue where they were and are handed back where they end), the same updates up to the
+        fp32 summation order of the gradient atomics."""
+        import ctypes
+        from . import _lib
+        st, smp = self.model, self.data_loader.sampler
+        m, ix = st.model, smp.index
+        dev = ix.device
+        steps = self.train_times * len(self.data_loader)
+        if steps == 0:
+            return []
+        a = _lib.KgTrainArgs()
+        p = lambda t: t.data_ptr() if t is not None else None                        # noqa: E731
+        a.head_hrt, a.tail_hrt = p(ix.head), p(ix.tail)
+        a.lef_head, a.rig_head, a.lef_tail, a.rig_tail = p(ix.lef_head), p(ix.rig_head), p(ix.lef_tail), p(ix.rig_tail)
+        a.left_mean, a.right_mean = (p(ix.left_mean), p(ix.right_mean)) if smp.bern else (None, None)
+        a.train_total, a.ent_total, a.rel_total = ix.train_total, ix.ent_total, ix.rel_total
+        seeds = torch.stack([smp._seeds[0], smp._seeds[1]]).contiguous()
+        a.seeds = seeds.data_ptr()
+        a.work_threads, a.neg_rate, a.mode = smp.W, smp.neg_rate, smp.mode
+        a.dim, a.p_norm, a.norm_flag, a.num_steps = m.dim, int(m.p_norm), int(bool(m.norm_flag)), steps
+        a.batch_size = smp.batch_size
+        ent, rel, nrm = m.ent_embeddings.weight.data, m.rel_embeddings.weight.data, m.norm_vector.weight.data
+        a.ent, a.rel, a.nrm = ent.data_ptr(), rel.data_ptr(), nrm.data_ptr()
+        a.margin, a.lr = float(st.loss.margin), float(self.optimizer.param_groups[0]["lr"])
+        loss = torch.empty(steps, dtype=torch.float32, device=dev)
+        nbytes = int(_lib.lib().skg_kg_train_scratch_bytes(smp.batch_size, smp.neg_rate, ix.ent_total, ix.rel_total, m.dim))
+        scratch = torch.empty(nbytes + 256, dtype=torch.uint8, device=dev)
+        off = (-scratch.data_ptr()) % 256
+        a.loss_out, a.scratch, a.scratch_bytes = loss.data_ptr(), scratch.data_ptr() + off, nbytes
+        with torch.cuda.device(dev):
+            _lib.call("skg_kg_train_steps", ctypes.byref(a), _lib.stream_ptr(dev))
+        smp._seeds[0].copy_(seeds[steps & 1])
+        for t in (m.ent_embeddings.weight, m.rel_embeddings.weight, m.norm_vector.weight):
+            t.data.add_(0)                                       # bump the version counters: the tables changed in place
+        per_epoch = loss.view(self.train_times, len(self.data_loader)).sum(1)
+        return [float(v) for v in per_epoch.cpu().tolist()]
 
     def _epoch(self) -> torch.Tensor:
         res = torch.zeros((), device=next(self.model.parameters()).device)
