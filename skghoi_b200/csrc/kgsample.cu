@@ -7,7 +7,7 @@
 // The reference cuts a batch into `workThreads` contiguous slices, one pthread each, every thread drawing from its own
 // linear congruential stream.  A batch item consumes a FIXED number of draws (1 to pick the positive, 2 per negative in
 // mode 0: the head/tail coin and the corrupted entity; 1 per negative in modes -1 / +1), so item j of thread `id` starts
-// at stream position (j - lef) * draws: one GPU thread per batch item jumps there in O(log) steps (an LCG composes as
+// at stream position (j - lef) * draws: one GPU thread per batch TRIPLE jumps to its item (and on to its negative) in O(log) steps (an LCG composes as
 // x -> a^k x + c (a^k - 1)/(a - 1)) and reproduces the reference's output BIT FOR BIT for any thread count, while the
 // per-thread seeds are advanced by the whole slice so that consecutive calls continue the same streams.
 #include "common.cuh"
@@ -81,40 +81,46 @@ __global__ void __launch_bounds__(128) kg_sample_kernel(KgIndex ix, const unsign
                                                         int64_t batch_size, int neg_rate, int mode,
                                                         int64_t* __restrict__ batch_h, int64_t* __restrict__ batch_t,
                                                         int64_t* __restrict__ batch_r, float* __restrict__ batch_y) {
-  const int64_t b = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  // One thread per TRIPLE of the batch: item b = j % batch_size, k = j / batch_size (0 = the positive, k >= 1 = negative
+  // k - 1).  A negative needs exactly `dpn` draws (the head/tail coin in mode 0 + the corrupted entity), so it jumps straight
+  // to its own position of the worker's stream and re-derives the positive with one extra draw: the neg_rate corruptions of
+  // an item (three dependent binary searches each) run in parallel instead of back to back in one thread.
+  const int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   const int64_t per = (batch_size % work_threads == 0) ? batch_size / work_threads : batch_size / work_threads + 1;
-  const unsigned long long draws = 1ull + (unsigned long long)neg_rate * (mode == 0 ? 2ull : 1ull);
-  if (b < work_threads) {                       // the seeds after the call: every worker advanced by its whole slice
-    int64_t lef = b * per, rig = (b + 1) * per;
+  const unsigned long long dpn = (mode == 0) ? 2ull : 1ull;
+  const unsigned long long draws = 1ull + (unsigned long long)neg_rate * dpn;
+  if (j < work_threads) {                       // the seeds after the call: every worker advanced by its whole slice
+    int64_t lef = j * per, rig = (j + 1) * per;
     if (rig > batch_size) rig = batch_size;
     const int64_t items = rig > lef ? rig - lef : 0;
-    seeds_out[b] = lcg_jump(seeds_in[b], (unsigned long long)items * draws);
+    seeds_out[j] = lcg_jump(seeds_in[j], (unsigned long long)items * draws);
   }
-  if (b >= batch_size) return;
+  if (j >= batch_size * (1 + (int64_t)neg_rate)) return;
+  const int64_t k = j / batch_size, b = j - k * batch_size;
   const int64_t id = b / per, lef0 = id * per;
   Lcg g{lcg_jump(seeds_in[id], (unsigned long long)(b - lef0) * draws)};
   const int64_t T = ix.T;
   const int64_t i = g.below(T);
   const int64_t h = ix.head[i], r = ix.head[T + i], t = ix.head[2 * T + i];
-  batch_h[b] = h; batch_t[b] = t; batch_r[b] = r; batch_y[b] = 1.f;
-  int64_t last = batch_size;
-  for (int times = 0; times < neg_rate; ++times) {
-    int64_t nh = h, nt = t;
-    bool corrupt_tail_entity;                   // true: keep the head, draw a new tail (corrupt_head in the reference's naming)
-    if (mode == 0) {
-      float prob = 500.f;
-      if (ix.left_mean) prob = __fdiv_rn(__fmul_rn(1000.f, ix.right_mean[r]), __fadd_rn(ix.right_mean[r], ix.left_mean[r]));
-      corrupt_tail_entity = (float)(g.next() % 1000ull) < prob;
-    } else {
-      corrupt_tail_entity = (mode != -1);
-    }
-    if (corrupt_tail_entity)
-      nt = corrupt(ix.head + T, ix.head + 2 * T, ix.lef_head, ix.rig_head, h, r, ix.E, t, g);
-    else
-      nh = corrupt(ix.tail + T, ix.tail, ix.lef_tail, ix.rig_tail, t, r, ix.E, h, g);
-    batch_h[b + last] = nh; batch_t[b + last] = nt; batch_r[b + last] = r; batch_y[b + last] = -1.f;
-    last += batch_size;
+  if (k == 0) {
+    batch_h[b] = h; batch_t[b] = t; batch_r[b] = r; batch_y[b] = 1.f;
+    return;
   }
+  g.s = lcg_jump(g.s, (unsigned long long)(k - 1) * dpn);
+  int64_t nh = h, nt = t;
+  bool corrupt_tail_entity;                   // true: keep the head, draw a new tail (corrupt_head in the reference's naming)
+  if (mode == 0) {
+    float prob = 500.f;
+    if (ix.left_mean) prob = __fdiv_rn(__fmul_rn(1000.f, ix.right_mean[r]), __fadd_rn(ix.right_mean[r], ix.left_mean[r]));
+    corrupt_tail_entity = (float)(g.next() % 1000ull) < prob;
+  } else {
+    corrupt_tail_entity = (mode != -1);
+  }
+  if (corrupt_tail_entity)
+    nt = corrupt(ix.head + T, ix.head + 2 * T, ix.lef_head, ix.rig_head, h, r, ix.E, t, g);
+  else
+    nh = corrupt(ix.tail + T, ix.tail, ix.lef_tail, ix.rig_tail, t, r, ix.E, h, g);
+  batch_h[j] = nh; batch_t[j] = nt; batch_r[j] = r; batch_y[j] = -1.f;
 }
 
 }  // namespace skg
@@ -134,7 +140,8 @@ extern "C" int skg_kg_sample(const int64_t* head_hrt, const int64_t* tail_hrt, c
   SKG_REQUIRE((left_mean == nullptr) == (right_mean == nullptr), "left_mean and right_mean come together (bern) or not at all");
   SKG_REQUIRE(seeds_in != seeds_out, "seeds_out must not alias seeds_in (every item reads the seeds of the call's start)");
   KgIndex ix{head_hrt, tail_hrt, lef_head, rig_head, lef_tail, rig_tail, left_mean, right_mean, train_total, ent_total};
-  const int64_t threads = batch_size > work_threads ? batch_size : work_threads;
+  const int64_t triples = batch_size * (1 + (int64_t)neg_rate);
+  const int64_t threads = triples > work_threads ? triples : work_threads;
   kg_sample_kernel<<<(int)ceil_div64(threads, 128), 128, 0, stream>>>(ix, (const unsigned long long*)seeds_in,
                                                                     (unsigned long long*)seeds_out, work_threads, batch_size,
                                                                     neg_rate, mode, batch_h, batch_t, batch_r, batch_y);
