@@ -100,3 +100,55 @@ def test_capacity_matches_exact_geometry_path():
         assert torch.equal(outs[True][k], outs[False][k]), k
     d = float((outs[True]["logits"] - outs[False]["logits"]).abs().max())
     assert d <= 1e-3 * float(outs[False]["logits"].abs().max()), d
+
+
+def test_session_error_behaviour_matches_reference():
+    """The serving session keeps the reference's errors: IndexError for an image with more boxes than the entity table has
+    rows (head.py:572), ValueError when humans are not first (head.py:840-841) -- also when the caller hands in its own
+    host meta, i.e. when the check runs inside skg_session_prepare."""
+    import numpy as np
+    from skghoi_b200 import engine
+    ih = _head()
+    batch = synthetic.make_batch([(3, 81)], seed=5)
+    args = ({"3": batch["features"]["3"].to(DEV)}, batch["image_shapes"], batch["box_features"].to(DEV),
+            [b.to(DEV) for b in batch["box_coords"]], [l.to(DEV) for l in batch["box_labels"]], [s.to(DEV) for s in batch["box_scores"]])
+    with torch.no_grad(), pytest.raises(IndexError):
+        ih.forward_from_pooled(*args)
+    batch = synthetic.make_batch([(3, 7)], seed=6)
+    labels = batch["box_labels"][0].clone()
+    labels[[0, 5]] = labels[[5, 0]]                           # a human behind an object
+    args = ({"3": batch["features"]["3"].to(DEV)}, batch["image_shapes"], batch["box_features"].to(DEV),
+            [b.to(DEV) for b in batch["box_coords"]], [labels.to(DEV)], [s.to(DEV) for s in batch["box_scores"]])
+    with torch.no_grad(), pytest.raises(ValueError, match="not permuted"):
+        ih.forward_from_pooled(*args)
+    meta = dict(n=[7], n_h=[3], labels=labels.numpy().astype(np.int64), scores=batch["box_scores"][0].numpy().astype(np.float32))
+    with torch.no_grad(), pytest.raises(ValueError, match="not permuted"):
+        ih.forward_from_pooled(*args, meta=meta)
+
+
+def test_session_skipped_and_empty_images_match_exact_path():
+    """Images the reference skips (no human, or a single box: head.py:829-839) and an all-empty batch through the session
+    path against the per-kernel orchestration (documented divergence from the reference: a skipped image yields an empty
+    result instead of misaligned rows, DESIGN 2 defect 6)."""
+    from skghoi_b200 import engine
+    ih = _head()
+    batch = synthetic.make_batch([(0, 3), (4, 9), (1, 1), (2, 6)], seed=31)
+    args = ({"3": batch["features"]["3"].to(DEV)}, batch["image_shapes"], batch["box_features"].to(DEV),
+            [b.to(DEV) for b in batch["box_coords"]], [l.to(DEV) for l in batch["box_labels"]], [s.to(DEV) for s in batch["box_scores"]])
+    outs = {}
+    for mode in (True, False):
+        engine.SESSION_PATH = mode
+        try:
+            with torch.no_grad():
+                res = ih.forward_from_pooled(*args)
+            torch.cuda.synchronize()
+            outs[mode] = [{k: v.clone() for k, v in r.items()} for r in res]
+        finally:
+            engine.SESSION_PATH = True
+    assert len(outs[True]) == len(outs[False]) == 4
+    for a, b in zip(outs[True], outs[False]):
+        for k in ("index", "prediction", "object", "boxes_h", "boxes_o"):
+            assert torch.equal(a[k], b[k]), k
+        if b["scores"].numel():
+            assert float((a["scores"] - b["scores"]).abs().max()) <= 1e-3 * float(b["scores"].abs().max()) + 1e-7
+    assert outs[True][0]["index"].numel() == 0 and outs[True][2]["index"].numel() == 0
