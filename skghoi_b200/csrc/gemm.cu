@@ -739,8 +739,9 @@ static int choose_splits(int M, int N, int K, int block_n, int64_t ws_bytes) {
   // the fp32 reduction through L2 costs ~10 us: it only pays for long-K problems (box_head: K = 12544)
   if (tiles * 2 > num_sms() || tiles > kSplitKCounters || num_k < 64) return 1;
   if (ws_bytes < (int64_t)kSplitKCounters * 4 + (int64_t)tiles * BM * block_n * 4) return 1;
+  static const int min_kb = [] { const char* e = getenv("SKG_SPLITK_MIN_KB"); const int v = e ? atoi(e) : 16; return v > 0 ? v : 16; }();
   int splits = num_sms() / tiles;
-  if (splits > num_k / 16) splits = num_k / 16;   // at least 16 k-blocks (K = 1024) per split
+  if (splits > num_k / min_kb) splits = num_k / min_kb;   // at least 16 k-blocks (K = 1024) per split (knob: experiments)
   return splits < 1 ? 1 : splits;
 }
 

@@ -29,7 +29,7 @@ with torch.no_grad():
 run = ih.__dict__["_skg_last_run"]
 g = engine.dominant_gemm_closure(ih, run)
 p = _lib.ptr
-B = 2048
+B = 16384        # 2^23 cells: the shape of bench.py's spatial roofline leg
 gen = torch.Generator().manual_seed(1)
 bx, _, _ = synthetic.make_detections([(16, 32)], [(800, 1216)], gen)
 boxes = bx[0].repeat(B, 1).to(dev)
