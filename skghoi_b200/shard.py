@@ -50,17 +50,21 @@ def shard_of(items: Sequence, cost: Sequence[int], rank: Optional[int] = None, w
     return [items[i] for i in partition_images(cost, world_size)[rank]]
 
 
-def average_normalisers(n_p: torch.Tensor, group=None) -> torch.Tensor:
+def average_normalisers(n_p: torch.Tensor, group=None, in_place: bool = False) -> torch.Tensor:
     """Rank-mean of the loss normalisers (reference head.py:167-172: all_reduce then divide by the world size).
-    One collective for all of them, no barrier; returns ``n_p`` unchanged when not distributed."""
+    One collective for all of them, no barrier; returns ``n_p`` unchanged when not distributed.  On NCCL the mean is the
+    collective's own reduction (``ReduceOp.AVG``: no clone, no divide launch); ``in_place`` lets the caller give up ``n_p``."""
     if not (dist.is_available() and dist.is_initialized()):
         return n_p
     world = dist.get_world_size(group)
     if world == 1:
         return n_p
-    out = n_p.clone()
+    out = n_p if in_place else n_p.clone()
+    if out.is_cuda and dist.get_backend(group) == "nccl":
+        dist.all_reduce(out, op=dist.ReduceOp.AVG, group=group)
+        return out
     dist.all_reduce(out, group=group)
-    return out / world
+    return out.div_(world) if in_place else out / world
 
 
 def max_over_ranks(values: Sequence[float], device=None, group=None) -> List[float]:
