@@ -159,6 +159,23 @@ int skg_gemm_bf16_wrapk(const void* A, int64_t lda, int a_k_wrap, const void* B,
                         int64_t scratch_bytes, cudaStream_t stream);
 int64_t skg_gemm_splitk_scratch_bytes(int max_tiles_m, int max_n);
 
+/* Allocation-free skg_gemm_bf16_splitk (csrc/noalloc.cu).  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid
+ * it).  Same GEMM, same arguments minus the scratch: the split-K scratch is a file-scope device array inside the library
+ * of SKG_GEMM_STATIC_SCRATCH_BYTES (every GPU that loads the library holds it until exit), and the call makes no
+ * cudaMalloc / cudaFree / allocating library call.
+ *   limit   ceil(M / 128) * 128 x ceil(N / 256) * 256 fp32 + 4096 bytes <= SKG_GEMM_STATIC_SCRATCH_BYTES (M x N up to
+ *           1024 x 1024 after padding; the head's box_head fc6 at up to 1024 boxes); larger shapes fail with
+ *           SKG_ERR_INVALID and a message naming the bytes needed -- nothing is launched
+ *   sharing every call on a device uses the ONE array; the part a call uses is cleared on `stream` in front of its launch
+ *           and left zero behind it.  Calls that overlap on the GPU (two streams, two threads) RACE: serialise them, or use
+ *           skg_gemm_bf16_splitk with one caller-owned region per stream.
+ * block_n = 0 (auto), 128 or 256.  Results equal skg_gemm_bf16_splitk's up to fp32 summation order. */
+#define SKG_GEMM_STATIC_SCRATCH_BYTES (4 * 1024 * 1024 + 4096)
+int skg_gemm_bf16_splitk_static(const void* A, int64_t lda, const void* B, int64_t ldb, int M, int N, int K,
+                                const skg_epilogue_group* groups, int num_groups, int block_n, cudaStream_t stream);
+int64_t skg_gemm_static_scratch_bytes(void);
+
 /* ---- glue kernels between the GEMMs (csrc/headops.cu) ---------------------------------------- */
 
 /* dst[r, 0:cols_pad] = bf16(relu?(src[r, 0:cols] + bias)), zero padded (operand packing for the GEMMs). */

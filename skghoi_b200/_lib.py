@@ -179,6 +179,8 @@ def epilogue_group(n_begin=0, relu=False, bias=None, mul_p=None, row_p=None, mul
 
 _SIGNATURES["skg_gemm_bf16_splitk"] = (I, [P, L, P, L, I, I, I, ctypes.POINTER(EpilogueGroup), I, I, P, L, P])
 _SIGNATURES["skg_gemm_splitk_scratch_bytes"] = (c_int64, [I, I])
+_SIGNATURES["skg_gemm_bf16_splitk_static"] = (I, [P, L, P, L, I, I, I, ctypes.POINTER(EpilogueGroup), I, I, P])
+_SIGNATURES["skg_gemm_static_scratch_bytes"] = (c_int64, [])
 
 
 def gemm_bf16(A, B, groups, M=None, N=None, K=None, block_n=0, scratch=None):
