@@ -53,7 +53,7 @@ def parse_args():
     ap.add_argument("--no-sweep", action="store_true", help="skip the C5 pair-count stress sweep (BASELINE configs[4])")
     ap.add_argument("--no-varying", action="store_true", help="skip the varying-geometry leg (fresh batch geometry every step)")
     ap.add_argument("--train-images", type=int, default=16, help="images per training step per GPU (configs[2]: 16)")
-    ap.add_argument("--train-steps", type=int, default=20)
+    ap.add_argument("--train-steps", type=int, default=40)
     ap.add_argument("--profile-e2e", action="store_true", help="cProfile of the (untimed) e2e loop to stderr, then exit")
     return ap.parse_args()
 
@@ -756,11 +756,16 @@ def measure_training(torch, dist, args, dev, rank, world, flush):
     if world > 1:
         dist.barrier()
     t_ms = shard.max_over_ranks([sum(s_.elapsed_time(e) for s_, e in ev)], device=dev)[0]
+    raw_steps = [s_.elapsed_time(e) for s_, e in ev]
+    per_step = sorted(raw_steps)
+    slow = [(i, round(t, 3)) for i, t in enumerate(raw_steps) if t > 1.15 * per_step[len(per_step) // 2]]
     pairs = n_img * args.humans * (args.boxes - 1)
     return {"workload": "interaction-head training step, batch %d images/GPU x (%d humans, %d boxes), data-parallel "
                         "(BASELINE configs[2])" % (n_img, args.humans, args.boxes),
             "value": pairs * world * args.train_steps / (t_ms * 1e-3), "unit": UNIT, "ms_per_step": t_ms / args.train_steps,
             "steps": args.train_steps, "n_gpus": world, "pairs_per_step_per_gpu": pairs,
+            "ms_per_step_rank0_min_median_max": [per_step[0], per_step[len(per_step) // 2], per_step[-1]],
+            "slow_steps_rank0": slow,
             "negatives": "TransH negatives drawn on the device (uniform without replacement per image, as head.py:939)",
             "step": "zero_grad + skg_head_forward(TRAIN) + post / losses + skg_head_backward (every dX / dW on the tcgen05 GEMM, trainops kernels) + %s + gradient unpack + fused SGD over flat parameter buffers"
                     % ("NCCL all-reduce of the 4 packed gradient groups, each started behind its stage event inside the backward "

@@ -369,6 +369,8 @@ class _GradAllReduce:
         self._views = None
         self._gflat_ptr = 0
         try:
+            if os.environ.get("SKG_DIST_LEGACY_ISSUE"):      # diagnostics: the plain dist.all_reduce issue path (A/B runs)
+                raise RuntimeError("legacy issue path requested")
             self._pg = group if group is not None else dist.distributed_c10d._get_default_group()
         except Exception:                                    # an older / newer torch without the private accessor
             self._pg = None
