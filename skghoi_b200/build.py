@@ -12,7 +12,7 @@ ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
 COMMON = ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC", "-I", os.path.join(ROOT, "include"), "-I", CSRC]
 # per-file extra flags: the elementwise parity kernels must not contract a*b+c into FMAs
 EXTRA = {"spatial.cu": ["-fmad=false"], "postproc.cu": ["-fmad=false"]}
-for _knob in ("SKG_EPI_WARPS", "SKG_PAIR_STAGES", "SKG_PAIR_STAGES_GATHER", "SKG_EPI_L1_PREFETCH"):   # experiment knobs of csrc/gemm.cu
+for _knob in ("SKG_EPI_WARPS", "SKG_PAIR_STAGES", "SKG_PAIR_STAGES_GATHER", "SKG_EPI_L1_PREFETCH", "SKG_EPI_SETMAXNREG"):   # experiment knobs of csrc/gemm.cu
     if os.environ.get(_knob):
         EXTRA.setdefault("gemm.cu", []).append("-D%s=%s" % (_knob, os.environ[_knob]))
 

@@ -39,6 +39,10 @@ constexpr bool kEpiL1Prefetch = SKG_EPI_L1_PREFETCH != 0;
 constexpr int kEpiParts = kEpiWarps / 4;   // column parts of a tile, one epilogue warp each per quadrant
 constexpr int kGemmThreads = 32 * (4 + kEpiWarps);  // warps: 0 TMA, 1 MMA, 2 TMEM alloc, 3 idle, 4..19 epilogue
 // epilogue features (compile-time mask FEAT of gemm_bf16_kernel; bias / ReLU / out_row are always available)
+#ifndef SKG_EPI_SETMAXNREG
+#define SKG_EPI_SETMAXNREG 1
+#endif
+constexpr bool kEpiSetMaxNReg = SKG_EPI_SETMAXNREG != 0;   // 0: every warp keeps the launch's register count (A/B builds)
 enum : uint32_t { F_P = 1, F_Q = 2, F_RAW = 4, F_RES = 8, F_DOT = 16, F_OB = 32, F_OF = 64, F_LO = 128, F_MASK = 256, F_ALL = 511 };
 constexpr int kEpiWarp0 = 4;
 constexpr int kMaxGroups = 4;
@@ -278,6 +282,14 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   const uint32_t tmem_base = *tmem_base_slot;
   asm volatile("griddepcontrol.wait;\n" ::: "memory");   // every predecessor grid has completed, its writes are visible
 
+  // Register reallocation between the warpgroups for the gather epilogues (the launch gives every thread 168): the TMA / MMA
+  // warpgroup runs two one-lane loops and hands registers to the two epilogue warpgroups, whose software-pipelined table
+  // rows spilled at 168 (same-box A/B on the fused fc_2 launch, 4096 x 4096 x 1024: 48.2 -> 46.5 us).  The setmaxnreg sits
+  // INSIDE the two role branches: ptxas budgets each branch by the setmaxnreg that dominates it.  Plain epilogues do not use
+  // it: they gain nothing (37.8 us either way), and with it on every launch the C2 step measured 2-3 % slower.
+  constexpr bool kSetMax = kEpiSetMaxNReg && kEpiWarps == 8 && (FEAT & F_P) != 0;
+  if (warp < kEpiWarp0) {
+  if (kSetMax) asm volatile("setmaxnreg.dec.sync.aligned.u32 40;\n");
   if (warp == 0) {
     // ===================== TMA producer =====================
     if (lane == 0) {
@@ -339,7 +351,9 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         if (++acc == 2) { acc = 0; acc_phase ^= 1; }
       }
     }
-  } else if (warp >= kEpiWarp0) {
+  }
+  } else {
+    if (kSetMax) asm volatile("setmaxnreg.inc.sync.aligned.u32 232;\n");
     // ===================== epilogue =====================
     // TMEM hands every thread one accumulator ROW (lane = row).  Touching global memory in that layout makes
     // each warp-wide access hit 32 different 128-byte lines, which the L1 serialises; so every 32x16 block is
