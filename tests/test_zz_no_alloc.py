@@ -4,7 +4,6 @@ skg_gemm_bf16_splitk (caller-owned scratch) on the same operands, two calls in a
 first left in the shared static array), within the fp32 tolerance of tests/test_gpu_gemm.py::test_gemm_split_k.
 
 Collected last on purpose (test_zz_*)."""
-import ctypes
 
 import pytest
 import torch
@@ -54,7 +53,15 @@ def test_static_scratch_gemm_matches_caller_scratch_gemm(M, N, K, block_n):
         _static(A, B, group, M, N, K, block_n)
         torch.cuda.synchronize()
         if call == 1:                                                   # (the first call may load the module lazily)
-            assert torch.cuda.mem_get_info(0)[0] >= free_before, "the call took device memory"
+            drop = free_before - torch.cuda.mem_get_info(0)[0]
+            if drop > 0:                                                # someone else on the device?  a call that allocates does so every time
+                drops = []
+                for _ in range(3):
+                    before = torch.cuda.mem_get_info(0)[0]
+                    _static(A, B, group, M, N, K, block_n)
+                    torch.cuda.synchronize()
+                    drops.append(before - torch.cuda.mem_get_info(0)[0])
+                assert min(drops) <= 0, "the call took device memory: %s" % (drops,)
             assert torch.cuda.memory_reserved(0) == torch_before
         torch.testing.assert_close(got32, want32, rtol=2e-3, atol=3e-3)
         torch.testing.assert_close(got16.float(), want16.float(), rtol=1e-2, atol=1e-2)
