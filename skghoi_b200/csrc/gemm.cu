@@ -8,7 +8,8 @@
 //   warp 0      : TMA producer  (cp.async.bulk.tensor 2D, 128B swizzle, mbarrier complete_tx)
 //   warp 1      : MMA issuer    (one elected lane issues tcgen05.mma M=128 x N=BN x K=16, fp32 accum in TMEM)
 //   warp 2      : TMEM allocator (2 accumulator buffers so the epilogue of tile i overlaps the MMAs of tile i+1)
-//   warps 4..11 : epilogue      (tcgen05.ld 32x32b -> registers -> smem transpose -> fused math -> coalesced global)
+//   warps 4..11 : epilogue      (tcgen05.ld 32x32b -> registers -> smem transpose -> fused math -> coalesced global);
+//                 the gather-epilogue variants move registers from warps 0..3 to these warps (setmaxnreg 40 / 232)
 // The epilogue is described per column group (skg_epilogue_group): bias, Hadamard product with
 // row-gathered fp32 tables (the MBF "fc_1(app) * fc_2(sp)" branch product, gathered through the
 // cell -> human / box row maps so the [pairs, 1024] appearance term is never materialised), ReLU,
@@ -37,7 +38,7 @@ constexpr bool kEpiPrefetch = kEpiWarps <= 8;
 #endif
 constexpr bool kEpiL1Prefetch = SKG_EPI_L1_PREFETCH != 0;
 constexpr int kEpiParts = kEpiWarps / 4;   // column parts of a tile, one epilogue warp each per quadrant
-constexpr int kGemmThreads = 32 * (4 + kEpiWarps);  // warps: 0 TMA, 1 MMA, 2 TMEM alloc, 3 idle, 4..19 epilogue
+constexpr int kGemmThreads = 32 * (4 + kEpiWarps);  // warps: 0 TMA, 1 MMA, 2 TMEM alloc, 3 idle, 4..(3 + kEpiWarps) epilogue
 // epilogue features (compile-time mask FEAT of gemm_bf16_kernel; bias / ReLU / out_row are always available)
 #ifndef SKG_EPI_SETMAXNREG
 #define SKG_EPI_SETMAXNREG 1
@@ -359,8 +360,9 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     // each warp-wide access hit 32 different 128-byte lines, which the L1 serialises; so every 32x16 block is
     // transposed through a private, XOR-swizzled 2 KB shared-memory patch and processed with
     // lane = (row % 8, 4 columns): a warp-wide float4 access then covers 8 rows x 64 contiguous bytes.
-    // 16 epilogue warps (4 per TMEM lane quadrant, a quarter of the tile's columns each) keep four warps per
-    // scheduler in flight; FEAT removes at compile time every epilogue feature the launch does not use.
+    // kEpiWarps epilogue warps (kEpiParts per TMEM lane quadrant, 1 / kEpiParts of the tile's columns each: 8 warps = two
+    // per scheduler with the gathered operands software-pipelined in registers); FEAT removes at compile time every
+    // epilogue feature the launch does not use.
     const int ew = warp - kEpiWarp0;
     const int quad = warp & 3;                            // TMEM lane quadrant this warp may access
     const int part = ew >> 2;                             // which quarter of the tile's columns this warp drains
