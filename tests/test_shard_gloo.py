@@ -32,6 +32,9 @@ def _worker(rank, world, port, out):
         n_p = torch.tensor([3.0 + rank, 10.0 * (rank + 1)])
         res["n_p"] = shard.average_normalisers(n_p).tolist()
         assert n_p.tolist() == [3.0 + rank, 10.0 * (rank + 1)]          # input left untouched
+        n_q = n_p.clone()
+        n_avg = shard.average_normalisers(n_q, in_place=True)           # the training pre-pass gives its buffer up
+        assert n_avg.data_ptr() == n_q.data_ptr() and n_avg.tolist() == res["n_p"]
         # 3. gradient buckets: small bucket size -> several buckets, one param without grad
         torch.manual_seed(0)
         net = torch.nn.Sequential(torch.nn.Linear(7, 5), torch.nn.ReLU(), torch.nn.Linear(5, 3), torch.nn.Linear(3, 2))
