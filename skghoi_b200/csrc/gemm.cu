@@ -289,6 +289,10 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   // INSIDE the two role branches: ptxas budgets each branch by the setmaxnreg that dominates it.  Plain epilogues do not use
   // it: they gain nothing (37.8 us either way), and with it on every launch the C2 step measured 2-3 % slower.
   constexpr bool kSetMax = kEpiSetMaxNReg && kEpiWarps == 8 && (FEAT & F_P) != 0;
+  // the pool must balance or setmaxnreg.inc waits forever: a kernel that contains setmaxnreg is launched with the largest
+  // count its launch bounds allow (65536 / 384 threads -> 168), warps 0..3 give back (168 - 40) x 128 registers and warps
+  // 4..11 take (232 - 168) x 256
+  static_assert(kGemmThreads != 384 || (168 - 40) * 128 >= (232 - 168) * 256, "setmaxnreg: the epilogue asks for more than the producer frees");
   if (warp < kEpiWarp0) {
   if (kSetMax) asm volatile("setmaxnreg.dec.sync.aligned.u32 40;\n");
   if (warp == 0) {
